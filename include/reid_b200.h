@@ -1,0 +1,161 @@
+/* reid_b200 — C-ABI of the B200-native retrieval-evaluation hot path.
+ *
+ * The reference (SuperbTUM/Multimodal-ReID @ 8dc4505d) is pure Python and has no FFI; the entry
+ * points below are the stage boundaries of its evaluate.py / reranking.py, each citing the
+ * reference lines it replaces.  The Python host layer (multimodal-reid_b200/{evaluate,reranking,
+ * engine}.py) binds them with ctypes; INTEGRATION.md shows the binding.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer owned by the caller; nothing is allocated behind the
+ *     caller's back and nothing is freed;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream); all work is
+ *     enqueued asynchronously on it;
+ *   - return value 0 = success, negative = error (REID_ERR_*); reid_last_error() returns a
+ *     thread-local description of the most recent failure;
+ *   - matrices are row-major with an explicit pitch `ld` counted in elements;
+ *   - "row window" arguments (row0, row_stride, rows) select the probe rows
+ *     row0 + l*row_stride, l in [0, rows): this is how ranks own a cyclic share of the N probes
+ *     (rank r of P passes row0=r, row_stride=P); outputs of such stages are indexed by l.
+ *   - there is no CPU fallback: on a device that is not compute capability 10.x every entry point
+ *     fails with REID_ERR_UNSUPPORTED.
+ */
+#ifndef REID_B200_H
+#define REID_B200_H
+
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define REID_API __attribute__((visibility("default")))
+#else
+#define REID_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define REID_ABI_VERSION 1
+
+#define REID_OK 0
+#define REID_ERR_CUDA (-1)
+#define REID_ERR_ARG (-2)
+#define REID_ERR_UNSUPPORTED (-3)
+#define REID_ERR_OVERFLOW (-4)
+
+#define REID_METRIC_SQEUCLIDEAN 0 /* evaluate.py:7-13  */
+#define REID_METRIC_ARCCOS 1      /* evaluate.py:16-26 */
+
+#define REID_ENGINE_AUTO 0
+#define REID_ENGINE_SIMT 1    /* fp32 FMA on CUDA cores (bring-up / cross-check engine) */
+#define REID_ENGINE_TCGEN05 2 /* 3xTF32 on tcgen05 tensor cores, TMA-fed, TMEM accumulators */
+
+typedef uint16_t reid_half; /* IEEE binary16 bit pattern */
+
+REID_API int reid_abi_version(void);
+REID_API const char* reid_last_error(void);
+/* 0 if `device` is an sm_100 part this library can run on, REID_ERR_UNSUPPORTED otherwise. */
+REID_API int reid_device_check(int device);
+
+/* int(np.around(k1/2)) + 1 with banker's rounding             (reranking.py:60) */
+REID_API int reid_half_k(int k1);
+/* structural bound on the support of one row of V: (k1+1) * (half_k + 1) */
+REID_API int reid_v_row_capacity(int k1);
+/* feature width padded to the MMA K multiple (32) */
+REID_API int reid_padded_width(int d);
+
+/* K13  evaluate.py:112-114, reranking.py:36-39.  Row L2-normalise (x / max(|x|, 1e-12)) when
+ * `normalize`, zero-pad to `dpad`, split into TF32 `hi` + exact residual `lo` (hi + lo == x),
+ * and emit sq[i] = sum x^2 and nrm[i] = sqrt(sq[i]) of the rows as written. */
+REID_API int reid_prepare_features(const float* X, int n, int d, int64_t ld_x, int normalize, float* hi,
+                          float* lo, int dpad, float* sq, float* nrm, void* stream);
+
+/* K1/K2/K3  evaluate.py:7-26, reranking.py:36-41.  out[i, j] for A rows i < m, B rows j < n.
+ * metric 0: (ra[i] + rb[j]) - 2 a.b with ra/rb = squared norms; metric 1: arccos(clip(a.b *
+ * (1 / (ra[i] * rb[j])))) with ra/rb = norms.  If rowmax_key != NULL the per-row maximum of
+ * `out` is folded in with atomicMax on an order-preserving int encoding (initialise the array
+ * with reid_rowmax_init). */
+REID_API int reid_dist(const float* Ahi, const float* Alo, const float* ra, int m, const float* Bhi,
+              const float* Blo, const float* rb, int n, int dpad, int metric, int engine,
+              float* out, int64_t ld_out, int32_t* rowmax_key, void* stream);
+REID_API int reid_rowmax_init(int32_t* rowmax_key, int rows, void* stream);
+/* K4 (first half)  reranking.py:46.  Stand-alone row maximum for a caller-supplied matrix. */
+REID_API int reid_rowmax(const float* D, int rows, int cols, int64_t ld, int32_t* rowmax_key, void* stream);
+/* decode the int encoding into floats (diagnostics / tests) */
+REID_API int reid_rowmax_decode(const int32_t* rowmax_key, int rows, float* out, void* stream);
+/* reranking.py:43-44 / :33-34.  dst[i, j] (+)= src[j, i]: the reference reads column i of the
+ * N x N matrix for probe i, the kernels read row i. */
+REID_API int reid_transpose_add(const float* src, int n, int64_t ld_src, float* dst, int64_t ld_dst,
+                       int accumulate, void* stream);
+
+/* K5  reranking.py:46,48.  For every row: the K smallest O[i, j] = D[i, j] / rowmax[i] in
+ * ascending (value, column) order -> nbr[rows, K] (and their values if nbr_val != NULL). */
+REID_API int reid_topk_rows(const float* D, int rows, int cols, int64_t ld, const int32_t* rowmax_key, int K,
+                   int32_t* nbr, float* nbr_val, void* stream);
+/* test hook: same, with the candidate buffer capped so the exact fallback path is exercised */
+REID_API int reid_topk_rows_capped(const float* D, int rows, int cols, int64_t ld, const int32_t* rowmax_key,
+                          int K, int32_t* nbr, float* nbr_val, int cap, void* stream);
+
+/* K6a  reranking.py:53-56, :60-64.  Reciprocal neighbour sets at depth k1+1 (rfull[N, k1+1],
+ * nfull[N]) and at depth half_k (rhalf[N, half_k], nhalf[N]) for all N rows of nbr[N, K]. */
+REID_API int reid_krecip_sets(const int32_t* nbr, int N, int K, int k1, int32_t* rfull, int32_t* nfull,
+                     int32_t* rhalf, int32_t* nhalf, void* stream);
+/* K6b  reranking.py:57-71.  2/3-rule expansion, unique, Gaussian weights -> V rows in ELL form
+ * (pitch reid_v_row_capacity(k1)): Vc columns ascending, Vv float16 weights, Vn counts.  D and
+ * rowmax_key are indexed by the local row l of the window. */
+REID_API int reid_krecip_V(const int32_t* rfull, const int32_t* nfull, const int32_t* rhalf,
+                  const int32_t* nhalf, int row0, int row_stride, int rows, int k1, const float* D,
+                  int64_t ld, const int32_t* rowmax_key, int32_t* Vc, reid_half* Vv, int32_t* Vn,
+                  void* stream);
+
+/* K7  reranking.py:73-78.  ub[l] = upper bound of |supp V_qe[row_l]|; exclusive scan to offsets;
+ * then the expansion itself into a CSR pool (Qc/Qv at qoff[l], Qn[l] entries, columns ascending).
+ * V (Vc/Vv/Vn, ELL pitch cap1) and nbr are global (all N rows). */
+REID_API int reid_qe_bound(const int32_t* nbr, int K, int k2, const int32_t* Vn, int row0, int row_stride,
+                  int rows, int32_t* ub, void* stream);
+REID_API int reid_exclusive_scan(const int32_t* in, int n, int64_t* out /* n+1 */, void* stream);
+REID_API int reid_qe_k2(const int32_t* nbr, int K, int k2, const int32_t* Vc, const reid_half* Vv,
+               const int32_t* Vn, int cap1, int row0, int row_stride, int rows, const int64_t* qoff,
+               int32_t* Qc, reid_half* Qv, int32_t* Qn, void* stream);
+REID_API int reid_qe_k2_capped(const int32_t* nbr, int K, int k2, const int32_t* Vc, const reid_half* Vv,
+                      const int32_t* Vn, int cap1, int row0, int row_stride, int rows,
+                      const int64_t* qoff, int cap_sort, int32_t* Qc, reid_half* Qv, int32_t* Qn,
+                      void* stream);
+/* offsets of an ELL matrix viewed as CSR: off[i] = i * pitch, i in [0, N] (k2 == 1: V_qe = V) */
+REID_API int reid_ell_offsets(int N, int pitch, int64_t* off, void* stream);
+
+/* K8  reranking.py:80-82.  Inverted index (CSC) of V_qe over all N rows: count, (scan), fill. */
+REID_API int reid_csc_count(const int32_t* Qc, const int64_t* qoff, const int32_t* Qn, int N,
+                   int32_t* colcnt /* zeroed, N */, void* stream);
+REID_API int reid_csc_fill(const int32_t* Qc, const reid_half* Qv, const int64_t* qoff, const int32_t* Qn,
+                  int N, const int64_t* colptr, int32_t* cursor /* zeroed, N */, int32_t* csc_row,
+                  reid_half* csc_val, void* stream);
+
+/* K9 + K10  reranking.py:84-100.  For the query window (global probe q0 + l*q_stride, l < nq):
+ * float16 Jaccard chain through the inverted index and
+ *   out[l, g - q] = fp32(fp16(J * fp16(c1))) + (D[l, g] / rowmax[l]) * c2   for g in [q, N)
+ * with c1 = 1 - lambda (rounded to float16 by the caller) and c2 = float32(lambda).
+ * jaccard_out (nullable, pitch ld_j, N columns) receives the float16 Jaccard rows for tests. */
+REID_API int reid_jaccard_mix(const int32_t* Qc, const reid_half* Qv, const int64_t* qoff, const int32_t* Qn,
+                     const int64_t* colptr, const int32_t* csc_row, const reid_half* csc_val,
+                     const float* D, int64_t ld, const int32_t* rowmax_key, int q0, int q_stride,
+                     int nq, int q, int N, float c1, float c2, float* out, int64_t ld_out,
+                     reid_half* jaccard_out, int64_t ld_j, void* stream);
+
+/* K11  evaluate.py:40.  Stable full ranking of every row (ascending distance, ties by column).
+ * Workspace: keyA, keyB, idxA of rows*g 32-bit words each. */
+REID_API int reid_rank_rows(const float* dist, int rows, int g, int64_t ld, uint32_t* keyA, uint32_t* keyB,
+                   int32_t* idxA, int32_t* ranked, void* stream);
+
+/* K12  evaluate.py:43-88.  Per-query AP (float64; -1 = query skipped), first-match rank, and
+ * the histogram / counter the CMC curve is built from (cmc_hist[max_rank] and n_valid zeroed by
+ * the caller; they are plain sums, so ranks all-reduce them). */
+REID_API int reid_score_rows(const int32_t* ranked, int q, int g, const int64_t* q_pid, const int64_t* g_pid,
+                    const int64_t* q_cam, const int64_t* g_cam, int max_rank, double* ap,
+                    int32_t* first_hit, int32_t* cmc_hist, int32_t* n_valid, void* stream);
+REID_API int reid_score_finalize(const double* ap, int q, const int32_t* cmc_hist, int max_rank,
+                        const int32_t* n_valid, float* cmc, double* mAP, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* REID_B200_H */

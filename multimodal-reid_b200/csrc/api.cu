@@ -1,0 +1,287 @@
+// extern "C" surface declared in include/reid_b200.h: argument validation + launch.
+#include <stdarg.h>
+#include <string.h>
+
+#include "../../include/reid_b200.h"
+#include "common.cuh"
+#include "kernels.h"
+
+namespace reid {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int check_launch(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("%s launch failed: %s", what, cudaGetErrorString(e));
+    return REID_ERR_CUDA;
+  }
+  return REID_OK;
+}
+
+__global__ void fill_i32_kernel(int* p, int n, int v) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
+}
+__global__ void rowmax_decode_kernel(const int* key, int n, float* out) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = ordered_int2f(key[i]);
+}
+
+// dst[i, j] (+)= src[j, i], 32x32 tiles through shared memory
+__global__ void __launch_bounds__(256)
+transpose_add_kernel(const float* __restrict__ src, int n, long long ld_src, float* __restrict__ dst,
+                     long long ld_dst, int accumulate) {
+  __shared__ float tile[32][33];
+  const int bx = blockIdx.x * 32, by = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int r = ty; r < 32; r += 8) {
+    int sr = bx + r, sc = by + tx;          // src row in [bx, bx+32), col in [by, by+32)
+    tile[r][tx] = (sr < n && sc < n) ? src[(long long)sr * ld_src + sc] : 0.0f;
+  }
+  __syncthreads();
+  for (int r = ty; r < 32; r += 8) {
+    int dr = by + r, dc = bx + tx;          // dst[dr, dc] = src[dc, dr]
+    if (dr < n && dc < n) {
+      float v = tile[tx][r];
+      float* p = dst + (long long)dr * ld_dst + dc;
+      *p = accumulate ? __fadd_rn(*p, v) : v;
+    }
+  }
+}
+
+int launch_transpose_add(const float* src, int n, long long ld_src, float* dst, long long ld_dst,
+                         int accumulate, cudaStream_t s) {
+  if (n == 0) return REID_OK;
+  dim3 grid(cdiv(n, 32), cdiv(n, 32));
+  transpose_add_kernel<<<grid, 256, 0, s>>>(src, n, ld_src, dst, ld_dst, accumulate);
+  return check_launch("transpose_add_kernel");
+}
+
+static int g_device_ok[64];   // 0 unknown, 1 ok, -1 unsupported
+
+static int require_sm100() {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) {
+    set_error("no CUDA device: %s", cudaGetErrorString(e));
+    return REID_ERR_UNSUPPORTED;
+  }
+  if (dev >= 0 && dev < 64 && g_device_ok[dev] == 1) return REID_OK;
+  int major = 0;
+  e = cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
+  if (e != cudaSuccess || major != 10) {
+    set_error("reid_b200 needs an sm_100 (B200) device; device %d is compute capability %d.x and "
+              "there is no CPU or other-architecture fallback", dev, major);
+    return REID_ERR_UNSUPPORTED;
+  }
+  if (dev >= 0 && dev < 64) g_device_ok[dev] = 1;
+  return REID_OK;
+}
+
+}  // namespace reid
+
+using namespace reid;
+
+#define ENTER()                       \
+  do {                                \
+    int _rc = require_sm100();        \
+    if (_rc != REID_OK) return _rc;   \
+  } while (0)
+#define S(stream) reinterpret_cast<cudaStream_t>(stream)
+#define H(p) reinterpret_cast<__half*>(p)
+#define HC(p) reinterpret_cast<const __half*>(p)
+
+extern "C" {
+
+int reid_abi_version(void) { return REID_ABI_VERSION; }
+const char* reid_last_error(void) { return g_err; }
+
+int reid_device_check(int device) {
+  int major = 0;
+  cudaError_t e = cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device);
+  if (e != cudaSuccess) {
+    set_error("cudaDeviceGetAttribute(%d): %s", device, cudaGetErrorString(e));
+    return REID_ERR_UNSUPPORTED;
+  }
+  if (major != 10) {
+    set_error("device %d is compute capability %d.x, need 10.x (sm_100a)", device, major);
+    return REID_ERR_UNSUPPORTED;
+  }
+  return REID_OK;
+}
+
+int reid_half_k(int k1) { return half_k(k1); }
+int reid_v_row_capacity(int k1) { return v_row_capacity(k1); }
+int reid_padded_width(int d) { return padded_width(d); }
+
+int reid_prepare_features(const float* X, int n, int d, int64_t ld_x, int normalize, float* hi, float* lo,
+                          int dpad, float* sq, float* nrm, void* stream) {
+  ENTER();
+  REID_REQUIRE(n >= 0 && d >= 1 && ld_x >= d, "prepare_features: bad shape n=%d d=%d ld=%lld", n, d,
+               (long long)ld_x);
+  REID_REQUIRE(dpad >= d && dpad % 32 == 0, "prepare_features: dpad=%d must be a multiple of 32 >= d=%d",
+               dpad, d);
+  return launch_prep(X, n, d, ld_x, normalize, hi, lo, dpad, sq, nrm, S(stream));
+}
+
+int reid_dist(const float* Ahi, const float* Alo, const float* ra, int m, const float* Bhi, const float* Blo,
+              const float* rb, int n, int dpad, int metric, int engine, float* out, int64_t ld_out,
+              int32_t* rowmax_key, void* stream) {
+  ENTER();
+  REID_REQUIRE(metric == 0 || metric == 1, "dist: unknown metric %d", metric);
+  REID_REQUIRE(m >= 0 && n >= 0 && dpad > 0 && dpad % 32 == 0 && ld_out >= n, "dist: bad shape");
+  if (engine == REID_ENGINE_AUTO) engine = REID_ENGINE_TCGEN05;
+  if (engine == REID_ENGINE_SIMT)
+    return launch_dist_simt(Ahi, Alo, ra, m, Bhi, Blo, rb, n, dpad, metric, out, ld_out, rowmax_key,
+                            S(stream));
+  if (engine == REID_ENGINE_TCGEN05)
+    return launch_dist_tc(Ahi, Alo, ra, m, Bhi, Blo, rb, n, dpad, metric, out, ld_out, rowmax_key,
+                          S(stream));
+  set_error("dist: unknown engine %d", engine);
+  return REID_ERR_ARG;
+}
+
+int reid_rowmax_init(int32_t* rowmax_key, int rows, void* stream) {
+  ENTER();
+  if (rows == 0) return REID_OK;
+  fill_i32_kernel<<<cdiv(rows, 256), 256, 0, S(stream)>>>(rowmax_key, rows, REID_ROWMAX_INIT);
+  return check_launch("fill_i32_kernel");
+}
+
+int reid_rowmax(const float* D, int rows, int cols, int64_t ld, int32_t* rowmax_key, void* stream) {
+  ENTER();
+  return launch_rowmax(D, rows, cols, ld, rowmax_key, S(stream));
+}
+
+int reid_rowmax_decode(const int32_t* rowmax_key, int rows, float* out, void* stream) {
+  ENTER();
+  if (rows == 0) return REID_OK;
+  rowmax_decode_kernel<<<cdiv(rows, 256), 256, 0, S(stream)>>>(rowmax_key, rows, out);
+  return check_launch("rowmax_decode_kernel");
+}
+
+int reid_transpose_add(const float* src, int n, int64_t ld_src, float* dst, int64_t ld_dst, int accumulate,
+                       void* stream) {
+  ENTER();
+  return launch_transpose_add(src, n, ld_src, dst, ld_dst, accumulate, S(stream));
+}
+
+int reid_topk_rows(const float* D, int rows, int cols, int64_t ld, const int32_t* rowmax_key, int K,
+                   int32_t* nbr, float* nbr_val, void* stream) {
+  ENTER();
+  return launch_select_topk(D, rows, cols, ld, rowmax_key, K, nbr, nbr_val, 0, S(stream));
+}
+
+int reid_topk_rows_capped(const float* D, int rows, int cols, int64_t ld, const int32_t* rowmax_key, int K,
+                          int32_t* nbr, float* nbr_val, int cap, void* stream) {
+  ENTER();
+  return launch_select_topk(D, rows, cols, ld, rowmax_key, K, nbr, nbr_val, cap, S(stream));
+}
+
+int reid_krecip_sets(const int32_t* nbr, int N, int K, int k1, int32_t* rfull, int32_t* nfull,
+                     int32_t* rhalf, int32_t* nhalf, void* stream) {
+  ENTER();
+  REID_REQUIRE(k1 >= 1, "krecip_sets: k1=%d", k1);
+  return launch_reciprocal_sets(nbr, N, K, k1, rfull, nfull, rhalf, nhalf, S(stream));
+}
+
+int reid_krecip_V(const int32_t* rfull, const int32_t* nfull, const int32_t* rhalf, const int32_t* nhalf,
+                  int row0, int row_stride, int rows, int k1, const float* D, int64_t ld,
+                  const int32_t* rowmax_key, int32_t* Vc, reid_half* Vv, int32_t* Vn, void* stream) {
+  ENTER();
+  REID_REQUIRE(k1 >= 1 && row_stride >= 1 && row0 >= 0, "krecip_V: bad window");
+  return launch_expand_weights(rfull, nfull, rhalf, nhalf, row0, row_stride, rows, k1, D, ld, rowmax_key,
+                               Vc, H(Vv), Vn, S(stream));
+}
+
+int reid_qe_bound(const int32_t* nbr, int K, int k2, const int32_t* Vn, int row0, int row_stride, int rows,
+                  int32_t* ub, void* stream) {
+  ENTER();
+  return launch_qe_bound(nbr, K, k2, Vn, row0, row_stride, rows, ub, S(stream));
+}
+
+int reid_exclusive_scan(const int32_t* in, int n, int64_t* out, void* stream) {
+  ENTER();
+  return launch_exclusive_scan(in, n, reinterpret_cast<long long*>(out), S(stream));
+}
+
+int reid_qe_k2_capped(const int32_t* nbr, int K, int k2, const int32_t* Vc, const reid_half* Vv,
+                      const int32_t* Vn, int cap1, int row0, int row_stride, int rows, const int64_t* qoff,
+                      int cap_sort, int32_t* Qc, reid_half* Qv, int32_t* Qn, void* stream) {
+  ENTER();
+  return launch_qe_expand(nbr, K, k2, Vc, HC(Vv), Vn, cap1, row0, row_stride, rows,
+                          reinterpret_cast<const long long*>(qoff), cap_sort, Qc, H(Qv), Qn, S(stream));
+}
+
+int reid_qe_k2(const int32_t* nbr, int K, int k2, const int32_t* Vc, const reid_half* Vv, const int32_t* Vn,
+               int cap1, int row0, int row_stride, int rows, const int64_t* qoff, int32_t* Qc,
+               reid_half* Qv, int32_t* Qn, void* stream) {
+  return reid_qe_k2_capped(nbr, K, k2, Vc, Vv, Vn, cap1, row0, row_stride, rows, qoff, 4096, Qc, Qv, Qn,
+                           stream);
+}
+
+int reid_ell_offsets(int N, int pitch, int64_t* off, void* stream) {
+  ENTER();
+  return launch_ell_offsets(N, pitch, reinterpret_cast<long long*>(off), S(stream));
+}
+
+int reid_csc_count(const int32_t* Qc, const int64_t* qoff, const int32_t* Qn, int N, int32_t* colcnt,
+                   void* stream) {
+  ENTER();
+  return launch_csc_count(Qc, reinterpret_cast<const long long*>(qoff), Qn, N, colcnt, S(stream));
+}
+
+int reid_csc_fill(const int32_t* Qc, const reid_half* Qv, const int64_t* qoff, const int32_t* Qn, int N,
+                  const int64_t* colptr, int32_t* cursor, int32_t* csc_row, reid_half* csc_val,
+                  void* stream) {
+  ENTER();
+  return launch_csc_fill(Qc, HC(Qv), reinterpret_cast<const long long*>(qoff), Qn, N,
+                         reinterpret_cast<const long long*>(colptr), cursor, csc_row, H(csc_val), S(stream));
+}
+
+int reid_jaccard_mix(const int32_t* Qc, const reid_half* Qv, const int64_t* qoff, const int32_t* Qn,
+                     const int64_t* colptr, const int32_t* csc_row, const reid_half* csc_val, const float* D,
+                     int64_t ld, const int32_t* rowmax_key, int q0, int q_stride, int nq, int q, int N,
+                     float c1, float c2, float* out, int64_t ld_out, reid_half* jaccard_out, int64_t ld_j,
+                     void* stream) {
+  ENTER();
+  REID_REQUIRE(q >= 0 && q <= N && q_stride >= 1, "jaccard_mix: bad shape q=%d N=%d", q, N);
+  return launch_jaccard_mix(Qc, HC(Qv), reinterpret_cast<const long long*>(qoff), Qn,
+                            reinterpret_cast<const long long*>(colptr), csc_row, HC(csc_val), D, ld,
+                            rowmax_key, q0, q_stride, nq, q, N, c1, c2, out, ld_out, H(jaccard_out), ld_j,
+                            S(stream));
+}
+
+int reid_rank_rows(const float* dist, int rows, int g, int64_t ld, uint32_t* keyA, uint32_t* keyB,
+                   int32_t* idxA, int32_t* ranked, void* stream) {
+  ENTER();
+  REID_REQUIRE(ld >= g, "rank_rows: pitch %lld < row length %d", (long long)ld, g);
+  return launch_rank_rows(dist, rows, g, ld, keyA, keyB, idxA, ranked, S(stream));
+}
+
+int reid_score_rows(const int32_t* ranked, int q, int g, const int64_t* q_pid, const int64_t* g_pid,
+                    const int64_t* q_cam, const int64_t* g_cam, int max_rank, double* ap, int32_t* first_hit,
+                    int32_t* cmc_hist, int32_t* n_valid, void* stream) {
+  ENTER();
+  REID_REQUIRE(max_rank >= 1 && max_rank <= g, "score_rows: max_rank=%d outside [1, g=%d]", max_rank, g);
+  return launch_score(ranked, q, g, reinterpret_cast<const long long*>(q_pid),
+                      reinterpret_cast<const long long*>(g_pid), reinterpret_cast<const long long*>(q_cam),
+                      reinterpret_cast<const long long*>(g_cam), max_rank, ap, first_hit, cmc_hist, n_valid,
+                      S(stream));
+}
+
+int reid_score_finalize(const double* ap, int q, const int32_t* cmc_hist, int max_rank, const int32_t* n_valid,
+                        float* cmc, double* mAP, void* stream) {
+  ENTER();
+  return launch_score_finalize(ap, q, cmc_hist, max_rank, n_valid, cmc, mAP, S(stream));
+}
+
+}  // extern "C"

@@ -1,0 +1,73 @@
+// Shared helpers for the reid_b200 kernels (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/reid_b200.h"
+
+namespace reid {
+
+void set_error(const char* fmt, ...);
+int check_launch(const char* what);            // cudaGetLastError -> REID_OK / REID_ERR_CUDA
+
+#define REID_CUDA(call)                                                              \
+  do {                                                                               \
+    cudaError_t _e = (call);                                                         \
+    if (_e != cudaSuccess) {                                                         \
+      reid::set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return REID_ERR_CUDA;                                                          \
+    }                                                                                \
+  } while (0)
+
+#define REID_REQUIRE(cond, ...)                                                      \
+  do {                                                                               \
+    if (!(cond)) {                                                                   \
+      reid::set_error(__VA_ARGS__);                                                  \
+      return REID_ERR_ARG;                                                           \
+    }                                                                                \
+  } while (0)
+
+constexpr unsigned FULL = 0xffffffffu;
+
+// float <-> order-preserving unsigned key (ascending float == ascending key).  -0.0 must be
+// canonicalised by the caller (x + 0.0f) so that it ties with +0.0 like numpy's sort does.
+__device__ __forceinline__ uint32_t f2key(float f) {
+  uint32_t b = __float_as_uint(f);
+  return b ^ ((b >> 31) ? 0xffffffffu : 0x80000000u);
+}
+__device__ __forceinline__ float key2f(uint32_t k) {
+  uint32_t b = k ^ ((k >> 31) ? 0x80000000u : 0xffffffffu);
+  return __uint_as_float(b);
+}
+// float -> signed int with the same ordering (for atomicMax on ints)
+__device__ __forceinline__ int f2ordered_int(float f) {
+  int b = __float_as_int(f);
+  return b >= 0 ? b : b ^ 0x7fffffff;
+}
+__device__ __forceinline__ float ordered_int2f(int k) {
+  return __int_as_float(k >= 0 ? k : k ^ 0x7fffffff);
+}
+#define REID_ROWMAX_INIT ((int)0x80000000)
+
+__device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
+
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(FULL, v, o));
+  return v;
+}
+__device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    unsigned long long w = __shfl_xor_sync(FULL, v, o);
+    v = w < v ? w : v;
+  }
+  return v;
+}
+
+static inline int cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
+static inline long long round_up(long long a, long long b) { return (a + b - 1) / b * b; }
+
+}  // namespace reid

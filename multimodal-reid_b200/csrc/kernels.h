@@ -1,0 +1,61 @@
+// Internal launcher declarations (one per kernel family).  The public surface is include/reid_b200.h.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+
+namespace reid {
+
+// int(np.around(k1 / 2)) + 1 with round-half-to-even (reranking.py:60)
+static inline int half_k(int k1) {
+  int f = k1 / 2;
+  if (k1 & 1) f += (f & 1);      // x.5 -> nearest even
+  return f + 1;
+}
+// structural bound on |E_i|: |R| + |R| * h  with |R| <= k1+1
+static inline int v_row_capacity(int k1) { return (k1 + 1) * (half_k(k1) + 1); }
+static inline int padded_width(int d) { return (d + 31) / 32 * 32; }
+
+int launch_prep(const float* X, int n, int d, long long ld_x, int normalize, float* hi, float* lo, int dp,
+                float* sq, float* nrm, cudaStream_t s);
+int launch_dist_simt(const float* Ahi, const float* Alo, const float* ra, int m, const float* Bhi,
+                     const float* Blo, const float* rb, int n, int dp, int metric, float* out,
+                     long long ld_out, int* rowmax_key, cudaStream_t s);
+int launch_dist_tc(const float* Ahi, const float* Alo, const float* ra, int m, const float* Bhi,
+                   const float* Blo, const float* rb, int n, int dp, int metric, float* out,
+                   long long ld_out, int* rowmax_key, cudaStream_t s);
+int launch_rowmax(const float* D, int rows, int cols, long long ld, int* key, cudaStream_t s);
+int launch_select_topk(const float* D, int rows, int cols, long long ld, const int* rowmax_key, int K,
+                       int* nbr, float* nbr_val, int cap_override, cudaStream_t s);
+int launch_reciprocal_sets(const int* nbr, int N, int K, int k1, int* rfull, int* nfull, int* rhalf,
+                           int* nhalf, cudaStream_t s);
+int launch_expand_weights(const int* rfull, const int* nfull, const int* rhalf, const int* nhalf, int row0,
+                          int row_stride, int rows, int k1, const float* D, long long ld, const int* rowmax_key, int* Vc,
+                          __half* Vv, int* Vn, cudaStream_t s);
+int launch_qe_bound(const int* nbr, int K, int k2, const int* Vn, int row0, int row_stride, int rows,
+                    int* ub, cudaStream_t s);
+int launch_exclusive_scan(const int* in, int n, long long* out, cudaStream_t s);
+int launch_qe_expand(const int* nbr, int K, int k2, const int* Vc, const __half* Vv, const int* Vn, int cap1,
+                     int row0, int row_stride, int rows, const long long* qoff, int cap_sort, int* Qc, __half* Qv, int* Qn,
+                     cudaStream_t s);
+int launch_ell_offsets(int N, int cap1, long long* off, cudaStream_t s);
+int launch_csc_count(const int* Qc, const long long* qoff, const int* Qn, int N, int* colcnt,
+                     cudaStream_t s);
+int launch_csc_fill(const int* Qc, const __half* Qv, const long long* qoff, const int* Qn, int N,
+                    const long long* colptr, int* cursor, int* csc_row, __half* csc_val, cudaStream_t s);
+int launch_jaccard_mix(const int* Qc, const __half* Qv, const long long* qoff, const int* Qn,
+                       const long long* colptr, const int* csc_row, const __half* csc_val, const float* D,
+                       long long ld, const int* rowmax_key, int q0, int q_stride, int nq_local, int q, int N, float c1,
+                       float c2, float* out, long long ld_out, __half* jaccard_out, long long ld_j,
+                       cudaStream_t s);
+int launch_rank_rows(const float* dist, int rows, int g, long long ld_dist, uint32_t* keyA, uint32_t* keyB,
+                     int* idxA, int* idx_out, cudaStream_t s);
+int launch_score(const int* ranked, int q, int g, const long long* q_pid, const long long* g_pid,
+                 const long long* q_cam, const long long* g_cam, int max_rank, double* ap, int* first_hit,
+                 int* cmc_hist, int* n_valid, cudaStream_t s);
+int launch_score_finalize(const double* ap, int q, const int* cmc_hist, int max_rank, const int* n_valid,
+                          float* cmc, double* mAP, cudaStream_t s);
+int launch_transpose_add(const float* src, int n, long long ld_src, float* dst, long long ld_dst, int accumulate,
+                         cudaStream_t s);
+
+}  // namespace reid

@@ -1,0 +1,204 @@
+// K7 (reranking.py:73-78): local query expansion.  The reference averages k2 dense N-wide float16
+// rows per probe (42 % of its run time); only the union of the k2 sparse supports is non-zero, so
+// each warp gathers the k2 sparse rows into shared memory, sorts the (column, neighbour-rank)
+// pairs and reduces each column in neighbour order:  fp16( fp32-sum / fp32(k2) ).
+#include "common.cuh"
+#include "np_exact.cuh"
+#include "kernels.h"
+
+namespace reid {
+
+// upper bound on |support(V_qe[i])| = sum of the k2 source row lengths
+__global__ void qe_bound_kernel(const int* __restrict__ nbr, int K, int k2, const int* __restrict__ Vn,
+                                int row0, int row_stride, int rows, int* __restrict__ ub) {
+  int l = blockIdx.x * blockDim.x + threadIdx.x;
+  if (l >= rows) return;
+  const long long i = row0 + (long long)l * row_stride;
+  int t = 0;
+  for (int r = 0; r < k2; ++r) t += Vn[nbr[i * K + r]];
+  ub[l] = t;
+}
+
+// single-CTA exclusive scan int32 -> int64 offsets (+ total at out[n]); n is ~1e5, this is noise
+__global__ void __launch_bounds__(1024)
+exclusive_scan_kernel(const int* __restrict__ in, int n, long long* __restrict__ out) {
+  __shared__ long long warp_tot[32];
+  __shared__ long long chunk_tot;
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  long long carry = 0;
+  for (int base = 0; base < n; base += 1024) {
+    const int i = base + tid;
+    long long v = i < n ? in[i] : 0;
+    long long x = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      long long y = __shfl_up_sync(FULL, x, o);
+      if (lane >= o) x += y;
+    }
+    if (lane == 31) warp_tot[w] = x;
+    __syncthreads();
+    if (w == 0) {
+      const long long t = warp_tot[lane];
+      long long s = t;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        long long y = __shfl_up_sync(FULL, s, o);
+        if (lane >= o) s += y;
+      }
+      warp_tot[lane] = s - t;     // exclusive warp offsets
+      if (lane == 31) chunk_tot = s;
+    }
+    __syncthreads();
+    if (i < n) out[i] = carry + warp_tot[w] + x - v;
+    carry += chunk_tot;
+    __syncthreads();
+  }
+  if (tid == 0) out[n] = carry;
+}
+
+int launch_exclusive_scan(const int* in, int n, long long* out, cudaStream_t s) {
+  exclusive_scan_kernel<<<1, 1024, 0, s>>>(in, n, out);
+  return check_launch("exclusive_scan_kernel");
+}
+
+__device__ __forceinline__ void warp_bitonic_u64(unsigned long long* a, int P, int lane) {
+  for (int k = 2; k <= P; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int t = lane; t < (P >> 1); t += 32) {
+        int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+        int p = i | j;
+        unsigned long long x = a[i], y = a[p];
+        bool up = (i & k) == 0;
+        if ((x > y) == up) { a[i] = y; a[p] = x; }
+      }
+      __syncwarp();
+    }
+  }
+}
+
+// entry = column << 32 | neighbour-rank << 16 | fp16 bits
+__global__ void __launch_bounds__(128)
+qe_expand_kernel(const int* __restrict__ nbr, int K, int k2, const int* __restrict__ Vc,
+                 const __half* __restrict__ Vv, const int* __restrict__ Vn, int cap1, int row0,
+                 int row_stride, int rows, const long long* __restrict__ qoff, int cap_sort, int* __restrict__ Qc,
+                 __half* __restrict__ Qv, int* __restrict__ Qn) {
+  extern __shared__ unsigned long long smem_q[];
+  const int wpb = blockDim.x >> 5;
+  const int w = threadIdx.x >> 5, lane = lane_id();
+  const int lrow = blockIdx.x * wpb + w;          // local row: qoff / Qn are indexed by it
+  if (lrow >= rows) return;
+  const long long row = row0 + (long long)lrow * row_stride;
+  unsigned long long* buf = smem_q + (long long)w * cap_sort;
+  const int* src = nbr + row * K;
+  const long long out0 = qoff[lrow];
+  const float kf = (float)k2;
+
+  int total = 0;
+  for (int r = 0; r < k2; ++r) total += Vn[src[r]];
+
+  if (total <= cap_sort) {
+    int fill = 0;
+    for (int r = 0; r < k2; ++r) {
+      const int s = src[r];
+      const int ns = Vn[s];
+      for (int j = lane; j < ns; j += 32) {
+        unsigned c = (unsigned)Vc[(long long)s * cap1 + j];
+        unsigned short hv = __half_as_ushort(Vv[(long long)s * cap1 + j]);
+        buf[fill + j] = ((unsigned long long)c << 32) | ((unsigned long long)r << 16) | hv;
+      }
+      fill += ns;
+    }
+    int P = 32;
+    while (P < total) P <<= 1;
+    for (int j = total + lane; j < P; j += 32) buf[j] = ~0ull;
+    __syncwarp();
+    warp_bitonic_u64(buf, P, lane);
+    int nout = 0;
+    for (int j0 = 0; j0 < total; j0 += 32) {
+      const int j = j0 + lane;
+      bool head = false;
+      unsigned col = 0;
+      float acc = 0.0f;
+      if (j < total) {
+        const unsigned long long e = buf[j];
+        col = (unsigned)(e >> 32);
+        head = (j == 0) || ((unsigned)(buf[j - 1] >> 32) != col);
+        if (head) {
+          acc = __half2float(__ushort_as_half((unsigned short)(e & 0xffffu)));
+          for (int t = j + 1; t < total; ++t) {
+            const unsigned long long e2 = buf[t];
+            if ((unsigned)(e2 >> 32) != col) break;
+            acc = __fadd_rn(acc, __half2float(__ushort_as_half((unsigned short)(e2 & 0xffffu))));
+          }
+        }
+      }
+      const unsigned bal = __ballot_sync(FULL, head);
+      if (head) {
+        const long long o = out0 + nout + __popc(bal & ((1u << lane) - 1));
+        Qc[o] = (int)col;
+        Qv[o] = __float2half_rn(__fdiv_rn(acc, kf));
+      }
+      nout += __popc(bal);
+    }
+    if (lane == 0) Qn[lrow] = nout;
+    return;
+  }
+
+  // Oversized union (does not fit the per-warp sort buffer): k2-way merge straight from global
+  // memory, one list head per lane.  Latency-bound, exact, rare.
+  int pos = 0, len = 0, s = 0;
+  if (lane < k2) { s = src[lane]; len = Vn[s]; }
+  int nout = 0;
+  while (true) {
+    unsigned head = (lane < k2 && pos < len) ? (unsigned)Vc[(long long)s * cap1 + pos] : 0xffffffffu;
+    unsigned mn = head;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mn = min(mn, __shfl_xor_sync(FULL, mn, o));
+    if (mn == 0xffffffffu) break;
+    const bool hit = head == mn;
+    float v = hit ? __half2float(Vv[(long long)s * cap1 + pos]) : 0.0f;
+    unsigned bal = __ballot_sync(FULL, hit);
+    float acc = 0.0f;
+    bool first = true;
+    while (bal) {
+      const int l = __ffs(bal) - 1;
+      const float t = __shfl_sync(FULL, v, l);
+      acc = first ? t : __fadd_rn(acc, t);
+      first = false;
+      bal &= bal - 1;
+    }
+    if (lane == 0) {
+      Qc[out0 + nout] = (int)mn;
+      Qv[out0 + nout] = __float2half_rn(__fdiv_rn(acc, kf));
+    }
+    ++nout;
+    if (hit) ++pos;
+  }
+  if (lane == 0) Qn[lrow] = nout;
+}
+
+int launch_qe_bound(const int* nbr, int K, int k2, const int* Vn, int row0, int row_stride, int rows,
+                    int* ub, cudaStream_t s) {
+  if (rows == 0) return REID_OK;
+  REID_REQUIRE(k2 >= 1 && k2 <= K && k2 <= 32, "qe: k2=%d outside [1, min(K=%d, 32)]", k2, K);
+  qe_bound_kernel<<<cdiv(rows, 256), 256, 0, s>>>(nbr, K, k2, Vn, row0, row_stride, rows, ub);
+  return check_launch("qe_bound_kernel");
+}
+
+int launch_qe_expand(const int* nbr, int K, int k2, const int* Vc, const __half* Vv, const int* Vn,
+                     int cap1, int row0, int row_stride, int rows, const long long* qoff, int cap_sort,
+                     int* Qc, __half* Qv, int* Qn, cudaStream_t s) {
+  if (rows == 0) return REID_OK;
+  REID_REQUIRE(k2 >= 1 && k2 <= K && k2 <= 32, "qe: k2=%d outside [1, min(K=%d, 32)]", k2, K);
+  REID_REQUIRE(cap_sort >= 32 && (cap_sort & (cap_sort - 1)) == 0 && cap_sort <= 16384,
+               "qe: sort capacity %d must be a power of two in [32, 16384]", cap_sort);
+  int wpb = 4;
+  while (wpb > 1 && (long long)wpb * cap_sort * 8 > 128 * 1024) wpb >>= 1;
+  const int smem = wpb * cap_sort * 8;
+  REID_CUDA(cudaFuncSetAttribute(qe_expand_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  qe_expand_kernel<<<cdiv(rows, wpb), wpb * 32, smem, s>>>(nbr, K, k2, Vc, Vv, Vn, cap1, row0,
+                                                          row_stride, rows, qoff, cap_sort, Qc, Qv, Qn);
+  return check_launch("qe_expand_kernel");
+}
+
+}  // namespace reid

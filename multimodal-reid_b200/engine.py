@@ -1,0 +1,415 @@
+"""Device-side orchestration of the retrieval-evaluation hot path.
+
+torch supplies device memory, the current stream and (for N > 1 ranks) the NCCL collectives; every
+arithmetic step is a kernel in libreid_b200.so reached through the C-ABI (include/reid_b200.h).
+
+Multi-GPU layout: rank r of P owns the probe rows {i : i mod P == r}.  Queries are
+the first rows, so both the N probes (stages K3–K7) and the q queries (K9–K12) are spread evenly.
+Three all-gathers move the neighbour lists, the V rows and the V_qe rows (MB-sized); the CMC
+histogram is an all-reduce and the per-query APs an all-gather.  Every row is produced by exactly
+one rank with the same kernel, so results do not depend on P.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import dataclasses
+
+import numpy as np
+import torch
+
+from . import _lib
+
+METRIC_SQEUCLIDEAN = 0
+METRIC_ARCCOS = 1
+ENGINES = {"auto": 0, "simt": 1, "tcgen05": 2}
+
+
+def _ptr(t):
+    return C.c_void_p(0) if t is None else C.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def half_k(k1: int) -> int:
+    return _lib.load().reid_half_k(int(k1))
+
+
+def v_row_capacity(k1: int) -> int:
+    return _lib.load().reid_v_row_capacity(int(k1))
+
+
+@dataclasses.dataclass
+class Features:
+    """Prepared feature rows: TF32 hi + residual lo (padded to dp), squared norms and norms."""
+    hi: torch.Tensor
+    lo: torch.Tensor
+    sq: torch.Tensor
+    nrm: torch.Tensor
+    n: int
+    d: int
+    dp: int
+
+
+class Comm:
+    """Cyclic row ownership + the collectives the path needs.  world == 1 is the identity."""
+
+    def __init__(self, group=None):
+        import torch.distributed as dist
+        self.dist = dist
+        self.group = group
+        if dist.is_available() and dist.is_initialized():
+            self.rank = dist.get_rank(group)
+            self.world = dist.get_world_size(group)
+        else:
+            self.rank, self.world = 0, 1
+
+    def local_count(self, n: int) -> int:
+        """#{i < n : i mod world == rank}"""
+        return (n - self.rank + self.world - 1) // self.world if n > self.rank else 0
+
+    def gather_rows(self, local: torch.Tensor, n: int) -> torch.Tensor:
+        """local[l] is global row rank + l*world; returns all n rows in global order."""
+        if self.world == 1:
+            return local
+        nmax = (n + self.world - 1) // self.world
+        pad = local
+        if local.shape[0] != nmax:
+            pad = local.new_zeros((nmax,) + tuple(local.shape[1:]))
+            pad[: local.shape[0]] = local
+        out = local.new_empty((self.world, nmax) + tuple(local.shape[1:]))
+        self.dist.all_gather_into_tensor(out, pad.contiguous(), group=self.group)
+        # [P, nmax, ...] -> interleave -> [nmax*P, ...]
+        out = out.transpose(0, 1).reshape((nmax * self.world,) + tuple(local.shape[1:]))
+        return out[:n].contiguous()
+
+    def gather_flat(self, local: torch.Tensor, size_max: int) -> torch.Tensor:
+        """Variable-length 1-D pools padded to size_max; returns [world, size_max]."""
+        if self.world == 1:
+            return local.reshape(1, -1)
+        pad = local.new_zeros((size_max,))
+        pad[: local.shape[0]] = local
+        out = local.new_empty((self.world, size_max))
+        self.dist.all_gather_into_tensor(out, pad, group=self.group)
+        return out
+
+    def all_reduce_sum(self, t: torch.Tensor) -> torch.Tensor:
+        if self.world > 1:
+            self.dist.all_reduce(t, group=self.group)
+        return t
+
+    def max_int(self, v: int, device) -> int:
+        if self.world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.int64, device=device)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX, group=self.group)
+        return int(t.item())
+
+
+class Engine:
+    def __init__(self, device=None, engine: str = "auto", comm: Comm | None = None):
+        if not torch.cuda.is_available():
+            raise _lib.ReidError("reid_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.lib = _lib.load()
+        rc = self.lib.reid_device_check(self.device.index or 0)
+        if rc != 0:
+            raise _lib.ReidError(self.lib.reid_last_error().decode())
+        self.engine = ENGINES[engine]
+        self.comm = comm or Comm()
+        self.timers = None          # dict stage -> list[(start_event, end_event)] when profiling
+
+    # ------------------------------------------------------------------ timing helpers
+    def enable_timers(self, on=True):
+        self.timers = {} if on else None
+
+    class _Span:
+        def __init__(self, eng, name):
+            self.eng, self.name = eng, name
+
+        def __enter__(self):
+            if self.eng.timers is not None:
+                self.a = torch.cuda.Event(enable_timing=True)
+                self.b = torch.cuda.Event(enable_timing=True)
+                self.a.record()
+            return self
+
+        def __exit__(self, *exc):
+            if self.eng.timers is not None:
+                self.b.record()
+                self.eng.timers.setdefault(self.name, []).append((self.a, self.b))
+            return False
+
+    def span(self, name):
+        return Engine._Span(self, name)
+
+    def stage_ms(self):
+        """{stage: total ms} since enable_timers(); synchronises."""
+        torch.cuda.synchronize(self.device)
+        return {k: sum(a.elapsed_time(b) for a, b in v) for k, v in (self.timers or {}).items()}
+
+    # ------------------------------------------------------------------ buffers
+    def _empty(self, shape, dtype):
+        return torch.empty(shape, dtype=dtype, device=self.device)
+
+    def _zeros(self, shape, dtype):
+        return torch.zeros(shape, dtype=dtype, device=self.device)
+
+    # ------------------------------------------------------------------ K13
+    def prepare(self, X: torch.Tensor, normalize: bool, row0: int = 0, row_stride: int = 1) -> Features:
+        """X: [n, d] float32 on the device (row-major).  A row window selects row0 + l*row_stride."""
+        assert X.is_cuda and X.dtype == torch.float32 and X.dim() == 2 and X.stride(1) == 1
+        n_all, d = X.shape
+        n = (n_all - row0 + row_stride - 1) // row_stride if n_all > row0 else 0
+        dp = self.lib.reid_padded_width(d)
+        hi = self._empty((n, dp), torch.float32)
+        lo = self._empty((n, dp), torch.float32)
+        sq = self._empty((n,), torch.float32)
+        nrm = self._empty((n,), torch.float32)
+        ld = X.stride(0)
+        base = X.data_ptr() + row0 * ld * 4
+        _lib.call("reid_prepare_features", C.c_void_p(base), n, d, ld * row_stride, int(normalize), _ptr(hi),
+                  _ptr(lo), dp, _ptr(sq), _ptr(nrm), _stream())
+        return Features(hi, lo, sq, nrm, n, d, dp)
+
+    # ------------------------------------------------------------------ K1/K2/K3
+    @staticmethod
+    def pitch(n: int) -> int:
+        return (n + 31) // 32 * 32
+
+    def dist(self, A: Features, B: Features, metric: int = METRIC_SQEUCLIDEAN, want_rowmax: bool = False,
+             engine: int | None = None):
+        """Returns (D [m, pitch] float32 — use D[:, :n] —, rowmax_key [m] int32 or None)."""
+        assert A.dp == B.dp
+        m, n = A.n, B.n
+        ld = self.pitch(n)
+        D = self._empty((m, ld), torch.float32)
+        key = None
+        if want_rowmax:
+            key = self._empty((m,), torch.int32)
+            _lib.call("reid_rowmax_init", _ptr(key), m, _stream())
+        ra, rb = (A.sq, B.sq) if metric == METRIC_SQEUCLIDEAN else (A.nrm, B.nrm)
+        _lib.call("reid_dist", _ptr(A.hi), _ptr(A.lo), _ptr(ra), m, _ptr(B.hi), _ptr(B.lo), _ptr(rb), n, A.dp,
+                  metric, self.engine if engine is None else engine, _ptr(D), ld, _ptr(key), _stream())
+        return D, key
+
+    def rowmax(self, D: torch.Tensor, cols: int) -> torch.Tensor:
+        key = self._empty((D.shape[0],), torch.int32)
+        _lib.call("reid_rowmax", _ptr(D), D.shape[0], cols, D.stride(0), _ptr(key), _stream())
+        return key
+
+    def rowmax_values(self, key: torch.Tensor) -> torch.Tensor:
+        out = self._empty((key.shape[0],), torch.float32)
+        _lib.call("reid_rowmax_decode", _ptr(key), key.shape[0], _ptr(out), _stream())
+        return out
+
+    def transposed(self, src: torch.Tensor, dst: torch.Tensor | None = None, accumulate: bool = False):
+        """dst[i, j] (+)= src[j, i] for a square matrix; dst is pitched."""
+        n = src.shape[0]
+        assert src.shape[1] >= n and src.dtype == torch.float32
+        if dst is None:
+            dst = self._empty((n, self.pitch(n)), torch.float32)
+        _lib.call("reid_transpose_add", _ptr(src), n, src.stride(0), _ptr(dst), dst.stride(0), int(accumulate),
+                  _stream())
+        return dst
+
+    # ------------------------------------------------------------------ K5
+    def topk_rows(self, D: torch.Tensor, cols: int, key: torch.Tensor, K: int, want_values=False, cap: int = 0):
+        rows = D.shape[0]
+        nbr = self._empty((rows, K), torch.int32)
+        val = self._empty((rows, K), torch.float32) if want_values else None
+        if cap:
+            _lib.call("reid_topk_rows_capped", _ptr(D), rows, cols, D.stride(0), _ptr(key), K, _ptr(nbr), _ptr(val),
+                      cap, _stream())
+        else:
+            _lib.call("reid_topk_rows", _ptr(D), rows, cols, D.stride(0), _ptr(key), K, _ptr(nbr), _ptr(val),
+                      _stream())
+        return (nbr, val) if want_values else nbr
+
+    # ------------------------------------------------------------------ K6
+    def krecip_sets(self, nbr: torch.Tensor, k1: int):
+        N, K = nbr.shape
+        h = half_k(k1)
+        rfull = self._empty((N, k1 + 1), torch.int32)
+        nfull = self._empty((N,), torch.int32)
+        rhalf = self._empty((N, h), torch.int32)
+        nhalf = self._empty((N,), torch.int32)
+        _lib.call("reid_krecip_sets", _ptr(nbr), N, K, k1, _ptr(rfull), _ptr(nfull), _ptr(rhalf), _ptr(nhalf),
+                  _stream())
+        return rfull, nfull, rhalf, nhalf
+
+    def krecip_V(self, sets, k1: int, D: torch.Tensor, key: torch.Tensor, row0=0, row_stride=1):
+        rfull, nfull, rhalf, nhalf = sets
+        rows = D.shape[0]
+        cap1 = v_row_capacity(k1)
+        Vc = self._empty((rows, cap1), torch.int32)
+        Vv = self._empty((rows, cap1), torch.float16)
+        Vn = self._empty((rows,), torch.int32)
+        _lib.call("reid_krecip_V", _ptr(rfull), _ptr(nfull), _ptr(rhalf), _ptr(nhalf), row0, row_stride, rows, k1,
+                  _ptr(D), D.stride(0), _ptr(key), _ptr(Vc), _ptr(Vv), _ptr(Vn), _stream())
+        return Vc, Vv, Vn
+
+    # ------------------------------------------------------------------ K7
+    def query_expansion(self, nbr, k2, Vc, Vv, Vn, rows, row0=0, row_stride=1, cap_sort: int = 0):
+        """Returns (Qc, Qv, qoff[rows+1] int64, Qn[rows]) for the row window."""
+        K = nbr.shape[1]
+        cap1 = Vc.shape[1]
+        ub = self._empty((rows,), torch.int32)
+        _lib.call("reid_qe_bound", _ptr(nbr), K, k2, _ptr(Vn), row0, row_stride, rows, _ptr(ub), _stream())
+        qoff = self._empty((rows + 1,), torch.int64)
+        _lib.call("reid_exclusive_scan", _ptr(ub), rows, _ptr(qoff), _stream())
+        total = int(qoff[rows].item())                 # 8-byte D2H: sizes the CSR pool
+        Qc = self._empty((max(total, 1),), torch.int32)
+        Qv = self._empty((max(total, 1),), torch.float16)
+        Qn = self._empty((rows,), torch.int32)
+        if cap_sort:
+            _lib.call("reid_qe_k2_capped", _ptr(nbr), K, k2, _ptr(Vc), _ptr(Vv), _ptr(Vn), cap1, row0, row_stride,
+                      rows, _ptr(qoff), cap_sort, _ptr(Qc), _ptr(Qv), _ptr(Qn), _stream())
+        else:
+            _lib.call("reid_qe_k2", _ptr(nbr), K, k2, _ptr(Vc), _ptr(Vv), _ptr(Vn), cap1, row0, row_stride, rows,
+                      _ptr(qoff), _ptr(Qc), _ptr(Qv), _ptr(Qn), _stream())
+        return Qc, Qv, qoff, Qn, total
+
+    # ------------------------------------------------------------------ K8
+    def inverted_index(self, Qc, Qv, qoff, Qn, N: int, nnz_bound: int):
+        colcnt = self._zeros((N,), torch.int32)
+        _lib.call("reid_csc_count", _ptr(Qc), _ptr(qoff), _ptr(Qn), N, _ptr(colcnt), _stream())
+        colptr = self._empty((N + 1,), torch.int64)
+        _lib.call("reid_exclusive_scan", _ptr(colcnt), N, _ptr(colptr), _stream())
+        cursor = self._zeros((N,), torch.int32)
+        csc_row = self._empty((max(nnz_bound, 1),), torch.int32)
+        csc_val = self._empty((max(nnz_bound, 1),), torch.float16)
+        _lib.call("reid_csc_fill", _ptr(Qc), _ptr(Qv), _ptr(qoff), _ptr(Qn), N, _ptr(colptr), _ptr(cursor),
+                  _ptr(csc_row), _ptr(csc_val), _stream())
+        return colptr, csc_row, csc_val
+
+    # ------------------------------------------------------------------ K9 + K10
+    def jaccard_mix(self, Qc, Qv, qoff, Qn, csc, D, key, q: int, N: int, lam: float, nq_local: int, q0=0,
+                    q_stride=1, want_jaccard=False):
+        colptr, csc_row, csc_val = csc
+        g = N - q
+        ldf = self.pitch(g)
+        out = self._empty((nq_local, ldf), torch.float32)
+        J = self._empty((nq_local, N), torch.float16) if want_jaccard else None
+        c1 = float(np.float16(1 - lam))            # fp16 array * python float: scalar cast to fp16 first
+        c2 = float(np.float32(lam))                # fp32 array * python float
+        _lib.call("reid_jaccard_mix", _ptr(Qc), _ptr(Qv), _ptr(qoff), _ptr(Qn), _ptr(colptr), _ptr(csc_row),
+                  _ptr(csc_val), _ptr(D), D.stride(0), _ptr(key), q0, q_stride, nq_local, q, N, c1, c2, _ptr(out),
+                  ldf, _ptr(J), N, _stream())
+        return (out, J) if want_jaccard else out
+
+    # ------------------------------------------------------------------ K4–K10 from a distance panel
+    def rerank_from_panel(self, D: torch.Tensor, key: torch.Tensor, q: int, N: int, k1: int, k2: int, lam: float,
+                          detail: dict | None = None) -> torch.Tensor:
+        """D: this rank's panel [n_local, pitch(N)] (row l = probe rank + l*world), key: its row
+        maxima.  Returns final[nq_local, pitch(g)] for this rank's queries (use [:, :g])."""
+        cm = self.comm
+        r, P = cm.rank, cm.world
+        nloc = D.shape[0]
+        K = max(k1 + 1, k2)
+        if N < K:
+            raise NotImplementedError(f"re-ranking needs at least max(k1+1, k2) = {K} samples, got {N}")
+        with self.span("select"):
+            nbr_local = self.topk_rows(D, N, key, K)
+        nbr = cm.gather_rows(nbr_local, N)
+        with self.span("krecip"):
+            sets = self.krecip_sets(nbr, k1)
+            Vc_l, Vv_l, Vn_l = self.krecip_V(sets, k1, D, key, r, P)
+        Vc, Vv, Vn = cm.gather_rows(Vc_l, N), cm.gather_rows(Vv_l, N), cm.gather_rows(Vn_l, N)
+        if k2 != 1:
+            with self.span("qe"):
+                Qc_l, Qv_l, qoff_l, Qn_l, total = self.query_expansion(nbr, k2, Vc, Vv, Vn, nloc, r, P)
+            if P == 1:
+                Qc, Qv, qoff, Qn, nnz_bound = Qc_l, Qv_l, qoff_l, Qn_l, total
+            else:
+                tmax = cm.max_int(total, self.device)
+                Qc = cm.gather_flat(Qc_l[:total], tmax).reshape(-1)
+                Qv = cm.gather_flat(Qv_l[:total], tmax).reshape(-1)
+                Qn = cm.gather_rows(Qn_l, N)
+                # global offset of row i = (i mod P) * tmax + qoff_rank[i div P]
+                offs = cm.gather_rows(qoff_l[:nloc], N)
+                owner = torch.arange(N, device=self.device, dtype=torch.int64) % P
+                qoff = torch.cat([offs + owner * tmax, offs.new_zeros(1)])
+                nnz_bound = tmax * P
+        else:
+            cap1 = Vc.shape[1]
+            qoff = self._empty((N + 1,), torch.int64)
+            _lib.call("reid_ell_offsets", N, cap1, _ptr(qoff), _stream())
+            Qc, Qv, Qn = Vc.reshape(-1), Vv.reshape(-1), Vn
+            nnz_bound = int(Vn.sum().item())
+        with self.span("csc"):
+            csc = self.inverted_index(Qc, Qv, qoff, Qn, N, nnz_bound)
+        nq_local = cm.local_count(q)
+        with self.span("jaccard_mix"):
+            res = self.jaccard_mix(Qc, Qv, qoff, Qn, csc, D, key, q, N, lam, nq_local, r, P,
+                                   want_jaccard=detail is not None)
+        if detail is not None:
+            final, J = res
+            detail.update(nbr=nbr, sets=sets, Vc=Vc, Vv=Vv, Vn=Vn, Qc=Qc, Qv=Qv, qoff=qoff, Qn=Qn, csc=csc, J=J)
+            return final
+        return res
+
+    def rerank_features(self, feats: torch.Tensor, q: int, k1: int, k2: int, lam: float, normalize: bool,
+                        detail: dict | None = None) -> torch.Tensor:
+        """feats: [N, d] float32 on the device, queries first (reranking.py:29-44 then the rest)."""
+        cm = self.comm
+        N = feats.shape[0]
+        with self.span("prep"):
+            allf = self.prepare(feats, normalize)
+            mine = allf if cm.world == 1 else self.prepare(feats, normalize, cm.rank, cm.world)
+        with self.span("dist"):
+            D, key = self.dist(mine, allf, METRIC_SQEUCLIDEAN, want_rowmax=True)
+        if detail is not None:
+            detail.update(D=D, key=key)
+        return self.rerank_from_panel(D, key, q, N, k1, k2, lam, detail)
+
+    # ------------------------------------------------------------------ K11 + K12
+    def rank_rows(self, dist: torch.Tensor, g: int) -> torch.Tensor:
+        rows = dist.shape[0]
+        keyA = self._empty((rows, g), torch.int32)
+        keyB = self._empty((rows, g), torch.int32)
+        idxA = self._empty((rows, g), torch.int32)
+        ranked = self._empty((rows, g), torch.int32)
+        _lib.call("reid_rank_rows", _ptr(dist), rows, g, dist.stride(0), _ptr(keyA), _ptr(keyB), _ptr(idxA),
+                  _ptr(ranked), _stream())
+        return ranked
+
+    def score(self, ranked: torch.Tensor, q_pids, g_pids, q_cams, g_cams, max_rank: int, q_total: int | None = None):
+        """ranked: this rank's [nq_local, g]; q_pids/q_cams: the matching local slices (int64).
+        Returns (cmc float32[max_rank] tensor, mAP float64 tensor[1], n_valid int tensor[1], ap[q])."""
+        cm = self.comm
+        nq, g = ranked.shape
+        ap = self._empty((nq,), torch.float64)
+        first = self._empty((nq,), torch.int32)
+        hist = self._zeros((max_rank,), torch.int32)
+        nvalid = self._zeros((1,), torch.int32)
+        with self.span("score"):
+            _lib.call("reid_score_rows", _ptr(ranked), nq, g, _ptr(q_pids), _ptr(g_pids), _ptr(q_cams), _ptr(g_cams),
+                      max_rank, _ptr(ap), _ptr(first), _ptr(hist), _ptr(nvalid), _stream())
+        q_all = nq if q_total is None else q_total
+        ap_all = cm.gather_rows(ap, q_all)
+        first_all = cm.gather_rows(first, q_all)
+        cm.all_reduce_sum(hist)
+        cm.all_reduce_sum(nvalid)
+        cmc = self._empty((max_rank,), torch.float32)
+        mAP = self._empty((1,), torch.float64)
+        _lib.call("reid_score_finalize", _ptr(ap_all), q_all, _ptr(hist), max_rank, _ptr(nvalid), _ptr(cmc),
+                  _ptr(mAP), _stream())
+        return cmc, mAP, nvalid, ap_all, first_all
+
+    def evaluate_dist(self, dist: torch.Tensor, g: int, q_pids, g_pids, q_cams, g_cams, max_rank: int,
+                      q_total: int | None = None):
+        with self.span("rank"):
+            ranked = self.rank_rows(dist, g)
+        return self.score(ranked, q_pids, g_pids, q_cams, g_cams, max_rank, q_total)
+
+
+_default = None
+
+
+def default_engine() -> Engine:
+    global _default
+    if _default is None:
+        _default = Engine()
+    return _default

@@ -1,0 +1,121 @@
+"""Drop-in for the reference's ``evaluate.py``: same names, arguments, prints, return types and
+quirks (squared distances; ``compute()`` ignores the constructor's ``max_rank`` and hard-codes
+k1=50, k2=15, lambda=0.3 when ``reranking=True``; AssertionError when no query has a match) with
+every array operation executed on a B200 by libreid_b200.so.  No CPU path."""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import engine as _engine
+from .reranking import re_ranking, re_ranking_device, _to_device_f32
+
+
+def _ids(x, device) -> torch.Tensor:
+    if isinstance(x, torch.Tensor):
+        t = x
+    else:
+        t = torch.from_numpy(np.ascontiguousarray(np.asarray(x)))
+    return t.to(device=device, dtype=torch.int64, non_blocking=True).contiguous()
+
+
+def _dist_matrix(qf, gf, metric) -> np.ndarray:
+    eng = _engine.default_engine()
+    out_dtype = qf.dtype if isinstance(qf, torch.Tensor) else torch.float32
+    A = eng.prepare(_to_device_f32(qf, eng.device), False)
+    B = eng.prepare(_to_device_f32(gf, eng.device), False)
+    D, _ = eng.dist(A, B, metric)
+    D = D[:, : B.n]
+    if metric == _engine.METRIC_SQEUCLIDEAN and out_dtype == torch.float16:
+        D = D.half()           # evaluate.py:7-13 returns the input dtype
+    return D.cpu().numpy()
+
+
+def euclidean_distance(qf, gf):
+    """evaluate.py:7-13 — squared L2, float32 numpy [m, n]."""
+    return _dist_matrix(qf, gf, _engine.METRIC_SQEUCLIDEAN)
+
+
+def cosine_similarity(qf, gf):
+    """evaluate.py:16-26 — arccos of the clipped cosine, float32 numpy [m, n]."""
+    return _dist_matrix(qf, gf, _engine.METRIC_ARCCOS)
+
+
+def eval_func_device(dist: torch.Tensor, g: int, q_pids, g_pids, q_camids, g_camids, max_rank=50,
+                     eng: _engine.Engine | None = None, q_total: int | None = None):
+    """dist: device tensor [q_local, >= g] float32 (row pitch free).  Returns (cmc, mAP) like
+    eval_func; only cmc[max_rank] and mAP leave the device."""
+    eng = eng or _engine.default_engine()
+    if g < max_rank:
+        max_rank = g
+        print("Note: number of gallery samples is quite small, got {}".format(g))
+    cmc, mAP, nvalid, _, _ = eng.evaluate_dist(dist, g, q_pids, g_pids, q_camids, g_camids, max_rank, q_total)
+    nv = int(nvalid.item())
+    assert nv > 0, "Error: all query identities do not appear in gallery"
+    return cmc.cpu().numpy(), np.float64(mAP.item())
+
+
+def eval_func(distmat, q_pids, g_pids, q_camids, g_camids, max_rank=50):
+    """evaluate.py:29-88 — Market-1501 CMC / mAP for a q x g distance matrix."""
+    eng = _engine.default_engine()
+    dev = eng.device
+    if isinstance(distmat, np.ndarray):
+        d = torch.from_numpy(np.ascontiguousarray(distmat))
+    else:
+        d = distmat
+    d = d.to(dev, non_blocking=True)
+    if d.dtype != torch.float32:
+        d = d.float()
+    d = d.contiguous()
+    num_q, num_g = d.shape
+    return eval_func_device(d, num_g, _ids(q_pids, dev), _ids(g_pids, dev), _ids(q_camids, dev),
+                            _ids(g_camids, dev), max_rank, eng)
+
+
+class R1_mAP_eval():
+    """evaluate.py:91-135.  ``update`` keeps tensors where they are (CPU or CUDA); ``compute``
+    moves them to the B200 once and returns (cmc float32[50], mAP float64)."""
+
+    def __init__(self, num_query, max_rank=50, feat_norm=True, reranking=False):
+        super(R1_mAP_eval, self).__init__()
+        self.num_query = num_query
+        self.max_rank = max_rank
+        self.feat_norm = feat_norm
+        self.reranking = reranking
+
+    def reset(self):
+        self.feats = []
+        self.pids = []
+        self.camids = []
+
+    def update(self, output):  # called once for each batch
+        feat, pid, camid = output
+        self.feats.append(feat.detach())
+        self.pids.extend(np.asarray(pid.cpu() if isinstance(pid, torch.Tensor) else pid))
+        self.camids.extend(np.asarray(camid.cpu() if isinstance(camid, torch.Tensor) else camid))
+
+    def compute(self):  # called after each epoch
+        eng = _engine.default_engine()
+        dev = eng.device
+        feats = torch.cat([_to_device_f32(f, dev) for f in self.feats], dim=0)
+        if self.feat_norm:
+            print("The test feature is normalized")
+        q = self.num_query
+        N = feats.shape[0]
+        g = N - q
+        pids = _ids(np.asarray(self.pids), dev)
+        camids = _ids(np.asarray(self.camids), dev)
+        if self.reranking:
+            print('=> Enter reranking')
+            dist = eng.rerank_features(feats, q, 50, 15, 0.3, normalize=self.feat_norm)   # evaluate.py:127
+        else:
+            print('=> Computing DistMat with euclidean_distance')
+            allf = eng.prepare(feats, self.feat_norm)
+            qf = _engine.Features(allf.hi[:q], allf.lo[:q], allf.sq[:q], allf.nrm[:q], q, allf.d, allf.dp)
+            gf = _engine.Features(allf.hi[q:], allf.lo[q:], allf.sq[q:], allf.nrm[q:], g, allf.d, allf.dp)
+            dist, _ = eng.dist(qf, gf, _engine.METRIC_SQEUCLIDEAN)
+        # evaluate.py:132 does not forward self.max_rank: always 50
+        cmc, mAP = eval_func_device(dist, g, pids[:q].contiguous(), pids[q:].contiguous(),
+                                    camids[:q].contiguous(), camids[q:].contiguous(), 50, eng)
+        print("Rank@{:d}:{:.1%}, Rank@{:d}:{:.1%}, Rank@{:d}:{:.1%}, mAP:{:.1%}".format(1, cmc[0], 5, cmc[4], 10, cmc[9], mAP))
+        return cmc, mAP

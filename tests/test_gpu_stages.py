@@ -1,0 +1,163 @@
+"""Stage-by-stage parity of the CUDA path against the CPU oracle on identical inputs.
+
+GEMM rounding is taken out of the picture by handing the oracle the distance matrix the GPU
+produced (the reference offers the same hook: re_ranking(..., local_distmat=D, only_local=True),
+reranking.py:33-34), so every stage after the contraction must agree BIT FOR BIT."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+CASES = [("tiny", 20, 6, 0), ("tiny", 50, 15, 1), ("tiny", 5, 1, 2), ("tiny", 25, 3, 3),
+         ("small", 20, 6, 0), ("small", 50, 15, 4), ("small", 7, 2, 5)]
+
+
+def _features(synth, name, seed, device):
+    sh = synth.SHAPES[name]
+    qf, gf, qp, gp, qc, gc = synth.make(sh, seed)
+    return sh, torch.cat([qf, gf]).to(device), qp, gp, qc, gc
+
+
+def test_prepare_matches_normalize(eng, synth, oracle):
+    sh, X, *_ = _features(synth, "small", 0, eng.device)
+    f = eng.prepare(X, True)
+    got = (f.hi + f.lo)[:, : sh.d].cpu().numpy()
+    want = oracle.l2_normalize(X.cpu().numpy())
+    np.testing.assert_allclose(got, want, rtol=2e-6, atol=1e-8)
+    assert torch.all(f.hi[:, sh.d:] == 0) and torch.all(f.lo[:, sh.d:] == 0)
+    hi = f.hi.cpu().numpy().view(np.uint32)
+    assert np.all(hi & 0x1FFF == 0), "hi part must be TF32-representable"
+    np.testing.assert_allclose(f.sq.cpu().numpy(), (want.astype(np.float64) ** 2).sum(1), rtol=1e-5)
+    # raw (un-normalised) preparation reproduces the input exactly
+    f2 = eng.prepare(X, False)
+    assert torch.equal((f2.hi + f2.lo)[:, : sh.d], X)
+
+
+@pytest.mark.parametrize("engine_name", ["simt", "tcgen05"])
+@pytest.mark.parametrize("name,seed", [("tiny", 0), ("small", 1), ("mid", 2)])
+def test_sq_euclidean_and_arccos(eng, engine_mod, synth, oracle, name, seed, engine_name):
+    sh, X, *_ = _features(synth, name, seed, eng.device)
+    code = engine_mod.ENGINES[engine_name]
+    f = eng.prepare(X, True)
+    xn = (f.hi + f.lo)[:, : sh.d].cpu().numpy()
+    q = sh.q
+    A = engine_mod.Features(f.hi[:q], f.lo[:q], f.sq[:q], f.nrm[:q], q, f.d, f.dp)
+    B = engine_mod.Features(f.hi[q:], f.lo[q:], f.sq[q:], f.nrm[q:], sh.g, f.d, f.dp)
+    D, key = eng.dist(A, B, engine_mod.METRIC_SQEUCLIDEAN, want_rowmax=True, engine=code)
+    got = D[:, : sh.g].cpu().numpy()
+    want = oracle.sq_euclidean(xn[:q], xn[q:])
+    ref64 = ((xn[:q, None, :].astype(np.float64) - xn[None, q:, :].astype(np.float64)) ** 2).sum(-1) \
+        if name != "mid" else None
+    # north_star tolerance: distances within 1e-4 relative; fp32 accumulation is far tighter
+    np.testing.assert_allclose(got, want, rtol=1e-4, atol=2e-6)
+    assert np.abs(got - want).max() < 5e-6
+    if ref64 is not None:
+        assert np.abs(got - ref64).max() < 5e-6
+    np.testing.assert_array_equal(eng.rowmax_values(key).cpu().numpy(), got.max(1))
+    # cosine / arccos on the raw (un-normalised) features, as evaluate.py:16-26 is called
+    fr = eng.prepare(X, False)
+    A = engine_mod.Features(fr.hi[:q], fr.lo[:q], fr.sq[:q], fr.nrm[:q], q, fr.d, fr.dp)
+    B = engine_mod.Features(fr.hi[q:], fr.lo[q:], fr.sq[q:], fr.nrm[q:], sh.g, fr.d, fr.dp)
+    Dc, _ = eng.dist(A, B, engine_mod.METRIC_ARCCOS, engine=code)
+    xr = X.cpu().numpy()
+    np.testing.assert_allclose(Dc[:, : sh.g].cpu().numpy(), oracle.arccos_distance(xr[:q], xr[q:]),
+                               rtol=1e-4, atol=1e-5)
+
+
+def _panel(eng, engine_mod, X, normalize=True):
+    f = eng.prepare(X, normalize)
+    D, key = eng.dist(f, f, engine_mod.METRIC_SQEUCLIDEAN, want_rowmax=True)
+    return D, key
+
+
+@pytest.mark.parametrize("name,k1,k2,seed", CASES)
+def test_rerank_stages_bit_exact(eng, engine_mod, synth, oracle, name, k1, k2, seed):
+    sh, X, qp, gp, qc, gc = _features(synth, name, seed, eng.device)
+    N, q = sh.q + sh.g, sh.q
+    D, key = _panel(eng, engine_mod, X)
+    Dh = D[:, :N].cpu().numpy()
+    det = {}
+    final = eng.rerank_from_panel(D, key, q, N, k1, k2, 0.3, detail=det)[:, : sh.g].cpu().numpy()
+    ref = oracle.rerank_from_dist(np.ascontiguousarray(Dh.T), q, k1, k2, 0.3, detail=True)
+
+    # K4: row maxima / K5: neighbour lists (stable (value, index) order on both sides)
+    np.testing.assert_array_equal(eng.rowmax_values(key).cpu().numpy(), Dh.max(1))
+    K = max(k1 + 1, k2)
+    np.testing.assert_array_equal(det["nbr"].cpu().numpy(), ref["nbr"][:, :K])
+    # K6: expansion sets and float16 weights
+    Vc, Vv, Vn = (det[k].cpu().numpy() for k in ("Vc", "Vv", "Vn"))
+    for i in range(N):
+        np.testing.assert_array_equal(Vc[i, : Vn[i]], ref["E"][i], err_msg=f"E[{i}]")
+        np.testing.assert_array_equal(Vv[i, : Vn[i]].view(np.uint16), ref["V"][i].view(np.uint16),
+                                      err_msg=f"V[{i}]")
+    # K7: query expansion
+    Qc, Qv, qoff, Qn = (det[k].cpu().numpy() for k in ("Qc", "Qv", "qoff", "Qn"))
+    for i in range(N):
+        a, n = qoff[i], Qn[i]
+        np.testing.assert_array_equal(Qc[a:a + n], ref["Qc"][i], err_msg=f"Qc[{i}]")
+        np.testing.assert_array_equal(Qv[a:a + n].view(np.uint16), ref["Qv"][i].view(np.uint16),
+                                      err_msg=f"Qv[{i}]")
+    # K8: inverted index (as sets per column; order inside a column is free)
+    colptr, crow, cval = (t.cpu().numpy() for t in det["csc"])
+    rptr, rrows, rvals = ref["inv"]
+    np.testing.assert_array_equal(colptr, rptr)
+    for c in range(0, N, max(1, N // 50)):
+        a, b = colptr[c], colptr[c + 1]
+        o = np.argsort(crow[a:b], kind="stable")
+        np.testing.assert_array_equal(crow[a:b][o], rrows[a:b])
+        np.testing.assert_array_equal(cval[a:b][o].view(np.uint16), rvals[a:b].view(np.uint16))
+    # K9: float16 Jaccard rows, K10: lambda mix — bit exact
+    np.testing.assert_array_equal(det["J"].cpu().numpy().view(np.uint16), ref["J"].view(np.uint16))
+    np.testing.assert_array_equal(final.view(np.uint32), ref["final"].view(np.uint32))
+
+    # K11 / K12 on the re-ranked matrix
+    cmc_o, map_o, aps_o, first_o = oracle.cmc_map(ref["final"], qp.numpy(), gp.numpy(), qc.numpy(), gc.numpy(),
+                                                  detail=True)
+    dev = eng.device
+    fin = torch.from_numpy(ref["final"]).to(dev)
+    ranked = eng.rank_rows(fin, sh.g).cpu().numpy()
+    np.testing.assert_array_equal(ranked, np.argsort(ref["final"], axis=1, kind="stable"))
+    cmc, mAP, nvalid, ap, first = eng.evaluate_dist(fin, sh.g, qp.to(dev), gp.to(dev), qc.to(dev), gc.to(dev),
+                                                   min(50, sh.g))
+    np.testing.assert_array_equal(cmc.cpu().numpy(), cmc_o)
+    assert abs(mAP.item() - map_o) < 1e-12
+    np.testing.assert_array_equal(first.cpu().numpy(), first_o)
+    ap = ap.cpu().numpy()
+    valid = ~np.isnan(aps_o)
+    np.testing.assert_allclose(ap[valid], aps_o[valid], rtol=0, atol=1e-14)
+    assert np.all(ap[~valid] == -1.0)
+    assert int(nvalid.item()) == int(valid.sum())
+
+
+def test_select_fallback_and_ties(eng, engine_mod, oracle):
+    """Massive ties (duplicated rows) and a capped candidate buffer force the exact arg-min path."""
+    g = torch.Generator().manual_seed(7)
+    base = torch.randn(40, 32, generator=g)
+    X = base.repeat(12, 1).to(eng.device)            # 480 rows, every row duplicated 12 times
+    N = X.shape[0]
+    D, key = _panel(eng, engine_mod, X)
+    Dh = D[:, :N].cpu().numpy()
+    O = oracle.normalized_rows(np.ascontiguousarray(Dh.T))
+    want = oracle.neighbour_lists(O, 21)
+    for cap in (0, 16):
+        nbr, val = eng.topk_rows(D, N, key, 21, want_values=True, cap=cap)
+        np.testing.assert_array_equal(nbr.cpu().numpy(), want, err_msg=f"cap={cap}")
+        np.testing.assert_array_equal(val.cpu().numpy(), np.take_along_axis(O, want.astype(np.int64), 1))
+
+
+def test_qe_merge_fallback(eng, engine_mod, synth, oracle):
+    """A tiny per-warp sort buffer forces the k2-way merge path; results must not change."""
+    sh, X, *_ = _features(synth, "tiny", 3, eng.device)
+    N = sh.q + sh.g
+    D, key = _panel(eng, engine_mod, X)
+    nbr = eng.topk_rows(D, N, key, 21)
+    sets = eng.krecip_sets(nbr, 20)
+    Vc, Vv, Vn = eng.krecip_V(sets, 20, D, key)
+    a = eng.query_expansion(nbr, 6, Vc, Vv, Vn, N)
+    b = eng.query_expansion(nbr, 6, Vc, Vv, Vn, N, cap_sort=32)
+    assert torch.equal(a[3], b[3])
+    qoff, Qn = a[2].cpu().numpy(), a[3].cpu().numpy()
+    for i in range(N):
+        s = slice(qoff[i], qoff[i] + Qn[i])
+        assert torch.equal(a[0][s], b[0][s]) and torch.equal(a[1][s].view(torch.int16), b[1][s].view(torch.int16))
