@@ -56,6 +56,9 @@ REID_API const char* reid_last_error(void);
 /* 0 if `device` is an sm_100 part this library can run on, REID_ERR_UNSUPPORTED otherwise. */
 REID_API int reid_device_check(int device);
 
+/* number of kernels this library has enqueued since it was loaded (host-side counter) */
+REID_API int64_t reid_launch_count(void);
+
 /* int(np.around(k1/2)) + 1 with banker's rounding             (reranking.py:60) */
 REID_API int reid_half_k(int k1);
 /* structural bound on the support of one row of V: (k1+1) * (half_k + 1) */

@@ -38,7 +38,8 @@ def _parse_header():
                 argtypes.append(_f)
             else:
                 raise ReidError(f"unhandled parameter type in header: {a!r}")
-        sigs[name] = (C.c_char_p if "char" in ret else C.c_int, argtypes)
+        restype = C.c_char_p if "char" in ret else (_l if "int64_t" in ret else C.c_int)
+        sigs[name] = (restype, argtypes)
     return sigs
 
 

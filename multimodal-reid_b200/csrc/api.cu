@@ -17,7 +17,11 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
+static unsigned long long g_launches = 0;   // kernels enqueued by this library (host-side count)
+void count_launches(int n) { __atomic_fetch_add(&g_launches, (unsigned long long)n, __ATOMIC_RELAXED); }
+
 int check_launch(const char* what) {
+  count_launches(1);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_error("%s launch failed: %s", what, cudaGetErrorString(e));
@@ -117,6 +121,8 @@ int reid_device_check(int device) {
   }
   return REID_OK;
 }
+
+int64_t reid_launch_count(void) { return (int64_t)__atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
 
 int reid_half_k(int k1) { return half_k(k1); }
 int reid_v_row_capacity(int k1) { return v_row_capacity(k1); }

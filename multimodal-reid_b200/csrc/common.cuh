@@ -10,7 +10,8 @@
 namespace reid {
 
 void set_error(const char* fmt, ...);
-int check_launch(const char* what);            // cudaGetLastError -> REID_OK / REID_ERR_CUDA
+int check_launch(const char* what);            // counts one launch; cudaGetLastError -> REID_OK / REID_ERR_CUDA
+void count_launches(int n);                    // extra launches of a multi-kernel launcher
 
 #define REID_CUDA(call)                                                              \
   do {                                                                               \

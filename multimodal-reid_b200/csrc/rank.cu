@@ -112,6 +112,7 @@ int launch_rank_rows(const float* dist, int rows, int g, long long ld_dist, uint
   rank_pass_kernel<false, false><<<rows, RK_T, 0, s>>>(dist, ld_dist, keyA, idxA, keyB, idx_out, g, 8);
   rank_pass_kernel<false, false><<<rows, RK_T, 0, s>>>(dist, ld_dist, keyB, idx_out, keyA, idxA, g, 16);
   rank_pass_kernel<false, true><<<rows, RK_T, 0, s>>>(dist, ld_dist, keyA, idxA, keyB, idx_out, g, 24);
+  count_launches(3);
   return check_launch("rank_pass_kernel");
 }
 

@@ -76,12 +76,14 @@ class R1_mAP_eval():
     """evaluate.py:91-135.  ``update`` keeps tensors where they are (CPU or CUDA); ``compute``
     moves them to the B200 once and returns (cmc float32[50], mAP float64)."""
 
-    def __init__(self, num_query, max_rank=50, feat_norm=True, reranking=False):
+    def __init__(self, num_query, max_rank=50, feat_norm=True, reranking=False, rerank_params=(50, 15, 0.3)):
         super(R1_mAP_eval, self).__init__()
         self.num_query = num_query
         self.max_rank = max_rank
         self.feat_norm = feat_norm
         self.reranking = reranking
+        # extension (keyword, default = the values the reference hard-codes at evaluate.py:127)
+        self.rerank_params = tuple(rerank_params)
 
     def reset(self):
         self.feats = []
@@ -107,7 +109,8 @@ class R1_mAP_eval():
         camids = _ids(np.asarray(self.camids), dev)
         if self.reranking:
             print('=> Enter reranking')
-            dist = eng.rerank_features(feats, q, 50, 15, 0.3, normalize=self.feat_norm)   # evaluate.py:127
+            k1, k2, lam = self.rerank_params                                          # evaluate.py:127
+            dist = eng.rerank_features(feats, q, k1, k2, lam, normalize=self.feat_norm)
         else:
             print('=> Computing DistMat with euclidean_distance')
             allf = eng.prepare(feats, self.feat_norm)

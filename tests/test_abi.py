@@ -1,0 +1,68 @@
+"""CPU: the C-ABI library builds, loads, exports every symbol include/reid_b200.h declares, and
+the host layer refuses to run without a B200 (no CPU fallback).  No compute calls here."""
+import ctypes
+import importlib
+import os
+import subprocess
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    _lib = importlib.import_module("multimodal-reid_b200._lib")
+    return _lib.load()
+
+
+def test_every_declared_symbol_is_exported(lib):
+    _lib = importlib.import_module("multimodal-reid_b200._lib")
+    names = _lib.header_symbols()
+    assert len(names) >= 25
+    raw = ctypes.CDLL(_lib.LIB_PATH)
+    for n in names:
+        assert hasattr(raw, n), f"{n} declared in include/reid_b200.h but not exported"
+    # and nothing but the declared surface leaks out of the library
+    out = subprocess.run(["nm", "-D", "--defined-only", _lib.LIB_PATH], capture_output=True, text=True).stdout
+    exported = {l.split()[-1] for l in out.splitlines() if " T " in l}
+    assert {e for e in exported if e.startswith("reid_")} == set(names)
+
+
+def test_host_constants(lib):
+    assert lib.reid_abi_version() == 1
+    assert [lib.reid_half_k(k) for k in (20, 50, 25, 5, 1)] == [11, 26, 13, 3, 1]     # reranking.py:60
+    assert lib.reid_v_row_capacity(20) == 21 * 12
+    assert [lib.reid_padded_width(d) for d in (512, 768, 1280, 1519, 64)] == [512, 768, 1280, 1536, 64]
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU behaviour")
+def test_no_cpu_fallback():
+    _lib = importlib.import_module("multimodal-reid_b200._lib")
+    ev = importlib.import_module("multimodal-reid_b200.evaluate")
+    with pytest.raises(_lib.ReidError):
+        ev.euclidean_distance(torch.randn(4, 8), torch.randn(5, 8))
+    rr = importlib.import_module("multimodal-reid_b200.reranking")
+    with pytest.raises(_lib.ReidError):
+        rr.re_ranking(torch.randn(4, 8), torch.randn(30, 8), 5, 2, 0.3)
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, "multimodal-reid_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert "import oracle" not in text and "from oracle" not in text, f
+
+
+def test_drop_in_names():
+    import evaluate
+    import reranking
+    for n in ("euclidean_distance", "cosine_similarity", "eval_func", "R1_mAP_eval", "re_ranking"):
+        assert hasattr(evaluate, n)
+    assert callable(reranking.re_ranking)
+    e = evaluate.R1_mAP_eval(5, max_rank=10, feat_norm=True, reranking=False)
+    e.reset()
+    assert (e.num_query, e.max_rank, e.feat_norm, e.reranking, e.feats, e.pids, e.camids) == (5, 10, True, False, [], [], [])

@@ -1,0 +1,141 @@
+"""GPU: the drop-in call surface (evaluate.py / reranking.py names) against the golden vectors
+frozen from the unmodified reference, and against the oracle on fresh seeds."""
+import contextlib
+import glob
+import io
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from parity import METRIC_TOL, assert_distances_close, assert_ranking_equal_mod_ties
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz")))
+
+
+@pytest.fixture(scope="module")
+def api():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import evaluate
+    import reranking
+    return evaluate, reranking
+
+
+@pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(p)[:-4] for p in GOLDEN])
+def test_golden(api, path):
+    evaluate, reranking = api
+    z = np.load(path)
+    q, k1, k2, lam = int(z["q"]), int(z["k1"]), int(z["k2"]), float(z["lam"])
+    f = torch.from_numpy(z["feats"])
+    raw = torch.from_numpy(z["raw"])
+    pids, cams = z["pids"], z["cams"]
+    # (1) same N x N matrix as the reference: bit-exact (reranking.py:33-34 hook)
+    if z["D"].size:
+        got = reranking.re_ranking(f[:q], f[q:], k1, k2, lam, local_distmat=z["D"], only_local=True)
+        assert got.dtype == np.float32 and got.shape == z["final"].shape
+        np.testing.assert_array_equal(got.view(np.uint32), z["final"].view(np.uint32))
+    # (2) own contraction: tolerance with fp16-flip classification
+    got = reranking.re_ranking(f[:q], f[q:], k1, k2, lam)
+    assert_distances_close(got, z["final"], what="re_ranking")
+    top = np.argsort(got, axis=1, kind="stable")[:, :10]
+    want_top = np.argsort(z["final"], axis=1, kind="stable")[:, :10]
+    # tie groups of the lambda-mix are wide (SURVEY hard part 3): compare keys, not indices
+    kg = np.take_along_axis(z["final"], top, 1)
+    kw = np.take_along_axis(z["final"], want_top, 1)
+    np.testing.assert_allclose(kg, kw, rtol=0, atol=1e-3)
+    # (3) distances
+    rows = z["eu"].shape[0]
+    eu = evaluate.euclidean_distance(f[:q], f[q:])
+    assert eu.dtype == np.float32 and eu.shape == (q, f.shape[0] - q)
+    np.testing.assert_allclose(eu[:rows], z["eu"], rtol=1e-4, atol=2e-6)
+    co = evaluate.cosine_similarity(raw[:q], raw[q:])
+    np.testing.assert_allclose(co[:rows], z["co"], rtol=1e-4, atol=1e-5)
+    # (4) scoring on the reference's own matrices
+    with contextlib.redirect_stdout(io.StringIO()):
+        cmc, mAP = evaluate.eval_func(z["final"], pids[:q], pids[q:], cams[:q], cams[q:])
+    assert cmc.dtype == np.float32 and isinstance(mAP, np.float64)
+    np.testing.assert_allclose(cmc, z["cmc_rr"], atol=METRIC_TOL)
+    assert abs(mAP - float(z["map_rr"])) < METRIC_TOL
+    # (5) the evaluator object, both modes (quirks: max_rank ignored, 50/15/0.3 hard-coded)
+    for flag, kc, km in ((False, "cmc_eval", "map_eval"), (True, "cmc_eval_rr", "map_eval_rr")):
+        e = evaluate.R1_mAP_eval(q, max_rank=10, feat_norm=True, reranking=flag)
+        e.reset()
+        buf = io.StringIO()
+        with contextlib.redirect_stdout(buf):
+            e.update((raw, torch.from_numpy(pids), torch.from_numpy(cams)))
+            cmc, mAP = e.compute()
+        assert cmc.shape == (50,)
+        np.testing.assert_allclose(cmc, z[kc], atol=METRIC_TOL)
+        assert abs(mAP - float(z[km])) < METRIC_TOL
+        assert "The test feature is normalized" in buf.getvalue() and "Rank@1" in buf.getvalue()
+
+
+def test_eval_func_edge_cases(api, oracle):
+    evaluate, _ = api
+    dist = np.array([[0.1, 0.2, 0.3, 0.4], [0.4, 0.3, 0.2, 0.1]], np.float32)
+    q_pids, q_cams = np.array([7, 9]), np.array([0, 1])
+    g_pids, g_cams = np.array([7, 5, 7, 9]), np.array([0, 0, 1, 1])
+    buf = io.StringIO()
+    with contextlib.redirect_stdout(buf):
+        cmc, mAP = evaluate.eval_func(dist, q_pids, g_pids, q_cams, g_cams)
+    assert "quite small" in buf.getvalue()           # evaluate.py:37-39
+    want_cmc, want_map = oracle.cmc_map(dist, q_pids, g_pids, q_cams, g_cams)
+    np.testing.assert_array_equal(cmc, want_cmc)
+    assert mAP == want_map
+    with pytest.raises(AssertionError, match="all query identities do not appear in gallery"):
+        with contextlib.redirect_stdout(io.StringIO()):
+            evaluate.eval_func(dist[1:], q_pids[1:], g_pids, q_cams[1:], g_cams)
+
+
+def test_local_distmat_additive(api, synth, oracle):
+    """reranking.py:43-44: local_distmat is added to the N x N matrix before normalisation."""
+    _, reranking = api
+    sh = synth.SHAPES["tiny"]
+    qf, gf, *_ = synth.make(sh, 5)
+    f = torch.nn.functional.normalize(torch.cat([qf, gf]), dim=1, p=2)
+    N = f.shape[0]
+    L = np.random.default_rng(0).random((N, N), dtype=np.float32) * np.float32(0.05)
+    got = reranking.re_ranking(f[: sh.q], f[sh.q:], 20, 6, 0.3, local_distmat=L)
+    D = oracle.sq_euclidean(f.numpy(), f.numpy()) + L
+    want = oracle.rerank_from_dist(D, sh.q, 20, 6, 0.3)
+    assert_distances_close(got, want, what="re_ranking + local_distmat")
+
+
+def test_fp16_and_cuda_inputs(api, synth):
+    evaluate, reranking = api
+    sh = synth.SHAPES["tiny"]
+    qf, gf, *_ = synth.make(sh, 6)
+    a = evaluate.euclidean_distance(qf.half(), gf.half())
+    assert a.dtype == np.float16                      # evaluate.py:7-13 returns the input dtype
+    b = evaluate.euclidean_distance(qf.half().float(), gf.half().float())
+    np.testing.assert_allclose(a.astype(np.float32), b, rtol=2e-3)
+    c = evaluate.euclidean_distance(qf.cuda(), gf.cuda())
+    d = evaluate.euclidean_distance(qf, gf)
+    np.testing.assert_array_equal(c, d)
+    r1 = reranking.re_ranking(qf.cuda(), gf.cuda(), 20, 6, 0.3)
+    r2 = reranking.re_ranking(qf, gf, 20, 6, 0.3)
+    np.testing.assert_array_equal(r1, r2)
+
+
+@pytest.mark.parametrize("name,seed", [("mid", 0)])
+def test_full_pipeline_vs_oracle(api, synth, oracle, name, seed):
+    """Larger instance, own contraction on both sides: tolerances of north_star."""
+    evaluate, reranking = api
+    sh = synth.SHAPES[name]
+    qf, gf, qp, gp, qc, gc = synth.make(sh, seed)
+    f = torch.nn.functional.normalize(torch.cat([qf, gf]), dim=1, p=2)
+    got = reranking.re_ranking(f[: sh.q], f[sh.q:], sh.k1, sh.k2, sh.lam)
+    want = oracle.re_ranking(f[: sh.q].numpy(), f[sh.q:].numpy(), sh.k1, sh.k2, sh.lam)
+    assert_distances_close(got, want, what="mid re_ranking")
+    with contextlib.redirect_stdout(io.StringIO()):
+        cmc, mAP = evaluate.eval_func(got, qp, gp, qc, gc)
+    c2, m2 = oracle.cmc_map(want, qp.numpy(), gp.numpy(), qc.numpy(), gc.numpy())
+    np.testing.assert_allclose(cmc, c2, atol=METRIC_TOL)
+    assert abs(mAP - m2) < METRIC_TOL
+    idx = np.argsort(got, axis=1, kind="stable")[:, :20]
+    idx2 = np.argsort(want, axis=1, kind="stable")[:, :20]
+    assert_ranking_equal_mod_ties(idx, idx2, want, tol=4.0 * 2.0 ** -11, what="top-20 of final")
