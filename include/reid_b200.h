@@ -45,10 +45,6 @@ extern "C" {
 #define REID_METRIC_SQEUCLIDEAN 0 /* evaluate.py:7-13  */
 #define REID_METRIC_ARCCOS 1      /* evaluate.py:16-26 */
 
-#define REID_ENGINE_AUTO 0
-#define REID_ENGINE_SIMT 1    /* fp32 FMA on CUDA cores (bring-up / cross-check engine) */
-#define REID_ENGINE_TCGEN05 2 /* 3xTF32 on tcgen05 tensor cores, TMA-fed, TMEM accumulators */
-
 typedef uint16_t reid_half; /* IEEE binary16 bit pattern */
 
 REID_API int reid_abi_version(void);
@@ -63,23 +59,34 @@ REID_API int64_t reid_launch_count(void);
 REID_API int reid_half_k(int k1);
 /* structural bound on the support of one row of V: (k1+1) * (half_k + 1) */
 REID_API int reid_v_row_capacity(int k1);
-/* feature width padded to the MMA K multiple (32) */
+/* feature width padded to the tensor-core K block (64) */
 REID_API int reid_padded_width(int d);
 
 /* K13  evaluate.py:112-114, reranking.py:36-39.  Row L2-normalise (x / max(|x|, 1e-12)) when
- * `normalize`, zero-pad to `dpad`, split into TF32 `hi` + exact residual `lo` (hi + lo == x),
- * and emit sq[i] = sum x^2 and nrm[i] = sqrt(sq[i]) of the rows as written. */
-REID_API int reid_prepare_features(const float* X, int n, int d, int64_t ld_x, int normalize, float* hi,
-                          float* lo, int dpad, float* sq, float* nrm, void* stream);
+ * `normalize`, zero-pad to `dpad` (reid_padded_width) -> x32[n, dpad]; sq[i] = sum x^2 and
+ * nrm[i] = sqrt(sq[i]) of the rows as written; amax[0] = float bits of max|x|; and the float16
+ * operands of the tensor-core contraction  x * 2^e = hi + lo  (hi = fp16(x * 2^e), lo = fp16 of the
+ * exact remainder; e = 14 - floor(log2 max|x|), one exponent per call). */
+REID_API int reid_prepare_features(const float* X, int n, int d, int64_t ld_x, int normalize, float* x32,
+                          reid_half* hi, reid_half* lo, int dpad, float* sq, float* nrm, uint32_t* amax,
+                          void* stream);
 
 /* K1/K2/K3  evaluate.py:7-26, reranking.py:36-41.  out[i, j] for A rows i < m, B rows j < n.
  * metric 0: (ra[i] + rb[j]) - 2 a.b with ra/rb = squared norms; metric 1: arccos(clip(a.b *
  * (1 / (ra[i] * rb[j])))) with ra/rb = norms.  If rowmax_key != NULL the per-row maximum of
  * `out` is folded in with atomicMax on an order-preserving int encoding (initialise the array
- * with reid_rowmax_init). */
-REID_API int reid_dist(const float* Ahi, const float* Alo, const float* ra, int m, const float* Bhi,
-              const float* Blo, const float* rb, int n, int dpad, int metric, int engine,
-              float* out, int64_t ld_out, int32_t* rowmax_key, void* stream);
+ * with reid_rowmax_init).  lda/ldb are row pitches in elements, so a rank's cyclic share of the
+ * probes is the same buffers with base + rank*dpad and pitch world*dpad.
+ *   reid_dist       tcgen05 tensor cores: float16 hi/lo operands, float32 accumulation in TMEM
+ *                   (hi.hi + hi.lo + lo.hi), TMA in and out.  The product path.
+ *   reid_dist_fp32  CUDA-core float32 FMA on x32: bring-up / cross-check engine. */
+REID_API int reid_dist(const reid_half* Ahi, const reid_half* Alo, int64_t lda, const float* ra,
+              const uint32_t* a_amax, int m, const reid_half* Bhi, const reid_half* Blo, int64_t ldb,
+              const float* rb, const uint32_t* b_amax, int n, int dpad, int metric, float* out,
+              int64_t ld_out, int32_t* rowmax_key, void* stream);
+REID_API int reid_dist_fp32(const float* A, int64_t lda, const float* ra, int m, const float* B, int64_t ldb,
+                   const float* rb, int n, int dpad, int metric, float* out, int64_t ld_out,
+                   int32_t* rowmax_key, void* stream);
 REID_API int reid_rowmax_init(int32_t* rowmax_key, int rows, void* stream);
 /* K4 (first half)  reranking.py:46.  Stand-alone row maximum for a caller-supplied matrix. */
 REID_API int reid_rowmax(const float* D, int rows, int cols, int64_t ld, int32_t* rowmax_key, void* stream);

@@ -128,31 +128,34 @@ int reid_half_k(int k1) { return half_k(k1); }
 int reid_v_row_capacity(int k1) { return v_row_capacity(k1); }
 int reid_padded_width(int d) { return padded_width(d); }
 
-int reid_prepare_features(const float* X, int n, int d, int64_t ld_x, int normalize, float* hi, float* lo,
-                          int dpad, float* sq, float* nrm, void* stream) {
+int reid_prepare_features(const float* X, int n, int d, int64_t ld_x, int normalize, float* x32, reid_half* hi,
+                          reid_half* lo, int dpad, float* sq, float* nrm, uint32_t* amax, void* stream) {
   ENTER();
   REID_REQUIRE(n >= 0 && d >= 1 && ld_x >= d, "prepare_features: bad shape n=%d d=%d ld=%lld", n, d,
                (long long)ld_x);
-  REID_REQUIRE(dpad >= d && dpad % 32 == 0, "prepare_features: dpad=%d must be a multiple of 32 >= d=%d",
+  REID_REQUIRE(dpad >= d && dpad % 64 == 0, "prepare_features: dpad=%d must be a multiple of 64 >= d=%d",
                dpad, d);
-  return launch_prep(X, n, d, ld_x, normalize, hi, lo, dpad, sq, nrm, S(stream));
+  return launch_prep(X, n, d, ld_x, normalize, x32, H(hi), H(lo), dpad, sq, nrm, amax, S(stream));
 }
 
-int reid_dist(const float* Ahi, const float* Alo, const float* ra, int m, const float* Bhi, const float* Blo,
-              const float* rb, int n, int dpad, int metric, int engine, float* out, int64_t ld_out,
+int reid_dist(const reid_half* Ahi, const reid_half* Alo, int64_t lda, const float* ra, const uint32_t* a_amax,
+              int m, const reid_half* Bhi, const reid_half* Blo, int64_t ldb, const float* rb,
+              const uint32_t* b_amax, int n, int dpad, int metric, float* out, int64_t ld_out,
               int32_t* rowmax_key, void* stream) {
   ENTER();
   REID_REQUIRE(metric == 0 || metric == 1, "dist: unknown metric %d", metric);
-  REID_REQUIRE(m >= 0 && n >= 0 && dpad > 0 && dpad % 32 == 0 && ld_out >= n, "dist: bad shape");
-  if (engine == REID_ENGINE_AUTO) engine = REID_ENGINE_TCGEN05;
-  if (engine == REID_ENGINE_SIMT)
-    return launch_dist_simt(Ahi, Alo, ra, m, Bhi, Blo, rb, n, dpad, metric, out, ld_out, rowmax_key,
-                            S(stream));
-  if (engine == REID_ENGINE_TCGEN05)
-    return launch_dist_tc(Ahi, Alo, ra, m, Bhi, Blo, rb, n, dpad, metric, out, ld_out, rowmax_key,
-                          S(stream));
-  set_error("dist: unknown engine %d", engine);
-  return REID_ERR_ARG;
+  REID_REQUIRE(m >= 0 && n >= 0 && dpad > 0 && ld_out >= n && lda >= dpad && ldb >= dpad, "dist: bad shape");
+  return launch_dist_tc(HC(Ahi), HC(Alo), lda, ra, a_amax, m, HC(Bhi), HC(Blo), ldb, rb, b_amax, n, dpad, metric,
+                        out, ld_out, rowmax_key, S(stream));
+}
+
+int reid_dist_fp32(const float* A, int64_t lda, const float* ra, int m, const float* B, int64_t ldb,
+                   const float* rb, int n, int dpad, int metric, float* out, int64_t ld_out, int32_t* rowmax_key,
+                   void* stream) {
+  ENTER();
+  REID_REQUIRE(metric == 0 || metric == 1, "dist: unknown metric %d", metric);
+  REID_REQUIRE(m >= 0 && n >= 0 && dpad > 0 && ld_out >= n && lda >= dpad && ldb >= dpad, "dist: bad shape");
+  return launch_dist_simt(A, lda, ra, m, B, ldb, rb, n, dpad, metric, out, ld_out, rowmax_key, S(stream));
 }
 
 int reid_rowmax_init(int32_t* rowmax_key, int rows, void* stream) {

@@ -1,6 +1,5 @@
-// Distance contraction, CUDA-core engine (fp32 FMA).  Bring-up and cross-check engine for the
-// tcgen05 path in dist_tcgen05.cu; same operands (hi/lo split, re-joined exactly on load) and the
-// same fused epilogues:
+// Distance contraction, CUDA-core engine (fp32 FMA on the float32 rows).  Bring-up and
+// cross-check engine for the tcgen05 path in dist_tcgen05.cu; same fused epilogues:
 //   metric 0: D = (|a|^2 + |b|^2) - 2 a.b          evaluate.py:7-13, reranking.py:36-41
 //   metric 1: arccos(clip(a.b * (1/(|a||b|))))     evaluate.py:16-26
 // plus an optional per-row running maximum (reranking.py:46 needs max_k D[k,i]).
@@ -22,9 +21,8 @@ __device__ __forceinline__ float dist_epilogue(int metric, float acc, float ra, 
 }
 
 __global__ void __launch_bounds__(256)
-dist_simt_kernel(const float* __restrict__ Ahi, const float* __restrict__ Alo,
-                 const float* __restrict__ ra, int m, const float* __restrict__ Bhi,
-                 const float* __restrict__ Blo, const float* __restrict__ rb, int n, int dp,
+dist_simt_kernel(const float* __restrict__ A, long long lda, const float* __restrict__ ra, int m,
+                 const float* __restrict__ B, long long ldb, const float* __restrict__ rb, int n, int dp,
                  int metric, float* __restrict__ out, long long ld_out, int* __restrict__ rowmax_key) {
   __shared__ float As[TK][TM + 4];
   __shared__ float Bs[TK][TN + 4];
@@ -46,17 +44,13 @@ dist_simt_kernel(const float* __restrict__ Ahi, const float* __restrict__ Alo,
     for (int h = 0; h < 2; ++h) {
       int r = m0 + lr + h * 64;
       if (r < m) {
-        float4 a = *reinterpret_cast<const float4*>(Ahi + (long long)r * dp + k0 + lk);
-        float4 b = *reinterpret_cast<const float4*>(Alo + (long long)r * dp + k0 + lk);
-        pa[h] = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);   // exact re-join
+        pa[h] = *reinterpret_cast<const float4*>(A + (long long)r * lda + k0 + lk);
       } else {
         pa[h] = make_float4(0.f, 0.f, 0.f, 0.f);
       }
       int c = n0 + lr + h * 64;
       if (c < n) {
-        float4 a = *reinterpret_cast<const float4*>(Bhi + (long long)c * dp + k0 + lk);
-        float4 b = *reinterpret_cast<const float4*>(Blo + (long long)c * dp + k0 + lk);
-        pb[h] = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+        pb[h] = *reinterpret_cast<const float4*>(B + (long long)c * ldb + k0 + lk);
       } else {
         pb[h] = make_float4(0.f, 0.f, 0.f, 0.f);
       }
@@ -124,14 +118,14 @@ dist_simt_kernel(const float* __restrict__ Ahi, const float* __restrict__ Alo,
   }
 }
 
-int launch_dist_simt(const float* Ahi, const float* Alo, const float* ra, int m, const float* Bhi,
-                     const float* Blo, const float* rb, int n, int dp, int metric, float* out,
-                     long long ld_out, int* rowmax_key, cudaStream_t s) {
+int launch_dist_simt(const float* A, long long lda, const float* ra, int m, const float* B, long long ldb,
+                     const float* rb, int n, int dp, int metric, float* out, long long ld_out,
+                     int* rowmax_key, cudaStream_t s) {
   if (m == 0 || n == 0) return REID_OK;
   REID_REQUIRE(dp % TK == 0, "dist_simt: padded width %d must be a multiple of %d", dp, TK);
-  REID_REQUIRE(ld_out % 4 == 0, "dist_simt: output pitch %lld must be a multiple of 4", ld_out);
+  REID_REQUIRE(ld_out % 4 == 0 && lda % 4 == 0 && ldb % 4 == 0, "dist_simt: pitches must be multiples of 4");
   dim3 grid(cdiv(n, TN), cdiv(m, TM));
-  dist_simt_kernel<<<grid, 256, 0, s>>>(Ahi, Alo, ra, m, Bhi, Blo, rb, n, dp, metric, out, ld_out,
+  dist_simt_kernel<<<grid, 256, 0, s>>>(A, lda, ra, m, B, ldb, rb, n, dp, metric, out, ld_out,
                                         rowmax_key);
   return check_launch("dist_simt_kernel");
 }

@@ -14,16 +14,17 @@ static inline int half_k(int k1) {
 }
 // structural bound on |E_i|: |R| + |R| * h  with |R| <= k1+1
 static inline int v_row_capacity(int k1) { return (k1 + 1) * (half_k(k1) + 1); }
-static inline int padded_width(int d) { return (d + 31) / 32 * 32; }
+static inline int padded_width(int d) { return (d + 63) / 64 * 64; }   // tensor-core K block
 
-int launch_prep(const float* X, int n, int d, long long ld_x, int normalize, float* hi, float* lo, int dp,
-                float* sq, float* nrm, cudaStream_t s);
-int launch_dist_simt(const float* Ahi, const float* Alo, const float* ra, int m, const float* Bhi,
-                     const float* Blo, const float* rb, int n, int dp, int metric, float* out,
-                     long long ld_out, int* rowmax_key, cudaStream_t s);
-int launch_dist_tc(const float* Ahi, const float* Alo, const float* ra, int m, const float* Bhi,
-                   const float* Blo, const float* rb, int n, int dp, int metric, float* out,
-                   long long ld_out, int* rowmax_key, cudaStream_t s);
+int launch_prep(const float* X, int n, int d, long long ld_x, int normalize, float* x32, __half* hi, __half* lo,
+                int dp, float* sq, float* nrm, uint32_t* amax, cudaStream_t s);
+int launch_dist_simt(const float* A, long long lda, const float* ra, int m, const float* B, long long ldb,
+                     const float* rb, int n, int dp, int metric, float* out, long long ld_out,
+                     int* rowmax_key, cudaStream_t s);
+int launch_dist_tc(const __half* Ahi, const __half* Alo, long long lda, const float* ra, const uint32_t* a_amax,
+                   int m, const __half* Bhi, const __half* Blo, long long ldb, const float* rb,
+                   const uint32_t* b_amax, int n, int dp, int metric, float* out, long long ld_out,
+                   int* rowmax_key, cudaStream_t s);
 int launch_rowmax(const float* D, int rows, int cols, long long ld, int* key, cudaStream_t s);
 int launch_select_topk(const float* D, int rows, int cols, long long ld, const int* rowmax_key, int K,
                        int* nbr, float* nbr_val, int cap_override, cudaStream_t s);

@@ -1,17 +1,21 @@
 // K13 prologue (evaluate.py:112-114, reranking.py:36-39): row L2-normalise, zero-pad the feature
-// width to the MMA K multiple, emit the TF32 hi / residual lo split the tensor-core contraction
-// consumes, and the per-row squared norm / norm used by the distance epilogues.
+// width to the MMA K-block multiple, emit the per-row squared norm / norm used by the distance
+// epilogues, and split the rows into the float16 hi/lo operands of the tensor-core contraction:
+//   x * 2^e = hi + lo,   hi = fp16(x * 2^e),   lo = fp16(x * 2^e - hi)
+// with one power-of-two exponent e per matrix chosen so that max|x| * 2^e lies in [2^14, 2^15)
+// (float16 keeps 11 significant bits down to 2^-14, so lo is a normal number for every element
+// within 2^17 of the largest one).
 #include "common.cuh"
 #include "kernels.h"
 
 namespace reid {
 
-// one warp per row
+// pass 1: one warp per row -> x32 (normalised, padded), sq, nrm, global max|x| (float bits)
 __global__ void __launch_bounds__(256) prep_rows_kernel(const float* __restrict__ X, int n, int d,
                                                         long long ld_x, int normalize,
-                                                        float* __restrict__ hi, float* __restrict__ lo,
-                                                        int dp, float* __restrict__ sq,
-                                                        float* __restrict__ nrm) {
+                                                        float* __restrict__ x32, int dp,
+                                                        float* __restrict__ sq, float* __restrict__ nrm,
+                                                        uint32_t* __restrict__ amax) {
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= n) return;
   const int lane = lane_id();
@@ -25,31 +29,71 @@ __global__ void __launch_bounds__(256) prep_rows_kernel(const float* __restrict_
   for (int o = 16; o > 0; o >>= 1) ss = __fadd_rn(ss, __shfl_xor_sync(FULL, ss, o));
   float denom = 1.0f;
   if (normalize) denom = fmaxf(sqrtf(ss), 1e-12f);     // F.normalize: x / max(||x||, eps)
-  float ss2 = 0.0f;
-  float* h = hi + (long long)row * dp;
-  float* l = lo + (long long)row * dp;
+  float ss2 = 0.0f, mx = 0.0f;
+  float* o32 = x32 + (long long)row * dp;
   for (int k = lane; k < dp; k += 32) {
     float y = 0.0f;
     if (k < d) y = normalize ? __fdiv_rn(x[k], denom) : x[k];
-    float yh = __uint_as_float(__float_as_uint(y) & 0xffffe000u);   // TF32: 1+8+10 bits
-    h[k] = yh;
-    l[k] = __fsub_rn(y, yh);                                         // exact residual
+    o32[k] = y;
     ss2 = __fmaf_rn(y, y, ss2);
+    mx = fmaxf(mx, fabsf(y));
   }
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) ss2 = __fadd_rn(ss2, __shfl_xor_sync(FULL, ss2, o));
+  for (int o = 16; o > 0; o >>= 1) {
+    ss2 = __fadd_rn(ss2, __shfl_xor_sync(FULL, ss2, o));
+    mx = fmaxf(mx, __shfl_xor_sync(FULL, mx, o));
+  }
   if (lane == 0) {
     sq[row] = ss2;
     nrm[row] = sqrtf(ss2);
+    if (mx == mx && mx < INFINITY) atomicMax(amax, __float_as_uint(mx));   // non-negative floats order as uints
   }
 }
 
-int launch_prep(const float* X, int n, int d, long long ld_x, int normalize, float* hi, float* lo,
-                int dp, float* sq, float* nrm, cudaStream_t s) {
+__device__ __forceinline__ int split_scale_exponent(uint32_t amax_bits) {   // == tc::scale_exponent
+  if ((amax_bits & 0x7fffffffu) == 0) return 0;
+  int E = (int)((amax_bits >> 23) & 0xff) - 127;
+  int e = 14 - E;
+  return max(-100, min(100, e));
+}
+
+// pass 2: hi/lo float16 split with the matrix-wide exponent; 4 elements per thread
+__global__ void __launch_bounds__(256) split_f16_kernel(const float* __restrict__ x32, long long total4,
+                                                        const uint32_t* __restrict__ amax,
+                                                        __half* __restrict__ hi, __half* __restrict__ lo) {
+  const int e = split_scale_exponent(*amax);
+  const float sc = exp2f((float)e);                    // exact power of two
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total4;
+       i += (long long)gridDim.x * blockDim.x) {
+    const float4 v = reinterpret_cast<const float4*>(x32)[i];
+    const float a[4] = {v.x * sc, v.y * sc, v.z * sc, v.w * sc};
+    __half h[4], l[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      h[j] = __float2half_rn(a[j]);
+      l[j] = __float2half_rn(__fsub_rn(a[j], __half2float(h[j])));
+    }
+    reinterpret_cast<uint2*>(hi)[i] = make_uint2(
+        (uint32_t)__half_as_ushort(h[0]) | ((uint32_t)__half_as_ushort(h[1]) << 16),
+        (uint32_t)__half_as_ushort(h[2]) | ((uint32_t)__half_as_ushort(h[3]) << 16));
+    reinterpret_cast<uint2*>(lo)[i] = make_uint2(
+        (uint32_t)__half_as_ushort(l[0]) | ((uint32_t)__half_as_ushort(l[1]) << 16),
+        (uint32_t)__half_as_ushort(l[2]) | ((uint32_t)__half_as_ushort(l[3]) << 16));
+  }
+}
+
+int launch_prep(const float* X, int n, int d, long long ld_x, int normalize, float* x32, __half* hi,
+                __half* lo, int dp, float* sq, float* nrm, uint32_t* amax, cudaStream_t s) {
+  REID_CUDA(cudaMemsetAsync(amax, 0, sizeof(uint32_t), s));
   if (n == 0) return REID_OK;
   const int wpb = 8;
-  prep_rows_kernel<<<cdiv(n, wpb), wpb * 32, 0, s>>>(X, n, d, ld_x, normalize, hi, lo, dp, sq, nrm);
-  return check_launch("prep_rows_kernel");
+  prep_rows_kernel<<<cdiv(n, wpb), wpb * 32, 0, s>>>(X, n, d, ld_x, normalize, x32, dp, sq, nrm, amax);
+  int rc = check_launch("prep_rows_kernel");
+  if (rc) return rc;
+  const long long total4 = (long long)n * dp / 4;
+  const int blocks = (int)((total4 + 255) / 256 < 148 * 8 ? (total4 + 255) / 256 : 148 * 8);
+  split_f16_kernel<<<blocks, 256, 0, s>>>(x32, total4, amax, hi, lo);
+  return check_launch("split_f16_kernel");
 }
 
 }  // namespace reid

@@ -42,14 +42,29 @@ def v_row_capacity(k1: int) -> int:
 
 @dataclasses.dataclass
 class Features:
-    """Prepared feature rows: TF32 hi + residual lo (padded to dp), squared norms and norms."""
-    hi: torch.Tensor
-    lo: torch.Tensor
-    sq: torch.Tensor
-    nrm: torch.Tensor
-    n: int
+    """Prepared feature rows (engine.prepare): float32 rows padded to dp, their float16 hi/lo split
+    for the tensor cores, squared norms, norms, and the matrix-wide max|x| that fixes the split's
+    power-of-two scale.  Row subsets are strided views of the same buffers (no copies)."""
+    x32: torch.Tensor      # [n, dp] float32 (view; row pitch = x32.stride(0))
+    hi: torch.Tensor       # [n, dp] float16
+    lo: torch.Tensor       # [n, dp] float16
+    sq: torch.Tensor       # [n] float32
+    nrm: torch.Tensor      # [n] float32
+    amax: torch.Tensor     # [1] int32 (float bits)
     d: int
-    dp: int
+
+    @property
+    def n(self) -> int:
+        return self.hi.shape[0]
+
+    @property
+    def dp(self) -> int:
+        return self.hi.shape[1]
+
+    def rows(self, sl: slice) -> "Features":
+        """Row subset; sq/nrm are compacted because the kernels index them by local row."""
+        return Features(self.x32[sl], self.hi[sl], self.lo[sl], self.sq[sl].contiguous(), self.nrm[sl].contiguous(),
+                        self.amax, self.d)
 
 
 class Comm:
@@ -157,21 +172,20 @@ class Engine:
         return torch.zeros(shape, dtype=dtype, device=self.device)
 
     # ------------------------------------------------------------------ K13
-    def prepare(self, X: torch.Tensor, normalize: bool, row0: int = 0, row_stride: int = 1) -> Features:
-        """X: [n, d] float32 on the device (row-major).  A row window selects row0 + l*row_stride."""
+    def prepare(self, X: torch.Tensor, normalize: bool) -> Features:
+        """X: [n, d] float32 on the device (row-major)."""
         assert X.is_cuda and X.dtype == torch.float32 and X.dim() == 2 and X.stride(1) == 1
-        n_all, d = X.shape
-        n = (n_all - row0 + row_stride - 1) // row_stride if n_all > row0 else 0
+        n, d = X.shape
         dp = self.lib.reid_padded_width(d)
-        hi = self._empty((n, dp), torch.float32)
-        lo = self._empty((n, dp), torch.float32)
+        x32 = self._empty((n, dp), torch.float32)
+        hi = self._empty((n, dp), torch.float16)
+        lo = self._empty((n, dp), torch.float16)
         sq = self._empty((n,), torch.float32)
         nrm = self._empty((n,), torch.float32)
-        ld = X.stride(0)
-        base = X.data_ptr() + row0 * ld * 4
-        _lib.call("reid_prepare_features", C.c_void_p(base), n, d, ld * row_stride, int(normalize), _ptr(hi),
-                  _ptr(lo), dp, _ptr(sq), _ptr(nrm), _stream())
-        return Features(hi, lo, sq, nrm, n, d, dp)
+        amax = self._empty((1,), torch.int32)
+        _lib.call("reid_prepare_features", _ptr(X), n, d, X.stride(0), int(normalize), _ptr(x32), _ptr(hi), _ptr(lo),
+                  dp, _ptr(sq), _ptr(nrm), _ptr(amax), _stream())
+        return Features(x32, hi, lo, sq, nrm, amax, d)
 
     # ------------------------------------------------------------------ K1/K2/K3
     @staticmethod
@@ -190,8 +204,14 @@ class Engine:
             key = self._empty((m,), torch.int32)
             _lib.call("reid_rowmax_init", _ptr(key), m, _stream())
         ra, rb = (A.sq, B.sq) if metric == METRIC_SQEUCLIDEAN else (A.nrm, B.nrm)
-        _lib.call("reid_dist", _ptr(A.hi), _ptr(A.lo), _ptr(ra), m, _ptr(B.hi), _ptr(B.lo), _ptr(rb), n, A.dp,
-                  metric, self.engine if engine is None else engine, _ptr(D), ld, _ptr(key), _stream())
+        engine = self.engine if engine is None else engine
+        if engine == ENGINES["simt"]:
+            _lib.call("reid_dist_fp32", _ptr(A.x32), A.x32.stride(0), _ptr(ra), m, _ptr(B.x32), B.x32.stride(0),
+                      _ptr(rb), n, A.dp, metric, _ptr(D), ld, _ptr(key), _stream())
+        else:
+            _lib.call("reid_dist", _ptr(A.hi), _ptr(A.lo), A.hi.stride(0), _ptr(ra), _ptr(A.amax), m, _ptr(B.hi),
+                      _ptr(B.lo), B.hi.stride(0), _ptr(rb), _ptr(B.amax), n, A.dp, metric, _ptr(D), ld, _ptr(key),
+                      _stream())
         return D, key
 
     def rowmax(self, D: torch.Tensor, cols: int) -> torch.Tensor:
@@ -357,7 +377,7 @@ class Engine:
         N = feats.shape[0]
         with self.span("prep"):
             allf = self.prepare(feats, normalize)
-            mine = allf if cm.world == 1 else self.prepare(feats, normalize, cm.rank, cm.world)
+            mine = allf if cm.world == 1 else allf.rows(slice(cm.rank, N, cm.world))
         with self.span("dist"):
             D, key = self.dist(mine, allf, METRIC_SQEUCLIDEAN, want_rowmax=True)
         if detail is not None:

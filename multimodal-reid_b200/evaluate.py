@@ -114,9 +114,7 @@ class R1_mAP_eval():
         else:
             print('=> Computing DistMat with euclidean_distance')
             allf = eng.prepare(feats, self.feat_norm)
-            qf = _engine.Features(allf.hi[:q], allf.lo[:q], allf.sq[:q], allf.nrm[:q], q, allf.d, allf.dp)
-            gf = _engine.Features(allf.hi[q:], allf.lo[q:], allf.sq[q:], allf.nrm[q:], g, allf.d, allf.dp)
-            dist, _ = eng.dist(qf, gf, _engine.METRIC_SQEUCLIDEAN)
+            dist, _ = eng.dist(allf.rows(slice(0, q)), allf.rows(slice(q, N)), _engine.METRIC_SQEUCLIDEAN)
         # evaluate.py:132 does not forward self.max_rank: always 50
         cmc, mAP = eval_func_device(dist, g, pids[:q].contiguous(), pids[q:].contiguous(),
                                     camids[:q].contiguous(), camids[q:].contiguous(), 50, eng)

@@ -37,7 +37,7 @@ def eng():
     if not torch.cuda.is_available():
         pytest.skip("no CUDA device")
     engine = importlib.import_module("multimodal-reid_b200.engine")
-    return engine.Engine(engine="simt")
+    return engine.Engine(engine="auto")
 
 
 @pytest.fixture(scope="session")
