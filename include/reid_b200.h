@@ -75,7 +75,8 @@ REID_API int reid_prepare_features(const float* X, int n, int d, int64_t ld_x, i
  * metric 0: (ra[i] + rb[j]) - 2 a.b with ra/rb = squared norms; metric 1: arccos(clip(a.b *
  * (1 / (ra[i] * rb[j])))) with ra/rb = norms.  If rowmax_key != NULL the per-row maximum of
  * `out` is folded in with atomicMax on an order-preserving int encoding (initialise the array
- * with reid_rowmax_init).  lda/ldb are row pitches in elements, so a rank's cyclic share of the
+ * with reid_rowmax_init).  If chunk_min != NULL (reid_dist only) it receives the minimum of every
+ * 32-column chunk, [m, ceil(n/32)], for reid_topk_rows_hinted.  lda/ldb are row pitches in elements, so a rank's cyclic share of the
  * probes is the same buffers with base + rank*dpad and pitch world*dpad.
  *   reid_dist       tcgen05 tensor cores: float16 hi/lo operands, float32 accumulation in TMEM
  *                   (hi.hi + hi.lo + lo.hi), TMA in and out.  The product path.
@@ -83,7 +84,7 @@ REID_API int reid_prepare_features(const float* X, int n, int d, int64_t ld_x, i
 REID_API int reid_dist(const reid_half* Ahi, const reid_half* Alo, int64_t lda, const float* ra,
               const uint32_t* a_amax, int m, const reid_half* Bhi, const reid_half* Blo, int64_t ldb,
               const float* rb, const uint32_t* b_amax, int n, int dpad, int metric, float* out,
-              int64_t ld_out, int32_t* rowmax_key, void* stream);
+              int64_t ld_out, int32_t* rowmax_key, float* chunk_min, void* stream);
 REID_API int reid_dist_fp32(const float* A, int64_t lda, const float* ra, int m, const float* B, int64_t ldb,
                    const float* rb, int n, int dpad, int metric, float* out, int64_t ld_out,
                    int32_t* rowmax_key, void* stream);
@@ -101,6 +102,9 @@ REID_API int reid_transpose_add(const float* src, int n, int64_t ld_src, float* 
  * ascending (value, column) order -> nbr[rows, K] (and their values if nbr_val != NULL). */
 REID_API int reid_topk_rows(const float* D, int rows, int cols, int64_t ld, const int32_t* rowmax_key, int K,
                    int32_t* nbr, float* nbr_val, void* stream);
+/* same result, reading only the chunks whose recorded minimum can hold a neighbour (~K of cols/32) */
+REID_API int reid_topk_rows_hinted(const float* D, int rows, int cols, int64_t ld, const int32_t* rowmax_key,
+                          const float* chunk_min, int K, int32_t* nbr, float* nbr_val, int cap, void* stream);
 /* test hook: same, with the candidate buffer capped so the exact fallback path is exercised */
 REID_API int reid_topk_rows_capped(const float* D, int rows, int cols, int64_t ld, const int32_t* rowmax_key,
                           int K, int32_t* nbr, float* nbr_val, int cap, void* stream);
@@ -162,6 +166,13 @@ REID_API int reid_rank_rows(const float* dist, int rows, int g, int64_t ld, uint
 REID_API int reid_score_rows(const int32_t* ranked, int q, int g, const int64_t* q_pid, const int64_t* g_pid,
                     const int64_t* q_cam, const int64_t* g_cam, int max_rank, double* ap,
                     int32_t* first_hit, int32_t* cmc_hist, int32_t* n_valid, void* stream);
+/* K11 + K12 fused (the evaluator's path)  evaluate.py:40-88.  Same outputs as reid_rank_rows +
+ * reid_score_rows, computed from the distance rows by counting: the kept rank of every true match is
+ * the number of non-junk entries before it in stable (distance, column) order; no ranking is
+ * materialised.  dist: [q, >= g] float32, pitch ld. */
+REID_API int reid_score_dist(const float* dist, int q, int g, int64_t ld, const int64_t* q_pid, const int64_t* g_pid,
+                    const int64_t* q_cam, const int64_t* g_cam, int max_rank, double* ap, int32_t* first_hit,
+                    int32_t* cmc_hist, int32_t* n_valid, void* stream);
 REID_API int reid_score_finalize(const double* ap, int q, const int32_t* cmc_hist, int max_rank,
                         const int32_t* n_valid, float* cmc, double* mAP, void* stream);
 

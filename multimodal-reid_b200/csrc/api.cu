@@ -141,12 +141,12 @@ int reid_prepare_features(const float* X, int n, int d, int64_t ld_x, int normal
 int reid_dist(const reid_half* Ahi, const reid_half* Alo, int64_t lda, const float* ra, const uint32_t* a_amax,
               int m, const reid_half* Bhi, const reid_half* Blo, int64_t ldb, const float* rb,
               const uint32_t* b_amax, int n, int dpad, int metric, float* out, int64_t ld_out,
-              int32_t* rowmax_key, void* stream) {
+              int32_t* rowmax_key, float* chunk_min, void* stream) {
   ENTER();
   REID_REQUIRE(metric == 0 || metric == 1, "dist: unknown metric %d", metric);
   REID_REQUIRE(m >= 0 && n >= 0 && dpad > 0 && ld_out >= n && lda >= dpad && ldb >= dpad, "dist: bad shape");
   return launch_dist_tc(HC(Ahi), HC(Alo), lda, ra, a_amax, m, HC(Bhi), HC(Blo), ldb, rb, b_amax, n, dpad, metric,
-                        out, ld_out, rowmax_key, S(stream));
+                        out, ld_out, rowmax_key, chunk_min, S(stream));
 }
 
 int reid_dist_fp32(const float* A, int64_t lda, const float* ra, int m, const float* B, int64_t ldb,
@@ -187,6 +187,13 @@ int reid_topk_rows(const float* D, int rows, int cols, int64_t ld, const int32_t
                    int32_t* nbr, float* nbr_val, void* stream) {
   ENTER();
   return launch_select_topk(D, rows, cols, ld, rowmax_key, K, nbr, nbr_val, 0, S(stream));
+}
+
+int reid_topk_rows_hinted(const float* D, int rows, int cols, int64_t ld, const int32_t* rowmax_key,
+                          const float* chunk_min, int K, int32_t* nbr, float* nbr_val, int cap, void* stream) {
+  ENTER();
+  REID_REQUIRE(chunk_min != nullptr, "topk_rows_hinted: chunk_min is NULL");
+  return launch_select_topk_hinted(D, rows, cols, ld, rowmax_key, chunk_min, K, nbr, nbr_val, cap, S(stream));
 }
 
 int reid_topk_rows_capped(const float* D, int rows, int cols, int64_t ld, const int32_t* rowmax_key, int K,
@@ -285,6 +292,18 @@ int reid_score_rows(const int32_t* ranked, int q, int g, const int64_t* q_pid, c
                       reinterpret_cast<const long long*>(g_pid), reinterpret_cast<const long long*>(q_cam),
                       reinterpret_cast<const long long*>(g_cam), max_rank, ap, first_hit, cmc_hist, n_valid,
                       S(stream));
+}
+
+int reid_score_dist(const float* dist, int q, int g, int64_t ld, const int64_t* q_pid, const int64_t* g_pid,
+                    const int64_t* q_cam, const int64_t* g_cam, int max_rank, double* ap, int32_t* first_hit,
+                    int32_t* cmc_hist, int32_t* n_valid, void* stream) {
+  ENTER();
+  REID_REQUIRE(max_rank >= 1 && max_rank <= g, "score_dist: max_rank=%d outside [1, g=%d]", max_rank, g);
+  REID_REQUIRE(ld >= g, "score_dist: pitch %lld < row length %d", (long long)ld, g);
+  return launch_score_dist(dist, q, g, ld, reinterpret_cast<const long long*>(q_pid),
+                           reinterpret_cast<const long long*>(g_pid), reinterpret_cast<const long long*>(q_cam),
+                           reinterpret_cast<const long long*>(g_cam), max_rank, ap, first_hit, cmc_hist, n_valid,
+                           S(stream));
 }
 
 int reid_score_finalize(const double* ap, int q, const int32_t* cmc_hist, int max_rank, const int32_t* n_valid,

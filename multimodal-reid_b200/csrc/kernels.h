@@ -24,7 +24,10 @@ int launch_dist_simt(const float* A, long long lda, const float* ra, int m, cons
 int launch_dist_tc(const __half* Ahi, const __half* Alo, long long lda, const float* ra, const uint32_t* a_amax,
                    int m, const __half* Bhi, const __half* Blo, long long ldb, const float* rb,
                    const uint32_t* b_amax, int n, int dp, int metric, float* out, long long ld_out,
-                   int* rowmax_key, cudaStream_t s);
+                   int* rowmax_key, float* chunk_min, cudaStream_t s);
+int launch_select_topk_hinted(const float* D, int rows, int cols, long long ld, const int* rowmax_key,
+                              const float* chunk_min, int K, int* nbr, float* nbr_val, int cap_override,
+                              cudaStream_t s);
 int launch_rowmax(const float* D, int rows, int cols, long long ld, int* key, cudaStream_t s);
 int launch_select_topk(const float* D, int rows, int cols, long long ld, const int* rowmax_key, int K,
                        int* nbr, float* nbr_val, int cap_override, cudaStream_t s);
@@ -54,6 +57,9 @@ int launch_rank_rows(const float* dist, int rows, int g, long long ld_dist, uint
 int launch_score(const int* ranked, int q, int g, const long long* q_pid, const long long* g_pid,
                  const long long* q_cam, const long long* g_cam, int max_rank, double* ap, int* first_hit,
                  int* cmc_hist, int* n_valid, cudaStream_t s);
+int launch_score_dist(const float* dist, int q, int g, long long ld, const long long* q_pid,
+                      const long long* g_pid, const long long* q_cam, const long long* g_cam, int max_rank,
+                      double* ap, int* first_hit, int* cmc_hist, int* n_valid, cudaStream_t s);
 int launch_score_finalize(const double* ap, int q, const int* cmc_hist, int max_rank, const int* n_valid,
                           float* cmc, double* mAP, cudaStream_t s);
 int launch_transpose_add(const float* src, int n, long long ld_src, float* dst, long long ld_dst, int accumulate,

@@ -77,7 +77,7 @@ __device__ __forceinline__ void warp_bitonic_u64(unsigned long long* a, int P, i
 }
 
 // entry = column << 32 | neighbour-rank << 16 | fp16 bits
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(256)
 qe_expand_kernel(const int* __restrict__ nbr, int K, int k2, const int* __restrict__ Vc,
                  const __half* __restrict__ Vv, const int* __restrict__ Vn, int cap1, int row0,
                  int row_stride, int rows, const long long* __restrict__ qoff, int cap_sort, int* __restrict__ Qc,
@@ -192,8 +192,8 @@ int launch_qe_expand(const int* nbr, int K, int k2, const int* Vc, const __half*
   REID_REQUIRE(k2 >= 1 && k2 <= K && k2 <= 32, "qe: k2=%d outside [1, min(K=%d, 32)]", k2, K);
   REID_REQUIRE(cap_sort >= 32 && (cap_sort & (cap_sort - 1)) == 0 && cap_sort <= 16384,
                "qe: sort capacity %d must be a power of two in [32, 16384]", cap_sort);
-  int wpb = 4;
-  while (wpb > 1 && (long long)wpb * cap_sort * 8 > 128 * 1024) wpb >>= 1;
+  int wpb = 8;                                        // keep a CTA's sort buffers <= 32 KB so several CTAs share an SM
+  while (wpb > 1 && (long long)wpb * cap_sort * 8 > 32 * 1024) wpb >>= 1;
   const int smem = wpb * cap_sort * 8;
   REID_CUDA(cudaFuncSetAttribute(qe_expand_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   qe_expand_kernel<<<cdiv(rows, wpb), wpb * 32, smem, s>>>(nbr, K, k2, Vc, Vv, Vn, cap1, row0,

@@ -71,67 +71,114 @@ __device__ __forceinline__ void bitonic_sort_u64(unsigned long long* a, int P) {
   }
 }
 
+// block-wide bitonic sort of P (power of two) 32-bit keys in shared memory, ascending
+template <int T>
+__device__ __forceinline__ void bitonic_sort_u32(uint32_t* a, int P) {
+  for (int k = 2; k <= P; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int t = threadIdx.x; t < (P >> 1); t += T) {
+        int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+        int p = i | j;
+        uint32_t x = a[i], y = a[p];
+        bool up = (i & k) == 0;
+        if ((x > y) == up) { a[i] = y; a[p] = x; }
+      }
+      __syncthreads();
+    }
+  }
+}
+
+// The ranking key is O = D / rowmax (reranking.py:46), an IEEE division per element.  Division by a
+// positive constant is monotone, so the candidate filter runs on the raw D values with plain float
+// compares and only the survivors (a few dozen per row) are divided:
+//   pass 1  every thread keeps the minimum D of its strided share; the K-th smallest of those T
+//           minima, tau_D, bounds the K-th smallest element from above (at most K threads own
+//           anything at or below it);
+//   bound   D* = the largest float whose quotient does not exceed tau_D / m  (>= tau_D; quotients
+//           of neighbouring floats can coincide, and entries tied in O are ordered by column);
+//   pass 2  (row now L2-resident) collect every D <= D*, form (O, column) keys, sort, emit K.
 template <int T>
 __global__ void __launch_bounds__(T)
 select_topk_kernel(const float* __restrict__ D, int rows, int cols, long long ld,
                    const int* __restrict__ rowmax_key, int K, int* __restrict__ nbr,
                    float* __restrict__ nbr_val, int cap_override) {
   __shared__ unsigned long long buf[SEL_CAP];
-  __shared__ unsigned long long tau_s;
+  __shared__ float dstar_s;
   __shared__ int cnt_s;
   const int row = blockIdx.x;
   const int tid = threadIdx.x;
   const float* p = D + (long long)row * ld;
   const float m = ordered_int2f(rowmax_key[row]);
   const int cap = cap_override > 0 ? min(cap_override, SEL_CAP) : SEL_CAP;
+  const bool monotone = m > 0.0f && m < INFINITY;      // otherwise (degenerate rows) filter on O itself
 
-  // pass 1: every thread keeps the minimum of its strided share of the row.  The K-th smallest
-  // of those T minima bounds the K-th smallest element from above, and at most K threads own
-  // anything at or below it.
-  unsigned long long best = ~0ull;
-  for (int c = tid * 4; c < cols; c += T * 4) {
-    if (c + 3 < cols) {
-      float4 v = *reinterpret_cast<const float4*>(p + c);
-      unsigned long long k0 = make_ck(v.x, m, c), k1 = make_ck(v.y, m, c + 1),
-                         k2 = make_ck(v.z, m, c + 2), k3 = make_ck(v.w, m, c + 3);
-      k0 = k0 < k1 ? k0 : k1; k2 = k2 < k3 ? k2 : k3; k0 = k0 < k2 ? k0 : k2;
-      best = best < k0 ? best : k0;
-    } else {
-      for (int j = c; j < cols; ++j) {
-        unsigned long long k0 = make_ck(p[j], m, j);
-        best = best < k0 ? best : k0;
+  uint32_t* kbuf = reinterpret_cast<uint32_t*>(buf);
+  if (monotone) {
+    float best = INFINITY;
+    for (int c = tid * 4; c < cols; c += T * 4) {
+      if (c + 3 < cols) {
+        const float4 v = *reinterpret_cast<const float4*>(p + c);
+        best = fminf(best, fminf(fminf(v.x, v.y), fminf(v.z, v.w)));
+      } else {
+        for (int j = c; j < cols; ++j) best = fminf(best, p[j]);
       }
     }
+    kbuf[tid] = f2key(best);
+  } else {
+    unsigned long long best = ~0ull;
+    for (int c = tid; c < cols; c += T) {
+      const unsigned long long k0 = make_ck(p[c], m, c);
+      best = best < k0 ? best : k0;
+    }
+    kbuf[tid] = (uint32_t)(best >> 32);                 // O key
   }
-  buf[tid] = best;
   if (tid == 0) cnt_s = 0;
   __syncthreads();
-  bitonic_sort_u64<T>(buf, T);
-  if (tid == 0) tau_s = buf[K - 1];
+  bitonic_sort_u32<T>(kbuf, T);
+  if (tid == 0) {
+    float x = key2f(kbuf[K - 1]);                       // tau_D (monotone) or tau_O
+    if (monotone) {
+      const float tau_o = __fdiv_rn(x, m);
+      for (int it = 0; it < 64; ++it) {                 // a handful of steps: quotients of adjacent floats rarely coincide
+        const float nx = x >= 0.0f ? __uint_as_float(__float_as_uint(x) + 1)
+                                   : (__float_as_uint(x) == 0x80000000u ? __uint_as_float(1u)
+                                                                        : __uint_as_float(__float_as_uint(x) - 1));
+        if (!(__fdiv_rn(nx, m) <= tau_o)) break;
+        x = nx;
+      }
+    }
+    dstar_s = x;
+  }
   __syncthreads();
-  const unsigned long long tau = tau_s;
+  const float dstar = dstar_s;
   __syncthreads();
 
-  // pass 2 (row now L2-resident): collect everything at or below the bound
+  // pass 2: collect everything at or below the bound
   for (int c = tid * 4; c < cols; c += T * 4) {
+    float vv[4];
+    int nv = 4;
     if (c + 3 < cols) {
-      float4 v = *reinterpret_cast<const float4*>(p + c);
-      float vv[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        unsigned long long k0 = make_ck(vv[j], m, c + j);
-        if (k0 <= tau) {
-          int pos = atomicAdd(&cnt_s, 1);
-          if (pos < cap) buf[pos] = k0;
-        }
-      }
+      const float4 v = *reinterpret_cast<const float4*>(p + c);
+      vv[0] = v.x; vv[1] = v.y; vv[2] = v.z; vv[3] = v.w;
     } else {
-      for (int j = c; j < cols; ++j) {
-        unsigned long long k0 = make_ck(p[j], m, j);
-        if (k0 <= tau) {
-          int pos = atomicAdd(&cnt_s, 1);
-          if (pos < cap) buf[pos] = k0;
-        }
+      nv = cols - c;
+      for (int j = 0; j < nv; ++j) vv[j] = p[c + j];
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (j >= nv) break;
+      bool take;
+      unsigned long long k0 = 0;
+      if (monotone) {
+        take = vv[j] <= dstar;
+        if (take) k0 = make_ck(vv[j], m, c + j);
+      } else {
+        k0 = make_ck(vv[j], m, c + j);
+        take = (uint32_t)(k0 >> 32) <= f2key(dstar);
+      }
+      if (take) {
+        const int pos = atomicAdd(&cnt_s, 1);
+        if (pos < cap) buf[pos] = k0;
       }
     }
   }
@@ -177,6 +224,153 @@ select_topk_kernel(const float* __restrict__ D, int rows, int cols, long long ld
       if (nbr_val) nbr_val[(long long)row * K + r] = key2f((uint32_t)(last >> 32));
     }
   }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Top-K with chunk minima.  The tensor-core epilogue (dist_tcgen05.cu) records the minimum of every
+// 32-column chunk of D.  K chunks whose minimum is <= tau hold K elements <= tau, so the K-th
+// smallest chunk minimum bounds the K-th smallest element, and only chunks whose minimum is <= D*
+// (typically ~K of N/32) can hold a neighbour: the kernel reads ~3 % of the matrix instead of all
+// of it.  One warp per row; the K-th smallest minimum is found by a bitwise binary search with
+// ballots (no sort), candidate chunks are read as coalesced 128-byte lines.
+// ---------------------------------------------------------------------------------------------
+constexpr int SELH_CAND = 256;      // candidate slots per warp
+constexpr int SELH_WPB = 4;
+
+__device__ __forceinline__ void warp_bitonic_u64_sel(unsigned long long* a, int P, int lane) {
+  for (int k = 2; k <= P; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int t = lane; t < (P >> 1); t += 32) {
+        int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+        int p = i | j;
+        unsigned long long x = a[i], y = a[p];
+        bool up = (i & k) == 0;
+        if ((x > y) == up) { a[i] = y; a[p] = x; }
+      }
+      __syncwarp();
+    }
+  }
+}
+
+__global__ void __launch_bounds__(SELH_WPB * 32)
+select_topk_hinted_kernel(const float* __restrict__ D, int rows, int cols, long long ld,
+                          const int* __restrict__ rowmax_key, const float* __restrict__ chunk_min, int nch,
+                          int K, int* __restrict__ nbr, float* __restrict__ nbr_val, int cap) {
+  extern __shared__ __align__(16) unsigned char smem_sh[];
+  const int w = threadIdx.x >> 5, lane = lane_id();
+  const int row = blockIdx.x * SELH_WPB + w;
+  if (row >= rows) return;
+  const size_t per_warp = (size_t)((nch + 1) & ~1) * 4 + SELH_CAND * 8;      // keeps the 64-bit slots aligned
+  uint32_t* ck = reinterpret_cast<uint32_t*>(smem_sh + w * per_warp + SELH_CAND * 8);   // chunk-min keys
+  unsigned long long* cand = reinterpret_cast<unsigned long long*>(smem_sh + w * per_warp);
+  const float* p = D + (long long)row * ld;
+  const float* cm = chunk_min + (long long)row * nch;
+  const float m = ordered_int2f(rowmax_key[row]);
+
+  for (int c = lane; c < nch; c += 32) ck[c] = f2key(cm[c]);
+  __syncwarp();
+  // K-th smallest chunk minimum: largest prefix t with #{key < t} < K, built bit by bit
+  uint32_t t = 0;
+  if (nch >= K) {
+    for (int bit = 31; bit >= 0; --bit) {
+      const uint32_t trial = t | (1u << bit);
+      int cnt = 0;
+      for (int c = lane; c < nch; c += 32) cnt += ck[c] < trial;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(FULL, cnt, o);
+      if (cnt < K) t = trial;                           // fewer than K keys below trial: the K-th is >= trial
+    }
+  } else {
+    t = 0xffffffffu;                                    // fewer chunks than K: every chunk is a candidate
+  }
+  float dstar = key2f(t);
+  if (m > 0.0f && m < INFINITY && nch >= K) {
+    const float tau_o = __fdiv_rn(dstar, m);
+    for (int it = 0; it < 64; ++it) {
+      const float x = dstar;
+      const float nx = x >= 0.0f ? __uint_as_float(__float_as_uint(x) + 1)
+                                 : (__float_as_uint(x) == 0x80000000u ? __uint_as_float(1u)
+                                                                      : __uint_as_float(__float_as_uint(x) - 1));
+      if (!(__fdiv_rn(nx, m) <= tau_o)) break;
+      dstar = nx;
+    }
+  } else {
+    dstar = INFINITY;                                   // degenerate maximum: no monotone filter, take everything
+  }
+  const uint32_t dkey = f2key(dstar);
+
+  // gather candidates from the qualifying chunks
+  int cnt = 0;
+  bool overflow = false;
+  for (int c0 = 0; c0 < nch && !overflow; c0 += 32) {
+    const int c = c0 + lane;
+    unsigned q = __ballot_sync(FULL, c < nch && ck[c] <= dkey);
+    while (q) {
+      const int cc = c0 + __ffs(q) - 1;
+      q &= q - 1;
+      const int col = cc * 32 + lane;
+      float v = INFINITY;
+      if (col < cols) v = p[col];
+      const bool take = col < cols && (v <= dstar || dstar == INFINITY);
+      const unsigned bt = __ballot_sync(FULL, take);
+      const int n_take = __popc(bt);
+      if (cnt + n_take > cap) { overflow = true; break; }
+      if (take) cand[cnt + __popc(bt & ((1u << lane) - 1))] = make_ck(v, m, col);
+      cnt += n_take;
+    }
+  }
+  __syncwarp();
+  if (!overflow) {
+    int P = 32;
+    while (P < cnt) P <<= 1;
+    for (int i = cnt + lane; i < P; i += 32) cand[i] = ~0ull;
+    __syncwarp();
+    warp_bitonic_u64_sel(cand, P, lane);
+    for (int i = lane; i < K; i += 32) {
+      const unsigned long long k0 = cand[i];
+      nbr[(long long)row * K + i] = (int)(unsigned)(k0 & 0xffffffffu);
+      if (nbr_val) nbr_val[(long long)row * K + i] = key2f((uint32_t)(k0 >> 32));
+    }
+    return;
+  }
+  // overflow (massive ties): K rounds of warp-wide arg-min over the qualifying chunks, each strictly
+  // above the previous pick.  Slow, exact, essentially never taken.
+  unsigned long long last = 0;
+  for (int r = 0; r < K; ++r) {
+    unsigned long long mine = ~0ull;
+    for (int cc = 0; cc < nch; ++cc) {
+      if (ck[cc] > dkey) continue;
+      const int col = cc * 32 + lane;
+      if (col < cols) {
+        const unsigned long long k0 = make_ck(p[col], m, col);
+        if ((r == 0 || k0 > last) && k0 < mine) mine = k0;
+      }
+    }
+    mine = warp_min_u64(mine);
+    last = mine;
+    if (lane == 0) {
+      nbr[(long long)row * K + r] = (int)(unsigned)(last & 0xffffffffu);
+      if (nbr_val) nbr_val[(long long)row * K + r] = key2f((uint32_t)(last >> 32));
+    }
+  }
+}
+
+int launch_select_topk_hinted(const float* D, int rows, int cols, long long ld, const int* rowmax_key,
+                              const float* chunk_min, int K, int* nbr, float* nbr_val, int cap_override,
+                              cudaStream_t s) {
+  if (rows == 0) return REID_OK;
+  REID_REQUIRE(K >= 1 && K <= 256, "select_topk: K=%d outside [1,256]", K);
+  REID_REQUIRE(cols >= K, "select_topk: row length %d is shorter than K=%d", cols, K);
+  const int nch = cdiv(cols, 32);
+  const size_t smem = SELH_WPB * ((size_t)((nch + 1) & ~1) * 4 + SELH_CAND * 8);
+  if (smem > 200 * 1024)                                // gallery too wide for the per-warp key table
+    return launch_select_topk(D, rows, cols, ld, rowmax_key, K, nbr, nbr_val, cap_override, s);
+  const int cap = cap_override > 0 ? (cap_override < SELH_CAND ? cap_override : SELH_CAND) : SELH_CAND;
+  REID_REQUIRE(cap >= K || cap_override > 0, "select_topk: K=%d exceeds the candidate buffer", K);
+  REID_CUDA(cudaFuncSetAttribute(select_topk_hinted_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  select_topk_hinted_kernel<<<cdiv(rows, SELH_WPB), SELH_WPB * 32, smem, s>>>(D, rows, cols, ld, rowmax_key,
+                                                                            chunk_min, nch, K, nbr, nbr_val, cap);
+  return check_launch("select_topk_hinted_kernel");
 }
 
 int launch_select_topk(const float* D, int rows, int cols, long long ld, const int* rowmax_key, int K,

@@ -193,8 +193,9 @@ class Engine:
         return (n + 31) // 32 * 32
 
     def dist(self, A: Features, B: Features, metric: int = METRIC_SQEUCLIDEAN, want_rowmax: bool = False,
-             engine: int | None = None):
-        """Returns (D [m, pitch] float32 — use D[:, :n] —, rowmax_key [m] int32 or None)."""
+             engine: int | None = None, want_chunk_min: bool = False):
+        """Returns (D [m, pitch] float32 — use D[:, :n] —, rowmax_key [m] int32 or None)
+        [, chunk_min [m, ceil(n/32)] float32 when want_chunk_min (tensor-core engine only)]."""
         assert A.dp == B.dp
         m, n = A.n, B.n
         ld = self.pitch(n)
@@ -205,14 +206,18 @@ class Engine:
             _lib.call("reid_rowmax_init", _ptr(key), m, _stream())
         ra, rb = (A.sq, B.sq) if metric == METRIC_SQEUCLIDEAN else (A.nrm, B.nrm)
         engine = self.engine if engine is None else engine
+        cmin = None
         if engine == ENGINES["simt"]:
+            assert not want_chunk_min, "chunk minima come from the tensor-core epilogue"
             _lib.call("reid_dist_fp32", _ptr(A.x32), A.x32.stride(0), _ptr(ra), m, _ptr(B.x32), B.x32.stride(0),
                       _ptr(rb), n, A.dp, metric, _ptr(D), ld, _ptr(key), _stream())
         else:
+            if want_chunk_min:
+                cmin = self._empty((m, (n + 31) // 32), torch.float32)
             _lib.call("reid_dist", _ptr(A.hi), _ptr(A.lo), A.hi.stride(0), _ptr(ra), _ptr(A.amax), m, _ptr(B.hi),
                       _ptr(B.lo), B.hi.stride(0), _ptr(rb), _ptr(B.amax), n, A.dp, metric, _ptr(D), ld, _ptr(key),
-                      _stream())
-        return D, key
+                      _ptr(cmin), _stream())
+        return (D, key, cmin) if want_chunk_min else (D, key)
 
     def rowmax(self, D: torch.Tensor, cols: int) -> torch.Tensor:
         key = self._empty((D.shape[0],), torch.int32)
@@ -235,11 +240,15 @@ class Engine:
         return dst
 
     # ------------------------------------------------------------------ K5
-    def topk_rows(self, D: torch.Tensor, cols: int, key: torch.Tensor, K: int, want_values=False, cap: int = 0):
+    def topk_rows(self, D: torch.Tensor, cols: int, key: torch.Tensor, K: int, want_values=False, cap: int = 0,
+                  chunk_min: torch.Tensor | None = None):
         rows = D.shape[0]
         nbr = self._empty((rows, K), torch.int32)
         val = self._empty((rows, K), torch.float32) if want_values else None
-        if cap:
+        if chunk_min is not None:
+            _lib.call("reid_topk_rows_hinted", _ptr(D), rows, cols, D.stride(0), _ptr(key), _ptr(chunk_min), K,
+                      _ptr(nbr), _ptr(val), cap, _stream())
+        elif cap:
             _lib.call("reid_topk_rows_capped", _ptr(D), rows, cols, D.stride(0), _ptr(key), K, _ptr(nbr), _ptr(val),
                       cap, _stream())
         else:
@@ -279,16 +288,17 @@ class Engine:
         _lib.call("reid_qe_bound", _ptr(nbr), K, k2, _ptr(Vn), row0, row_stride, rows, _ptr(ub), _stream())
         qoff = self._empty((rows + 1,), torch.int64)
         _lib.call("reid_exclusive_scan", _ptr(ub), rows, _ptr(qoff), _stream())
-        total = int(qoff[rows].item())                 # 8-byte D2H: sizes the CSR pool
+        # 16-byte D2H: pool size and the longest union (sizes the per-warp sort buffers)
+        total, ub_max = (int(v) for v in torch.stack([qoff[rows], ub.max().to(torch.int64)]).tolist()) if rows else (0, 0)
         Qc = self._empty((max(total, 1),), torch.int32)
         Qv = self._empty((max(total, 1),), torch.float16)
         Qn = self._empty((rows,), torch.int32)
-        if cap_sort:
-            _lib.call("reid_qe_k2_capped", _ptr(nbr), K, k2, _ptr(Vc), _ptr(Vv), _ptr(Vn), cap1, row0, row_stride,
-                      rows, _ptr(qoff), cap_sort, _ptr(Qc), _ptr(Qv), _ptr(Qn), _stream())
-        else:
-            _lib.call("reid_qe_k2", _ptr(nbr), K, k2, _ptr(Vc), _ptr(Vv), _ptr(Vn), cap1, row0, row_stride, rows,
-                      _ptr(qoff), _ptr(Qc), _ptr(Qv), _ptr(Qn), _stream())
+        if not cap_sort:
+            cap_sort = 32
+            while cap_sort < min(ub_max, 4096):
+                cap_sort *= 2
+        _lib.call("reid_qe_k2_capped", _ptr(nbr), K, k2, _ptr(Vc), _ptr(Vv), _ptr(Vn), cap1, row0, row_stride,
+                  rows, _ptr(qoff), cap_sort, _ptr(Qc), _ptr(Qv), _ptr(Qn), _stream())
         return Qc, Qv, qoff, Qn, total
 
     # ------------------------------------------------------------------ K8
@@ -321,7 +331,7 @@ class Engine:
 
     # ------------------------------------------------------------------ K4–K10 from a distance panel
     def rerank_from_panel(self, D: torch.Tensor, key: torch.Tensor, q: int, N: int, k1: int, k2: int, lam: float,
-                          detail: dict | None = None) -> torch.Tensor:
+                          detail: dict | None = None, chunk_min: torch.Tensor | None = None) -> torch.Tensor:
         """D: this rank's panel [n_local, pitch(N)] (row l = probe rank + l*world), key: its row
         maxima.  Returns final[nq_local, pitch(g)] for this rank's queries (use [:, :g])."""
         cm = self.comm
@@ -331,7 +341,7 @@ class Engine:
         if N < K:
             raise NotImplementedError(f"re-ranking needs at least max(k1+1, k2) = {K} samples, got {N}")
         with self.span("select"):
-            nbr_local = self.topk_rows(D, N, key, K)
+            nbr_local = self.topk_rows(D, N, key, K, chunk_min=chunk_min)
         nbr = cm.gather_rows(nbr_local, N)
         with self.span("krecip"):
             sets = self.krecip_sets(nbr, k1)
@@ -379,10 +389,13 @@ class Engine:
             allf = self.prepare(feats, normalize)
             mine = allf if cm.world == 1 else allf.rows(slice(cm.rank, N, cm.world))
         with self.span("dist"):
-            D, key = self.dist(mine, allf, METRIC_SQEUCLIDEAN, want_rowmax=True)
+            if self.engine == ENGINES["simt"]:
+                (D, key), cmin = self.dist(mine, allf, METRIC_SQEUCLIDEAN, want_rowmax=True), None
+            else:
+                D, key, cmin = self.dist(mine, allf, METRIC_SQEUCLIDEAN, want_rowmax=True, want_chunk_min=True)
         if detail is not None:
             detail.update(D=D, key=key)
-        return self.rerank_from_panel(D, key, q, N, k1, k2, lam, detail)
+        return self.rerank_from_panel(D, key, q, N, k1, k2, lam, detail, chunk_min=cmin)
 
     # ------------------------------------------------------------------ K11 + K12
     def rank_rows(self, dist: torch.Tensor, g: int) -> torch.Tensor:
@@ -395,18 +408,14 @@ class Engine:
                   _ptr(ranked), _stream())
         return ranked
 
-    def score(self, ranked: torch.Tensor, q_pids, g_pids, q_cams, g_cams, max_rank: int, q_total: int | None = None):
-        """ranked: this rank's [nq_local, g]; q_pids/q_cams: the matching local slices (int64).
-        Returns (cmc float32[max_rank] tensor, mAP float64 tensor[1], n_valid int tensor[1], ap[q])."""
+    def _score_common(self, launch, nq, max_rank, q_total):
         cm = self.comm
-        nq, g = ranked.shape
         ap = self._empty((nq,), torch.float64)
         first = self._empty((nq,), torch.int32)
         hist = self._zeros((max_rank,), torch.int32)
         nvalid = self._zeros((1,), torch.int32)
         with self.span("score"):
-            _lib.call("reid_score_rows", _ptr(ranked), nq, g, _ptr(q_pids), _ptr(g_pids), _ptr(q_cams), _ptr(g_cams),
-                      max_rank, _ptr(ap), _ptr(first), _ptr(hist), _ptr(nvalid), _stream())
+            launch(ap, first, hist, nvalid)
         q_all = nq if q_total is None else q_total
         ap_all = cm.gather_rows(ap, q_all)
         first_all = cm.gather_rows(first, q_all)
@@ -418,11 +427,32 @@ class Engine:
                   _ptr(mAP), _stream())
         return cmc, mAP, nvalid, ap_all, first_all
 
+    def score(self, ranked: torch.Tensor, q_pids, g_pids, q_cams, g_cams, max_rank: int, q_total: int | None = None):
+        """K12 on a materialised ranking.  ranked: this rank's [nq_local, g]; q_pids/q_cams: the
+        matching local slices (int64).  Returns (cmc float32[max_rank], mAP float64[1], n_valid[1],
+        ap[q], first_hit[q]) as device tensors."""
+        nq, g = ranked.shape
+
+        def launch(ap, first, hist, nvalid):
+            _lib.call("reid_score_rows", _ptr(ranked), nq, g, _ptr(q_pids), _ptr(g_pids), _ptr(q_cams), _ptr(g_cams),
+                      max_rank, _ptr(ap), _ptr(first), _ptr(hist), _ptr(nvalid), _stream())
+        return self._score_common(launch, nq, max_rank, q_total)
+
     def evaluate_dist(self, dist: torch.Tensor, g: int, q_pids, g_pids, q_cams, g_cams, max_rank: int,
-                      q_total: int | None = None):
-        with self.span("rank"):
-            ranked = self.rank_rows(dist, g)
-        return self.score(ranked, q_pids, g_pids, q_cams, g_cams, max_rank, q_total)
+                      q_total: int | None = None, materialize_ranking: bool = False):
+        """K11 + K12 from distance rows [nq_local, >= g].  Default: the fused counting kernel
+        (reid_score_dist); materialize_ranking=True goes through the explicit stable ranking
+        (reid_rank_rows + reid_score_rows) — same results."""
+        if materialize_ranking:
+            with self.span("rank"):
+                ranked = self.rank_rows(dist, g)
+            return self.score(ranked, q_pids, g_pids, q_cams, g_cams, max_rank, q_total)
+        nq = dist.shape[0]
+
+        def launch(ap, first, hist, nvalid):
+            _lib.call("reid_score_dist", _ptr(dist), nq, g, dist.stride(0), _ptr(q_pids), _ptr(g_pids), _ptr(q_cams),
+                      _ptr(g_cams), max_rank, _ptr(ap), _ptr(first), _ptr(hist), _ptr(nvalid), _stream())
+        return self._score_common(launch, nq, max_rank, q_total)
 
 
 _default = None
