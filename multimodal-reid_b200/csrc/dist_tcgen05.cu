@@ -10,8 +10,10 @@
 // the epilogue's  (ra + rb) - 2 * acc * 2^-(ea+eb)  rounds exactly like the reference's addmm_.
 //
 // Structure (one CTA per SM, persistent over 128 x 256 output tiles):
-//   warp 0      TMA producer: 4 boxes per K block (A_hi, A_lo: 128 x 64; B_hi, B_lo: 256 x 64 fp16,
-//               128-byte swizzle) into a 2-stage shared-memory ring, completion on mbarriers
+//   warp 0      TMA producer: 4 boxes per K block (A_hi, A_lo: 128 x BK; B_hi, B_lo: 256 x BK fp16,
+//               rows = one swizzle span) into a 192 KB shared-memory ring (2 stages of BK = 64; 4 of BK = 32
+//               measured 7 % slower: the kernel is bound by shared-memory bandwidth, not latency),
+//               completion on mbarriers
 //   warp 1      allocates TMEM (2 accumulators x 256 columns) and issues tcgen05.mma
 //               (cta_group::1, M=128, N=256, K=16) from one lane; tcgen05.commit frees ring slots
 //               and publishes the finished accumulator
@@ -29,8 +31,12 @@
 namespace reid {
 namespace tc {
 
-constexpr int BM = 128, BN = 256, BK = 64, UK = 16;
-constexpr int STAGES = 2;
+#ifndef REID_TC_BK
+#define REID_TC_BK 64
+#endif
+constexpr int BM = 128, BN = 256, BK = REID_TC_BK, UK = 16;     // BK * 2 bytes = the TMA / UMMA swizzle width
+constexpr int STAGES = BK == 64 ? 2 : 4;
+static_assert(BK == 64 || BK == 32, "K block must be one 128-byte or one 64-byte swizzle row");
 constexpr uint32_t A_BYTES = BM * BK * 2;                 // 16 KB
 constexpr uint32_t B_BYTES = BN * BK * 2;                 // 32 KB
 constexpr uint32_t STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;   // 96 KB
@@ -110,13 +116,14 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
-// K-major operand tile, 128-byte swizzle: rows of 128 B, 8-row groups 1024 B apart.
+// K-major operand tile whose rows are exactly one swizzle span (BK * 2 bytes: 128 B or 64 B);
+// 8-row groups are 8 * span bytes apart.
 __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr) {
   uint64_t d = 0;
   d |= (uint64_t)((saddr >> 4) & 0x3fff);        // start address
-  d |= (uint64_t)(1024 >> 4) << 32;              // stride byte offset (between 8-row groups)
+  d |= (uint64_t)((8 * BK * 2) >> 4) << 32;      // stride byte offset (between 8-row groups)
   d |= (uint64_t)1 << 46;                        // descriptor version (sm_100)
-  d |= (uint64_t)2 << 61;                        // SWIZZLE_128B
+  d |= (uint64_t)(BK == 64 ? 2 : 4) << 61;       // SWIZZLE_128B / SWIZZLE_64B
   return d;
 }
 // kind::f16: A = B = F16, D = F32, both K-major, M = 128, N = 256
@@ -151,13 +158,14 @@ dist_tc_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant_
   uint8_t* epi_base = smem + STAGES * STAGE_BYTES;
   float* rb_s = reinterpret_cast<float*>(epi_base + EPI_BYTES);
   uint64_t* bars = reinterpret_cast<uint64_t*>(epi_base + EPI_BYTES + RB_BYTES);
-  // bars: [0,2) full, [2,4) empty, [4,6) tmem_full, [6,8) tmem_empty; then the TMEM base address
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+  // bars: STAGES full, STAGES empty, 2 tmem_full, 2 tmem_empty; then the TMEM base address
+  static_assert((2 * STAGES + 4 + 1) * 8 <= 128, "barrier block overflows its 128 bytes");
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
   const uint32_t bar0 = smem_u32(bars);
   auto FULL_B = [&](int s) { return bar0 + 8u * s; };
-  auto EMPTY_B = [&](int s) { return bar0 + 8u * (2 + s); };
-  auto TFULL_B = [&](int s) { return bar0 + 8u * (4 + s); };
-  auto TEMPTY_B = [&](int s) { return bar0 + 8u * (6 + s); };
+  auto EMPTY_B = [&](int s) { return bar0 + 8u * (STAGES + s); };
+  auto TFULL_B = [&](int s) { return bar0 + 8u * (2 * STAGES + s); };
+  auto TEMPTY_B = [&](int s) { return bar0 + 8u * (2 * STAGES + 2 + s); };
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int mblocks = (m + BM - 1) / BM, nblocks = (n + BN - 1) / BN;
@@ -335,7 +343,8 @@ static EncodeTiledFn encode_fn() {
 }
 
 static int make_map(CUtensorMap* map, CUtensorMapDataType dt, int esize, const void* base, long long cols,
-                    long long rows, long long ld_elems, int box_cols, int box_rows, const char* what) {
+                    long long rows, long long ld_elems, int box_cols, int box_rows, const char* what,
+                    CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) {
     set_error("cuTensorMapEncodeTiled is not available from the driver");
@@ -346,7 +355,7 @@ static int make_map(CUtensorMap* map, CUtensorMapDataType dt, int esize, const v
   cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = fn(map, dt, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                  swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("cuTensorMapEncodeTiled(%s) failed with CUresult %d (base %p, %lld x %lld, ld %lld)", what, (int)r,
               base, rows, cols, ld_elems);
@@ -368,11 +377,12 @@ int launch_dist_tc(const __half* Ahi, const __half* Alo, long long lda, const fl
                "dist_tc: row pitches must keep rows 16-byte aligned (lda=%lld ldb=%lld ld_out=%lld)", lda, ldb,
                ld_out);
   CUtensorMap mAhi, mAlo, mBhi, mBlo, mOut;
+  const CUtensorMapSwizzle OPSWZ = BK == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
   int rc;
-  if ((rc = make_map(&mAhi, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, Ahi, dp, m, lda, BK, BM, "A_hi"))) return rc;
-  if ((rc = make_map(&mAlo, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, Alo, dp, m, lda, BK, BM, "A_lo"))) return rc;
-  if ((rc = make_map(&mBhi, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, Bhi, dp, n, ldb, BK, BN, "B_hi"))) return rc;
-  if ((rc = make_map(&mBlo, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, Blo, dp, n, ldb, BK, BN, "B_lo"))) return rc;
+  if ((rc = make_map(&mAhi, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, Ahi, dp, m, lda, BK, BM, "A_hi", OPSWZ))) return rc;
+  if ((rc = make_map(&mAlo, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, Alo, dp, m, lda, BK, BM, "A_lo", OPSWZ))) return rc;
+  if ((rc = make_map(&mBhi, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, Bhi, dp, n, ldb, BK, BN, "B_hi", OPSWZ))) return rc;
+  if ((rc = make_map(&mBlo, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, Blo, dp, n, ldb, BK, BN, "B_lo", OPSWZ))) return rc;
   if ((rc = make_map(&mOut, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, out, n, m, ld_out, 32, 32, "out"))) return rc;
   int dev = 0, sms = 0;
   REID_CUDA(cudaGetDevice(&dev));

@@ -70,11 +70,13 @@ class Features:
 class Comm:
     """Cyclic row ownership + the collectives the path needs.  world == 1 is the identity."""
 
-    def __init__(self, group=None):
+    def __init__(self, group=None, single: bool = False):
         import torch.distributed as dist
         self.dist = dist
         self.group = group
-        if dist.is_available() and dist.is_initialized():
+        if single:
+            self.rank, self.world = 0, 1
+        elif dist.is_available() and dist.is_initialized():
             self.rank = dist.get_rank(group)
             self.world = dist.get_world_size(group)
         else:

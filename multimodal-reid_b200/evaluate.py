@@ -63,13 +63,17 @@ def eval_func(distmat, q_pids, g_pids, q_camids, g_camids, max_rank=50):
         d = torch.from_numpy(np.ascontiguousarray(distmat))
     else:
         d = distmat
+    num_q, num_g = d.shape
+    cm = eng.comm
+    mine = slice(cm.rank, num_q, cm.world)          # one process per GPU: every rank scores its share of the queries
+    if cm.world > 1:
+        d = d[mine]
     d = d.to(dev, non_blocking=True)
     if d.dtype != torch.float32:
         d = d.float()
     d = d.contiguous()
-    num_q, num_g = d.shape
-    return eval_func_device(d, num_g, _ids(q_pids, dev), _ids(g_pids, dev), _ids(q_camids, dev),
-                            _ids(g_camids, dev), max_rank, eng)
+    return eval_func_device(d, num_g, _ids(q_pids, dev)[mine].contiguous(), _ids(g_pids, dev),
+                            _ids(q_camids, dev)[mine].contiguous(), _ids(g_camids, dev), max_rank, eng, q_total=num_q)
 
 
 class R1_mAP_eval():
@@ -114,9 +118,12 @@ class R1_mAP_eval():
         else:
             print('=> Computing DistMat with euclidean_distance')
             allf = eng.prepare(feats, self.feat_norm)
-            dist, _ = eng.dist(allf.rows(slice(0, q)), allf.rows(slice(q, N)), _engine.METRIC_SQEUCLIDEAN)
+            dist, _ = eng.dist(allf.rows(slice(eng.comm.rank, q, eng.comm.world)), allf.rows(slice(q, N)),
+                               _engine.METRIC_SQEUCLIDEAN)
         # evaluate.py:132 does not forward self.max_rank: always 50
-        cmc, mAP = eval_func_device(dist, g, pids[:q].contiguous(), pids[q:].contiguous(),
-                                    camids[:q].contiguous(), camids[q:].contiguous(), 50, eng)
+        cm = eng.comm
+        mine = slice(cm.rank, q, cm.world)          # `dist` holds this rank's queries (rank, rank + world, ...)
+        cmc, mAP = eval_func_device(dist, g, pids[:q][mine].contiguous(), pids[q:].contiguous(),
+                                    camids[:q][mine].contiguous(), camids[q:].contiguous(), 50, eng, q_total=q)
         print("Rank@{:d}:{:.1%}, Rank@{:d}:{:.1%}, Rank@{:d}:{:.1%}, mAP:{:.1%}".format(1, cmc[0], 5, cmc[4], 10, cmc[9], mAP))
         return cmc, mAP

@@ -1,0 +1,52 @@
+"""Run under torchrun (one rank per GPU; or gloo on CPU for the host-side logic only):
+   python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tests/multi_rank_check.py
+
+Asserts that the row-sharded pipeline returns, on every rank, exactly the bits a single rank
+computes alone (SURVEY.md §8e invariance requirement): the re-ranked rows of this rank's queries,
+the per-query APs, the CMC curve and mAP."""
+import importlib
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    rank = int(os.environ["RANK"])
+    world = int(os.environ["WORLD_SIZE"])
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    engine = importlib.import_module("multimodal-reid_b200.engine")
+    synth = importlib.import_module("multimodal-reid_b200.synth")
+    multi = engine.Engine(dev)
+    single = engine.Engine(dev, comm=engine.Comm(single=True))
+    assert multi.comm.world == world and single.comm.world == 1
+    for name, k1, k2, seed in (("small", 20, 6, 0), ("small", 50, 15, 1), ("mid", 20, 6, 2), ("tiny", 7, 1, 3)):
+        sh = synth.SHAPES[name]
+        qf, gf, qp, gp, qc, gc = synth.make(sh, seed)
+        feats = torch.cat([qf, gf]).to(dev)
+        q, g = sh.q, sh.g
+        ids = [t.to(dev) for t in (qp, gp, qc, gc)]
+        ref = single.rerank_features(feats, q, k1, k2, 0.3, normalize=True)
+        got = multi.rerank_features(feats, q, k1, k2, 0.3, normalize=True)
+        mine = slice(rank, q, world)
+        assert torch.equal(got[:, :g], ref[mine, :g]), f"{name}: rank {rank} rows differ from the single-rank result"
+        r1 = single.evaluate_dist(ref, g, *ids, 50)
+        r2 = multi.evaluate_dist(got, g, ids[0][mine].contiguous(), ids[1], ids[2][mine].contiguous(), ids[3], 50,
+                                 q_total=q)
+        for a, b, what in zip(r1, r2, ("cmc", "mAP", "n_valid", "ap", "first_hit")):
+            assert torch.equal(a, b), f"{name}: {what} differs on rank {rank}"
+        if rank == 0:
+            print(f"{name} k1={k1} k2={k2}: {world}-rank result == 1-rank result, mAP {float(r2[1]):.6f}", flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -139,3 +139,16 @@ def test_full_pipeline_vs_oracle(api, synth, oracle, name, seed):
     idx = np.argsort(got, axis=1, kind="stable")[:, :20]
     idx2 = np.argsort(want, axis=1, kind="stable")[:, :20]
     assert_ranking_equal_mod_ties(idx, idx2, want, tol=4.0 * 2.0 ** -11, what="top-20 of final")
+
+
+def test_two_ranks_match_one_rank():
+    """Launches tests/multi_rank_check.py on 2 GPUs when the box has them (NCCL); skipped on 1 GPU."""
+    import subprocess
+    import sys
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29533",
+                        os.path.join(root, "tests", "multi_rank_check.py")], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
