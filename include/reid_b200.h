@@ -137,12 +137,14 @@ REID_API int reid_qe_k2_capped(const int32_t* nbr, int K, int k2, const int32_t*
 /* offsets of an ELL matrix viewed as CSR: off[i] = i * pitch, i in [0, N] (k2 == 1: V_qe = V) */
 REID_API int reid_ell_offsets(int N, int pitch, int64_t* off, void* stream);
 
-/* K8  reranking.py:80-82.  Inverted index (CSC) of V_qe over all N rows: count, (scan), fill. */
+/* K8  reranking.py:80-82.  Inverted index (CSC) of V_qe over all N rows: count, (scan), fill.
+ * csc_ent[p] = row | (uint64)float16_bits << 32 for p in [colptr[c], colptr[c+1]): one 8-byte entry per
+ * non-zero so that a column is one contiguous, 8-byte aligned stream for cp.async. */
 REID_API int reid_csc_count(const int32_t* Qc, const int64_t* qoff, const int32_t* Qn, int N,
                    int32_t* colcnt /* zeroed, N */, void* stream);
 REID_API int reid_csc_fill(const int32_t* Qc, const reid_half* Qv, const int64_t* qoff, const int32_t* Qn,
-                  int N, const int64_t* colptr, int32_t* cursor /* zeroed, N */, int32_t* csc_row,
-                  reid_half* csc_val, void* stream);
+                  int N, const int64_t* colptr, int32_t* cursor /* zeroed, N */, uint64_t* csc_ent,
+                  void* stream);
 
 /* K9 + K10  reranking.py:84-100.  For the query window (global probe q0 + l*q_stride, l < nq):
  * float16 Jaccard chain through the inverted index and
@@ -150,10 +152,34 @@ REID_API int reid_csc_fill(const int32_t* Qc, const reid_half* Qv, const int64_t
  * with c1 = 1 - lambda (rounded to float16 by the caller) and c2 = float32(lambda).
  * jaccard_out (nullable, pitch ld_j, N columns) receives the float16 Jaccard rows for tests. */
 REID_API int reid_jaccard_mix(const int32_t* Qc, const reid_half* Qv, const int64_t* qoff, const int32_t* Qn,
-                     const int64_t* colptr, const int32_t* csc_row, const reid_half* csc_val,
+                     const int64_t* colptr, const uint64_t* csc_ent,
                      const float* D, int64_t ld, const int32_t* rowmax_key, int q0, int q_stride,
                      int nq, int q, int N, float c1, float c2, float* out, int64_t ld_out,
                      reid_half* jaccard_out, int64_t ld_j, void* stream);
+
+/* Identity index for the fused scorer  evaluate.py:43, :53-55.  Groups the gallery columns by pid (open-addressing
+ * hash on the 64-bit id, then a counting sort by slot) so that a query finds the handful of gallery entries
+ * sharing its identity -- the only ones that can be junk or true matches -- without scanning g_pid.
+ * T = reid_pid_index_slots(g) (a power of two >= 2g).  Workspace: keys[T] 64-bit, cnt[T+1], cursor[T+1],
+ * start[T+2] (int64), list[g]. */
+REID_API int reid_pid_index_slots(int g);
+REID_API int reid_pid_index(const int64_t* g_pid, int g, int T, uint64_t* keys, int32_t* cnt, int64_t* start,
+                   int32_t* cursor, int32_t* list, void* stream);
+
+/* K9 + K10 + K11 + K12 fused (the evaluator's path)  reranking.py:84-100 then evaluate.py:40-88.
+ * reid_jaccard_mix plus, per query, AP / first-match rank / CMC histogram computed from the mixed row while it
+ * is produced: the kept rank of every true match is the number of non-junk entries at or before it in stable
+ * (distance, column) order.  `out` may be NULL: then the q x g re-ranked matrix is never written.
+ * q_pid / q_cam: ids of this window's queries [nq]; g_cam [g]; keys/start/list/T from reid_pid_index.
+ * Score outputs as in reid_score_rows. */
+REID_API int reid_jaccard_score(const int32_t* Qc, const reid_half* Qv, const int64_t* qoff, const int32_t* Qn,
+                       const int64_t* colptr, const uint64_t* csc_ent,
+                       const float* D, int64_t ld, const int32_t* rowmax_key, int q0, int q_stride,
+                       int nq, int q, int N, float c1, float c2, float* out, int64_t ld_out,
+                       const int64_t* q_pid, const int64_t* q_cam, const int64_t* g_cam,
+                       const uint64_t* pid_keys, const int64_t* pid_start, const int32_t* pid_list, int pid_T,
+                       int max_rank, double* ap, int32_t* first_hit, int32_t* cmc_hist, int32_t* n_valid,
+                       void* stream);
 
 /* K11  evaluate.py:40.  Stable full ranking of every row (ascending distance, ties by column).
  * Workspace: keyA, keyB, idxA of rows*g 32-bit words each. */

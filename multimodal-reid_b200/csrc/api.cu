@@ -256,24 +256,60 @@ int reid_csc_count(const int32_t* Qc, const int64_t* qoff, const int32_t* Qn, in
 }
 
 int reid_csc_fill(const int32_t* Qc, const reid_half* Qv, const int64_t* qoff, const int32_t* Qn, int N,
-                  const int64_t* colptr, int32_t* cursor, int32_t* csc_row, reid_half* csc_val,
-                  void* stream) {
+                  const int64_t* colptr, int32_t* cursor, uint64_t* csc_ent, void* stream) {
   ENTER();
   return launch_csc_fill(Qc, HC(Qv), reinterpret_cast<const long long*>(qoff), Qn, N,
-                         reinterpret_cast<const long long*>(colptr), cursor, csc_row, H(csc_val), S(stream));
+                         reinterpret_cast<const long long*>(colptr), cursor,
+                         reinterpret_cast<unsigned long long*>(csc_ent), S(stream));
 }
 
 int reid_jaccard_mix(const int32_t* Qc, const reid_half* Qv, const int64_t* qoff, const int32_t* Qn,
-                     const int64_t* colptr, const int32_t* csc_row, const reid_half* csc_val, const float* D,
+                     const int64_t* colptr, const uint64_t* csc_ent, const float* D,
                      int64_t ld, const int32_t* rowmax_key, int q0, int q_stride, int nq, int q, int N,
                      float c1, float c2, float* out, int64_t ld_out, reid_half* jaccard_out, int64_t ld_j,
                      void* stream) {
   ENTER();
   REID_REQUIRE(q >= 0 && q <= N && q_stride >= 1, "jaccard_mix: bad shape q=%d N=%d", q, N);
   return launch_jaccard_mix(Qc, HC(Qv), reinterpret_cast<const long long*>(qoff), Qn,
-                            reinterpret_cast<const long long*>(colptr), csc_row, HC(csc_val), D, ld,
-                            rowmax_key, q0, q_stride, nq, q, N, c1, c2, out, ld_out, H(jaccard_out), ld_j,
+                            reinterpret_cast<const long long*>(colptr),
+                            reinterpret_cast<const unsigned long long*>(csc_ent), D, ld, rowmax_key, q0, q_stride, nq, q, N, c1, c2, out, ld_out, H(jaccard_out), ld_j,
                             S(stream));
+}
+
+int reid_pid_index_slots(int g) {
+  long long T = 64;
+  while (T < 2 * (long long)g) T <<= 1;
+  return (int)T;
+}
+
+int reid_pid_index(const int64_t* g_pid, int g, int T, uint64_t* keys, int32_t* cnt, int64_t* start,
+                   int32_t* cursor, int32_t* list, void* stream) {
+  ENTER();
+  REID_REQUIRE(g >= 0, "pid_index: g=%d", g);
+  return launch_pid_index(reinterpret_cast<const long long*>(g_pid), g, T,
+                          reinterpret_cast<unsigned long long*>(keys), cnt, reinterpret_cast<long long*>(start),
+                          cursor, list, S(stream));
+}
+
+int reid_jaccard_score(const int32_t* Qc, const reid_half* Qv, const int64_t* qoff, const int32_t* Qn,
+                       const int64_t* colptr, const uint64_t* csc_ent, const float* D,
+                       int64_t ld, const int32_t* rowmax_key, int q0, int q_stride, int nq, int q, int N, float c1,
+                       float c2, float* out, int64_t ld_out, const int64_t* q_pid, const int64_t* q_cam,
+                       const int64_t* g_cam, const uint64_t* pid_keys, const int64_t* pid_start,
+                       const int32_t* pid_list, int pid_T, int max_rank, double* ap, int32_t* first_hit,
+                       int32_t* cmc_hist, int32_t* n_valid, void* stream) {
+  ENTER();
+  REID_REQUIRE(q >= 0 && q <= N && q_stride >= 1, "jaccard_score: bad shape q=%d N=%d", q, N);
+  REID_REQUIRE(ap != nullptr, "jaccard_score: ap is NULL (use reid_jaccard_mix for the matrix alone)");
+  return launch_jaccard_score(Qc, HC(Qv), reinterpret_cast<const long long*>(qoff), Qn,
+                              reinterpret_cast<const long long*>(colptr),
+                              reinterpret_cast<const unsigned long long*>(csc_ent), D, ld, rowmax_key,
+                              q0, q_stride, nq, q, N, c1, c2, out, ld_out, nullptr, 0,
+                              reinterpret_cast<const long long*>(q_pid), reinterpret_cast<const long long*>(q_cam),
+                              reinterpret_cast<const long long*>(g_cam),
+                              reinterpret_cast<const unsigned long long*>(pid_keys),
+                              reinterpret_cast<const long long*>(pid_start), pid_list, pid_T, max_rank, ap,
+                              first_hit, cmc_hist, n_valid, S(stream));
 }
 
 int reid_rank_rows(const float* dist, int rows, int g, int64_t ld, uint32_t* keyA, uint32_t* keyB,

@@ -46,12 +46,22 @@ int launch_ell_offsets(int N, int cap1, long long* off, cudaStream_t s);
 int launch_csc_count(const int* Qc, const long long* qoff, const int* Qn, int N, int* colcnt,
                      cudaStream_t s);
 int launch_csc_fill(const int* Qc, const __half* Qv, const long long* qoff, const int* Qn, int N,
-                    const long long* colptr, int* cursor, int* csc_row, __half* csc_val, cudaStream_t s);
+                    const long long* colptr, int* cursor, unsigned long long* csc_ent, cudaStream_t s);
 int launch_jaccard_mix(const int* Qc, const __half* Qv, const long long* qoff, const int* Qn,
-                       const long long* colptr, const int* csc_row, const __half* csc_val, const float* D,
+                       const long long* colptr, const unsigned long long* csc_ent, const float* D,
                        long long ld, const int* rowmax_key, int q0, int q_stride, int nq_local, int q, int N, float c1,
                        float c2, float* out, long long ld_out, __half* jaccard_out, long long ld_j,
                        cudaStream_t s);
+int launch_pid_index(const long long* g_pid, int g, int T, unsigned long long* keys, int* cnt, long long* start,
+                     int* cursor, int* list, cudaStream_t s);
+int launch_jaccard_score(const int* Qc, const __half* Qv, const long long* qoff, const int* Qn,
+                         const long long* colptr, const unsigned long long* csc_ent, const float* D,
+                         long long ld, const int* rowmax_key, int q0, int q_stride, int nq_local, int q, int N,
+                         float c1, float c2, float* out, long long ld_out, __half* jaccard_out, long long ld_j,
+                         const long long* q_pid, const long long* q_cam, const long long* g_cam,
+                         const unsigned long long* pid_keys, const long long* pid_start, const int* pid_list,
+                         int pid_T, int max_rank, double* ap, int* first_hit, int* cmc_hist, int* n_valid,
+                         cudaStream_t s);
 int launch_rank_rows(const float* dist, int rows, int g, long long ld_dist, uint32_t* keyA, uint32_t* keyB,
                      int* idxA, int* idx_out, cudaStream_t s);
 int launch_score(const int* ranked, int q, int g, const long long* q_pid, const long long* g_pid,

@@ -228,14 +228,21 @@ select_topk_kernel(const float* __restrict__ D, int rows, int cols, long long ld
 
 // ---------------------------------------------------------------------------------------------
 // Top-K with chunk minima.  The tensor-core epilogue (dist_tcgen05.cu) records the minimum of every
-// 32-column chunk of D.  K chunks whose minimum is <= tau hold K elements <= tau, so the K-th
-// smallest chunk minimum bounds the K-th smallest element, and only chunks whose minimum is <= D*
-// (typically ~K of N/32) can hold a neighbour: the kernel reads ~3 % of the matrix instead of all
-// of it.  One warp per row; the K-th smallest minimum is found by a bitwise binary search with
-// ballots (no sort), candidate chunks are read as coalesced 128-byte lines.
+// 32-column chunk of D.  K chunks whose minimum is <= tau hold K elements <= tau, so the K-th smallest of
+// ANY K-or-more chunk minima bounds the K-th smallest element.  One warp per row:
+//   pass 1  every lane streams its share of the row's chunk minima (coalesced, unrolled) and keeps its S
+//           smallest in registers (32*S >= K); tau = the K-th smallest of those 32*S values, found by a
+//           bitwise search with ballots on registers.  (The exact K-th smallest chunk minimum would be a
+//           slightly tighter bound -- ~K qualifying chunks instead of ~1.6 K -- at the price of a shared-memory
+//           copy of the row's minima and 32 passes over it.)
+//   bound   D* = the largest float whose quotient by the row maximum does not exceed tau / m.
+//   pass 2  chunk minima again (L1/L2 hits): chunks with minimum <= D* are listed, their 128-byte lines fetched
+//           eight at a time, entries <= D* become (O, column) keys, sorted, first K emitted.
+// The kernel reads N/32 minima + ~1.6 K lines per row instead of the row.
 // ---------------------------------------------------------------------------------------------
 constexpr int SELH_CAND = 256;      // candidate slots per warp
-constexpr int SELH_WPB = 4;
+constexpr int SELH_LIST = 512;      // qualifying-chunk slots per warp
+constexpr int SELH_WPB = 8;
 
 __device__ __forceinline__ void warp_bitonic_u64_sel(unsigned long long* a, int P, int lane) {
   for (int k = 2; k <= P; k <<= 1) {
@@ -252,39 +259,62 @@ __device__ __forceinline__ void warp_bitonic_u64_sel(unsigned long long* a, int 
   }
 }
 
+template <int S>
 __global__ void __launch_bounds__(SELH_WPB * 32)
 select_topk_hinted_kernel(const float* __restrict__ D, int rows, int cols, long long ld,
                           const int* __restrict__ rowmax_key, const float* __restrict__ chunk_min, int nch,
-                          int K, int* __restrict__ nbr, float* __restrict__ nbr_val, int cap) {
-  extern __shared__ __align__(16) unsigned char smem_sh[];
+                          int K, int* __restrict__ nbr, float* __restrict__ nbr_val, int cap, int list_cap) {
+  __shared__ unsigned long long cand_s[SELH_WPB][SELH_CAND];
+  __shared__ int list_s[SELH_WPB][SELH_LIST];
   const int w = threadIdx.x >> 5, lane = lane_id();
   const int row = blockIdx.x * SELH_WPB + w;
   if (row >= rows) return;
-  const size_t per_warp = (size_t)((nch + 1) & ~1) * 4 + SELH_CAND * 8;      // keeps the 64-bit slots aligned
-  uint32_t* ck = reinterpret_cast<uint32_t*>(smem_sh + w * per_warp + SELH_CAND * 8);   // chunk-min keys
-  unsigned long long* cand = reinterpret_cast<unsigned long long*>(smem_sh + w * per_warp);
+  unsigned long long* cand = cand_s[w];
+  int* list = list_s[w];
   const float* p = D + (long long)row * ld;
   const float* cm = chunk_min + (long long)row * nch;
   const float m = ordered_int2f(rowmax_key[row]);
 
-  for (int c = lane; c < nch; c += 32) ck[c] = f2key(cm[c]);
-  __syncwarp();
-  // K-th smallest chunk minimum: largest prefix t with #{key < t} < K, built bit by bit
-  uint32_t t = 0;
+  // pass 1: the S smallest chunk minima of this lane's share, ascending in keep[]
+  float keep[S];
+#pragma unroll
+  for (int s = 0; s < S; ++s) keep[s] = INFINITY;
+  {
+    int c = lane;
+    for (; c + 7 * 32 < nch; c += 8 * 32) {
+      float v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = __ldg(cm + c + u * 32);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        float x = v[u];
+#pragma unroll
+        for (int s = 0; s < S; ++s) { const float lo = fminf(keep[s], x); x = fmaxf(keep[s], x); keep[s] = lo; }
+      }
+    }
+    for (; c < nch; c += 32) {
+      float x = __ldg(cm + c);
+#pragma unroll
+      for (int s = 0; s < S; ++s) { const float lo = fminf(keep[s], x); x = fmaxf(keep[s], x); keep[s] = lo; }
+    }
+  }
+  // K-th smallest of the 32*S kept values: largest prefix t with #{key < t} < K, built bit by bit
+  uint32_t t = 0xffffffffu;                               // fewer chunks than K: every chunk is a candidate
   if (nch >= K) {
+    uint32_t kk[S];
+#pragma unroll
+    for (int s = 0; s < S; ++s) kk[s] = f2key(keep[s]);
+    t = 0;
     for (int bit = 31; bit >= 0; --bit) {
       const uint32_t trial = t | (1u << bit);
       int cnt = 0;
-      for (int c = lane; c < nch; c += 32) cnt += ck[c] < trial;
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(FULL, cnt, o);
-      if (cnt < K) t = trial;                           // fewer than K keys below trial: the K-th is >= trial
+      for (int s = 0; s < S; ++s) cnt += __popc(__ballot_sync(FULL, kk[s] < trial));
+      if (cnt < K) t = trial;                             // fewer than K keys below trial: the K-th is >= trial
     }
-  } else {
-    t = 0xffffffffu;                                    // fewer chunks than K: every chunk is a candidate
   }
   float dstar = key2f(t);
-  if (m > 0.0f && m < INFINITY && nch >= K) {
+  if (m > 0.0f && m < INFINITY && nch >= K && dstar == dstar) {
     const float tau_o = __fdiv_rn(dstar, m);
     for (int it = 0; it < 64; ++it) {
       const float x = dstar;
@@ -297,25 +327,38 @@ select_topk_hinted_kernel(const float* __restrict__ D, int rows, int cols, long 
   } else {
     dstar = INFINITY;                                   // degenerate maximum: no monotone filter, take everything
   }
-  const uint32_t dkey = f2key(dstar);
 
-  // gather candidates from the qualifying chunks
-  int cnt = 0;
+  // pass 2a: list the qualifying chunks
+  int nlist = 0;
   bool overflow = false;
-  for (int c0 = 0; c0 < nch && !overflow; c0 += 32) {
+  for (int c0 = 0; c0 < nch; c0 += 32) {
     const int c = c0 + lane;
-    unsigned q = __ballot_sync(FULL, c < nch && ck[c] <= dkey);
-    while (q) {
-      const int cc = c0 + __ffs(q) - 1;
-      q &= q - 1;
-      const int col = cc * 32 + lane;
-      float v = INFINITY;
-      if (col < cols) v = p[col];
-      const bool take = col < cols && (v <= dstar || dstar == INFINITY);
+    const bool take = c < nch && (__ldg(cm + c) <= dstar || dstar == INFINITY);
+    const unsigned b = __ballot_sync(FULL, take);
+    const int n_take = __popc(b);
+    if (nlist + n_take > list_cap) { overflow = true; break; }
+    if (take) list[nlist + __popc(b & ((1u << lane) - 1))] = c;
+    nlist += n_take;
+  }
+  __syncwarp();
+  // pass 2b: fetch their lines eight at a time, keep entries <= D*
+  int cnt = 0;
+  for (int l0 = 0; l0 < nlist && !overflow; l0 += 8) {
+    float v[8];
+    int col[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      col[u] = l0 + u < nlist ? list[l0 + u] * 32 + lane : cols;
+      v[u] = col[u] < cols ? __ldg(p + col[u]) : INFINITY;
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const bool take = col[u] < cols && (v[u] <= dstar || dstar == INFINITY);
       const unsigned bt = __ballot_sync(FULL, take);
       const int n_take = __popc(bt);
+      if (n_take == 0) continue;
       if (cnt + n_take > cap) { overflow = true; break; }
-      if (take) cand[cnt + __popc(bt & ((1u << lane) - 1))] = make_ck(v, m, col);
+      if (take) cand[cnt + __popc(bt & ((1u << lane) - 1))] = make_ck(v[u], m, col[u]);
       cnt += n_take;
     }
   }
@@ -339,7 +382,7 @@ select_topk_hinted_kernel(const float* __restrict__ D, int rows, int cols, long 
   for (int r = 0; r < K; ++r) {
     unsigned long long mine = ~0ull;
     for (int cc = 0; cc < nch; ++cc) {
-      if (ck[cc] > dkey) continue;
+      if (!(__ldg(cm + cc) <= dstar || dstar == INFINITY)) continue;
       const int col = cc * 32 + lane;
       if (col < cols) {
         const unsigned long long k0 = make_ck(p[col], m, col);
@@ -362,14 +405,18 @@ int launch_select_topk_hinted(const float* D, int rows, int cols, long long ld, 
   REID_REQUIRE(K >= 1 && K <= 256, "select_topk: K=%d outside [1,256]", K);
   REID_REQUIRE(cols >= K, "select_topk: row length %d is shorter than K=%d", cols, K);
   const int nch = cdiv(cols, 32);
-  const size_t smem = SELH_WPB * ((size_t)((nch + 1) & ~1) * 4 + SELH_CAND * 8);
-  if (smem > 200 * 1024)                                // gallery too wide for the per-warp key table
-    return launch_select_topk(D, rows, cols, ld, rowmax_key, K, nbr, nbr_val, cap_override, s);
   const int cap = cap_override > 0 ? (cap_override < SELH_CAND ? cap_override : SELH_CAND) : SELH_CAND;
+  const int list_cap = cap_override > 0 ? (cap_override < SELH_LIST ? cap_override : SELH_LIST) : SELH_LIST;
   REID_REQUIRE(cap >= K || cap_override > 0, "select_topk: K=%d exceeds the candidate buffer", K);
-  REID_CUDA(cudaFuncSetAttribute(select_topk_hinted_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  select_topk_hinted_kernel<<<cdiv(rows, SELH_WPB), SELH_WPB * 32, smem, s>>>(D, rows, cols, ld, rowmax_key,
-                                                                            chunk_min, nch, K, nbr, nbr_val, cap);
+  const int grid = cdiv(rows, SELH_WPB), threads = SELH_WPB * 32;
+#define REID_SELH(SS)                                                                                          \
+  select_topk_hinted_kernel<SS><<<grid, threads, 0, s>>>(D, rows, cols, ld, rowmax_key, chunk_min, nch, K, nbr, \
+                                                         nbr_val, cap, list_cap)
+  if (K <= 32) REID_SELH(1);
+  else if (K <= 64) REID_SELH(2);
+  else if (K <= 128) REID_SELH(4);
+  else REID_SELH(8);
+#undef REID_SELH
   return check_launch("select_topk_hinted_kernel");
 }
 

@@ -310,32 +310,70 @@ class Engine:
         colptr = self._empty((N + 1,), torch.int64)
         _lib.call("reid_exclusive_scan", _ptr(colcnt), N, _ptr(colptr), _stream())
         cursor = self._zeros((N,), torch.int32)
-        csc_row = self._empty((max(nnz_bound, 1),), torch.int32)
-        csc_val = self._empty((max(nnz_bound, 1),), torch.float16)
+        csc_ent = self._empty((max(nnz_bound, 1),), torch.int64)     # row | float16 bits << 32
         _lib.call("reid_csc_fill", _ptr(Qc), _ptr(Qv), _ptr(qoff), _ptr(Qn), N, _ptr(colptr), _ptr(cursor),
-                  _ptr(csc_row), _ptr(csc_val), _stream())
-        return colptr, csc_row, csc_val
+                  _ptr(csc_ent), _stream())
+        return colptr, csc_ent
 
     # ------------------------------------------------------------------ K9 + K10
     def jaccard_mix(self, Qc, Qv, qoff, Qn, csc, D, key, q: int, N: int, lam: float, nq_local: int, q0=0,
                     q_stride=1, want_jaccard=False):
-        colptr, csc_row, csc_val = csc
+        colptr, csc_ent = csc
         g = N - q
         ldf = self.pitch(g)
         out = self._empty((nq_local, ldf), torch.float32)
         J = self._empty((nq_local, N), torch.float16) if want_jaccard else None
         c1 = float(np.float16(1 - lam))            # fp16 array * python float: scalar cast to fp16 first
         c2 = float(np.float32(lam))                # fp32 array * python float
-        _lib.call("reid_jaccard_mix", _ptr(Qc), _ptr(Qv), _ptr(qoff), _ptr(Qn), _ptr(colptr), _ptr(csc_row),
-                  _ptr(csc_val), _ptr(D), D.stride(0), _ptr(key), q0, q_stride, nq_local, q, N, c1, c2, _ptr(out),
+        _lib.call("reid_jaccard_mix", _ptr(Qc), _ptr(Qv), _ptr(qoff), _ptr(Qn), _ptr(colptr), _ptr(csc_ent),
+                  _ptr(D), D.stride(0), _ptr(key), q0, q_stride, nq_local, q, N, c1, c2, _ptr(out),
                   ldf, _ptr(J), N, _stream())
         return (out, J) if want_jaccard else out
 
+    # ------------------------------------------------------------------ identity index + fused K9–K12
+    def pid_index(self, g_pids: torch.Tensor):
+        """Groups the gallery columns by pid (evaluate.py:43, :53-55) for reid_jaccard_score."""
+        g = g_pids.shape[0]
+        T = self.lib.reid_pid_index_slots(g)
+        keys = self._empty((T,), torch.int64)
+        cnt = self._empty((T + 1,), torch.int32)
+        cursor = self._empty((T + 1,), torch.int32)
+        start = self._empty((T + 2,), torch.int64)
+        lst = self._empty((max(g, 1),), torch.int32)
+        _lib.call("reid_pid_index", _ptr(g_pids), g, T, _ptr(keys), _ptr(cnt), _ptr(start), _ptr(cursor), _ptr(lst),
+                  _stream())
+        return keys, start, lst, T
+
+    def jaccard_score(self, Qc, Qv, qoff, Qn, csc, D, key, q: int, N: int, lam: float, nq_local: int, q0, q_stride,
+                      ids, max_rank: int, want_final: bool):
+        """Fused K9–K12 for this rank's queries.  ids = (q_pids_local, g_pids, q_cams_local, g_cams).
+        Returns (final or None, (cmc, mAP, n_valid, ap_all, first_all))."""
+        colptr, csc_ent = csc
+        q_pids, g_pids, q_cams, g_cams = ids
+        g = N - q
+        out, ldf = None, 0
+        if want_final:
+            ldf = self.pitch(g)
+            out = self._empty((nq_local, ldf), torch.float32)
+        keys, start, lst, T = self.pid_index(g_pids)
+        c1 = float(np.float16(1 - lam))
+        c2 = float(np.float32(lam))
+
+        def launch(ap, first, hist, nvalid):
+            _lib.call("reid_jaccard_score", _ptr(Qc), _ptr(Qv), _ptr(qoff), _ptr(Qn), _ptr(colptr), _ptr(csc_ent),
+                      _ptr(D), D.stride(0), _ptr(key), q0, q_stride, nq_local, q, N, c1, c2, _ptr(out),
+                      ldf, _ptr(q_pids), _ptr(q_cams), _ptr(g_cams), _ptr(keys), _ptr(start), _ptr(lst), T, max_rank,
+                      _ptr(ap), _ptr(first), _ptr(hist), _ptr(nvalid), _stream())
+        return out, self._score_common(launch, nq_local, max_rank, q, span="jaccard_score")
+
     # ------------------------------------------------------------------ K4–K10 from a distance panel
     def rerank_from_panel(self, D: torch.Tensor, key: torch.Tensor, q: int, N: int, k1: int, k2: int, lam: float,
-                          detail: dict | None = None, chunk_min: torch.Tensor | None = None) -> torch.Tensor:
+                          detail: dict | None = None, chunk_min: torch.Tensor | None = None,
+                          score: tuple | None = None, want_final: bool = True):
         """D: this rank's panel [n_local, pitch(N)] (row l = probe rank + l*world), key: its row
-        maxima.  Returns final[nq_local, pitch(g)] for this rank's queries (use [:, :g])."""
+        maxima.  Returns final[nq_local, pitch(g)] for this rank's queries (use [:, :g]).
+        With score = ((q_pids_local, g_pids, q_cams_local, g_cams), max_rank) the last stage is the
+        fused Jaccard + mix + CMC/mAP kernel and the return value is (final or None, score results)."""
         cm = self.comm
         r, P = cm.rank, cm.world
         nloc = D.shape[0]
@@ -373,6 +411,11 @@ class Engine:
         with self.span("csc"):
             csc = self.inverted_index(Qc, Qv, qoff, Qn, N, nnz_bound)
         nq_local = cm.local_count(q)
+        if score is not None:
+            assert detail is None
+            ids, max_rank = score
+            return self.jaccard_score(Qc, Qv, qoff, Qn, csc, D, key, q, N, lam, nq_local, r, P, ids, max_rank,
+                                      want_final)
         with self.span("jaccard_mix"):
             res = self.jaccard_mix(Qc, Qv, qoff, Qn, csc, D, key, q, N, lam, nq_local, r, P,
                                    want_jaccard=detail is not None)
@@ -383,7 +426,7 @@ class Engine:
         return res
 
     def rerank_features(self, feats: torch.Tensor, q: int, k1: int, k2: int, lam: float, normalize: bool,
-                        detail: dict | None = None) -> torch.Tensor:
+                        detail: dict | None = None, score: tuple | None = None, want_final: bool = True):
         """feats: [N, d] float32 on the device, queries first (reranking.py:29-44 then the rest)."""
         cm = self.comm
         N = feats.shape[0]
@@ -397,7 +440,18 @@ class Engine:
                 D, key, cmin = self.dist(mine, allf, METRIC_SQEUCLIDEAN, want_rowmax=True, want_chunk_min=True)
         if detail is not None:
             detail.update(D=D, key=key)
-        return self.rerank_from_panel(D, key, q, N, k1, k2, lam, detail, chunk_min=cmin)
+        return self.rerank_from_panel(D, key, q, N, k1, k2, lam, detail, chunk_min=cmin, score=score,
+                                      want_final=want_final)
+
+    def evaluate_reranked(self, feats: torch.Tensor, q: int, pids: torch.Tensor, cams: torch.Tensor, k1: int, k2: int,
+                          lam: float, normalize: bool, max_rank: int = 50):
+        """The evaluator's hot path end to end (evaluate.py:110-132 with reranking=True): features and ids of
+        all N samples (queries first) -> (cmc, mAP, n_valid, ap, first_hit); the q x g matrix is never written."""
+        cm = self.comm
+        mine = slice(cm.rank, q, cm.world)
+        ids = (pids[:q][mine].contiguous(), pids[q:].contiguous(), cams[:q][mine].contiguous(), cams[q:].contiguous())
+        _, res = self.rerank_features(feats, q, k1, k2, lam, normalize, score=(ids, max_rank), want_final=False)
+        return res
 
     # ------------------------------------------------------------------ K11 + K12
     def rank_rows(self, dist: torch.Tensor, g: int) -> torch.Tensor:
@@ -410,13 +464,13 @@ class Engine:
                   _ptr(ranked), _stream())
         return ranked
 
-    def _score_common(self, launch, nq, max_rank, q_total):
+    def _score_common(self, launch, nq, max_rank, q_total, span="score"):
         cm = self.comm
         ap = self._empty((nq,), torch.float64)
         first = self._empty((nq,), torch.int32)
         hist = self._zeros((max_rank,), torch.int32)
         nvalid = self._zeros((1,), torch.int32)
-        with self.span("score"):
+        with self.span(span):
             launch(ap, first, hist, nvalid)
         q_all = nq if q_total is None else q_total
         ap_all = cm.gather_rows(ap, q_all)

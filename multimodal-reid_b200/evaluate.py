@@ -114,7 +114,16 @@ class R1_mAP_eval():
         if self.reranking:
             print('=> Enter reranking')
             k1, k2, lam = self.rerank_params                                          # evaluate.py:127
-            dist = eng.rerank_features(feats, q, k1, k2, lam, normalize=self.feat_norm)
+            # evaluate.py:132 does not forward self.max_rank: always 50
+            max_rank = 50
+            if g < max_rank:
+                max_rank = g
+                print("Note: number of gallery samples is quite small, got {}".format(g))
+            cmc, mAP, nvalid, _, _ = eng.evaluate_reranked(feats, q, pids, camids, k1, k2, lam, self.feat_norm, max_rank)
+            assert int(nvalid.item()) > 0, "Error: all query identities do not appear in gallery"
+            cmc, mAP = cmc.cpu().numpy(), np.float64(mAP.item())
+            print("Rank@{:d}:{:.1%}, Rank@{:d}:{:.1%}, Rank@{:d}:{:.1%}, mAP:{:.1%}".format(1, cmc[0], 5, cmc[4], 10, cmc[9], mAP))
+            return cmc, mAP
         else:
             print('=> Computing DistMat with euclidean_distance')
             allf = eng.prepare(feats, self.feat_norm)

@@ -132,7 +132,9 @@ def test_rerank_stages_bit_exact(eng, engine_mod, synth, oracle, name, k1, k2, s
         np.testing.assert_array_equal(Qv[a:a + n].view(np.uint16), ref["Qv"][i].view(np.uint16),
                                       err_msg=f"Qv[{i}]")
     # K8: inverted index (as sets per column; order inside a column is free)
-    colptr, crow, cval = (t.cpu().numpy() for t in det["csc"])
+    colptr, cent = (t.cpu().numpy() for t in det["csc"])
+    crow = (cent & 0xffffffff).astype(np.int32)
+    cval = ((cent >> 32) & 0xffff).astype(np.uint16).view(np.float16)
     rptr, rrows, rvals = ref["inv"]
     np.testing.assert_array_equal(colptr, rptr)
     for c in range(0, N, max(1, N // 50)):
@@ -165,6 +167,50 @@ def test_rerank_stages_bit_exact(eng, engine_mod, synth, oracle, name, k1, k2, s
     np.testing.assert_allclose(ap[valid], aps_o[valid], rtol=0, atol=1e-14)
     assert np.all(ap[~valid] == -1.0)
     assert int(nvalid.item()) == int(valid.sum())
+
+    # fused K9-K12 (the evaluator's path): same matrix bits when asked for it, same metrics either way
+    mr = min(50, sh.g)
+    for want_final in (True, False):
+        fin2, res = eng.rerank_from_panel(D, key, q, N, k1, k2, 0.3, score=(ids, mr), want_final=want_final)
+        if want_final:
+            np.testing.assert_array_equal(fin2[:, : sh.g].cpu().numpy().view(np.uint32), ref["final"].view(np.uint32))
+        else:
+            assert fin2 is None
+        cmc2, map2, nv2, ap2, first2 = res
+        assert torch.equal(cmc2, cmc) and torch.equal(first2, first) and torch.equal(nv2, nvalid), want_final
+        np.testing.assert_allclose(ap2.cpu().numpy(), ap, rtol=0, atol=1e-14)
+        assert abs(map2.item() - map_o) < 1e-12
+
+
+def test_fused_score_many_matches_junk_and_odd_ids(eng, engine_mod, synth, oracle):
+    """Identity groups larger than one shared-memory slice (512), camera junk, absent identities, negative and
+    INT64_MIN ids: the fused Jaccard+score kernel must agree with the explicit ranking on its own matrix."""
+    sh, X, *_ = _features(synth, "mid", 5, eng.device)
+    N, q, g = sh.q + sh.g, sh.q, sh.g
+    rng = np.random.default_rng(11)
+    odd = np.array([-(2 ** 63), -7, 0, 3, 2 ** 40], dtype=np.int64)
+    g_pids = odd[rng.integers(0, 4, g)]                # ~1075 gallery entries per identity; 2**40 never appears
+    q_pids = odd[rng.integers(0, 5, q)]                # a fifth of the queries have no match at all
+    g_cams = rng.integers(0, 3, g).astype(np.int64)
+    q_cams = rng.integers(0, 3, q).astype(np.int64)
+    dev = eng.device
+    ids = tuple(torch.from_numpy(a).to(dev) for a in (q_pids, g_pids, q_cams, g_cams))
+    D, key = _panel(eng, engine_mod, X)
+    for k1, k2 in ((20, 6), (6, 1)):
+        final = eng.rerank_from_panel(D, key, q, N, k1, k2, 0.3)
+        want = eng.evaluate_dist(final, g, *ids, 50, materialize_ranking=True)
+        want_cmc, want_map, want_ap, want_first = oracle.cmc_map(final[:, :g].cpu().numpy(), q_pids, g_pids, q_cams,
+                                                                 g_cams, detail=True)
+        for want_final in (False, True):
+            fin2, got = eng.rerank_from_panel(D, key, q, N, k1, k2, 0.3, score=(ids, 50), want_final=want_final)
+            if want_final:
+                assert torch.equal(fin2[:, :g], final[:, :g])
+            assert torch.equal(got[0], want[0]) and torch.equal(got[2], want[2]) and torch.equal(got[4], want[4])
+            np.testing.assert_allclose(got[3].cpu().numpy(), want[3].cpu().numpy(), rtol=0, atol=1e-13)
+            np.testing.assert_array_equal(got[0].cpu().numpy(), want_cmc)
+            np.testing.assert_array_equal(got[4].cpu().numpy(), want_first)
+            assert abs(got[1].item() - want_map) < 1e-12
+            assert int(got[2].item()) == int((~np.isnan(want_ap)).sum()) < q
 
 
 def test_select_fallback_and_ties(eng, engine_mod, oracle):
