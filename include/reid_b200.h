@@ -146,6 +146,13 @@ REID_API int reid_csc_fill(const int32_t* Qc, const reid_half* Qv, const int64_t
                   int N, const int64_t* colptr, int32_t* cursor /* zeroed, N */, uint64_t* csc_ent,
                   void* stream);
 
+/* Workspace of the sparse Jaccard path (reid_jaccard_mix / reid_jaccard_score with ws != NULL): one packed
+ * overlap record per query -- bitmap of the touched probes, prefix popcounts, up to `cap` float16 overlaps --
+ * plus the list of queries that touch more than `cap` probes (those are finished by the dense kernel, one
+ * 2N-byte shared-memory row per query).  Returns 0 when the sparse path cannot be used for this N / cap;
+ * pass ws = NULL then (dense path for every query). */
+REID_API int64_t reid_jaccard_ws_bytes(int nq, int N, int cap);
+
 /* K9 + K10  reranking.py:84-100.  For the query window (global probe q0 + l*q_stride, l < nq):
  * float16 Jaccard chain through the inverted index and
  *   out[l, g - q] = fp32(fp16(J * fp16(c1))) + (D[l, g] / rowmax[l]) * c2   for g in [q, N)
@@ -155,7 +162,7 @@ REID_API int reid_jaccard_mix(const int32_t* Qc, const reid_half* Qv, const int6
                      const int64_t* colptr, const uint64_t* csc_ent,
                      const float* D, int64_t ld, const int32_t* rowmax_key, int q0, int q_stride,
                      int nq, int q, int N, float c1, float c2, float* out, int64_t ld_out,
-                     reid_half* jaccard_out, int64_t ld_j, void* stream);
+                     reid_half* jaccard_out, int64_t ld_j, void* ws, int64_t ws_bytes, int cap, void* stream);
 
 /* Identity index for the fused scorer  evaluate.py:43, :53-55.  Groups the gallery columns by pid (open-addressing
  * hash on the 64-bit id, then a counting sort by slot) so that a query finds the handful of gallery entries
@@ -179,7 +186,7 @@ REID_API int reid_jaccard_score(const int32_t* Qc, const reid_half* Qv, const in
                        const int64_t* q_pid, const int64_t* q_cam, const int64_t* g_cam,
                        const uint64_t* pid_keys, const int64_t* pid_start, const int32_t* pid_list, int pid_T,
                        int max_rank, double* ap, int32_t* first_hit, int32_t* cmc_hist, int32_t* n_valid,
-                       void* stream);
+                       void* ws, int64_t ws_bytes, int cap, void* stream);
 
 /* K11  evaluate.py:40.  Stable full ranking of every row (ascending distance, ties by column).
  * Workspace: keyA, keyB, idxA of rows*g 32-bit words each. */

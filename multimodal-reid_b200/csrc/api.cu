@@ -263,17 +263,21 @@ int reid_csc_fill(const int32_t* Qc, const reid_half* Qv, const int64_t* qoff, c
                          reinterpret_cast<unsigned long long*>(csc_ent), S(stream));
 }
 
+int64_t reid_jaccard_ws_bytes(int nq, int N, int cap) {
+  return (int64_t)launch_jaccard_ws_bytes(nq, N, cap);
+}
+
 int reid_jaccard_mix(const int32_t* Qc, const reid_half* Qv, const int64_t* qoff, const int32_t* Qn,
                      const int64_t* colptr, const uint64_t* csc_ent, const float* D,
                      int64_t ld, const int32_t* rowmax_key, int q0, int q_stride, int nq, int q, int N,
                      float c1, float c2, float* out, int64_t ld_out, reid_half* jaccard_out, int64_t ld_j,
-                     void* stream) {
+                     void* ws, int64_t ws_bytes, int cap, void* stream) {
   ENTER();
   REID_REQUIRE(q >= 0 && q <= N && q_stride >= 1, "jaccard_mix: bad shape q=%d N=%d", q, N);
   return launch_jaccard_mix(Qc, HC(Qv), reinterpret_cast<const long long*>(qoff), Qn,
                             reinterpret_cast<const long long*>(colptr),
-                            reinterpret_cast<const unsigned long long*>(csc_ent), D, ld, rowmax_key, q0, q_stride, nq, q, N, c1, c2, out, ld_out, H(jaccard_out), ld_j,
-                            S(stream));
+                            reinterpret_cast<const unsigned long long*>(csc_ent), D, ld, rowmax_key, q0, q_stride, nq,
+                            q, N, c1, c2, out, ld_out, H(jaccard_out), ld_j, ws, ws_bytes, cap, S(stream));
 }
 
 int reid_pid_index_slots(int g) {
@@ -297,7 +301,7 @@ int reid_jaccard_score(const int32_t* Qc, const reid_half* Qv, const int64_t* qo
                        float c2, float* out, int64_t ld_out, const int64_t* q_pid, const int64_t* q_cam,
                        const int64_t* g_cam, const uint64_t* pid_keys, const int64_t* pid_start,
                        const int32_t* pid_list, int pid_T, int max_rank, double* ap, int32_t* first_hit,
-                       int32_t* cmc_hist, int32_t* n_valid, void* stream) {
+                       int32_t* cmc_hist, int32_t* n_valid, void* ws, int64_t ws_bytes, int cap, void* stream) {
   ENTER();
   REID_REQUIRE(q >= 0 && q <= N && q_stride >= 1, "jaccard_score: bad shape q=%d N=%d", q, N);
   REID_REQUIRE(ap != nullptr, "jaccard_score: ap is NULL (use reid_jaccard_mix for the matrix alone)");
@@ -309,7 +313,7 @@ int reid_jaccard_score(const int32_t* Qc, const reid_half* Qv, const int64_t* qo
                               reinterpret_cast<const long long*>(g_cam),
                               reinterpret_cast<const unsigned long long*>(pid_keys),
                               reinterpret_cast<const long long*>(pid_start), pid_list, pid_T, max_rank, ap,
-                              first_hit, cmc_hist, n_valid, S(stream));
+                              first_hit, cmc_hist, n_valid, ws, ws_bytes, cap, S(stream));
 }
 
 int reid_rank_rows(const float* dist, int rows, int g, int64_t ld, uint32_t* keyA, uint32_t* keyB,

@@ -18,8 +18,7 @@
 //            Junk entries are taken out of the bins afterwards.  With `out` the row is also written.
 //   phase 4  prefix sums over the bins: kept rank and match count of every match -> AP (float64),
 //            first-hit rank -> CMC histogram; identical to ranking the row explicitly.
-#include "common.cuh"
-#include "np_exact.cuh"
+#include "jaccard_common.cuh"
 #include "kernels.h"
 
 namespace reid {
@@ -27,25 +26,6 @@ namespace reid {
 // ---------------------------------------------------------------------------------------------
 // identity index: open-addressing hash table pid -> slot, counting sort of the gallery by slot
 // ---------------------------------------------------------------------------------------------
-constexpr unsigned long long PID_EMPTY = 0x8000000000000000ull;    // INT64_MIN: handled by slot T
-
-__device__ __forceinline__ unsigned pid_hash(unsigned long long x) {
-  x ^= x >> 33; x *= 0xff51afd7ed558ccdull; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ull; x ^= x >> 33;
-  return (unsigned)x;
-}
-__device__ __forceinline__ int pid_find(const unsigned long long* __restrict__ keys, int T, long long pid) {
-  const unsigned long long k = (unsigned long long)pid;
-  if (k == PID_EMPTY) return T;
-  unsigned h = pid_hash(k) & (unsigned)(T - 1);
-  for (int probe = 0; probe < T; ++probe) {
-    const unsigned long long cur = keys[h];
-    if (cur == k) return (int)h;
-    if (cur == PID_EMPTY) return -1;
-    h = (h + 1) & (unsigned)(T - 1);
-  }
-  return -1;
-}
-
 __global__ void pid_init_kernel(unsigned long long* keys, int* cnt, int* cursor, int T) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i <= T) { cnt[i] = 0; cursor[i] = 0; if (i < T) keys[i] = PID_EMPTY; }
@@ -121,84 +101,6 @@ struct JsLayout {
   }
 };
 
-struct ScoreArgs {
-  const long long* q_pid;            // [nq] this launch's queries
-  const long long* q_cam;            // [nq]
-  const long long* g_cam;            // [g]
-  const unsigned long long* keys;    // identity index (launch_pid_index)
-  const long long* start;
-  const int* list;
-  int T;
-  int max_rank;
-  double* ap;                        // [nq]; NULL disables scoring
-  int* first_hit;                    // [nq]
-  int* cmc_hist;                     // [max_rank]
-  int* n_valid;                      // [1]
-};
-
-// final[i, g] = fp32(fp16(J * fp16(1 - lambda))) + fp32(O * fp32(lambda))          (reranking.py:93-95)
-__device__ __forceinline__ float final_value(__half tg, float d, float m, float c1h, float c2) {
-  const float ol = __fmul_rn(__fdiv_rn(d, m), c2);
-  if (__half_as_ushort(tg) == 0) return __fadd_rn(c1h, ol);       // J = 1 exactly, fp16(1 * c1h) = c1h
-  const __half J = jaccard_from_overlap(tg);
-  const __half Jl = __float2half_rn(__fmul_rn(__half2float(J), c1h));
-  return __fadd_rn(__half2float(Jl), ol);
-}
-__device__ __forceinline__ unsigned long long final_key(float f, int col) {
-  return ((unsigned long long)f2key(__fadd_rn(f, 0.0f)) << 32) | (unsigned)col;
-}
-__device__ __forceinline__ int lower_bound_u64(const unsigned long long* a, int n, unsigned long long key) {
-  int lo = 0, hi = n;                                              // #{a[i] < key}
-  while (lo < hi) {
-    const int mid = (lo + hi) >> 1;
-    if (a[mid] < key) lo = mid + 1; else hi = mid;
-  }
-  return lo;
-}
-// hv[bin] += 1 with the lanes that hit the same bin combined first
-__device__ __forceinline__ void bin_add(int* hv, int bin) {
-  const unsigned act = __activemask();
-  const unsigned peers = __match_any_sync(act, bin);
-  if ((int)(threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(hv + bin, __popc(peers));
-}
-// final0(x) = final_value(t = 0, x) is monotone non-decreasing in x for m > 0, c2 > 0 (every step is a
-// monotone rounding).  thr(f, strict) = the largest float x, in the total order of f2ordered_int, with
-// final0(x) <= f (or < f when strict); -inf if there is none.
-__device__ __forceinline__ bool final0_pred(int x, float f, bool strict, float m, float c1h, float c2) {
-  const float v = final_value(__ushort_as_half(0), ordered_int2f(x), m, c1h, c2);
-  return strict ? v < f : v <= f;
-}
-// One warp, one threshold: the algebraic inverse (f - c1h) / c2 * m lands within a few ulps, so the 32 lanes
-// test 32 consecutive floats around it at once; only if the flip is not inside that window does lane 0 bisect.
-__device__ __noinline__ float final0_threshold_warp(float f, bool strict, float m, float c1h, float c2) {
-  const int lane = threadIdx.x & 31;
-  const int lo0 = f2ordered_int(-INFINITY), hi0 = f2ordered_int(INFINITY);
-  const float est = (f - c1h) / c2 * m;
-  int x0 = (est == est) ? f2ordered_int(fminf(fmaxf(est, -1e30f), 1e30f)) : 0;
-  const unsigned okm = __ballot_sync(FULL, final0_pred(x0 - 16 + lane, f, strict, m, c1h, c2));
-  if ((okm & 1u) && !(okm >> 31) && ((okm + 1) & okm) == 0)       // 1...10...0: the flip is inside the window
-    return ordered_int2f(x0 - 16 + __popc(okm) - 1);
-  float r = -INFINITY;
-  if (lane == 0 && final0_pred(lo0, f, strict, m, c1h, c2)) {
-    int lo = lo0, hi = hi0;
-    while (lo < hi) {
-      const int mid = (int)(((long long)lo + (long long)hi + 1) >> 1);
-      if (final0_pred(mid, f, strict, m, c1h, c2)) lo = mid; else hi = mid - 1;
-    }
-    r = ordered_int2f(lo);
-  }
-  return __shfl_sync(FULL, r, 0);
-}
-
-__device__ __forceinline__ void cp_async8(void* smem_dst, const void* gsrc) {
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)),
-               "l"(gsrc)
-               : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-
 #ifdef REID_JS_PROFILE
 __device__ unsigned long long g_js_prof[8];
 #define JS_TICK(i) do { __syncthreads(); if (threadIdx.x == 0) { long long _n = clock64(); atomicAdd(&g_js_prof[i], (unsigned long long)(_n - _t0)); _t0 = _n; } } while (0)
@@ -243,14 +145,14 @@ __device__ __noinline__ void js_drain_zero(const unsigned long long* qz, int cnt
 }
 
 template <int T>
-__global__ void __launch_bounds__(T)
-jaccard_score_kernel(const int* __restrict__ Qc, const __half* __restrict__ Qv,
-                     const long long* __restrict__ qoff, const int* __restrict__ Qn,
-                     const long long* __restrict__ colptr, const unsigned long long* __restrict__ csc_ent,
-                     const float* __restrict__ D, long long ld,
-                     const int* __restrict__ rowmax_key, int q0, int q_stride, int q, int N, int Npad, float c1,
-                     float c2, float* __restrict__ out, long long ld_out,
-                     __half* __restrict__ jaccard_out, long long ld_j, ScoreArgs sc) {
+__device__ __forceinline__ void
+js_dense_query(const int qi, const int* __restrict__ Qc, const __half* __restrict__ Qv,
+               const long long* __restrict__ qoff, const int* __restrict__ Qn,
+               const long long* __restrict__ colptr, const unsigned long long* __restrict__ csc_ent,
+               const float* __restrict__ D, long long ld,
+               const int* __restrict__ rowmax_key, int q0, int q_stride, int q, int N, int Npad, float c1,
+               float c2, float* __restrict__ out, long long ld_out,
+               __half* __restrict__ jaccard_out, long long ld_j, const ScoreArgs& sc) {
   extern __shared__ __align__(16) unsigned char smem_j[];
   __half* t = reinterpret_cast<__half*>(smem_j);
   unsigned char* aux = smem_j + (((size_t)Npad * 2 + 15) & ~(size_t)15);
@@ -268,7 +170,7 @@ jaccard_score_kernel(const int* __restrict__ Qc, const __half* __restrict__ Qv,
 
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   unsigned long long* wq = reinterpret_cast<unsigned long long*>(aux + JsLayout::queue) + w * 2 * JS_QSLOTS;
-  const int qi = blockIdx.x;            // local query index (D / rowmax / out rows)
+  // qi: local query index (D / rowmax / out rows)
   const long long row = q0 + (long long)qi * q_stride;   // global probe index (V_qe row)
 #ifdef REID_JS_PROFILE
   long long _t0 = clock64();
@@ -582,6 +484,7 @@ jaccard_score_kernel(const int* __restrict__ Qc, const __half* __restrict__ Qv,
             const unsigned excl = incl - mine;
             const int totA = (int)(tot & 0xffffu), totZ = (int)(tot >> 16);
             if (totA) {
+              if (na + totA > JS_QSLOTS && na > 0) { js_drain_overlap(qa, na, t, m, c1h, c2, q, mk, P, maxkey, hv); na = 0; }       // make room: partial pass
               if (na + totA <= JS_QSLOTS) {
                 int pos = na + (int)(excl & 0xffffu);
 #pragma unroll
@@ -605,6 +508,7 @@ jaccard_score_kernel(const int* __restrict__ Qc, const __half* __restrict__ Qv,
               }
             }
             if (totZ) {
+              if (nzq + totZ > JS_QSLOTS && nzq > 0) { js_drain_zero(qz, nzq, thrA, thrB, mk, P, hv); nzq = 0; }
               if (nzq + totZ <= JS_QSLOTS) {
                 int pos = nzq + (int)(excl >> 16);
 #pragma unroll
@@ -690,6 +594,41 @@ jaccard_score_kernel(const int* __restrict__ Qc, const __half* __restrict__ Qv,
   }
 }
 
+// One CTA per query (over_list == NULL), or a persistent grid over the queries the sparse path handed back.
+template <int T>
+__global__ void __launch_bounds__(T)
+jaccard_score_kernel(const int* __restrict__ Qc, const __half* __restrict__ Qv,
+                     const long long* __restrict__ qoff, const int* __restrict__ Qn,
+                     const long long* __restrict__ colptr, const unsigned long long* __restrict__ csc_ent,
+                     const float* __restrict__ D, long long ld,
+                     const int* __restrict__ rowmax_key, int q0, int q_stride, int q, int N, int Npad, float c1,
+                     float c2, float* __restrict__ out, long long ld_out,
+                     __half* __restrict__ jaccard_out, long long ld_j, ScoreArgs sc,
+                     const int* __restrict__ over_list, const int* __restrict__ over_n) {
+  if (over_list == nullptr) {
+    js_dense_query<T>(blockIdx.x, Qc, Qv, qoff, Qn, colptr, csc_ent, D, ld, rowmax_key, q0, q_stride, q, N, Npad, c1, c2,
+                      out, ld_out, jaccard_out, ld_j, sc);
+    return;
+  }
+  const int n = *over_n;
+  for (int i = blockIdx.x; i < n; i += gridDim.x) {
+    js_dense_query<T>(over_list[i], Qc, Qv, qoff, Qn, colptr, csc_ent, D, ld, rowmax_key, q0, q_stride, q, N, Npad, c1,
+                      c2, out, ld_out, jaccard_out, ld_j, sc);
+    __syncthreads();
+  }
+}
+
+// sparse path (jaccard_sparse.cu)
+long long jaccard_sparse_ws_bytes(int nq, int N, int cap);
+bool jaccard_sparse_fits(int N, int cap);
+int launch_jaccard_sparse(const int* Qc, const __half* Qv, const long long* qoff, const int* Qn,
+                          const long long* colptr, const unsigned long long* csc_ent, const float* D, long long ld,
+                          const int* rowmax_key, int q0, int q_stride, int nq_local, int q, int N, float c1, float c2,
+                          float* out, long long ld_out, const ScoreArgs& sc, void* ws, int cap, int** over_list,
+                          int** over_n, cudaStream_t s);
+
+// ws != NULL (ws_bytes >= jaccard_sparse_ws_bytes) selects the sparse path: per-query packed overlap records, with
+// the dense kernel below run afterwards as a persistent grid over the queries that did not fit `cap`.
 int launch_jaccard_score(const int* Qc, const __half* Qv, const long long* qoff, const int* Qn,
                          const long long* colptr, const unsigned long long* csc_ent, const float* D,
                          long long ld, const int* rowmax_key, int q0, int q_stride, int nq_local, int q, int N,
@@ -697,7 +636,7 @@ int launch_jaccard_score(const int* Qc, const __half* Qv, const long long* qoff,
                          const long long* q_pid, const long long* q_cam, const long long* g_cam,
                          const unsigned long long* pid_keys, const long long* pid_start, const int* pid_list,
                          int pid_T, int max_rank, double* ap, int* first_hit, int* cmc_hist, int* n_valid,
-                         cudaStream_t s) {
+                         void* ws, long long ws_bytes, int cap, cudaStream_t s) {
   if (nq_local == 0) return REID_OK;
   const int Npad = (int)round_up(N, 8);
   const int threads = N <= 32768 ? 256 : 512;
@@ -714,18 +653,34 @@ int launch_jaccard_score(const int* Qc, const __half* Qv, const long long* qoff,
                  "jaccard_score: scoring needs the id vectors, the identity index and all outputs");
     REID_REQUIRE(max_rank >= 1 && max_rank <= N - q, "jaccard_score: max_rank=%d outside [1, g=%d]", max_rank, N - q);
   }
+  int* over_list = nullptr;
+  int* over_n = nullptr;
+  int grid = nq_local;
+  if (ws != nullptr && jaccard_out == nullptr) {
+    REID_REQUIRE(jaccard_sparse_fits(N, cap), "jaccard: sparse capacity %d does not fit (N=%d)", cap, N);
+    REID_REQUIRE(ws_bytes >= jaccard_sparse_ws_bytes(nq_local, N, cap),
+                 "jaccard: workspace of %lld B is smaller than reid_jaccard_ws_bytes() = %lld B", ws_bytes,
+                 jaccard_sparse_ws_bytes(nq_local, N, cap));
+    const int rc = launch_jaccard_sparse(Qc, Qv, qoff, Qn, colptr, csc_ent, D, ld, rowmax_key, q0, q_stride, nq_local, q,
+                                         N, c1, c2, out, ld_out, sc, ws, cap, &over_list, &over_n, s);
+    if (rc) return rc;
+    int dev = 0, sms = 0;
+    REID_CUDA(cudaGetDevice(&dev));
+    REID_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    grid = nq_local < 2 * sms ? nq_local : 2 * sms;
+  }
   if (N <= 32768) {
     REID_CUDA(cudaFuncSetAttribute(jaccard_score_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    (int)smem));
-    jaccard_score_kernel<256><<<nq_local, 256, smem, s>>>(Qc, Qv, qoff, Qn, colptr, csc_ent, D, ld,
-                                                          rowmax_key, q0, q_stride, q, N, Npad, c1, c2, out, ld_out,
-                                                          jaccard_out, ld_j, sc);
+    jaccard_score_kernel<256><<<grid, 256, smem, s>>>(Qc, Qv, qoff, Qn, colptr, csc_ent, D, ld,
+                                                      rowmax_key, q0, q_stride, q, N, Npad, c1, c2, out, ld_out,
+                                                      jaccard_out, ld_j, sc, over_list, over_n);
   } else {
     REID_CUDA(cudaFuncSetAttribute(jaccard_score_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    (int)smem));
-    jaccard_score_kernel<512><<<nq_local, 512, smem, s>>>(Qc, Qv, qoff, Qn, colptr, csc_ent, D, ld,
-                                                          rowmax_key, q0, q_stride, q, N, Npad, c1, c2, out, ld_out,
-                                                          jaccard_out, ld_j, sc);
+    jaccard_score_kernel<512><<<grid, 512, smem, s>>>(Qc, Qv, qoff, Qn, colptr, csc_ent, D, ld,
+                                                      rowmax_key, q0, q_stride, q, N, Npad, c1, c2, out, ld_out,
+                                                      jaccard_out, ld_j, sc, over_list, over_n);
   }
 #ifdef REID_JS_PROFILE
   {
@@ -746,10 +701,14 @@ int launch_jaccard_mix(const int* Qc, const __half* Qv, const long long* qoff, c
                        const long long* colptr, const unsigned long long* csc_ent,
                        const float* D, long long ld, const int* rowmax_key, int q0, int q_stride,
                        int nq_local, int q, int N, float c1, float c2, float* out, long long ld_out, __half* jaccard_out,
-                       long long ld_j, cudaStream_t s) {
+                       long long ld_j, void* ws, long long ws_bytes, int cap, cudaStream_t s) {
   return launch_jaccard_score(Qc, Qv, qoff, Qn, colptr, csc_ent, D, ld, rowmax_key, q0, q_stride, nq_local,
                               q, N, c1, c2, out, ld_out, jaccard_out, ld_j, nullptr, nullptr, nullptr, nullptr,
-                              nullptr, nullptr, 0, 0, nullptr, nullptr, nullptr, nullptr, s);
+                              nullptr, nullptr, 0, 0, nullptr, nullptr, nullptr, nullptr, ws, ws_bytes, cap, s);
+}
+
+long long launch_jaccard_ws_bytes(int nq, int N, int cap) {
+  return jaccard_sparse_fits(N, cap) ? jaccard_sparse_ws_bytes(nq, N, cap) : 0;
 }
 
 }  // namespace reid

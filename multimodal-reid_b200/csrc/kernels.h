@@ -50,8 +50,8 @@ int launch_csc_fill(const int* Qc, const __half* Qv, const long long* qoff, cons
 int launch_jaccard_mix(const int* Qc, const __half* Qv, const long long* qoff, const int* Qn,
                        const long long* colptr, const unsigned long long* csc_ent, const float* D,
                        long long ld, const int* rowmax_key, int q0, int q_stride, int nq_local, int q, int N, float c1,
-                       float c2, float* out, long long ld_out, __half* jaccard_out, long long ld_j,
-                       cudaStream_t s);
+                       float c2, float* out, long long ld_out, __half* jaccard_out, long long ld_j, void* ws,
+                       long long ws_bytes, int cap, cudaStream_t s);
 int launch_pid_index(const long long* g_pid, int g, int T, unsigned long long* keys, int* cnt, long long* start,
                      int* cursor, int* list, cudaStream_t s);
 int launch_jaccard_score(const int* Qc, const __half* Qv, const long long* qoff, const int* Qn,
@@ -61,7 +61,8 @@ int launch_jaccard_score(const int* Qc, const __half* Qv, const long long* qoff,
                          const long long* q_pid, const long long* q_cam, const long long* g_cam,
                          const unsigned long long* pid_keys, const long long* pid_start, const int* pid_list,
                          int pid_T, int max_rank, double* ap, int* first_hit, int* cmc_hist, int* n_valid,
-                         cudaStream_t s);
+                         void* ws, long long ws_bytes, int cap, cudaStream_t s);
+long long launch_jaccard_ws_bytes(int nq, int N, int cap);   // 0 if the sparse path cannot be used for this N / cap
 int launch_rank_rows(const float* dist, int rows, int g, long long ld_dist, uint32_t* keyA, uint32_t* keyB,
                      int* idxA, int* idx_out, cudaStream_t s);
 int launch_score(const int* ranked, int q, int g, const long long* q_pid, const long long* g_pid,

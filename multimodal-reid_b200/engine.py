@@ -136,6 +136,9 @@ class Engine:
         self.engine = ENGINES[engine]
         self.comm = comm or Comm()
         self.timers = None          # dict stage -> list[(start_event, end_event)] when profiling
+        # Jaccard stage: packed per-query overlap records (jaccard_sparse.cu) with up to `sparse_cap` touched probes;
+        # denser queries fall back to the dense shared-memory row (jaccard_score.cu).  sparse_cap = 0: dense only.
+        self.sparse_cap = 8192
 
     # ------------------------------------------------------------------ timing helpers
     def enable_timers(self, on=True):
@@ -315,6 +318,14 @@ class Engine:
                   _ptr(csc_ent), _stream())
         return colptr, csc_ent
 
+    def _jaccard_ws(self, nq_local: int, N: int, force_dense: bool = False):
+        if force_dense or not self.sparse_cap:
+            return None, 0
+        nbytes = int(self.lib.reid_jaccard_ws_bytes(nq_local, N, self.sparse_cap))
+        if nbytes <= 0:
+            return None, 0
+        return self._empty((nbytes,), torch.uint8), nbytes
+
     # ------------------------------------------------------------------ K9 + K10
     def jaccard_mix(self, Qc, Qv, qoff, Qn, csc, D, key, q: int, N: int, lam: float, nq_local: int, q0=0,
                     q_stride=1, want_jaccard=False):
@@ -325,9 +336,10 @@ class Engine:
         J = self._empty((nq_local, N), torch.float16) if want_jaccard else None
         c1 = float(np.float16(1 - lam))            # fp16 array * python float: scalar cast to fp16 first
         c2 = float(np.float32(lam))                # fp32 array * python float
+        ws, ws_bytes = self._jaccard_ws(nq_local, N, force_dense=want_jaccard)
         _lib.call("reid_jaccard_mix", _ptr(Qc), _ptr(Qv), _ptr(qoff), _ptr(Qn), _ptr(colptr), _ptr(csc_ent),
                   _ptr(D), D.stride(0), _ptr(key), q0, q_stride, nq_local, q, N, c1, c2, _ptr(out),
-                  ldf, _ptr(J), N, _stream())
+                  ldf, _ptr(J), N, _ptr(ws), ws_bytes, self.sparse_cap, _stream())
         return (out, J) if want_jaccard else out
 
     # ------------------------------------------------------------------ identity index + fused K9–K12
@@ -358,12 +370,13 @@ class Engine:
         keys, start, lst, T = self.pid_index(g_pids)
         c1 = float(np.float16(1 - lam))
         c2 = float(np.float32(lam))
+        ws, ws_bytes = self._jaccard_ws(nq_local, N)
 
         def launch(ap, first, hist, nvalid):
             _lib.call("reid_jaccard_score", _ptr(Qc), _ptr(Qv), _ptr(qoff), _ptr(Qn), _ptr(colptr), _ptr(csc_ent),
                       _ptr(D), D.stride(0), _ptr(key), q0, q_stride, nq_local, q, N, c1, c2, _ptr(out),
                       ldf, _ptr(q_pids), _ptr(q_cams), _ptr(g_cams), _ptr(keys), _ptr(start), _ptr(lst), T, max_rank,
-                      _ptr(ap), _ptr(first), _ptr(hist), _ptr(nvalid), _stream())
+                      _ptr(ap), _ptr(first), _ptr(hist), _ptr(nvalid), _ptr(ws), ws_bytes, self.sparse_cap, _stream())
         return out, self._score_common(launch, nq_local, max_rank, q, span="jaccard_score")
 
     # ------------------------------------------------------------------ K4–K10 from a distance panel

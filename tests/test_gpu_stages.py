@@ -170,8 +170,11 @@ def test_rerank_stages_bit_exact(eng, engine_mod, synth, oracle, name, k1, k2, s
 
     # fused K9-K12 (the evaluator's path): same matrix bits when asked for it, same metrics either way
     mr = min(50, sh.g)
-    for want_final in (True, False):
+    saved_cap = eng.sparse_cap
+    for want_final, cap in ((True, saved_cap), (False, saved_cap), (True, 0), (False, 0), (False, 64), (True, 64)):
+        eng.sparse_cap = cap               # packed records / dense rows / records with most queries overflowing
         fin2, res = eng.rerank_from_panel(D, key, q, N, k1, k2, 0.3, score=(ids, mr), want_final=want_final)
+        eng.sparse_cap = saved_cap
         if want_final:
             np.testing.assert_array_equal(fin2[:, : sh.g].cpu().numpy().view(np.uint32), ref["final"].view(np.uint32))
         else:
@@ -196,8 +199,12 @@ def test_fused_score_many_matches_junk_and_odd_ids(eng, engine_mod, synth, oracl
     dev = eng.device
     ids = tuple(torch.from_numpy(a).to(dev) for a in (q_pids, g_pids, q_cams, g_cams))
     D, key = _panel(eng, engine_mod, X)
-    for k1, k2 in ((20, 6), (6, 1)):
+    saved_cap = eng.sparse_cap
+    for k1, k2, cap in ((20, 6, saved_cap), (6, 1, saved_cap), (20, 6, 0), (20, 6, 1024)):
+        eng.sparse_cap = 0
         final = eng.rerank_from_panel(D, key, q, N, k1, k2, 0.3)
+        eng.sparse_cap = cap
+        assert torch.equal(eng.rerank_from_panel(D, key, q, N, k1, k2, 0.3)[:, :g], final[:, :g])
         want = eng.evaluate_dist(final, g, *ids, 50, materialize_ranking=True)
         want_cmc, want_map, want_ap, want_first = oracle.cmc_map(final[:, :g].cpu().numpy(), q_pids, g_pids, q_cams,
                                                                  g_cams, detail=True)
@@ -211,6 +218,7 @@ def test_fused_score_many_matches_junk_and_odd_ids(eng, engine_mod, synth, oracl
             np.testing.assert_array_equal(got[4].cpu().numpy(), want_first)
             assert abs(got[1].item() - want_map) < 1e-12
             assert int(got[2].item()) == int((~np.isnan(want_ap)).sum()) < q
+    eng.sparse_cap = saved_cap
 
 
 def test_select_fallback_and_ties(eng, engine_mod, oracle):
