@@ -81,6 +81,12 @@ REID_API int reid_prepare_features(const float* X, int n, int d, int64_t ld_x, i
  *   reid_dist       tcgen05 tensor cores: float16 hi/lo operands, float32 accumulation in TMEM
  *                   (hi.hi + hi.lo + lo.hi), TMA in and out.  The product path.
  *   reid_dist_fp32  CUDA-core float32 FMA on x32: bring-up / cross-check engine. */
+/* When A and B of reid_dist are the same rows (same pointers, pitches, norms; m == n) the contraction computes only
+ * the tiles touching the upper triangle and stores every off-diagonal tile a second time transposed (with the
+ * mirrored rows' maxima and chunk minima): outside its 256-wide diagonal blocks the N x N matrix of re-ranking is an
+ * exact mirror, at half the tensor-core work.  Process-global switch, on by default; off = every tile computed (what a rank owning a strided
+ * subset of the rows runs anyway). */
+REID_API int reid_set_symmetric_contraction(int on);
 REID_API int reid_dist(const reid_half* Ahi, const reid_half* Alo, int64_t lda, const float* ra,
               const uint32_t* a_amax, int m, const reid_half* Bhi, const reid_half* Blo, int64_t ldb,
               const float* rb, const uint32_t* b_amax, int n, int dpad, int metric, float* out,

@@ -138,6 +138,11 @@ int reid_prepare_features(const float* X, int n, int d, int64_t ld_x, int normal
   return launch_prep(X, n, d, ld_x, normalize, x32, H(hi), H(lo), dpad, sq, nrm, amax, S(stream));
 }
 
+int reid_set_symmetric_contraction(int on) {
+  set_symmetric_contraction(on);
+  return REID_OK;
+}
+
 int reid_dist(const reid_half* Ahi, const reid_half* Alo, int64_t lda, const float* ra, const uint32_t* a_amax,
               int m, const reid_half* Bhi, const reid_half* Blo, int64_t ldb, const float* rb,
               const uint32_t* b_amax, int n, int dpad, int metric, float* out, int64_t ld_out,

@@ -147,13 +147,56 @@ __device__ __forceinline__ void tile_coords(int t, int mblocks, int nblocks, int
   nb = r / gsz;
 }
 
+// Symmetric mode (A and B are the same rows: the N x N matrix of re-ranking).  D[i, j] = D[j, i], so only tiles that
+// touch the upper triangle are computed -- (mb, nb) with mb <= 2 nb + 1 in units of BM = 128 rows and BN = 256
+// columns -- and every tile strictly above the 256-wide diagonal band (mb < 2 nb) is also stored transposed, with
+// the row maxima and 32-column chunk minima of the mirrored rows.  Each element is written exactly once.  Tiles are
+// enumerated group by group (RASTER_GROUP m-blocks), column-block-major inside a group, like the full raster.
+__host__ __device__ inline int sym_col_count(int g, int gsz, int nb) {       // tiles of group g in column block nb
+  const int c = 2 * nb + 2 - RASTER_GROUP * g;
+  return c < 0 ? 0 : (c > gsz ? gsz : c);
+}
+__host__ __device__ inline int sym_first_nb(int g) { return g == 0 ? 0 : (RASTER_GROUP / 2) * g; }
+__host__ __device__ inline long long sym_group_tiles(int g, int mblocks, int nblocks) {
+  const int gsz = min(RASTER_GROUP, mblocks - RASTER_GROUP * g);
+  long long tot = 0;
+  int nb = sym_first_nb(g);
+  for (int s = 0; s < RASTER_GROUP / 2 && nb < nblocks; ++s, ++nb) tot += sym_col_count(g, gsz, nb);   // staircase
+  if (nb < nblocks) tot += (long long)(nblocks - nb) * gsz;
+  return tot;
+}
+struct SymCursor {           // t only grows between calls
+  int g = 0;
+  long long base = 0;
+  __device__ void locate(long long t, int mblocks, int nblocks, int& mb, int& nb) {
+    for (;;) {
+      const long long c = sym_group_tiles(g, mblocks, nblocks);
+      if (t < base + c) break;
+      base += c;
+      ++g;
+    }
+    const int gsz = min(RASTER_GROUP, mblocks - RASTER_GROUP * g);
+    int r = (int)(t - base);
+    nb = sym_first_nb(g);
+    for (int s = 0; s < RASTER_GROUP / 2; ++s) {
+      const int c = sym_col_count(g, gsz, nb);
+      if (r < c) { mb = RASTER_GROUP * g + r; return; }
+      r -= c;
+      ++nb;
+    }
+    nb += r / gsz;
+    mb = RASTER_GROUP * g + r % gsz;
+  }
+};
+
 __global__ void __launch_bounds__(THREADS, 1)
 dist_tc_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant__ CUtensorMap tmAlo,
                const __grid_constant__ CUtensorMap tmBhi, const __grid_constant__ CUtensorMap tmBlo,
                const __grid_constant__ CUtensorMap tmOut, const float* __restrict__ ra,
                const float* __restrict__ rb, const uint32_t* __restrict__ a_amax,
                const uint32_t* __restrict__ b_amax, int m, int n, int kblocks, int metric,
-               int* __restrict__ rowmax_key, float* __restrict__ chunk_min, int nchunks) {
+               int* __restrict__ rowmax_key, float* __restrict__ chunk_min, int nchunks, int symmetric,
+               int ntiles) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* epi_base = smem + STAGES * STAGE_BYTES;
   float* rb_s = reinterpret_cast<float*>(epi_base + EPI_BYTES);
@@ -169,7 +212,6 @@ dist_tc_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant_
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int mblocks = (m + BM - 1) / BM, nblocks = (n + BN - 1) / BN;
-  const int ntiles = mblocks * nblocks;
 
   if (warp == 0 && lane == 0) {
     if (smem_u32(smem) & 1023u) __trap();          // swizzle-128B needs a 1024-byte aligned base
@@ -194,9 +236,10 @@ dist_tc_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant_
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
       int stage = 0, phase = 0;
+      SymCursor cur;
       for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
         int mb, nb;
-        tile_coords(t, mblocks, nblocks, mb, nb);
+        if (symmetric) cur.locate(t, mblocks, nblocks, mb, nb); else tile_coords(t, mblocks, nblocks, mb, nb);
         const int m0 = mb * BM, n0 = nb * BN;
         for (int kb = 0; kb < kblocks; ++kb) {
           mbar_wait(EMPTY_B(stage), phase ^ 1);
@@ -248,10 +291,12 @@ dist_tc_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant_
     const float inv_scale = exp2f((float)(-(scale_exponent(*a_amax) + scale_exponent(*b_amax))));
     const float neg2 = -2.0f * inv_scale;
     int it = 0, nstore = 0;
+    SymCursor cur;
     for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++it) {
       int mb, nb;
-      tile_coords(t, mblocks, nblocks, mb, nb);
+      if (symmetric) cur.locate(t, mblocks, nblocks, mb, nb); else tile_coords(t, mblocks, nblocks, mb, nb);
       const int m0 = mb * BM, n0 = nb * BN;
+      const bool mirror = symmetric && mb < 2 * nb;
       const int as = it & 1, aph = (it >> 1) & 1;
       float* rbt = rb_s + (it & 1) * BN;
       for (int j = et; j < BN; j += 128) rbt[j] = (n0 + j < n) ? rb[n0 + j] : 0.0f;
@@ -310,6 +355,38 @@ dist_tc_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant_
             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
           }
           ++nstore;
+          if (mirror) {
+            // the same box transposed: out[col0 + j, m0 + quad*32 + lane] = o[j]; then lane L reads back row L of
+            // the transposed box (= column col0 + L of this tile) for the mirrored row's maximum and chunk minimum
+            uint8_t* tb = my_epi + (nstore & 1) * EPI_BOX_BYTES;
+            if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              *reinterpret_cast<float*>(tb + j * 128 + (((lane >> 2) ^ (j & 7)) << 4) + ((lane & 3) << 2)) = o[j];
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) {
+              tma_store_2d(&tmOut, smem_u32(tb), m0 + quad * 32, col0);
+              asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+            ++nstore;
+            const int rows_ok = m - (m0 + quad * 32);               // valid rows of the direct box (>= 1 here)
+            float tmx = -INFINITY, tmn = INFINITY;
+#pragma unroll
+            for (int c4 = 0; c4 < 8; ++c4) {
+              const float4 v = *reinterpret_cast<const float4*>(tb + lane * 128 + ((c4 ^ (lane & 7)) << 4));
+              const float e[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                if (c4 * 4 + k < rows_ok) { tmx = fmaxf(tmx, e[k]); tmn = fminf(tmn, e[k]); }
+            }
+            const int trow = col0 + lane;
+            if (trow < n) {
+              if (chunk_min) chunk_min[(long long)trow * nchunks + ((m0 + quad * 32) >> 5)] = tmn;
+              if (rowmax_key) atomicMax(rowmax_key + trow, f2ordered_int(tmx));
+            }
+          }
         }
       }
       if (rowmax_key && row < m && mx > -INFINITY) atomicMax(rowmax_key + row, f2ordered_int(mx));
@@ -366,6 +443,9 @@ static int make_map(CUtensorMap* map, CUtensorMapDataType dt, int esize, const v
 
 }  // namespace tc
 
+static int g_symmetric_enabled = 1;
+void set_symmetric_contraction(int on) { g_symmetric_enabled = on ? 1 : 0; }
+
 int launch_dist_tc(const __half* Ahi, const __half* Alo, long long lda, const float* ra, const uint32_t* a_amax,
                    int m, const __half* Bhi, const __half* Blo, long long ldb, const float* rb,
                    const uint32_t* b_amax, int n, int dp, int metric, float* out, long long ld_out,
@@ -388,10 +468,20 @@ int launch_dist_tc(const __half* Ahi, const __half* Alo, long long lda, const fl
   REID_CUDA(cudaGetDevice(&dev));
   REID_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   REID_CUDA(cudaFuncSetAttribute(dist_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
-  const int ntiles = cdiv(m, BM) * cdiv(n, BN);
-  const int grid = ntiles < sms ? ntiles : sms;
+  // same rows on both sides and a square output: compute the upper triangle only and mirror it
+  const int symmetric = (Ahi == Bhi && Alo == Blo && lda == ldb && ra == rb && a_amax == b_amax && m == n &&
+                         g_symmetric_enabled) ? 1 : 0;
+  const int mblocks = cdiv(m, BM), nblocks = cdiv(n, BN);
+  long long ntiles = (long long)mblocks * nblocks;
+  if (symmetric) {
+    ntiles = 0;
+    for (int g = 0; g * RASTER_GROUP < mblocks; ++g) ntiles += sym_group_tiles(g, mblocks, nblocks);
+  }
+  REID_REQUIRE(ntiles < (1ll << 31), "dist_tc: too many tiles");
+  const int grid = ntiles < sms ? (int)ntiles : sms;
   dist_tc_kernel<<<grid, THREADS, SMEM_BYTES, s>>>(mAhi, mAlo, mBhi, mBlo, mOut, ra, rb, a_amax, b_amax, m, n,
-                                                  dp / BK, metric, rowmax_key, chunk_min, cdiv(n, 32));
+                                                  dp / BK, metric, rowmax_key, chunk_min, cdiv(n, 32), symmetric,
+                                                  (int)ntiles);
   return check_launch("dist_tc_kernel");
 }
 

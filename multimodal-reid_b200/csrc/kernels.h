@@ -25,6 +25,7 @@ int launch_dist_tc(const __half* Ahi, const __half* Alo, long long lda, const fl
                    int m, const __half* Bhi, const __half* Blo, long long ldb, const float* rb,
                    const uint32_t* b_amax, int n, int dp, int metric, float* out, long long ld_out,
                    int* rowmax_key, float* chunk_min, cudaStream_t s);
+void set_symmetric_contraction(int on);
 int launch_select_topk_hinted(const float* D, int rows, int cols, long long ld, const int* rowmax_key,
                               const float* chunk_min, int K, int* nbr, float* nbr_val, int cap_override,
                               cudaStream_t s);

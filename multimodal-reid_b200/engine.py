@@ -139,6 +139,9 @@ class Engine:
         # Jaccard stage: packed per-query overlap records (jaccard_sparse.cu) with up to `sparse_cap` touched probes;
         # denser queries fall back to the dense shared-memory row (jaccard_score.cu).  sparse_cap = 0: dense only.
         self.sparse_cap = 8192
+        # N x N contraction of one rank owning every row: upper-triangle tiles only, mirrored (dist_tcgen05.cu).
+        # Ranks of a multi-GPU job own strided row subsets and always run the full schedule.
+        self.symmetric = True
 
     # ------------------------------------------------------------------ timing helpers
     def enable_timers(self, on=True):
@@ -219,6 +222,7 @@ class Engine:
         else:
             if want_chunk_min:
                 cmin = self._empty((m, (n + 31) // 32), torch.float32)
+            self.lib.reid_set_symmetric_contraction(int(self.symmetric))
             _lib.call("reid_dist", _ptr(A.hi), _ptr(A.lo), A.hi.stride(0), _ptr(ra), _ptr(A.amax), m, _ptr(B.hi),
                       _ptr(B.lo), B.hi.stride(0), _ptr(rb), _ptr(B.amax), n, A.dp, metric, _ptr(D), ld, _ptr(key),
                       _ptr(cmin), _stream())

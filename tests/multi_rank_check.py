@@ -26,6 +26,7 @@ def main():
     synth = importlib.import_module("multimodal-reid_b200.synth")
     multi = engine.Engine(dev)
     single = engine.Engine(dev, comm=engine.Comm(single=True))
+    single.symmetric = False        # compare against the full tile schedule: that is what every rank of a job runs
     assert multi.comm.world == world and single.comm.world == 1
     for name, k1, k2, seed in (("small", 20, 6, 0), ("small", 50, 15, 1), ("mid", 20, 6, 2), ("tiny", 7, 1, 3)):
         sh = synth.SHAPES[name]

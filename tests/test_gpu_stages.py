@@ -92,10 +92,27 @@ def test_tensor_core_contraction_accuracy(eng, engine_mod, n, d, normalize):
         err = float((got - ref).abs().max()) / scale
         assert err < (1.0e-5 * max(1.0, f.dp / 512) if name == "tcgen05" else 4e-6), (name, err)
         np.testing.assert_array_equal(eng.rowmax_values(key).cpu().numpy(), D[:, :n].max(1).values.cpu().numpy())
-    # strided row window (what a rank of a multi-GPU job passes): same numbers as the full run
-    Dfull, _ = eng.dist(f, f, engine_mod.METRIC_SQEUCLIDEAN)
+    # strided row window (what a rank of a multi-GPU job passes): same numbers as the full tile schedule
+    eng.symmetric = False
+    Dfull, kfull, cfull = eng.dist(f, f, engine_mod.METRIC_SQEUCLIDEAN, want_rowmax=True, want_chunk_min=True)
+    eng.symmetric = True
     Dwin, _ = eng.dist(f.rows(slice(1, n, 3)), f, engine_mod.METRIC_SQEUCLIDEAN)
     assert torch.equal(Dwin[:, :n], Dfull[1::3, :n])
+    # symmetric schedule (upper-triangle tiles + mirrored stores): tiles of the upper triangle and the diagonal blocks
+    # carry the bits of the full schedule, the rest is their exact mirror (within an accumulator ulp of the full
+    # schedule's own lower triangle); row maxima and chunk minima describe ITS matrix
+    Dsym, ksym, csym = eng.dist(f, f, engine_mod.METRIC_SQEUCLIDEAN, want_rowmax=True, want_chunk_min=True)
+    S, Fm = Dsym[:, :n], Dfull[:, :n]
+    blk = torch.arange(n, device=S.device) >> 8                      # 256-wide diagonal blocks are computed directly
+    upper = blk[:, None] <= blk[None, :]
+    assert torch.equal(S[upper], Fm[upper])                           # direct tiles: the same bits as the full schedule
+    off = blk[:, None] != blk[None, :]
+    assert torch.equal(S[off], S.T[off])                              # everything else is an exact mirror
+    assert float((S - Fm).abs().max()) <= 4e-6 * scale
+    np.testing.assert_array_equal(eng.rowmax_values(ksym).cpu().numpy(), S.max(1).values.cpu().numpy())
+    pad = (-n) % 32
+    Sp = torch.nn.functional.pad(S, (0, pad), value=float("inf")).reshape(n, -1, 32).min(2).values
+    assert torch.equal(csym, Sp)
 
 
 def _panel(eng, engine_mod, X, normalize=True):
