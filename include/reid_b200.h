@@ -87,6 +87,9 @@ REID_API int reid_prepare_features(const float* X, int n, int d, int64_t ld_x, i
  * exact mirror, at half the tensor-core work.  Process-global switch, on by default; off = every tile computed (what a rank owning a strided
  * subset of the rows runs anyway). */
 REID_API int reid_set_symmetric_contraction(int on);
+/* Diagnostics: with the environment variable REID_TC_DBG & 64 set, block 0 of reid_dist's kernel records
+ * {clock64, globaltimer ns} at entry and exit; this copies the four values to HOST memory (synchronises). */
+REID_API int reid_dist_clock_probe(int64_t* host_out4);
 REID_API int reid_dist(const reid_half* Ahi, const reid_half* Alo, int64_t lda, const float* ra,
               const uint32_t* a_amax, int m, const reid_half* Bhi, const reid_half* Blo, int64_t ldb,
               const float* rb, const uint32_t* b_amax, int n, int dpad, int metric, float* out,

@@ -138,6 +138,11 @@ int reid_prepare_features(const float* X, int n, int d, int64_t ld_x, int normal
   return launch_prep(X, n, d, ld_x, normalize, x32, H(hi), H(lo), dpad, sq, nrm, amax, S(stream));
 }
 
+int reid_dist_clock_probe(int64_t* host_out4) {
+  ENTER();
+  return dist_clock_probe(reinterpret_cast<long long*>(host_out4));
+}
+
 int reid_set_symmetric_contraction(int on) {
   set_symmetric_contraction(on);
   return REID_OK;

@@ -443,10 +443,9 @@ static int make_map(CUtensorMap* map, CUtensorMapDataType dt, int esize, const v
 
 }  // namespace tc
 
-static int g_symmetric_enabled = 1;
-void set_symmetric_contraction(int on) { g_symmetric_enabled = on ? 1 : 0; }
-
-int launch_dist_tc(const __half* Ahi, const __half* Alo, long long lda, const float* ra, const uint32_t* a_amax,
+// Single-CTA variant (cta_group::1), kept for A/B measurements against the CTA-pair kernel (dist_tc2.cu):
+// REID_TC_PAIR=0 in the environment routes reid_dist here.
+int launch_dist_tc1(const __half* Ahi, const __half* Alo, long long lda, const float* ra, const uint32_t* a_amax,
                    int m, const __half* Bhi, const __half* Blo, long long ldb, const float* rb,
                    const uint32_t* b_amax, int n, int dp, int metric, float* out, long long ld_out,
                    int* rowmax_key, float* chunk_min, cudaStream_t s) {
@@ -470,7 +469,7 @@ int launch_dist_tc(const __half* Ahi, const __half* Alo, long long lda, const fl
   REID_CUDA(cudaFuncSetAttribute(dist_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
   // same rows on both sides and a square output: compute the upper triangle only and mirror it
   const int symmetric = (Ahi == Bhi && Alo == Blo && lda == ldb && ra == rb && a_amax == b_amax && m == n &&
-                         g_symmetric_enabled) ? 1 : 0;
+                         symmetric_contraction_enabled()) ? 1 : 0;
   const int mblocks = cdiv(m, BM), nblocks = cdiv(n, BN);
   long long ntiles = (long long)mblocks * nblocks;
   if (symmetric) {

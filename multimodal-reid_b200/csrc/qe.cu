@@ -19,17 +19,33 @@ __global__ void qe_bound_kernel(const int* __restrict__ nbr, int K, int k2, cons
   ub[l] = t;
 }
 
-// single-CTA exclusive scan int32 -> int64 offsets (+ total at out[n]); n is ~1e5, this is noise
+// single-CTA exclusive scan int32 -> int64 offsets (+ total at out[n]); n is ~1e5.  Every thread owns SCAN_ITEMS
+// consecutive entries per pass (one pass covers 16 K entries), so the barrier count stays small.
+constexpr int SCAN_ITEMS = 16;
 __global__ void __launch_bounds__(1024)
 exclusive_scan_kernel(const int* __restrict__ in, int n, long long* __restrict__ out) {
   __shared__ long long warp_tot[32];
-  __shared__ long long chunk_tot;
+  __shared__ long long chunk_tot[2];
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   long long carry = 0;
-  for (int base = 0; base < n; base += 1024) {
-    const int i = base + tid;
-    long long v = i < n ? in[i] : 0;
-    long long x = v;
+  int pass = 0;
+  for (int base = 0; base < n; base += 1024 * SCAN_ITEMS, ++pass) {
+    const int i0 = base + tid * SCAN_ITEMS;
+    int v[SCAN_ITEMS];
+    if (i0 + SCAN_ITEMS <= n && ((reinterpret_cast<uintptr_t>(in + i0) & 15) == 0)) {
+#pragma unroll
+      for (int k = 0; k < SCAN_ITEMS; k += 4) {
+        const int4 x = __ldg(reinterpret_cast<const int4*>(in + i0 + k));
+        v[k] = x.x; v[k + 1] = x.y; v[k + 2] = x.z; v[k + 3] = x.w;
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < SCAN_ITEMS; ++k) v[k] = i0 + k < n ? in[i0 + k] : 0;
+    }
+    long long mine = 0;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) mine += v[k];
+    long long x = mine;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
       long long y = __shfl_up_sync(FULL, x, o);
@@ -46,11 +62,16 @@ exclusive_scan_kernel(const int* __restrict__ in, int n, long long* __restrict__
         if (lane >= o) s += y;
       }
       warp_tot[lane] = s - t;     // exclusive warp offsets
-      if (lane == 31) chunk_tot = s;
+      if (lane == 31) chunk_tot[pass & 1] = s;
     }
     __syncthreads();
-    if (i < n) out[i] = carry + warp_tot[w] + x - v;
-    carry += chunk_tot;
+    long long run = carry + warp_tot[w] + x - mine;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) {
+      if (i0 + k < n) out[i0 + k] = run;
+      run += v[k];
+    }
+    carry += chunk_tot[pass & 1];
     __syncthreads();
   }
   if (tid == 0) out[n] = carry;
