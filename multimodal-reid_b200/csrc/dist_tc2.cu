@@ -396,8 +396,8 @@ dist_tc2_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant
           for (int j = 0; j < 32; ++j)
             if (j < ncols) { mx = fmaxf(mx, o[j]); cmn = fminf(cmn, o[j]); }
         }
-        if (chunk_min && row_ok) chunk_min[(long long)row * nchunks + (col0 >> 5)] = cmn;
-        {
+        if (chunk_min && row_ok && !(dbg & 32)) chunk_min[(long long)row * nchunks + (col0 >> 5)] = cmn;
+        if (!(dbg & 16)) {
           uint8_t* buf = my_epi + (EPI_BUFS == 2 ? (nstore & 1) : 0) * EPI_BOX_BYTES;
           if (lane == 0) {
             if (EPI_BUFS == 2) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
@@ -426,11 +426,12 @@ dist_tc2_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant
           if (ncols == 32 && r0 + 32 <= m) {                    // warp-uniform: the whole box is inside
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
-              *orow = o[j];
+              if (!(dbg & 4)) *orow = o[j];
               orow += ld_out;
               float rmx, rmn;
+              if (dbg & 8) { rmx = o[j]; rmn = o[j]; } else {
               asm volatile("redux.sync.max.f32 %0, %1, 0xffffffff;" : "=f"(rmx) : "f"(o[j]));
-              asm volatile("redux.sync.min.f32 %0, %1, 0xffffffff;" : "=f"(rmn) : "f"(o[j]));
+              asm volatile("redux.sync.min.f32 %0, %1, 0xffffffff;" : "=f"(rmn) : "f"(o[j])); }
               tmx = lane == j ? rmx : tmx;
               tmn = lane == j ? rmn : tmn;
             }
@@ -450,8 +451,8 @@ dist_tc2_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant
           }
           const int trow = col0 + lane;
           if (trow < n) {
-            if (chunk_min) chunk_min[(long long)trow * nchunks + (r0 >> 5)] = tmn;
-            if (rowmax_key) atomicMax(rowmax_key + trow, f2ordered_int(tmx));
+            if (chunk_min && !(dbg & 2)) chunk_min[(long long)trow * nchunks + (r0 >> 5)] = tmn;
+            if (rowmax_key && !(dbg & 1)) atomicMax(rowmax_key + trow, f2ordered_int(tmx));
           }
         }
       }
@@ -558,7 +559,8 @@ int launch_dist_tc(const __half* Ahi, const __half* Alo, long long lda, const fl
   REID_REQUIRE(ntiles < (1ll << 30), "dist_tc: too many tiles");
   const int pairs = sms / 2;
   const int clusters = ntiles < pairs ? (int)ntiles : pairs;
-  static const int dbg = getenv("REID_TC_DBG") ? atoi(getenv("REID_TC_DBG")) : 0;
+  const char* dbg_env = getenv("REID_TC_DBG");          // diagnostics only (scratch/dist_knobs.py)
+  const int dbg = dbg_env ? atoi(dbg_env) : 0;
   dist_tc2_kernel<<<2 * clusters, THREADS, SMEM_BYTES, s>>>(mAhi, mAlo, mBhi, mBlo, mOut, ra, rb, a_amax, b_amax, m, n,
                                                             dp / BK, metric, rowmax_key, chunk_min, cdiv(n, 32),
                                                             symmetric, (int)ntiles, out, ld_out, dbg);

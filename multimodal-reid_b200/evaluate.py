@@ -76,6 +76,45 @@ def eval_func(distmat, q_pids, g_pids, q_camids, g_camids, max_rank=50):
                             _ids(q_camids, dev)[mine].contiguous(), _ids(g_camids, dev), max_rank, eng, q_total=num_q)
 
 
+class _IdStore:
+    """The evaluator's ``pids`` / ``camids`` (evaluate.py:101-102, 107-108).  The reference extends a Python list with
+    one numpy scalar per sample and turns it back into an array in compute() -- milliseconds of interpreter time per
+    evaluation at Duke scale, more than the whole GPU pipeline.  Batches are kept as they arrive instead; the list is
+    only built when somebody reads the attribute, and from then on it is the source of truth (it may have been edited)."""
+
+    def __init__(self, initial=None):
+        self.chunks = []
+        self.listed = None
+        if initial is not None and len(initial):
+            self.listed = initial if isinstance(initial, list) else list(initial)
+
+    @staticmethod
+    def _as_numpy(x):
+        return np.asarray(x.cpu() if isinstance(x, torch.Tensor) else x)
+
+    def extend(self, x):
+        if self.listed is not None:
+            self.listed.extend(self._as_numpy(x))
+        else:
+            self.chunks.append(x.detach() if isinstance(x, torch.Tensor) else np.asarray(x))
+
+    def as_list(self):
+        if self.listed is None:
+            self.listed = []
+            for c in self.chunks:
+                self.listed.extend(self._as_numpy(c))
+            self.chunks = []
+        return self.listed
+
+    def to_device(self, device) -> torch.Tensor:
+        if self.listed is not None:
+            return _ids(np.asarray(self.listed), device)
+        parts = [_ids(c, device).reshape(-1) for c in self.chunks]
+        if not parts:
+            return torch.empty((0,), dtype=torch.int64, device=device)
+        return parts[0] if len(parts) == 1 else torch.cat(parts)
+
+
 class R1_mAP_eval():
     """evaluate.py:91-135.  ``update`` keeps tensors where they are (CPU or CUDA); ``compute``
     moves them to the B200 once and returns (cmc float32[50], mAP float64)."""
@@ -94,11 +133,29 @@ class R1_mAP_eval():
         self.pids = []
         self.camids = []
 
+    # public list attributes like the reference's; backed by _IdStore so that update()/compute() stay off the
+    # interpreter's per-element path unless a caller actually looks at (or assigns) the lists
+    @property
+    def pids(self):
+        return self._pid_store.as_list()
+
+    @pids.setter
+    def pids(self, value):
+        self._pid_store = _IdStore(value)
+
+    @property
+    def camids(self):
+        return self._cam_store.as_list()
+
+    @camids.setter
+    def camids(self, value):
+        self._cam_store = _IdStore(value)
+
     def update(self, output):  # called once for each batch
         feat, pid, camid = output
         self.feats.append(feat.detach())
-        self.pids.extend(np.asarray(pid.cpu() if isinstance(pid, torch.Tensor) else pid))
-        self.camids.extend(np.asarray(camid.cpu() if isinstance(camid, torch.Tensor) else camid))
+        self._pid_store.extend(pid)
+        self._cam_store.extend(camid)
 
     def compute(self):  # called after each epoch
         eng = _engine.default_engine()
@@ -109,8 +166,8 @@ class R1_mAP_eval():
         q = self.num_query
         N = feats.shape[0]
         g = N - q
-        pids = _ids(np.asarray(self.pids), dev)
-        camids = _ids(np.asarray(self.camids), dev)
+        pids = self._pid_store.to_device(dev)
+        camids = self._cam_store.to_device(dev)
         if self.reranking:
             print('=> Enter reranking')
             k1, k2, lam = self.rerank_params                                          # evaluate.py:127
