@@ -16,8 +16,9 @@
 //               both epilogues
 //   warps 2..9  epilogue of this CTA's 128 rows x 256 columns (two warps per TMEM lane quadrant), as in the single-CTA
 //               kernel: fused formula, row maxima, 32-column chunk minima, TMA store of 32 x 32 boxes, mirrored tiles
-//               (symmetric mode: tiles mb < nb of the upper triangle) stored transposed straight from registers with
-//               redux.sync.f32 for the mirrored rows' maxima / chunk minima.  The peer's warps release the accumulator
+//               (symmetric mode: tiles mb < nb of the upper triangle) stored transposed straight from registers (one
+//               128-byte line per column); the mirrored rows' maxima / chunk minima come from a transposed pass
+//               through the warp's staging box.  The peer's warps release the accumulator
 //               with remote arrives on the leader's barrier.
 #include <cuda.h>
 #include <cstdlib>
@@ -83,9 +84,11 @@ __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
-// arrive on a barrier of any CTA of the cluster (shared::cluster address from mapa)
+// arrive on a barrier of any CTA of the cluster (shared::cluster address from mapa).  Relaxed: the accumulator
+// hand-over is ordered by tcgen05.wait::ld + tcgen05.fence::before_thread_sync; a release at cluster scope would
+// first drain this thread's outstanding global stores (ncu r01c: 24 % of the kernel's stall samples).
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_bar) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   asm volatile(
@@ -396,14 +399,42 @@ dist_tc2_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant
           for (int j = 0; j < 32; ++j)
             if (j < ncols) { mx = fmaxf(mx, o[j]); cmn = fminf(cmn, o[j]); }
         }
-        if (chunk_min && row_ok && !(dbg & 32)) chunk_min[(long long)row * nchunks + (col0 >> 5)] = cmn;
-        if (!(dbg & 16)) {
-          uint8_t* buf = my_epi + (EPI_BUFS == 2 ? (nstore & 1) : 0) * EPI_BOX_BYTES;
-          if (lane == 0) {
-            if (EPI_BUFS == 2) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
-            else asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        if (chunk_min && row_ok) chunk_min[(long long)row * nchunks + (col0 >> 5)] = cmn;
+        uint8_t* buf = my_epi + (EPI_BUFS == 2 ? (nstore & 1) : 0) * EPI_BOX_BYTES;
+        if (lane == 0) {
+          if (EPI_BUFS == 2) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          else asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        }
+        __syncwarp();
+        float tmx = -INFINITY, tmn = INFINITY;
+        if (mirror) {
+          // mirrored rows' maximum / chunk minimum: the box goes through the staging buffer transposed (word (j, lane)
+          // in row j, 16-byte chunks swizzled by row), lane L reads row L back = column col0 + L over the warp's rows
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            *reinterpret_cast<float*>(buf + j * 128 + (((lane >> 2) ^ (j & 7)) << 4) + ((lane & 3) << 2)) = o[j];
+          __syncwarp();
+          const int rows_ok = m - r0;                            // valid rows of the direct box (>= 1 here)
+          if (rows_ok >= 32) {
+#pragma unroll
+            for (int c4 = 0; c4 < 8; ++c4) {
+              const float4 x = *reinterpret_cast<const float4*>(buf + lane * 128 + ((c4 ^ (lane & 7)) << 4));
+              tmx = fmaxf(fmaxf(tmx, fmaxf(x.x, x.y)), fmaxf(x.z, x.w));
+              tmn = fminf(fminf(tmn, fminf(x.x, x.y)), fminf(x.z, x.w));
+            }
+          } else {
+#pragma unroll
+            for (int c4 = 0; c4 < 8; ++c4) {
+              const float4 x = *reinterpret_cast<const float4*>(buf + lane * 128 + ((c4 ^ (lane & 7)) << 4));
+              const float e[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                if (c4 * 4 + k < rows_ok) { tmx = fmaxf(tmx, e[k]); tmn = fminf(tmn, e[k]); }
+            }
           }
           __syncwarp();
+        }
+        {
           uint8_t* rowp = buf + lane * 128;
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
@@ -419,40 +450,23 @@ dist_tc2_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant
           ++nstore;
         }
         if (mirror) {
-          // the same box transposed: out[col0 + j, r0 + lane] = o[j] -- one 128-byte line per j -- and the mirrored
-          // rows' maximum / chunk minimum: lane L keeps the reduction over the warp of column col0 + L
+          // the same box transposed, straight from registers: out[col0 + j, r0 + lane] = o[j], one 128-byte line per j
           float* orow = out + (long long)col0 * ld_out + row;
-          float tmx = -INFINITY, tmn = INFINITY;
-          if (ncols == 32 && r0 + 32 <= m) {                    // warp-uniform: the whole box is inside
+          if (ncols == 32 && row_ok) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
-              if (!(dbg & 4)) *orow = o[j];
+              *orow = o[j];
               orow += ld_out;
-              float rmx, rmn;
-              if (dbg & 8) { rmx = o[j]; rmn = o[j]; } else {
-              asm volatile("redux.sync.max.f32 %0, %1, 0xffffffff;" : "=f"(rmx) : "f"(o[j]));
-              asm volatile("redux.sync.min.f32 %0, %1, 0xffffffff;" : "=f"(rmn) : "f"(o[j])); }
-              tmx = lane == j ? rmx : tmx;
-              tmn = lane == j ? rmn : tmn;
             }
-          } else {
-#pragma unroll 1
-            for (int j = 0; j < ncols; ++j) {
-              float oj = o[0];
+          } else if (row_ok) {
 #pragma unroll
-              for (int k = 1; k < 32; ++k) oj = j == k ? o[k] : oj;
-              if (row_ok) orow[(long long)j * ld_out] = oj;
-              float rmx, rmn;
-              asm volatile("redux.sync.max.f32 %0, %1, 0xffffffff;" : "=f"(rmx) : "f"(row_ok ? oj : -INFINITY));
-              asm volatile("redux.sync.min.f32 %0, %1, 0xffffffff;" : "=f"(rmn) : "f"(row_ok ? oj : INFINITY));
-              tmx = lane == j ? rmx : tmx;
-              tmn = lane == j ? rmn : tmn;
-            }
+            for (int j = 0; j < 32; ++j)
+              if (j < ncols) orow[(long long)j * ld_out] = o[j];
           }
           const int trow = col0 + lane;
           if (trow < n) {
-            if (chunk_min && !(dbg & 2)) chunk_min[(long long)trow * nchunks + (r0 >> 5)] = tmn;
-            if (rowmax_key && !(dbg & 1)) atomicMax(rowmax_key + trow, f2ordered_int(tmx));
+            if (chunk_min) chunk_min[(long long)trow * nchunks + (r0 >> 5)] = tmn;
+            if (rowmax_key) atomicMax(rowmax_key + trow, f2ordered_int(tmx));
           }
         }
       }
