@@ -304,15 +304,29 @@ def main():
 
     # ---- roofline of the dominant kernel (N x N distance contraction)
     rows_local = cm.local_count(N)
-    flops = 2.0 * rows_local * N * d          # algorithmic, per launch (this rank's panel)
+    flops = 2.0 * rows_local * N * d          # algorithmic, per launch (this rank's panel): SURVEY.md 8(d)
     dist_ms = stages.get("dist", float("nan"))
     tf32_peak = peaks["bf16_sustained"] / 2.0
     achieved = flops / (dist_ms * 1e-3) / 1e12
-    roofline = {"kernel": "dist (N x N squared-L2 contraction, engine=%s)" % args.engine, "bound": "tensor",
+    # what the tensor pipe is actually asked to do: 3 fp16 MMAs (hi.hi + hi.lo + lo.hi) over the 256 x 256 tiles the
+    # schedule computes -- the upper triangle only when one rank owns every row (symmetric mode)
+    T_n, dp = -(-N // 256), -(-d // 64) * 64
+    tiles = T_n * (T_n + 1) // 2 if (world == 1 and eng.symmetric) else -(-rows_local // 256) * T_n
+    issued = 3.0 * tiles * 2.0 * 256 * 256 * dp
+    issued_tf = issued / (dist_ms * 1e-3) / 1e12
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if world == 1 and os.path.exists(tpath):
+        with open(tpath) as f:
+            traffic = json.load(f).get(shape.name, {}).get("dist_tc2_kernel")
+    roofline = {"kernel": "dist_tc2_kernel (N x N squared-L2 contraction, tcgen05 cta_group::2)", "bound": "tensor",
                 "achieved": achieved, "peak": tf32_peak, "unit": "TFLOP/s", "frac": achieved / tf32_peak,
-                "peak_source": f"{peaks['source']}: bf16_tflops_sustained/2 (TF32-equivalent dense)",
-                "traffic": None, "ms": dist_ms,
-                "algorithmic_flops_per_launch": flops}
+                "peak_source": f"{peaks['source']}: bf16_tflops_sustained/2 (TF32-equivalent dense; the kernel runs "
+                               "inside a long step and the chip power-throttles to ~1.4-1.5 GHz under it)",
+                "traffic": traffic, "traffic_source": "profiles/traffic.json (ncu --set full, dram read+write per launch)",
+                "ms": dist_ms, "algorithmic_flops_per_launch": flops,
+                "issued_fp16_tflops": issued_tf, "issued_frac_of_bf16_sustained": issued_tf / peaks["bf16_sustained"],
+                "tiles_256x256": tiles, "symmetric_schedule": bool(world == 1 and eng.symmetric)}
     hbm = {}
     # algorithmic bytes: selection reads the chunk minima (+ ~K candidate lines per row); the fused
     # Jaccard/score kernel streams its queries' rows of D once and writes nothing q x g

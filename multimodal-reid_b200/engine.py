@@ -399,26 +399,29 @@ class Engine:
             raise NotImplementedError(f"re-ranking needs at least max(k1+1, k2) = {K} samples, got {N}")
         with self.span("select"):
             nbr_local = self.topk_rows(D, N, key, K, chunk_min=chunk_min)
-        nbr = cm.gather_rows(nbr_local, N)
+        with self.span("x_nbr"):
+            nbr = cm.gather_rows(nbr_local, N)
         with self.span("krecip"):
             sets = self.krecip_sets(nbr, k1)
             Vc_l, Vv_l, Vn_l = self.krecip_V(sets, k1, D, key, r, P)
-        Vc, Vv, Vn = cm.gather_rows(Vc_l, N), cm.gather_rows(Vv_l, N), cm.gather_rows(Vn_l, N)
+        with self.span("x_V"):
+            Vc, Vv, Vn = cm.gather_rows(Vc_l, N), cm.gather_rows(Vv_l, N), cm.gather_rows(Vn_l, N)
         if k2 != 1:
             with self.span("qe"):
                 Qc_l, Qv_l, qoff_l, Qn_l, total = self.query_expansion(nbr, k2, Vc, Vv, Vn, nloc, r, P)
             if P == 1:
                 Qc, Qv, qoff, Qn, nnz_bound = Qc_l, Qv_l, qoff_l, Qn_l, total
             else:
-                tmax = cm.max_int(total, self.device)
-                Qc = cm.gather_flat(Qc_l[:total], tmax).reshape(-1)
-                Qv = cm.gather_flat(Qv_l[:total], tmax).reshape(-1)
-                Qn = cm.gather_rows(Qn_l, N)
-                # global offset of row i = (i mod P) * tmax + qoff_rank[i div P]
-                offs = cm.gather_rows(qoff_l[:nloc], N)
-                owner = torch.arange(N, device=self.device, dtype=torch.int64) % P
-                qoff = torch.cat([offs + owner * tmax, offs.new_zeros(1)])
-                nnz_bound = tmax * P
+                with self.span("x_qe"):
+                    tmax = cm.max_int(total, self.device)
+                    Qc = cm.gather_flat(Qc_l[:total], tmax).reshape(-1)
+                    Qv = cm.gather_flat(Qv_l[:total], tmax).reshape(-1)
+                    Qn = cm.gather_rows(Qn_l, N)
+                    # global offset of row i = (i mod P) * tmax + qoff_rank[i div P]
+                    offs = cm.gather_rows(qoff_l[:nloc], N)
+                    owner = torch.arange(N, device=self.device, dtype=torch.int64) % P
+                    qoff = torch.cat([offs + owner * tmax, offs.new_zeros(1)])
+                    nnz_bound = tmax * P
         else:
             cap1 = Vc.shape[1]
             qoff = self._empty((N + 1,), torch.int64)
@@ -490,10 +493,11 @@ class Engine:
         with self.span(span):
             launch(ap, first, hist, nvalid)
         q_all = nq if q_total is None else q_total
-        ap_all = cm.gather_rows(ap, q_all)
-        first_all = cm.gather_rows(first, q_all)
-        cm.all_reduce_sum(hist)
-        cm.all_reduce_sum(nvalid)
+        with self.span("x_score"):
+            ap_all = cm.gather_rows(ap, q_all)
+            first_all = cm.gather_rows(first, q_all)
+            cm.all_reduce_sum(hist)
+            cm.all_reduce_sum(nvalid)
         cmc = self._empty((max_rank,), torch.float32)
         mAP = self._empty((1,), torch.float64)
         _lib.call("reid_score_finalize", _ptr(ap_all), q_all, _ptr(hist), max_rank, _ptr(nvalid), _ptr(cmc),
