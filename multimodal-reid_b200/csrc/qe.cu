@@ -19,20 +19,60 @@ __global__ void qe_bound_kernel(const int* __restrict__ nbr, int K, int k2, cons
   ub[l] = t;
 }
 
-// single-CTA exclusive scan int32 -> int64 offsets (+ total at out[n]); n is ~1e5.  Every thread owns SCAN_ITEMS
-// consecutive entries per pass (one pass covers 16 K entries), so the barrier count stays small.
+// Exclusive scan int32 -> int64 offsets (+ total at out[n]); n is 2e4 .. 2e6 (row counts, identity-index slots).
+// Every CTA scans 16 K entries (16 per thread) and chains its total to the next CTA through a per-launch epoch flag:
+// at most 128 CTAs, all resident at once (one per SM), so the chain cannot deadlock.
 constexpr int SCAN_ITEMS = 16;
+constexpr int SCAN_TILE = 1024 * SCAN_ITEMS;
+constexpr int SCAN_MAX_CTAS = 128;
+__device__ unsigned long long g_scan_sum[SCAN_MAX_CTAS];      // inclusive total up to and including CTA b
+__device__ unsigned int g_scan_epoch[SCAN_MAX_CTAS];
+
 __global__ void __launch_bounds__(1024)
-exclusive_scan_kernel(const int* __restrict__ in, int n, long long* __restrict__ out) {
+exclusive_scan_kernel(const int* __restrict__ in, int n, long long* __restrict__ out, unsigned int epoch,
+                      int tiles_per_cta) {
   __shared__ long long warp_tot[32];
   __shared__ long long chunk_tot[2];
+  __shared__ long long s_prefix;
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-  long long carry = 0;
+  const int first = blockIdx.x * tiles_per_cta * SCAN_TILE;
+  const int last = min(n, first + tiles_per_cta * SCAN_TILE);
+  // pass 1 (only when chained): this CTA's total, published before the prefix of the earlier CTAs is known
+  long long prefix = 0;
+  if (gridDim.x > 1) {
+    long long mine = 0;
+    for (int i = first + tid; i < last; i += 1024) mine += in[i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(FULL, mine, o);
+    if (lane == 0) warp_tot[w] = mine;
+    __syncthreads();
+    if (w == 0) {
+      long long t = warp_tot[lane];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(FULL, t, o);
+      if (lane == 0) {
+        long long before = 0;
+        if (blockIdx.x > 0) {
+          volatile unsigned int* ep = g_scan_epoch + (blockIdx.x - 1);
+          while (*ep != epoch) __nanosleep(20);
+          __threadfence();
+          before = (long long)*(volatile unsigned long long*)(g_scan_sum + blockIdx.x - 1);
+        }
+        *(volatile unsigned long long*)(g_scan_sum + blockIdx.x) = (unsigned long long)(before + t);
+        __threadfence();
+        *(volatile unsigned int*)(g_scan_epoch + blockIdx.x) = epoch;
+        s_prefix = before;
+      }
+    }
+    __syncthreads();
+    prefix = s_prefix;
+  }
+  long long carry = prefix;
   int pass = 0;
-  for (int base = 0; base < n; base += 1024 * SCAN_ITEMS, ++pass) {
+  for (int base = first; base < last; base += SCAN_TILE, ++pass) {
     const int i0 = base + tid * SCAN_ITEMS;
     int v[SCAN_ITEMS];
-    if (i0 + SCAN_ITEMS <= n && ((reinterpret_cast<uintptr_t>(in + i0) & 15) == 0)) {
+    if (i0 + SCAN_ITEMS <= last && ((reinterpret_cast<uintptr_t>(in + i0) & 15) == 0)) {
 #pragma unroll
       for (int k = 0; k < SCAN_ITEMS; k += 4) {
         const int4 x = __ldg(reinterpret_cast<const int4*>(in + i0 + k));
@@ -40,7 +80,7 @@ exclusive_scan_kernel(const int* __restrict__ in, int n, long long* __restrict__
       }
     } else {
 #pragma unroll
-      for (int k = 0; k < SCAN_ITEMS; ++k) v[k] = i0 + k < n ? in[i0 + k] : 0;
+      for (int k = 0; k < SCAN_ITEMS; ++k) v[k] = i0 + k < last ? in[i0 + k] : 0;
     }
     long long mine = 0;
 #pragma unroll
@@ -55,30 +95,35 @@ exclusive_scan_kernel(const int* __restrict__ in, int n, long long* __restrict__
     __syncthreads();
     if (w == 0) {
       const long long t = warp_tot[lane];
-      long long s = t;
+      long long s2 = t;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
-        long long y = __shfl_up_sync(FULL, s, o);
-        if (lane >= o) s += y;
+        long long y = __shfl_up_sync(FULL, s2, o);
+        if (lane >= o) s2 += y;
       }
-      warp_tot[lane] = s - t;     // exclusive warp offsets
-      if (lane == 31) chunk_tot[pass & 1] = s;
+      warp_tot[lane] = s2 - t;     // exclusive warp offsets
+      if (lane == 31) chunk_tot[pass & 1] = s2;
     }
     __syncthreads();
     long long run = carry + warp_tot[w] + x - mine;
 #pragma unroll
     for (int k = 0; k < SCAN_ITEMS; ++k) {
-      if (i0 + k < n) out[i0 + k] = run;
+      if (i0 + k < last) out[i0 + k] = run;
       run += v[k];
     }
     carry += chunk_tot[pass & 1];
     __syncthreads();
   }
-  if (tid == 0) out[n] = carry;
+  if (tid == 0 && blockIdx.x == gridDim.x - 1) out[n] = carry;
 }
 
 int launch_exclusive_scan(const int* in, int n, long long* out, cudaStream_t s) {
-  exclusive_scan_kernel<<<1, 1024, 0, s>>>(in, n, out);
+  static unsigned int epoch = 0;
+  const int tiles = n > 0 ? (n + SCAN_TILE - 1) / SCAN_TILE : 1;
+  const int per_cta = (tiles + SCAN_MAX_CTAS - 1) / SCAN_MAX_CTAS;
+  const int ctas = (tiles + per_cta - 1) / per_cta;
+  if (++epoch == 0) ++epoch;                       // 0 is the state of a fresh module
+  exclusive_scan_kernel<<<ctas, 1024, 0, s>>>(in, n, out, epoch, per_cta);
   return check_launch("exclusive_scan_kernel");
 }
 

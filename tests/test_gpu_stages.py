@@ -301,3 +301,24 @@ def test_score_dist_many_matches_and_ties(eng, oracle):
         ok = ~np.isnan(want_ap)
         np.testing.assert_allclose(ap[ok], want_ap[ok], rtol=0, atol=1e-13)
         assert ap[6] == -1.0
+
+
+@pytest.mark.parametrize("n", [0, 1, 31, 1000, 16384, 16385, 100001, 2200003])
+def test_exclusive_scan_matches_numpy(eng, n):
+    """reid_exclusive_scan (CSR / CSC offsets, identity index): single CTA and the chained multi-CTA schedule."""
+    import ctypes as C
+    import importlib
+    _lib = importlib.import_module("multimodal-reid_b200._lib")
+    rng = np.random.default_rng(n)
+    x = rng.integers(0, 1000, n, dtype=np.int32)
+    # one unaligned view as well: the kernel vectorises only 16-byte aligned groups
+    for off in (0, 1):
+        buf = torch.zeros(n + 4, dtype=torch.int32, device=eng.device)
+        buf[off: off + n] = torch.from_numpy(x).to(eng.device)
+        src = buf[off: off + n]
+        out = torch.full((n + 1,), -1, dtype=torch.int64, device=eng.device)
+        for _ in range(2):      # twice: the chain's epoch flags must not leak between launches
+            _lib.call("reid_exclusive_scan", C.c_void_p(src.data_ptr()), n, C.c_void_p(out.data_ptr()),
+                      C.c_void_p(torch.cuda.current_stream().cuda_stream))
+        want = np.concatenate([[0], np.cumsum(x.astype(np.int64))])
+        assert np.array_equal(out.cpu().numpy(), want)
