@@ -111,6 +111,33 @@ class Comm:
         self.dist.all_gather_into_tensor(out, pad, group=self.group)
         return out
 
+    def gather_stack(self, local: torch.Tensor) -> torch.Tensor:
+        """All ranks pass the same shape; returns [world, *shape] (rank-major, one NCCL call)."""
+        local = local.contiguous()
+        if self.world == 1:
+            return local.unsqueeze(0)
+        out = local.new_empty((self.world,) + tuple(local.shape))
+        self.dist.all_gather_into_tensor(out, local, group=self.group)
+        return out
+
+    def nmax(self, n: int) -> int:
+        return (n + self.world - 1) // self.world
+
+    def pad_rows(self, local: torch.Tensor, n: int) -> torch.Tensor:
+        """Zero-pads this rank's rows to ceil(n / world) so that every rank contributes the same shape."""
+        nm = self.nmax(n)
+        if local.shape[0] == nm:
+            return local
+        pad = local.new_zeros((nm,) + tuple(local.shape[1:]))
+        pad[: local.shape[0]] = local
+        return pad
+
+    @staticmethod
+    def interleave(stacked: torch.Tensor, n: int) -> torch.Tensor:
+        """stacked[r, l] is global row r + l*world -> [n, ...] in global order (a view; copy with .contiguous())."""
+        P, nm = stacked.shape[0], stacked.shape[1]
+        return stacked.transpose(0, 1).reshape((nm * P,) + tuple(stacked.shape[2:]))[:n]
+
     def all_reduce_sum(self, t: torch.Tensor) -> torch.Tensor:
         if self.world > 1:
             self.dist.all_reduce(t, group=self.group)
@@ -142,6 +169,7 @@ class Engine:
         # N x N contraction of one rank owning every row: upper-triangle tiles only, mirrored (dist_tcgen05.cu).
         # Ranks of a multi-GPU job own strided row subsets and always run the full schedule.
         self.symmetric = True
+        self._cw_hint = {}          # k1 -> width of the V rows exchanged between ranks (see rerank_from_panel)
 
     # ------------------------------------------------------------------ timing helpers
     def enable_timers(self, on=True):
@@ -310,6 +338,42 @@ class Engine:
                   rows, _ptr(qoff), cap_sort, _ptr(Qc), _ptr(Qv), _ptr(Qn), _stream())
         return Qc, Qv, qoff, Qn, total
 
+    def _query_expansion_sharded(self, nbr, k2, Vc, Vv, Vn, Vn_true, N: int):
+        """K7 for this rank's rows + the exchange.  Every rank bounds the union size of EVERY row (cheap), so pool
+        sizes and offsets of all ranks are known everywhere without a collective: one 8(P+1)-byte D2H sizes the
+        buffers, two all-gathers move the pools (int32: columns | counts, float16: values; same pitch, so one offset
+        array addresses both)."""
+        cm = self.comm
+        r, P = cm.rank, cm.world
+        nloc, nm = cm.local_count(N), cm.nmax(N)
+        K, cap1 = nbr.shape[1], Vc.shape[1]
+        with self.span("qe"):
+            ub = self._zeros((nm * P,), torch.int32)
+            _lib.call("reid_qe_bound", _ptr(nbr), K, k2, _ptr(Vn), 0, 1, N, _ptr(ub), _stream())
+            ub_rm = ub.view(nm, P).t()                               # [P, nm]: row l of rank p
+            incl = torch.cumsum(ub_rm, dim=1, dtype=torch.int64)
+            totals = incl[:, -1]
+            stats = torch.cat([totals, ub.max().to(torch.int64).reshape(1), Vn_true.max().to(torch.int64).reshape(1)]).tolist()
+            tmax, total, ub_max, widest = max(stats[:P]), stats[r], stats[P], stats[P + 1]
+            excl = incl - ub_rm
+            pitch = (tmax + nm + 7) // 8 * 8                         # pool | per-row counts, in elements
+            ibuf = self._zeros((pitch,), torch.int32)
+            hbuf = self._zeros((pitch,), torch.float16)
+            qoff_l = torch.cat([excl[r, :nloc], totals[r: r + 1]]).contiguous()
+            Qn_l = ibuf[tmax: tmax + nloc]
+            cap_sort = 32
+            while cap_sort < min(ub_max, 4096):
+                cap_sort *= 2
+            _lib.call("reid_qe_k2_capped", _ptr(nbr), K, k2, _ptr(Vc), _ptr(Vv), _ptr(Vn), cap1, r, P, nloc,
+                      _ptr(qoff_l), cap_sort, _ptr(ibuf), _ptr(hbuf), _ptr(Qn_l), _stream())
+        with self.span("x_qe"):
+            iall = cm.gather_stack(ibuf)                             # [P, pitch]
+            hall = cm.gather_stack(hbuf)
+            Qn = cm.interleave(iall[:, tmax: tmax + nm], N).contiguous()
+            base = torch.arange(P, device=self.device, dtype=torch.int64).unsqueeze(1) * pitch
+            qoff = torch.cat([cm.interleave(excl + base, N), excl.new_zeros(1)]).contiguous()
+        return iall.reshape(-1), hall.reshape(-1), qoff, Qn, pitch * P, widest
+
     # ------------------------------------------------------------------ K8
     def inverted_index(self, Qc, Qv, qoff, Qn, N: int, nnz_bound: int):
         colcnt = self._zeros((N,), torch.int32)
@@ -404,25 +468,37 @@ class Engine:
         with self.span("krecip"):
             sets = self.krecip_sets(nbr, k1)
             Vc_l, Vv_l, Vn_l = self.krecip_V(sets, k1, D, key, r, P)
-        with self.span("x_V"):
-            Vc, Vv, Vn = cm.gather_rows(Vc_l, N), cm.gather_rows(Vv_l, N), cm.gather_rows(Vn_l, N)
-        if k2 != 1:
-            with self.span("qe"):
-                Qc_l, Qv_l, qoff_l, Qn_l, total = self.query_expansion(nbr, k2, Vc, Vv, Vn, nloc, r, P)
-            if P == 1:
-                Qc, Qv, qoff, Qn, nnz_bound = Qc_l, Qv_l, qoff_l, Qn_l, total
-            else:
-                with self.span("x_qe"):
-                    tmax = cm.max_int(total, self.device)
-                    Qc = cm.gather_flat(Qc_l[:total], tmax).reshape(-1)
-                    Qv = cm.gather_flat(Qv_l[:total], tmax).reshape(-1)
-                    Qn = cm.gather_rows(Qn_l, N)
-                    # global offset of row i = (i mod P) * tmax + qoff_rank[i div P]
-                    offs = cm.gather_rows(qoff_l[:nloc], N)
-                    owner = torch.arange(N, device=self.device, dtype=torch.int64) % P
-                    qoff = torch.cat([offs + owner * tmax, offs.new_zeros(1)])
-                    nnz_bound = tmax * P
+        if P == 1:
+            Vc, Vv, Vn = Vc_l, Vv_l, Vn_l
+            if k2 != 1:
+                with self.span("qe"):
+                    Qc, Qv, qoff, Qn, nnz_bound = self.query_expansion(nbr, k2, Vc, Vv, Vn, nloc, r, P)
         else:
+            # The ELL rows are (k1+1)(h+1) wide but hold ~k1 entries: only a prefix of `cw` entries per row is exchanged,
+            # columns and values packed into one byte record per row (one all-gather instead of two 20 MB ones).  cw is
+            # remembered from the previous call; the widest row of THIS call comes back with the pool sizes below (the
+            # step's single host read), and if it did not fit the exchange is repeated with the right width.
+            with self.span("x_V"):
+                Vn = cm.gather_rows(Vn_l, N)
+            cw = min(self._cw_hint.get(k1, 64), Vc_l.shape[1])
+            while True:
+                with self.span("x_V"):
+                    rec = torch.cat([Vc_l[:, :cw].contiguous().view(torch.uint8).reshape(nloc, 4 * cw),
+                                     Vv_l[:, :cw].contiguous().view(torch.uint8).reshape(nloc, 2 * cw)], dim=1)
+                    allrec = cm.interleave(cm.gather_stack(cm.pad_rows(rec, N)), N)          # [N, 6 cw] view
+                    Vc = allrec[:, : 4 * cw].contiguous().view(torch.int32)
+                    Vv = allrec[:, 4 * cw:].contiguous().view(torch.float16)
+                    Vn_fit = torch.clamp(Vn, max=cw)          # keeps a too-narrow attempt inside its buffers
+                if k2 != 1:
+                    Qc, Qv, qoff, Qn, nnz_bound, widest = self._query_expansion_sharded(nbr, k2, Vc, Vv, Vn_fit, Vn, N)
+                else:
+                    widest = int(Vn.max().item())
+                self._cw_hint[k1] = min(Vc_l.shape[1], (widest + 7) // 8 * 8 + 8)
+                if widest <= cw:
+                    break
+                cw = self._cw_hint[k1]
+            Vn = Vn_fit
+        if k2 == 1:
             cap1 = Vc.shape[1]
             qoff = self._empty((N + 1,), torch.int64)
             _lib.call("reid_ell_offsets", N, cap1, _ptr(qoff), _stream())
@@ -494,10 +570,18 @@ class Engine:
             launch(ap, first, hist, nvalid)
         q_all = nq if q_total is None else q_total
         with self.span("x_score"):
-            ap_all = cm.gather_rows(ap, q_all)
-            first_all = cm.gather_rows(first, q_all)
-            cm.all_reduce_sum(hist)
-            cm.all_reduce_sum(nvalid)
+            if cm.world == 1:
+                ap_all, first_all = ap, first
+            else:
+                # one all-gather (AP float64 | first hit int32 as bytes) and one all-reduce (histogram | n_valid)
+                rec = torch.cat([cm.pad_rows(ap, q_all).view(torch.uint8), cm.pad_rows(first, q_all).view(torch.uint8)])
+                allrec = cm.gather_stack(rec)
+                nm = cm.nmax(q_all)
+                ap_all = cm.interleave(allrec[:, : 8 * nm].contiguous().view(torch.float64), q_all).contiguous()
+                first_all = cm.interleave(allrec[:, 8 * nm:].contiguous().view(torch.int32), q_all).contiguous()
+                both = torch.cat([hist, nvalid])
+                cm.all_reduce_sum(both)
+                hist, nvalid = both[:max_rank].contiguous(), both[max_rank:].contiguous()
         cmc = self._empty((max_rank,), torch.float32)
         mAP = self._empty((1,), torch.float64)
         _lib.call("reid_score_finalize", _ptr(ap_all), q_all, _ptr(hist), max_rank, _ptr(nvalid), _ptr(cmc),
