@@ -86,6 +86,14 @@ class Comm:
         """#{i < n : i mod world == rank}"""
         return (n - self.rank + self.world - 1) // self.world if n > self.rank else 0
 
+    def _all_gather(self, local: torch.Tensor) -> torch.Tensor:
+        """One all-gather of equally shaped contiguous tensors -> [world, *shape].  The output is allocated in the
+        concatenated form (world * shape[0], ...), which every backend accepts (gloo rejects the stacked form)."""
+        flat = local.reshape(1) if local.dim() == 0 else local
+        out = flat.new_empty((self.world * flat.shape[0],) + tuple(flat.shape[1:]))
+        self.dist.all_gather_into_tensor(out, flat, group=self.group)
+        return out.view((self.world,) + tuple(local.shape))
+
     def gather_rows(self, local: torch.Tensor, n: int) -> torch.Tensor:
         """local[l] is global row rank + l*world; returns all n rows in global order."""
         if self.world == 1:
@@ -95,8 +103,7 @@ class Comm:
         if local.shape[0] != nmax:
             pad = local.new_zeros((nmax,) + tuple(local.shape[1:]))
             pad[: local.shape[0]] = local
-        out = local.new_empty((self.world, nmax) + tuple(local.shape[1:]))
-        self.dist.all_gather_into_tensor(out, pad.contiguous(), group=self.group)
+        out = self._all_gather(pad.contiguous())
         # [P, nmax, ...] -> interleave -> [nmax*P, ...]
         out = out.transpose(0, 1).reshape((nmax * self.world,) + tuple(local.shape[1:]))
         return out[:n].contiguous()
@@ -107,18 +114,14 @@ class Comm:
             return local.reshape(1, -1)
         pad = local.new_zeros((size_max,))
         pad[: local.shape[0]] = local
-        out = local.new_empty((self.world, size_max))
-        self.dist.all_gather_into_tensor(out, pad, group=self.group)
-        return out
+        return self._all_gather(pad)
 
     def gather_stack(self, local: torch.Tensor) -> torch.Tensor:
         """All ranks pass the same shape; returns [world, *shape] (rank-major, one NCCL call)."""
         local = local.contiguous()
         if self.world == 1:
             return local.unsqueeze(0)
-        out = local.new_empty((self.world,) + tuple(local.shape))
-        self.dist.all_gather_into_tensor(out, local, group=self.group)
-        return out
+        return self._all_gather(local)
 
     def nmax(self, n: int) -> int:
         return (n + self.world - 1) // self.world
@@ -137,6 +140,17 @@ class Comm:
         """stacked[r, l] is global row r + l*world -> [n, ...] in global order (a view; copy with .contiguous())."""
         P, nm = stacked.shape[0], stacked.shape[1]
         return stacked.transpose(0, 1).reshape((nm * P,) + tuple(stacked.shape[2:]))[:n]
+
+    @staticmethod
+    def pool_layout(ub: torch.Tensor, P: int):
+        """ub: [nm * P] upper bounds of the rows' union sizes in GLOBAL row order (zero for padding rows).
+        Rank p stores its rows' unions back to back in its own pool, in row order.  Returns (totals[P], excl[P, nm]):
+        pool sizes and the offset of row p + l*P inside rank p's pool -- what every rank can compute without
+        talking to the others."""
+        nm = ub.shape[0] // P
+        ub_rm = ub.view(nm, P).t()                               # [P, nm]: row l of rank p
+        incl = torch.cumsum(ub_rm, dim=1, dtype=torch.int64)
+        return incl[:, -1], incl - ub_rm
 
     def all_reduce_sum(self, t: torch.Tensor) -> torch.Tensor:
         if self.world > 1:
@@ -350,12 +364,9 @@ class Engine:
         with self.span("qe"):
             ub = self._zeros((nm * P,), torch.int32)
             _lib.call("reid_qe_bound", _ptr(nbr), K, k2, _ptr(Vn), 0, 1, N, _ptr(ub), _stream())
-            ub_rm = ub.view(nm, P).t()                               # [P, nm]: row l of rank p
-            incl = torch.cumsum(ub_rm, dim=1, dtype=torch.int64)
-            totals = incl[:, -1]
+            totals, excl = cm.pool_layout(ub, P)
             stats = torch.cat([totals, ub.max().to(torch.int64).reshape(1), Vn_true.max().to(torch.int64).reshape(1)]).tolist()
             tmax, total, ub_max, widest = max(stats[:P]), stats[r], stats[P], stats[P + 1]
-            excl = incl - ub_rm
             pitch = (tmax + nm + 7) // 8 * 8                         # pool | per-row counts, in elements
             ibuf = self._zeros((pitch,), torch.int32)
             hbuf = self._zeros((pitch,), torch.float16)
