@@ -183,6 +183,7 @@ class Engine:
         # N x N contraction of one rank owning every row: upper-triangle tiles only, mirrored (dist_tcgen05.cu).
         # Ranks of a multi-GPU job own strided row subsets and always run the full schedule.
         self.symmetric = True
+        self.qe_replicate_below = 300_000   # N * k2 up to which every rank runs the query expansion for all rows
         self._cw_hint = {}          # k1 -> width of the V rows exchanged between ranks (see rerank_from_panel)
 
     # ------------------------------------------------------------------ timing helpers
@@ -331,8 +332,9 @@ class Engine:
         return Vc, Vv, Vn
 
     # ------------------------------------------------------------------ K7
-    def query_expansion(self, nbr, k2, Vc, Vv, Vn, rows, row0=0, row_stride=1, cap_sort: int = 0):
-        """Returns (Qc, Qv, qoff[rows+1] int64, Qn[rows]) for the row window."""
+    def query_expansion(self, nbr, k2, Vc, Vv, Vn, rows, row0=0, row_stride=1, cap_sort: int = 0, extra=None):
+        """Returns (Qc, Qv, qoff[rows+1] int64, Qn[rows], pool size) for the row window.  `extra`: a one-element
+        device tensor read back with the sizes (same D2H); its value is left in self.last_extra."""
         K = nbr.shape[1]
         cap1 = Vc.shape[1]
         ub = self._empty((rows,), torch.int32)
@@ -340,7 +342,12 @@ class Engine:
         qoff = self._empty((rows + 1,), torch.int64)
         _lib.call("reid_exclusive_scan", _ptr(ub), rows, _ptr(qoff), _stream())
         # 16-byte D2H: pool size and the longest union (sizes the per-warp sort buffers)
-        total, ub_max = (int(v) for v in torch.stack([qoff[rows], ub.max().to(torch.int64)]).tolist()) if rows else (0, 0)
+        stats = [qoff[rows].reshape(1), ub.max().to(torch.int64).reshape(1)] if rows else []
+        if extra is not None:
+            stats.append(extra.to(torch.int64).reshape(1))
+        vals = [int(v) for v in torch.cat(stats).tolist()] if stats else []
+        total, ub_max = (vals[0], vals[1]) if rows else (0, 0)
+        self.last_extra = vals[-1] if extra is not None else None
         Qc = self._empty((max(total, 1),), torch.int32)
         Qv = self._empty((max(total, 1),), torch.float16)
         Qn = self._empty((rows,), torch.int32)
@@ -486,21 +493,29 @@ class Engine:
                     Qc, Qv, qoff, Qn, nnz_bound = self.query_expansion(nbr, k2, Vc, Vv, Vn, nloc, r, P)
         else:
             # The ELL rows are (k1+1)(h+1) wide but hold ~k1 entries: only a prefix of `cw` entries per row is exchanged,
-            # columns and values packed into one byte record per row (one all-gather instead of two 20 MB ones).  cw is
+            # count, columns and values packed into one byte record per row (one all-gather for the whole of V).  cw is
             # remembered from the previous call; the widest row of THIS call comes back with the pool sizes below (the
             # step's single host read), and if it did not fit the exchange is repeated with the right width.
-            with self.span("x_V"):
-                Vn = cm.gather_rows(Vn_l, N)
             cw = min(self._cw_hint.get(k1, 64), Vc_l.shape[1])
+            replicate = k2 != 1 and N * k2 <= self.qe_replicate_below
             while True:
                 with self.span("x_V"):
-                    rec = torch.cat([Vc_l[:, :cw].contiguous().view(torch.uint8).reshape(nloc, 4 * cw),
+                    rec = torch.cat([Vn_l.view(torch.uint8).reshape(nloc, 4),
+                                     Vc_l[:, :cw].contiguous().view(torch.uint8).reshape(nloc, 4 * cw),
                                      Vv_l[:, :cw].contiguous().view(torch.uint8).reshape(nloc, 2 * cw)], dim=1)
-                    allrec = cm.interleave(cm.gather_stack(cm.pad_rows(rec, N)), N)          # [N, 6 cw] view
-                    Vc = allrec[:, : 4 * cw].contiguous().view(torch.int32)
-                    Vv = allrec[:, 4 * cw:].contiguous().view(torch.float16)
+                    allrec = cm.interleave(cm.gather_stack(cm.pad_rows(rec, N)), N)          # [N, 4 + 6 cw] view
+                    Vn = allrec[:, :4].contiguous().view(torch.int32).reshape(N)
+                    Vc = allrec[:, 4: 4 + 4 * cw].contiguous().view(torch.int32)
+                    Vv = allrec[:, 4 + 4 * cw:].contiguous().view(torch.float16)
                     Vn_fit = torch.clamp(Vn, max=cw)          # keeps a too-narrow attempt inside its buffers
-                if k2 != 1:
+                if replicate:
+                    # small problems: every rank expands all N rows itself (0.1 ms at Duke scale) instead of two more
+                    # latency-bound all-gathers
+                    with self.span("qe"):
+                        Qc, Qv, qoff, Qn, nnz_bound = self.query_expansion(nbr, k2, Vc, Vv, Vn_fit, N, 0, 1,
+                                                                           extra=Vn.max())
+                    widest = self.last_extra
+                elif k2 != 1:
                     Qc, Qv, qoff, Qn, nnz_bound, widest = self._query_expansion_sharded(nbr, k2, Vc, Vv, Vn_fit, Vn, N)
                 else:
                     widest = int(Vn.max().item())
@@ -584,14 +599,14 @@ class Engine:
             if cm.world == 1:
                 ap_all, first_all = ap, first
             else:
-                # one all-gather (AP float64 | first hit int32 as bytes) and one all-reduce (histogram | n_valid)
-                rec = torch.cat([cm.pad_rows(ap, q_all).view(torch.uint8), cm.pad_rows(first, q_all).view(torch.uint8)])
-                allrec = cm.gather_stack(rec)
+                # one all-gather: AP float64 | first hit int32 | this rank's CMC histogram and n_valid, as bytes
                 nm = cm.nmax(q_all)
+                rec = torch.cat([cm.pad_rows(ap, q_all).view(torch.uint8), cm.pad_rows(first, q_all).view(torch.uint8),
+                                 hist.view(torch.uint8), nvalid.view(torch.uint8)])
+                allrec = cm.gather_stack(rec)
                 ap_all = cm.interleave(allrec[:, : 8 * nm].contiguous().view(torch.float64), q_all).contiguous()
-                first_all = cm.interleave(allrec[:, 8 * nm:].contiguous().view(torch.int32), q_all).contiguous()
-                both = torch.cat([hist, nvalid])
-                cm.all_reduce_sum(both)
+                first_all = cm.interleave(allrec[:, 8 * nm: 12 * nm].contiguous().view(torch.int32), q_all).contiguous()
+                both = allrec[:, 12 * nm:].contiguous().view(torch.int32).sum(0, dtype=torch.int32)
                 hist, nvalid = both[:max_rank].contiguous(), both[max_rank:].contiguous()
         cmc = self._empty((max_rank,), torch.float32)
         mAP = self._empty((1,), torch.float64)

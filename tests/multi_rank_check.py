@@ -35,9 +35,12 @@ def main():
         q, g = sh.q, sh.g
         ids = [t.to(dev) for t in (qp, gp, qc, gc)]
         ref = single.rerank_features(feats, q, k1, k2, 0.3, normalize=True)
-        got = multi.rerank_features(feats, q, k1, k2, 0.3, normalize=True)
         mine = slice(rank, q, world)
-        assert torch.equal(got[:, :g], ref[mine, :g]), f"{name}: rank {rank} rows differ from the single-rank result"
+        for below in (300_000, 0):          # query expansion replicated on every rank / sharded + exchanged
+            multi.qe_replicate_below = below
+            got = multi.rerank_features(feats, q, k1, k2, 0.3, normalize=True)
+            assert torch.equal(got[:, :g], ref[mine, :g]), \
+                f"{name}: rank {rank} rows differ from the single-rank result (qe_replicate_below={below})"
         r1 = single.evaluate_dist(ref, g, *ids, 50)
         r2 = multi.evaluate_dist(got, g, ids[0][mine].contiguous(), ids[1], ids[2][mine].contiguous(), ids[3], 50,
                                  q_total=q)

@@ -42,11 +42,15 @@ def _worker(rank, world, port, n_rows, ret):
             cw = 4
             ci = torch.from_numpy((mine[:, None] * 100 + np.arange(cw)).astype(np.int32)).reshape(-1, cw)
             cv = torch.from_numpy((mine[:, None] + np.arange(cw) / 8).astype(np.float16)).reshape(-1, cw)
-            rec = torch.cat([ci.contiguous().view(torch.uint8).reshape(mine.size, 4 * cw),
+            cn = torch.from_numpy((mine % 5).astype(np.int32))
+            rec = torch.cat([cn.view(torch.uint8).reshape(mine.size, 4),
+                             ci.contiguous().view(torch.uint8).reshape(mine.size, 4 * cw),
                              cv.contiguous().view(torch.uint8).reshape(mine.size, 2 * cw)], dim=1)
             allrec = cm.interleave(cm.gather_stack(cm.pad_rows(rec, n)), n)
-            gi = allrec[:, : 4 * cw].contiguous().view(torch.int32)
-            gv = allrec[:, 4 * cw:].contiguous().view(torch.float16)
+            gn = allrec[:, :4].contiguous().view(torch.int32).reshape(n)
+            gi = allrec[:, 4: 4 + 4 * cw].contiguous().view(torch.int32)
+            gv = allrec[:, 4 + 4 * cw:].contiguous().view(torch.float16)
+            assert np.array_equal(gn.numpy(), np.arange(n) % 5)
             assert np.array_equal(gi.numpy(), np.arange(n)[:, None] * 100 + np.arange(cw))
             assert np.array_equal(gv.numpy(), (np.arange(n)[:, None] + np.arange(cw) / 8).astype(np.float16))
             # pool layout: every rank derives every rank's pool size and row offsets from the global bounds
@@ -65,18 +69,23 @@ def _worker(rank, world, port, n_rows, ret):
             for i in range(n):
                 p, l = i % world, i // world
                 assert qoff[i] == p * pitch + (np.cumsum(ub[p::world]) - ub[p::world])[l]
-            # scores: AP (float64) | first hit (int32) as one byte record, histogram | n_valid as one reduce
+            # scores: AP (float64) | first hit (int32) | this rank's histogram and n_valid, one byte record per rank
             ap = torch.from_numpy(mine.astype(np.float64) / 7)
             first = torch.from_numpy(mine.astype(np.int32) * 3)
-            r = torch.cat([cm.pad_rows(ap, n).view(torch.uint8), cm.pad_rows(first, n).view(torch.uint8)])
+            hist = torch.full((5,), rank + 1, dtype=torch.int32)
+            nvalid = torch.tensor([mine.size], dtype=torch.int32)
+            r = torch.cat([cm.pad_rows(ap, n).view(torch.uint8), cm.pad_rows(first, n).view(torch.uint8),
+                           hist.view(torch.uint8), nvalid.view(torch.uint8)])
             allr = cm.gather_stack(r)
             nm = cm.nmax(n)
             ap_all = cm.interleave(allr[:, : 8 * nm].contiguous().view(torch.float64), n)
-            first_all = cm.interleave(allr[:, 8 * nm:].contiguous().view(torch.int32), n)
+            first_all = cm.interleave(allr[:, 8 * nm: 12 * nm].contiguous().view(torch.int32), n)
             assert np.array_equal(ap_all.numpy(), np.arange(n) / 7) and np.array_equal(first_all.numpy(), np.arange(n) * 3)
-            both = torch.cat([torch.full((5,), rank + 1, dtype=torch.int32), torch.tensor([mine.size], dtype=torch.int32)])
-            cm.all_reduce_sum(both)
+            both = allr[:, 12 * nm:].contiguous().view(torch.int32).sum(0, dtype=torch.int32)
             assert both[:5].tolist() == [sum(range(1, world + 1))] * 5 and int(both[5]) == n
+            chk = torch.tensor([rank + 1], dtype=torch.int32)
+            cm.all_reduce_sum(chk)
+            assert int(chk) == sum(range(1, world + 1))
             assert cm.max_int(rank * 5 + n, "cpu") == (world - 1) * 5 + n
         dist.barrier()
         dist.destroy_process_group()
