@@ -169,7 +169,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="duke")
     ap.add_argument("--engine", default="auto", choices=["auto", "simt", "tcgen05"])
-    ap.add_argument("--cpu-scale", type=int, default=4, help="CPU sample = workload with q and g divided by this")
+    ap.add_argument("--cpu-scale", type=int, default=2, help="CPU sample = workload with q and g divided by this")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--stages", action="store_true", help="print a per-stage table to stderr")
