@@ -7,9 +7,9 @@
 // SM, which is what the ordered float16 accumulation needs: it is one long dependent chain per query
 // (~90 instructions per column, ~60-130 columns) that only other queries can hide.
 //
-//   overlap_sparse_kernel   one WARP per query.  Pass A marks the targets of all the query's column lists in the
+//   overlap_sparse_kernel   four warps per query.  Pass A marks the targets of all the query's column lists in the
 //                           bitmap (order-free), prefix-sums it, pass B walks the columns in ascending order
-//                           (cp.async ring, __syncwarp per column) adding min(V_qe[i,c], V_qe[g,c]) into the packed
+//                           (cp.async ring, one CTA barrier per column) adding min(V_qe[i,c], V_qe[g,c]) into the packed
 //                           values with the reference's fp16 rounding after every add.  The record goes to global
 //                           memory.  Queries touching more than `cap` targets are put on an overflow list and
 //                           handled by the dense kernel (jaccard_score.cu).
@@ -39,7 +39,10 @@ static inline __host__ __device__ SparseRec sparse_rec(int N, int cap) {
   return r;
 }
 
-__global__ void __launch_bounds__(32)
+constexpr int OS_WARPS = 4;     // warps per query: entries of one column list hit distinct targets, so they run in parallel
+constexpr int OS_T = 32 * OS_WARPS;
+
+__global__ void __launch_bounds__(OS_T)
 overlap_sparse_kernel(const int* __restrict__ Qc, const __half* __restrict__ Qv,
                       const long long* __restrict__ qoff, const int* __restrict__ Qn,
                       const long long* __restrict__ colptr, const unsigned long long* __restrict__ csc_ent,
@@ -54,34 +57,35 @@ overlap_sparse_kernel(const int* __restrict__ Qc, const __half* __restrict__ Qv,
   long long* cstart = reinterpret_cast<long long*>(ring + OS_RING * OS_SLOT);
   int* clen = reinterpret_cast<int*>(cstart + OS_CHUNK);
   float* cval = reinterpret_cast<float*>(clen + OS_CHUNK);
+  __shared__ int s_wtot[OS_WARPS];
 
-  const int lane = threadIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   const int qi = blockIdx.x;
   const long long row = q0 + (long long)qi * q_stride;
   const long long o = qoff[row];
   const int nq = Qn[row];
   const int nw = R.nw;
 
-  for (int i = lane; i < nw; i += 32) bm[i] = 0;
-  __syncwarp();
+  for (int i = tid; i < nw; i += OS_T) bm[i] = 0;
 
   auto stage = [&](int base, int nc) {
-    __syncwarp();
-    for (int i = lane; i < nc; i += 32) {
+    __syncthreads();
+    for (int i = tid; i < nc; i += OS_T) {
       const int c = Qc[o + base + i];
       const long long a = colptr[c];
       cstart[i] = a;
       clen[i] = (int)(colptr[c + 1] - a);
       cval[i] = __half2float(Qv[o + base + i]);
     }
-    __syncwarp();
+    __syncthreads();
   };
 
   // ---------------------------------------------------------------- pass A: which targets does the query touch
+  // (order-free: warp w takes the column lists w, w + OS_WARPS, ... four at a time per lane)
   for (int base = 0; base < nq; base += OS_CHUNK) {
     const int nc = min(OS_CHUNK, nq - base);
     stage(base, nc);
-    for (int e0 = 0; e0 < nc; e0 += 4) {                  // four column lists in flight per lane
+    for (int e0 = 4 * w; e0 < nc; e0 += 4 * OS_WARPS) {
       int g[4][3];
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
@@ -107,37 +111,49 @@ overlap_sparse_kernel(const int* __restrict__ Qc, const __half* __restrict__ Qv,
       }
     }
   }
-  __syncwarp();
-  // exclusive prefix popcounts per word
-  int total = 0;
-  for (int w0 = 0; w0 < nw; w0 += 32) {
+  __syncthreads();
+  // exclusive prefix popcounts per word: every warp scans a contiguous quarter, then the quarters are offset
+  const int per_w = (nw + OS_WARPS - 1) / OS_WARPS;
+  const int wbeg = min(nw, w * per_w), wend = min(nw, wbeg + per_w);
+  int run = 0;
+  for (int w0 = wbeg; w0 < wend; w0 += 32) {
     const int i = w0 + lane;
-    const int c = i < nw ? __popc(bm[i]) : 0;
+    const int c = i < wend ? __popc(bm[i]) : 0;
     int incl = c;
 #pragma unroll
     for (int off = 1; off < 32; off <<= 1) {
       const int y = __shfl_up_sync(FULL, incl, off);
       if (lane >= off) incl += y;
     }
-    if (i < nw) pre[i] = (unsigned short)min(total + incl - c, 65535);
-    total += __shfl_sync(FULL, incl, 31);
+    if (i < wend) pre[i] = (unsigned short)min(run + incl - c, 65535);          // offset added below
+    run += __shfl_sync(FULL, incl, 31);
+  }
+  if (lane == 0) s_wtot[w] = run;
+  __syncthreads();
+  int before = 0, total = 0;
+#pragma unroll
+  for (int k = 0; k < OS_WARPS; ++k) {
+    if (k < w) before += s_wtot[k];
+    total += s_wtot[k];
   }
   if (total > cap) {                                      // too dense for the packed form: the dense kernel takes it
-    if (lane == 0) {
+    if (tid == 0) {
       rec_count[qi] = -1;
       over_list[atomicAdd(over_n, 1)] = qi;
     }
     return;
   }
-  for (int i = lane; i < total; i += 32) vals[i] = __ushort_as_half(0);
-  __syncwarp();
+  if (before)
+    for (int i = wbeg + lane; i < wend; i += 32) pre[i] = (unsigned short)(pre[i] + before);
+  for (int i = tid; i < total; i += OS_T) vals[i] = __ushort_as_half(0);
 
   // ---------------------------------------------------------------- pass B: ordered fp16 accumulation
+  // columns one after the other (the reference's rounding sequence per target), the entries of a column across the CTA
   auto issue = [&](int c) {
     const int len = min(clen[c], OS_SLOT);
     const unsigned long long* src = csc_ent + cstart[c];
     unsigned long long* dst = ring + (c % OS_RING) * OS_SLOT;
-    for (int p = lane; p < len; p += 32) cp_async8(dst + p, src + p);
+    for (int p = tid; p < len; p += OS_T) cp_async8(dst + p, src + p);
   };
   auto add = [&](unsigned long long ent, float vi) {
     const unsigned g = (unsigned)(ent & 0xffffffffu);
@@ -146,59 +162,32 @@ overlap_sparse_kernel(const int* __restrict__ Qc, const __half* __restrict__ Qv,
     const float vg = __half2float(__ushort_as_half((unsigned short)(ent >> 32)));
     vals[slot] = __float2half_rn(__fadd_rn(__half2float(vals[slot]), fminf(vi, vg)));
   };
+  static_assert(OS_SLOT == OS_T, "one ring entry per thread");
   for (int base = 0; base < nq; base += OS_CHUNK) {
     const int nc = min(OS_CHUNK, nq - base);
-    stage(base, nc);
+    stage(base, nc);                                               // also orders the prefix / zeroing above
 #pragma unroll
-    for (int s = 0; s < OS_RING - 1; ++s) {
-      if (s < nc) issue(s);
+    for (int s2 = 0; s2 < OS_RING - 1; ++s2) {
+      if (s2 < nc) issue(s2);
       cp_async_commit();
     }
     for (int e = 0; e < nc; ++e) {
-      if (e + OS_RING - 1 < nc) issue(e + OS_RING - 1);
+      cp_async_wait<OS_RING - 2>();                                // this thread's part of column e has landed
+      __syncthreads();                                             // column e staged by all threads; column e-1 applied
+      if (e + OS_RING - 1 < nc) issue(e + OS_RING - 1);            // into the slot column e-1 has just left
       cp_async_commit();
-      cp_async_wait<OS_RING - 1>();
       const float vi = cval[e];
       const int len = clen[e];
       const unsigned long long* slotp = ring + (e % OS_RING) * OS_SLOT;
-      const int lim = min(len, OS_SLOT);
-      for (int p0 = 0; p0 < lim; p0 += 128) {                      // entries of one column hit distinct targets:
-        unsigned long long ent[4];                                 // four independent read-modify-write chains
-        int sl[4];
-        float tv[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const int p = p0 + u * 32 + lane;
-          ent[u] = p < lim ? slotp[p] : ~0ull;
-        }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const unsigned g = (unsigned)(ent[u] & 0xffffffffu);
-          sl[u] = 0;
-          tv[u] = 0.0f;
-          if (ent[u] != ~0ull) {
-            const unsigned wd = bm[g >> 5];
-            sl[u] = (int)pre[g >> 5] + __popc(wd & ((1u << (g & 31)) - 1));
-            tv[u] = __half2float(vals[sl[u]]);
-          }
-        }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          if (ent[u] != ~0ull) {
-            const float vg = __half2float(__ushort_as_half((unsigned short)(ent[u] >> 32)));
-            vals[sl[u]] = __float2half_rn(__fadd_rn(tv[u], fminf(vi, vg)));
-          }
-        }
-      }
+      if (tid < len) add(slotp[tid], vi);                          // len <= OS_SLOT entries: one per thread
       if (len > OS_SLOT) {
         const unsigned long long* src = csc_ent + cstart[e];
-        for (int p = OS_SLOT + lane; p < len; p += 32) add(src[p], vi);
+        for (int p = OS_SLOT + tid; p < len; p += OS_T) add(src[p], vi);
       }
-      __syncwarp();                                                // next column sees this one's stores
     }
     cp_async_wait<0>();
   }
-  __syncwarp();
+  __syncthreads();
 
   // ---------------------------------------------------------------- the record
   unsigned char* rec = recs + (size_t)qi * R.bytes;
@@ -206,9 +195,9 @@ overlap_sparse_kernel(const int* __restrict__ Qc, const __half* __restrict__ Qv,
     uint4* dst = reinterpret_cast<uint4*>(rec);
     const uint4* src = reinterpret_cast<const uint4*>(smem_o);
     const size_t n16 = (R.vals + (((size_t)total * 2 + 15) & ~(size_t)15)) >> 4;
-    for (size_t i = lane; i < n16; i += 32) dst[i] = src[i];
+    for (size_t i = tid; i < n16; i += OS_T) dst[i] = src[i];
   }
-  if (lane == 0) rec_count[qi] = total;
+  if (tid == 0) rec_count[qi] = total;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -645,7 +634,7 @@ int launch_jaccard_sparse(const int* Qc, const __half* Qv, const long long* qoff
   REID_CUDA(cudaMemsetAsync(*over_n, 0, 4, s));
   const size_t smem1 = R.bytes + (size_t)OS_RING * OS_SLOT * 8 + OS_CHUNK * 16;
   REID_CUDA(cudaFuncSetAttribute(overlap_sparse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
-  overlap_sparse_kernel<<<nq_local, 32, smem1, s>>>(Qc, Qv, qoff, Qn, colptr, csc_ent, q0, q_stride, N, cap, recs,
+  overlap_sparse_kernel<<<nq_local, OS_T, smem1, s>>>(Qc, Qv, qoff, Qn, colptr, csc_ent, q0, q_stride, N, cap, recs,
                                                     rec_count, *over_list, *over_n);
   int rc = check_launch("overlap_sparse_kernel");
   if (rc) return rc;
