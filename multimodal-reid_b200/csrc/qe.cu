@@ -154,7 +154,7 @@ qe_expand_kernel(const int* __restrict__ nbr, int K, int k2, const int* __restri
   const int lrow = blockIdx.x * wpb + w;          // local row: qoff / Qn are indexed by it
   if (lrow >= rows) return;
   const long long row = row0 + (long long)lrow * row_stride;
-  unsigned long long* buf = smem_q + (long long)w * cap_sort;
+  unsigned long long* buf = smem_q + (long long)w * cap_sort * 2;
   const int* src = nbr + row * K;
   const long long out0 = qoff[lrow];
   const float kf = (float)k2;
@@ -163,22 +163,48 @@ qe_expand_kernel(const int* __restrict__ nbr, int K, int k2, const int* __restri
   for (int r = 0; r < k2; ++r) total += Vn[src[r]];
 
   if (total <= cap_sort) {
-    int fill = 0;
-    for (int r = 0; r < k2; ++r) {
-      const int s = src[r];
-      const int ns = Vn[s];
-      for (int j = lane; j < ns; j += 32) {
-        unsigned c = (unsigned)Vc[(long long)s * cap1 + j];
-        unsigned short hv = __half_as_ushort(Vv[(long long)s * cap1 + j]);
-        buf[fill + j] = ((unsigned long long)c << 32) | ((unsigned long long)r << 16) | hv;
+    // The k2 rows are sorted by column already: instead of sorting the concatenation, every entry finds its place in
+    // the merged order by binary searches in the other k2 - 1 lists (entries of equal column stay in neighbour order,
+    // which is the order the reference's mean adds them in).  ~4x fewer instructions than a bitonic network here.
+    unsigned long long* stage = buf + cap_sort;           // second half of this warp's buffer: the lists as loaded
+    int my_off = 0, my_len = 0;                           // lane r < k2: start and length of list r in `stage`
+    {
+      int fill = 0;
+      for (int r = 0; r < k2; ++r) {
+        const int s = src[r];
+        const int ns = Vn[s];
+        for (int j = lane; j < ns; j += 32) {
+          unsigned c = (unsigned)Vc[(long long)s * cap1 + j];
+          unsigned short hv = __half_as_ushort(Vv[(long long)s * cap1 + j]);
+          stage[fill + j] = ((unsigned long long)c << 32) | ((unsigned long long)r << 16) | hv;
+        }
+        if (lane == r) { my_off = fill; my_len = ns; }
+        fill += ns;
       }
-      fill += ns;
     }
-    int P = 32;
-    while (P < total) P <<= 1;
-    for (int j = total + lane; j < P; j += 32) buf[j] = ~0ull;
     __syncwarp();
-    warp_bitonic_u64(buf, P, lane);
+    for (int j0 = 0; j0 < total; j0 += 32) {
+      const int j = j0 + lane;
+      const bool on = j < total;
+      const unsigned long long e = on ? stage[j] : 0ull;
+      const unsigned col = (unsigned)(e >> 32);
+      const int r = (int)((e >> 16) & 0xffffu);
+      int rank = 0;
+      for (int r2 = 0; r2 < k2; ++r2) {
+        const int off2 = __shfl_sync(FULL, my_off, r2), len2 = __shfl_sync(FULL, my_len, r2);
+        if (!on) continue;
+        if (r2 == r) { rank += j - off2; continue; }
+        int lo = 0, hi = len2;                            // #{entries of list r2 with column < col}
+        while (lo < hi) {
+          const int mid = (lo + hi) >> 1;
+          if ((unsigned)(stage[off2 + mid] >> 32) < col) lo = mid + 1; else hi = mid;
+        }
+        if (r2 < r && lo < len2 && (unsigned)(stage[off2 + lo] >> 32) == col) ++lo;   // an equal column of an earlier list
+        rank += lo;
+      }
+      if (on) buf[rank] = e;
+    }
+    __syncwarp();
     int nout = 0;
     for (int j0 = 0; j0 < total; j0 += 32) {
       const int j = j0 + lane;
@@ -256,11 +282,11 @@ int launch_qe_expand(const int* nbr, int K, int k2, const int* Vc, const __half*
                      int* Qc, __half* Qv, int* Qn, cudaStream_t s) {
   if (rows == 0) return REID_OK;
   REID_REQUIRE(k2 >= 1 && k2 <= K && k2 <= 32, "qe: k2=%d outside [1, min(K=%d, 32)]", k2, K);
-  REID_REQUIRE(cap_sort >= 32 && (cap_sort & (cap_sort - 1)) == 0 && cap_sort <= 16384,
-               "qe: sort capacity %d must be a power of two in [32, 16384]", cap_sort);
-  int wpb = 8;                                        // keep a CTA's sort buffers <= 32 KB so several CTAs share an SM
-  while (wpb > 1 && (long long)wpb * cap_sort * 8 > 32 * 1024) wpb >>= 1;
-  const int smem = wpb * cap_sort * 8;
+  REID_REQUIRE(cap_sort >= 32 && (cap_sort & (cap_sort - 1)) == 0 && cap_sort <= 8192,
+               "qe: sort capacity %d must be a power of two in [32, 8192]", cap_sort);
+  int wpb = 8;                                        // keep a CTA's merge buffers <= 32 KB so several CTAs share an SM
+  while (wpb > 1 && (long long)wpb * cap_sort * 16 > 32 * 1024) wpb >>= 1;
+  const int smem = wpb * cap_sort * 16;              // per warp: merged order | the lists as loaded
   REID_CUDA(cudaFuncSetAttribute(qe_expand_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   qe_expand_kernel<<<cdiv(rows, wpb), wpb * 32, smem, s>>>(nbr, K, k2, Vc, Vv, Vn, cap1, row0,
                                                           row_stride, rows, qoff, cap_sort, Qc, Qv, Qn);
