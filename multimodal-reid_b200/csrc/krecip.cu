@@ -13,32 +13,44 @@
 namespace reid {
 
 // R_depth(i) = { nbr[i][r] : r < depth, i in nbr[nbr[i][r]][0:depth] }, kept in list order.
-__global__ void __launch_bounds__(256)
+// One warp per row; the (k1+1)^2 (neighbour r, position j) probes of the neighbours' lists are independent loads
+// spread over the lanes (a serial walk over r paid one L2 round trip per neighbour), hits are collected as bit masks
+// and compacted in list order.
+constexpr int RS_WPB = 8;
+constexpr int RS_MAXK = 128;           // k1 + 1 <= 128
+__global__ void __launch_bounds__(RS_WPB * 32)
 reciprocal_sets_kernel(const int* __restrict__ nbr, int N, int K, int k1p, int h,
                        int* __restrict__ rfull, int* __restrict__ nfull,
                        int* __restrict__ rhalf, int* __restrict__ nhalf) {
-  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  __shared__ unsigned bits[RS_WPB][2][RS_MAXK / 32];
+  const int w = threadIdx.x >> 5;
+  const int row = blockIdx.x * RS_WPB + w;
   if (row >= N) return;
   const int lane = lane_id();
   const int* mine = nbr + (long long)row * K;
-  int cf = 0, ch = 0;
-  for (int r = 0; r < k1p; ++r) {
+  if (lane < 2 * (RS_MAXK / 32)) (&bits[w][0][0])[lane] = 0;
+  __syncwarp();
+  const int npairs = k1p * k1p;
+  for (int p = lane; p < npairs; p += 32) {
+    const int r = p / k1p, j = p - r * k1p;
     const int c = mine[r];
-    const int* theirs = nbr + (long long)c * K;
-    bool hf = false, hh = false;
-    for (int j = lane; j < k1p; j += 32) {
-      bool eq = theirs[j] == row;
-      hf |= eq;
-      hh |= eq && (j < h);
+    if (nbr[(long long)c * K + j] == row) {
+      atomicOr(&bits[w][0][r >> 5], 1u << (r & 31));
+      if (j < h && r < h) atomicOr(&bits[w][1][r >> 5], 1u << (r & 31));
     }
-    const bool anyf = __any_sync(FULL, hf);
-    const bool anyh = __any_sync(FULL, hh) && (r < h);
-    if (lane == 0) {
-      if (anyf) rfull[(long long)row * k1p + cf] = c;
-      if (anyh) rhalf[(long long)row * h + ch] = c;
-    }
-    cf += anyf;
-    ch += anyh;
+  }
+  __syncwarp();
+  int cf = 0, ch = 0;
+  for (int r0 = 0; r0 < k1p; r0 += 32) {
+    const int r = r0 + lane;
+    const bool f = r < k1p && ((bits[w][0][r0 >> 5] >> lane) & 1u);
+    const bool hb = r < k1p && ((bits[w][1][r0 >> 5] >> lane) & 1u);
+    const unsigned bf = __ballot_sync(FULL, f), bh = __ballot_sync(FULL, hb);
+    const unsigned below = (1u << lane) - 1u;
+    if (f) rfull[(long long)row * k1p + cf + __popc(bf & below)] = mine[r];
+    if (hb) rhalf[(long long)row * h + ch + __popc(bh & below)] = mine[r];
+    cf += __popc(bf);
+    ch += __popc(bh);
   }
   if (lane == 0) { nfull[row] = cf; nhalf[row] = ch; }
 }
@@ -59,7 +71,7 @@ __device__ __forceinline__ void warp_bitonic_i32(int* a, int P, int lane) {
   }
 }
 
-// per-warp shared memory: R list [k1p] | E list [capP] | weights [cap1]
+// per-warp shared memory: R list [k1p] | E list [capP] | weights [cap1] | 3 x [k1p] candidate bookkeeping
 __global__ void __launch_bounds__(128)
 expand_weights_kernel(const int* __restrict__ rfull, const int* __restrict__ nfull,
                       const int* __restrict__ rhalf, const int* __restrict__ nhalf, int row0,
@@ -72,7 +84,7 @@ expand_weights_kernel(const int* __restrict__ rfull, const int* __restrict__ nfu
   const int lrow = blockIdx.x * wpb + w;          // local row: D / rowmax / V are indexed by it
   if (lrow >= rows) return;
   const int row = row0 + lrow * row_stride;       // global probe index
-  const int per_warp = k1p + capP + cap1;
+  const int per_warp = k1p + capP + cap1 + 3 * k1p;
   int* R = smem_i + (long long)w * per_warp;
   int* E = R + k1p;
   float* W = reinterpret_cast<float*>(E + capP);
@@ -84,24 +96,42 @@ expand_weights_kernel(const int* __restrict__ rfull, const int* __restrict__ nfu
     E[j] = v;
   }
   __syncwarp();
-  int nE = nR;
-  for (int a = 0; a < nR; ++a) {
-    const int c = R[a];
-    const int nc = nhalf[c];
-    int inter = 0;
-    for (int j0 = 0; j0 < nc; j0 += 32) {
-      const int j = j0 + lane;
+  // 2/3 rule for every candidate c = R[a] (reranking.py:60-67), all (candidate, half-list entry) pairs in parallel:
+  // lanes take pairs p = a * h + j; an entry counts if it is in R; candidate a is accepted if 3 * |Rc & R| > 2 * |Rc|
+  int* cntS = reinterpret_cast<int*>(W + cap1);       // [k1p] |Rc & R|
+  int* ncS = cntS + k1p;                              // [k1p] |Rc|
+  int* offS = ncS + k1p;                              // [k1p] where an accepted Rc goes in E, -1 if rejected
+  for (int a = lane; a < nR; a += 32) { cntS[a] = 0; ncS[a] = nhalf[R[a]]; }
+  __syncwarp();
+  const int npairs = nR * h;
+  for (int p = lane; p < npairs; p += 32) {
+    const int a = p / h, j = p - a * h;
+    if (j < ncS[a]) {
+      const int v = rhalf[(long long)R[a] * h + j];
       bool member = false;
-      if (j < nc) {
-        const int v = rhalf[(long long)c * h + j];
-        for (int b = 0; b < nR; ++b) member |= (R[b] == v);
-      }
-      inter += __popc(__ballot_sync(FULL, member));
+      for (int b = 0; b < nR; ++b) member |= (R[b] == v);
+      if (member) atomicAdd(&cntS[a], 1);
     }
-    if (3 * inter > 2 * nc) {                      // len(intersect) > 2/3 * len(candidate set)
-      for (int j = lane; j < nc; j += 32) E[nE + j] = rhalf[(long long)c * h + j];
-      nE += nc;
+  }
+  __syncwarp();
+  int nE = nR;
+  for (int a0 = 0; a0 < nR; a0 += 32) {
+    const int a = a0 + lane;
+    const bool acc = a < nR && 3 * cntS[a] > 2 * ncS[a];       // len(intersect) > 2/3 * len(candidate set)
+    const int len = acc ? ncS[a] : 0;
+    int incl = len;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(FULL, incl, o);
+      if (lane >= o) incl += y;
     }
+    if (a < nR) offS[a] = acc ? nE + incl - len : -1;
+    nE += __shfl_sync(FULL, incl, 31);
+  }
+  __syncwarp();
+  for (int p = lane; p < npairs; p += 32) {
+    const int a = p / h, j = p - a * h;
+    if (offS[a] >= 0 && j < ncS[a]) E[offS[a] + j] = rhalf[(long long)R[a] * h + j];
   }
   __syncwarp();
   // sort + unique (np.unique, reranking.py:69)
@@ -146,7 +176,8 @@ int launch_reciprocal_sets(const int* nbr, int N, int K, int k1, int* rfull, int
   if (N == 0) return REID_OK;
   const int k1p = k1 + 1, h = half_k(k1);
   REID_REQUIRE(K >= k1p, "reciprocal_sets: neighbour table width %d < k1+1=%d", K, k1p);
-  const int wpb = 8;
+  REID_REQUIRE(k1p <= RS_MAXK, "reciprocal_sets: k1+1=%d exceeds %d", k1p, RS_MAXK);
+  const int wpb = RS_WPB;
   reciprocal_sets_kernel<<<cdiv(N, wpb), wpb * 32, 0, s>>>(nbr, N, K, k1p, h, rfull, nfull, rhalf,
                                                          nhalf);
   return check_launch("reciprocal_sets_kernel");
@@ -160,7 +191,7 @@ int launch_expand_weights(const int* rfull, const int* nfull, const int* rhalf, 
   const int cap1 = v_row_capacity(k1);
   int capP = 32;
   while (capP < cap1) capP <<= 1;
-  const int per_warp = (k1p + capP + cap1) * 4;
+  const int per_warp = (k1p + capP + cap1 + 3 * k1p) * 4;
   int wpb = 4;
   while (wpb > 1 && per_warp * wpb > 200 * 1024) wpb >>= 1;
   REID_REQUIRE(per_warp * wpb <= 227 * 1024, "expand_weights: k1=%d needs %d B of shared memory", k1,
