@@ -61,6 +61,8 @@ REID_API int reid_half_k(int k1);
 REID_API int reid_v_row_capacity(int k1);
 /* feature width padded to the tensor-core K block (64) */
 REID_API int reid_padded_width(int d);
+/* row pitch (floats) of reid_dist's chunk_min output for n columns: 8 slots per 256-column tile, >= ceil(n/32) */
+REID_API int reid_chunk_pitch(int n);
 
 /* K13  evaluate.py:112-114, reranking.py:36-39.  Row L2-normalise (x / max(|x|, 1e-12)) when
  * `normalize`, zero-pad to `dpad` (reid_padded_width) -> x32[n, dpad]; sq[i] = sum x^2 and
@@ -76,7 +78,7 @@ REID_API int reid_prepare_features(const float* X, int n, int d, int64_t ld_x, i
  * (1 / (ra[i] * rb[j])))) with ra/rb = norms.  If rowmax_key != NULL the per-row maximum of
  * `out` is folded in with atomicMax on an order-preserving int encoding (initialise the array
  * with reid_rowmax_init).  If chunk_min != NULL (reid_dist only) it receives the minimum of every
- * 32-column chunk, [m, ceil(n/32)], for reid_topk_rows_hinted.  lda/ldb are row pitches in elements, so a rank's cyclic share of the
+ * 32-column chunk, [m, ceil(n/32)] with row pitch reid_chunk_pitch(n), for reid_topk_rows_hinted.  lda/ldb are row pitches in elements, so a rank's cyclic share of the
  * probes is the same buffers with base + rank*dpad and pitch world*dpad.
  *   reid_dist       tcgen05 tensor cores: float16 hi/lo operands, float32 accumulation in TMEM
  *                   (hi.hi + hi.lo + lo.hi), TMA in and out.  The product path.

@@ -127,6 +127,7 @@ int64_t reid_launch_count(void) { return (int64_t)__atomic_load_n(&g_launches, _
 int reid_half_k(int k1) { return half_k(k1); }
 int reid_v_row_capacity(int k1) { return v_row_capacity(k1); }
 int reid_padded_width(int d) { return padded_width(d); }
+int reid_chunk_pitch(int n) { return chunk_pitch(n); }
 
 int reid_prepare_features(const float* X, int n, int d, int64_t ld_x, int normalize, float* x32, reid_half* hi,
                           reid_half* lo, int dpad, float* sq, float* nrm, uint32_t* amax, void* stream) {

@@ -479,7 +479,7 @@ int launch_dist_tc1(const __half* Ahi, const __half* Alo, long long lda, const f
   REID_REQUIRE(ntiles < (1ll << 31), "dist_tc: too many tiles");
   const int grid = ntiles < sms ? (int)ntiles : sms;
   dist_tc_kernel<<<grid, THREADS, SMEM_BYTES, s>>>(mAhi, mAlo, mBhi, mBlo, mOut, ra, rb, a_amax, b_amax, m, n,
-                                                  dp / BK, metric, rowmax_key, chunk_min, cdiv(n, 32), symmetric,
+                                                  dp / BK, metric, rowmax_key, chunk_min, chunk_pitch(n), symmetric,
                                                   (int)ntiles);
   return check_launch("dist_tc_kernel");
 }

@@ -15,6 +15,8 @@ static inline int half_k(int k1) {
 // structural bound on |E_i|: |R| + |R| * h  with |R| <= k1+1
 static inline int v_row_capacity(int k1) { return (k1 + 1) * (half_k(k1) + 1); }
 static inline int padded_width(int d) { return (d + 63) / 64 * 64; }   // tensor-core K block
+// row pitch of the 32-column chunk minima: 8 slots per 256-column tile, so a tile's slots are 16-byte aligned groups
+static inline int chunk_pitch(int n) { return 8 * ((n + 255) / 256); }
 
 int launch_prep(const float* X, int n, int d, long long ld_x, int normalize, float* x32, __half* hi, __half* lo,
                 int dp, float* sq, float* nrm, uint32_t* amax, cudaStream_t s);

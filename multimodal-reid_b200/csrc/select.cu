@@ -263,7 +263,7 @@ template <int S>
 __global__ void __launch_bounds__(SELH_WPB * 32)
 select_topk_hinted_kernel(const float* __restrict__ D, int rows, int cols, long long ld,
                           const int* __restrict__ rowmax_key, const float* __restrict__ chunk_min, int nch,
-                          int K, int* __restrict__ nbr, float* __restrict__ nbr_val, int cap, int list_cap) {
+                          int cm_pitch, int K, int* __restrict__ nbr, float* __restrict__ nbr_val, int cap, int list_cap) {
   __shared__ unsigned long long cand_s[SELH_WPB][SELH_CAND];
   __shared__ int list_s[SELH_WPB][SELH_LIST];
   const int w = threadIdx.x >> 5, lane = lane_id();
@@ -272,7 +272,7 @@ select_topk_hinted_kernel(const float* __restrict__ D, int rows, int cols, long 
   unsigned long long* cand = cand_s[w];
   int* list = list_s[w];
   const float* p = D + (long long)row * ld;
-  const float* cm = chunk_min + (long long)row * nch;
+  const float* cm = chunk_min + (long long)row * cm_pitch;
   const float m = ordered_int2f(rowmax_key[row]);
 
   // pass 1: the S smallest chunk minima of this lane's share, ascending in keep[]
@@ -410,7 +410,7 @@ int launch_select_topk_hinted(const float* D, int rows, int cols, long long ld, 
   REID_REQUIRE(cap >= K || cap_override > 0, "select_topk: K=%d exceeds the candidate buffer", K);
   const int grid = cdiv(rows, SELH_WPB), threads = SELH_WPB * 32;
 #define REID_SELH(SS)                                                                                          \
-  select_topk_hinted_kernel<SS><<<grid, threads, 0, s>>>(D, rows, cols, ld, rowmax_key, chunk_min, nch, K, nbr, \
+  select_topk_hinted_kernel<SS><<<grid, threads, 0, s>>>(D, rows, cols, ld, rowmax_key, chunk_min, nch, chunk_pitch(cols), K, nbr, \
                                                          nbr_val, cap, list_cap)
   if (K <= 32) REID_SELH(1);
   else if (K <= 64) REID_SELH(2);

@@ -264,7 +264,7 @@ class Engine:
                       _ptr(rb), n, A.dp, metric, _ptr(D), ld, _ptr(key), _stream())
         else:
             if want_chunk_min:
-                cmin = self._empty((m, (n + 31) // 32), torch.float32)
+                cmin = self._empty((m, self.lib.reid_chunk_pitch(n)), torch.float32)[:, : (n + 31) // 32]
             self.lib.reid_set_symmetric_contraction(int(self.symmetric))
             _lib.call("reid_dist", _ptr(A.hi), _ptr(A.lo), A.hi.stride(0), _ptr(ra), _ptr(A.amax), m, _ptr(B.hi),
                       _ptr(B.lo), B.hi.stride(0), _ptr(rb), _ptr(B.amax), n, A.dp, metric, _ptr(D), ld, _ptr(key),
