@@ -295,7 +295,7 @@ def main():
             step_e2e()
         e2e_ms, _, (cmc_e, map_e), _ = timed(step_e2e, args.steps)
         h2d = feats_h.numel() * 4 + pids_h.numel() * 8 + cams_h.numel() * 8
-        d2h = 50 * 4 + 8 + 4 + 8          # cmc, mAP, n_valid, CSR pool size
+        d2h = 50 * 4 + 8 + 4 + 8          # cmc, mAP, n_valid, longest-union hint (async, pinned)
         e2e = {"value": q * g * args.steps / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms / args.steps,
                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "mAP": float(map_e),
                "api": "evaluate.R1_mAP_eval(reranking=True).update(host tensors).compute()"}

@@ -183,6 +183,11 @@ class Engine:
         # N x N contraction of one rank owning every row: upper-triangle tiles only, mirrored (dist_tcgen05.cu).
         # Ranks of a multi-GPU job own strided row subsets and always run the full schedule.
         self.symmetric = True
+        self.qe_nosync_bytes = 4 << 30       # budget for sizing the query-expansion pools without a host read
+        self._ubmax_pinned = torch.zeros(1, dtype=torch.int64).pin_memory()
+        self._ubmax_event = torch.cuda.Event()
+        self._ubmax_pending = False
+        self._ubmax_seen = 256
         self.qe_replicate_below = 300_000   # N * k2 up to which every rank runs the query expansion for all rows
         self._cw_hint = {}          # k1 -> width of the V rows exchanged between ranks (see rerank_from_panel)
 
@@ -331,6 +336,16 @@ class Engine:
                   _ptr(D), D.stride(0), _ptr(key), _ptr(Vc), _ptr(Vv), _ptr(Vn), _stream())
         return Vc, Vv, Vn
 
+    def _qe_cap_hint(self) -> int:
+        """Power-of-two merge-buffer size covering the longest union seen by the previous no-sync call (256 at first)."""
+        if self._ubmax_pending and self._ubmax_event.query():
+            self._ubmax_seen = int(self._ubmax_pinned[0])
+            self._ubmax_pending = False
+        cap = 32
+        while cap < min(self._ubmax_seen, 4096):
+            cap *= 2
+        return cap
+
     # ------------------------------------------------------------------ K7
     def query_expansion(self, nbr, k2, Vc, Vv, Vn, rows, row0=0, row_stride=1, cap_sort: int = 0, extra=None):
         """Returns (Qc, Qv, qoff[rows+1] int64, Qn[rows], pool size) for the row window.  `extra`: a one-element
@@ -342,19 +357,30 @@ class Engine:
         qoff = self._empty((rows + 1,), torch.int64)
         _lib.call("reid_exclusive_scan", _ptr(ub), rows, _ptr(qoff), _stream())
         # 16-byte D2H: pool size and the longest union (sizes the per-warp sort buffers)
-        stats = [qoff[rows].reshape(1), ub.max().to(torch.int64).reshape(1)] if rows else []
-        if extra is not None:
-            stats.append(extra.to(torch.int64).reshape(1))
-        vals = [int(v) for v in torch.cat(stats).tolist()] if stats else []
-        total, ub_max = (vals[0], vals[1]) if rows else (0, 0)
-        self.last_extra = vals[-1] if extra is not None else None
+        bound = rows * k2 * cap1                      # structural: a union of k2 rows of at most cap1 entries each
+        if extra is None and not cap_sort and 0 < bound * 14 <= self.qe_nosync_bytes:
+            # No host read in the middle of the step: the pools are sized by the structural bound (6 B per entry here,
+            # 8 B in the inverted index) and the per-warp merge buffers by the longest union of the PREVIOUS call, which
+            # arrives through a pinned buffer; rows longer than that take the kernel's exact k2-way merge fallback.
+            total = bound
+            cap_sort = self._qe_cap_hint()
+            self._ubmax_pinned.copy_(ub.max().to(torch.int64).reshape(1), non_blocking=True)
+            self._ubmax_event.record()
+            self._ubmax_pending = True
+        else:
+            stats = [qoff[rows].reshape(1), ub.max().to(torch.int64).reshape(1)] if rows else []
+            if extra is not None:
+                stats.append(extra.to(torch.int64).reshape(1))
+            vals = [int(v) for v in torch.cat(stats).tolist()] if stats else []
+            total, ub_max = (vals[0], vals[1]) if rows else (0, 0)
+            self.last_extra = vals[-1] if extra is not None else None
+            if not cap_sort:
+                cap_sort = 32
+                while cap_sort < min(ub_max, 4096):
+                    cap_sort *= 2
         Qc = self._empty((max(total, 1),), torch.int32)
         Qv = self._empty((max(total, 1),), torch.float16)
         Qn = self._empty((rows,), torch.int32)
-        if not cap_sort:
-            cap_sort = 32
-            while cap_sort < min(ub_max, 4096):
-                cap_sort *= 2
         _lib.call("reid_qe_k2_capped", _ptr(nbr), K, k2, _ptr(Vc), _ptr(Vv), _ptr(Vn), cap1, row0, row_stride,
                   rows, _ptr(qoff), cap_sort, _ptr(Qc), _ptr(Qv), _ptr(Qn), _stream())
         return Qc, Qv, qoff, Qn, total
