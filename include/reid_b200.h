@@ -86,8 +86,10 @@ REID_API int reid_prepare_features(const float* X, int n, int d, int64_t ld_x, i
 /* When A and B of reid_dist are the same rows (same pointers, pitches, norms; m == n) the contraction computes only
  * the tiles touching the upper triangle and stores every off-diagonal tile a second time transposed (with the
  * mirrored rows' maxima and chunk minima): outside its 256-wide diagonal blocks the N x N matrix of re-ranking is an
- * exact mirror, at half the tensor-core work.  Process-global switch, on by default; off = every tile computed (what a rank owning a strided
- * subset of the rows runs anyway). */
+ * exact mirror, at half the tensor-core work.  Process-global switch: 1 (default) as described; 0 = every tile computed
+ * (what a rank owning a strided subset of the rows runs anyway); 2 = upper-only: mirrored tiles are NOT stored (their row
+ * maxima and chunk minima still are) -- half the output stream; entries left of a row's 256-wide diagonal block are then
+ * undefined and consumers must read D[col, row] instead (the _tri entry points do). */
 REID_API int reid_set_symmetric_contraction(int on);
 /* Diagnostics: with the environment variable REID_TC_DBG & 64 set, block 0 of reid_dist's kernel records
  * {clock64, globaltimer ns} at entry and exit; this copies the four values to HOST memory (synchronises). */
@@ -116,6 +118,11 @@ REID_API int reid_topk_rows(const float* D, int rows, int cols, int64_t ld, cons
 /* same result, reading only the chunks whose recorded minimum can hold a neighbour (~K of cols/32) */
 REID_API int reid_topk_rows_hinted(const float* D, int rows, int cols, int64_t ld, const int32_t* rowmax_key,
                           const float* chunk_min, int K, int32_t* nbr, float* nbr_val, int cap, void* stream);
+/* same for the square symmetric matrix of reid_dist's upper-only mode (reid_set_symmetric_contraction(2)): entries left of
+ * a row's 256-wide diagonal block are read from their mirror image D[col, row] */
+REID_API int reid_topk_rows_hinted_tri(const float* D, int rows, int cols, int64_t ld, const int32_t* rowmax_key,
+                              const float* chunk_min, int K, int32_t* nbr, float* nbr_val, int cap, int upper_only,
+                              void* stream);
 /* test hook: same, with the candidate buffer capped so the exact fallback path is exercised */
 REID_API int reid_topk_rows_capped(const float* D, int rows, int cols, int64_t ld, const int32_t* rowmax_key,
                           int K, int32_t* nbr, float* nbr_val, int cap, void* stream);
@@ -131,6 +138,11 @@ REID_API int reid_krecip_V(const int32_t* rfull, const int32_t* nfull, const int
                   const int32_t* nhalf, int row0, int row_stride, int rows, int k1, const float* D,
                   int64_t ld, const int32_t* rowmax_key, int32_t* Vc, reid_half* Vv, int32_t* Vn,
                   void* stream);
+/* all N rows on one rank, D optionally in upper-only form (see reid_topk_rows_hinted_tri) */
+REID_API int reid_krecip_V_tri(const int32_t* rfull, const int32_t* nfull, const int32_t* rhalf,
+                      const int32_t* nhalf, int rows, int k1, const float* D, int64_t ld,
+                      const int32_t* rowmax_key, int32_t* Vc, reid_half* Vv, int32_t* Vn, int upper_only,
+                      void* stream);
 
 /* K7  reranking.py:73-78.  ub[l] = upper bound of |supp V_qe[row_l]|; exclusive scan to offsets;
  * then the expansion itself into a CSR pool (Qc/Qv at qoff[l], Qn[l] entries, columns ascending).

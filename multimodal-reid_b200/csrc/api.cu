@@ -204,7 +204,16 @@ int reid_topk_rows_hinted(const float* D, int rows, int cols, int64_t ld, const 
                           const float* chunk_min, int K, int32_t* nbr, float* nbr_val, int cap, void* stream) {
   ENTER();
   REID_REQUIRE(chunk_min != nullptr, "topk_rows_hinted: chunk_min is NULL");
-  return launch_select_topk_hinted(D, rows, cols, ld, rowmax_key, chunk_min, K, nbr, nbr_val, cap, S(stream));
+  return launch_select_topk_hinted(D, rows, cols, ld, rowmax_key, chunk_min, K, nbr, nbr_val, cap, 0, S(stream));
+}
+
+int reid_topk_rows_hinted_tri(const float* D, int rows, int cols, int64_t ld, const int32_t* rowmax_key,
+                              const float* chunk_min, int K, int32_t* nbr, float* nbr_val, int cap, int upper_only,
+                              void* stream) {
+  ENTER();
+  REID_REQUIRE(chunk_min != nullptr, "topk_rows_hinted: chunk_min is NULL");
+  return launch_select_topk_hinted(D, rows, cols, ld, rowmax_key, chunk_min, K, nbr, nbr_val, cap, upper_only ? 1 : 0,
+                                   S(stream));
 }
 
 int reid_topk_rows_capped(const float* D, int rows, int cols, int64_t ld, const int32_t* rowmax_key, int K,
@@ -226,7 +235,16 @@ int reid_krecip_V(const int32_t* rfull, const int32_t* nfull, const int32_t* rha
   ENTER();
   REID_REQUIRE(k1 >= 1 && row_stride >= 1 && row0 >= 0, "krecip_V: bad window");
   return launch_expand_weights(rfull, nfull, rhalf, nhalf, row0, row_stride, rows, k1, D, ld, rowmax_key,
-                               Vc, H(Vv), Vn, S(stream));
+                               Vc, H(Vv), Vn, 0, S(stream));
+}
+
+int reid_krecip_V_tri(const int32_t* rfull, const int32_t* nfull, const int32_t* rhalf, const int32_t* nhalf,
+                      int rows, int k1, const float* D, int64_t ld, const int32_t* rowmax_key, int32_t* Vc,
+                      reid_half* Vv, int32_t* Vn, int upper_only, void* stream) {
+  ENTER();
+  REID_REQUIRE(k1 >= 1, "krecip_V: bad k1");
+  return launch_expand_weights(rfull, nfull, rhalf, nhalf, 0, 1, rows, k1, D, ld, rowmax_key, Vc, H(Vv), Vn,
+                               upper_only ? 1 : 0, S(stream));
 }
 
 int reid_qe_bound(const int32_t* nbr, int K, int k2, const int32_t* Vn, int row0, int row_stride, int rows,

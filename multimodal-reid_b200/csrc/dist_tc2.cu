@@ -352,6 +352,7 @@ dist_tc2_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant
       const int r0 = mb * BM + row_in_tile;    // first row of this warp's 32
       const int n0 = nb * BN;
       const bool mirror = symmetric && mb < nb;
+      const bool store_mirror = symmetric == 1;   // mode 2: consumers read the lower triangle transposed
       const int as = it & 1, aph = (it >> 1) & 1;
       float* rbt = rb_s + (it & 1) * BN;
       rbt[et] = rb_next;
@@ -465,7 +466,8 @@ dist_tc2_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant
         if (mirror) {
           // the same box transposed, straight from registers: out[col0 + j, r0 + lane] = o[j], one 128-byte line per j
           float* orow = out + (long long)col0 * ld_out + row;
-          if (ncols == 32 && row_ok) {
+          if (!store_mirror) {
+          } else if (ncols == 32 && row_ok) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
               *orow = o[j];
@@ -541,8 +543,8 @@ static int make_map(CUtensorMap* map, CUtensorMapDataType dt, int esize, const v
 
 }  // namespace tc2
 
-static int g_symmetric_enabled = 1;
-void set_symmetric_contraction(int on) { g_symmetric_enabled = on ? 1 : 0; }
+static int g_symmetric_enabled = 1;     // 0 off, 1 upper triangle computed + mirrored, 2 upper triangle only
+void set_symmetric_contraction(int on) { g_symmetric_enabled = on < 0 ? 0 : (on > 2 ? 1 : on); }
 int symmetric_contraction_enabled() { return g_symmetric_enabled; }
 
 int dist_clock_probe(long long* host_out4) {
@@ -579,7 +581,7 @@ int launch_dist_tc(const __half* Ahi, const __half* Alo, long long lda, const fl
   REID_CUDA(cudaFuncSetAttribute(dist_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
   // same rows on both sides and a square output: compute the upper triangle only and mirror it
   const int symmetric = (Ahi == Bhi && Alo == Blo && lda == ldb && ra == rb && a_amax == b_amax && m == n &&
-                         g_symmetric_enabled) ? 1 : 0;
+                         g_symmetric_enabled) ? g_symmetric_enabled : 0;
   const int mblocks = cdiv(m, BM), nblocks = cdiv(n, BN);
   long long ntiles = (long long)mblocks * nblocks;
   if (symmetric) {

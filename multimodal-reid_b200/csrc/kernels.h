@@ -36,7 +36,7 @@ int launch_dist_tc1(const __half* Ahi, const __half* Alo, long long lda, const f
 int dist_clock_probe(long long* host_out4);
 int launch_select_topk_hinted(const float* D, int rows, int cols, long long ld, const int* rowmax_key,
                               const float* chunk_min, int K, int* nbr, float* nbr_val, int cap_override,
-                              cudaStream_t s);
+                              int upper_only, cudaStream_t s);
 int launch_rowmax(const float* D, int rows, int cols, long long ld, int* key, cudaStream_t s);
 int launch_select_topk(const float* D, int rows, int cols, long long ld, const int* rowmax_key, int K,
                        int* nbr, float* nbr_val, int cap_override, cudaStream_t s);
@@ -44,7 +44,7 @@ int launch_reciprocal_sets(const int* nbr, int N, int K, int k1, int* rfull, int
                            int* nhalf, cudaStream_t s);
 int launch_expand_weights(const int* rfull, const int* nfull, const int* rhalf, const int* nhalf, int row0,
                           int row_stride, int rows, int k1, const float* D, long long ld, const int* rowmax_key, int* Vc,
-                          __half* Vv, int* Vn, cudaStream_t s);
+                          __half* Vv, int* Vn, int upper_only, cudaStream_t s);
 int launch_qe_bound(const int* nbr, int K, int k2, const int* Vn, int row0, int row_stride, int rows,
                     int* ub, cudaStream_t s);
 int launch_exclusive_scan(const int* in, int n, long long* out, cudaStream_t s);

@@ -77,7 +77,7 @@ expand_weights_kernel(const int* __restrict__ rfull, const int* __restrict__ nfu
                       const int* __restrict__ rhalf, const int* __restrict__ nhalf, int row0,
                       int row_stride, int rows, int k1p, int h, const float* __restrict__ D, long long ld,
                       const int* __restrict__ rowmax_key, int cap1, int capP,
-                      int* __restrict__ Vc, __half* __restrict__ Vv, int* __restrict__ Vn) {
+                      int* __restrict__ Vc, __half* __restrict__ Vv, int* __restrict__ Vn, int upper_only) {
   extern __shared__ int smem_i[];
   const int wpb = blockDim.x >> 5;
   const int w = threadIdx.x >> 5, lane = lane_id();
@@ -159,7 +159,9 @@ expand_weights_kernel(const int* __restrict__ rfull, const int* __restrict__ nfu
   const float m = ordered_int2f(rowmax_key[lrow]);
   const float* drow = D + (long long)lrow * ld;
   for (int j = lane; j < nU; j += 32) {
-    float o = __fdiv_rn(drow[E[j]], m);
+    const int e = E[j];                       // upper_only: left of the row's diagonal block only the mirror image exists
+    const float dv = (upper_only && e < (lrow & ~255)) ? D[(long long)e * ld + lrow] : drow[e];
+    float o = __fdiv_rn(dv, m);
     W[j] = np_expf(-o);
   }
   __syncwarp();
@@ -185,8 +187,9 @@ int launch_reciprocal_sets(const int* nbr, int N, int K, int k1, int* rfull, int
 
 int launch_expand_weights(const int* rfull, const int* nfull, const int* rhalf, const int* nhalf,
                           int row0, int row_stride, int rows, int k1, const float* D, long long ld,
-                          const int* rowmax_key, int* Vc, __half* Vv, int* Vn, cudaStream_t s) {
+                          const int* rowmax_key, int* Vc, __half* Vv, int* Vn, int upper_only, cudaStream_t s) {
   if (rows == 0) return REID_OK;
+  REID_REQUIRE(!upper_only || (row0 == 0 && row_stride == 1), "expand_weights: upper_only needs all rows on one rank");
   const int k1p = k1 + 1, h = half_k(k1);
   const int cap1 = v_row_capacity(k1);
   int capP = 32;
@@ -200,7 +203,7 @@ int launch_expand_weights(const int* rfull, const int* nfull, const int* rhalf, 
   REID_CUDA(cudaFuncSetAttribute(expand_weights_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   expand_weights_kernel<<<cdiv(rows, wpb), wpb * 32, smem, s>>>(rfull, nfull, rhalf, nhalf, row0,
                                                                row_stride, rows, k1p, h, D, ld,
-                                                               rowmax_key, cap1, capP, Vc, Vv, Vn);
+                                                               rowmax_key, cap1, capP, Vc, Vv, Vn, upper_only);
   return check_launch("expand_weights_kernel");
 }
 

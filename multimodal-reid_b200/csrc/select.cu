@@ -263,7 +263,8 @@ template <int S>
 __global__ void __launch_bounds__(SELH_WPB * 32)
 select_topk_hinted_kernel(const float* __restrict__ D, int rows, int cols, long long ld,
                           const int* __restrict__ rowmax_key, const float* __restrict__ chunk_min, int nch,
-                          int cm_pitch, int K, int* __restrict__ nbr, float* __restrict__ nbr_val, int cap, int list_cap) {
+                          int cm_pitch, int K, int* __restrict__ nbr, float* __restrict__ nbr_val, int cap, int list_cap,
+                          int upper_only) {
   __shared__ unsigned long long cand_s[SELH_WPB][SELH_CAND];
   __shared__ int list_s[SELH_WPB][SELH_LIST];
   const int w = threadIdx.x >> 5, lane = lane_id();
@@ -272,6 +273,10 @@ select_topk_hinted_kernel(const float* __restrict__ D, int rows, int cols, long 
   unsigned long long* cand = cand_s[w];
   int* list = list_s[w];
   const float* p = D + (long long)row * ld;
+  // upper_only: D is the symmetric N x N matrix with only the tiles on and above the 256-wide diagonal blocks stored;
+  // an entry left of this row's diagonal block is read from its mirror image D[col, row] (bit-identical by construction)
+  const int tri0 = upper_only ? (row & ~255) : 0;
+  auto ldD = [&](int col) { return col < tri0 ? __ldg(D + (long long)col * ld + row) : __ldg(p + col); };
   const float* cm = chunk_min + (long long)row * cm_pitch;
   const float m = ordered_int2f(rowmax_key[row]);
 
@@ -349,7 +354,7 @@ select_topk_hinted_kernel(const float* __restrict__ D, int rows, int cols, long 
 #pragma unroll
     for (int u = 0; u < 8; ++u) {
       col[u] = l0 + u < nlist ? list[l0 + u] * 32 + lane : cols;
-      v[u] = col[u] < cols ? __ldg(p + col[u]) : INFINITY;
+      v[u] = col[u] < cols ? ldD(col[u]) : INFINITY;
     }
 #pragma unroll
     for (int u = 0; u < 8; ++u) {
@@ -385,7 +390,7 @@ select_topk_hinted_kernel(const float* __restrict__ D, int rows, int cols, long 
       if (!(__ldg(cm + cc) <= dstar || dstar == INFINITY)) continue;
       const int col = cc * 32 + lane;
       if (col < cols) {
-        const unsigned long long k0 = make_ck(p[col], m, col);
+        const unsigned long long k0 = make_ck(ldD(col), m, col);
         if ((r == 0 || k0 > last) && k0 < mine) mine = k0;
       }
     }
@@ -400,10 +405,11 @@ select_topk_hinted_kernel(const float* __restrict__ D, int rows, int cols, long 
 
 int launch_select_topk_hinted(const float* D, int rows, int cols, long long ld, const int* rowmax_key,
                               const float* chunk_min, int K, int* nbr, float* nbr_val, int cap_override,
-                              cudaStream_t s) {
+                              int upper_only, cudaStream_t s) {
   if (rows == 0) return REID_OK;
   REID_REQUIRE(K >= 1 && K <= 256, "select_topk: K=%d outside [1,256]", K);
   REID_REQUIRE(cols >= K, "select_topk: row length %d is shorter than K=%d", cols, K);
+  REID_REQUIRE(!upper_only || rows == cols, "select_topk: upper_only needs the square N x N matrix (%d x %d)", rows, cols);
   const int nch = cdiv(cols, 32);
   const int cap = cap_override > 0 ? (cap_override < SELH_CAND ? cap_override : SELH_CAND) : SELH_CAND;
   const int list_cap = cap_override > 0 ? (cap_override < SELH_LIST ? cap_override : SELH_LIST) : SELH_LIST;
@@ -411,7 +417,7 @@ int launch_select_topk_hinted(const float* D, int rows, int cols, long long ld, 
   const int grid = cdiv(rows, SELH_WPB), threads = SELH_WPB * 32;
 #define REID_SELH(SS)                                                                                          \
   select_topk_hinted_kernel<SS><<<grid, threads, 0, s>>>(D, rows, cols, ld, rowmax_key, chunk_min, nch, chunk_pitch(cols), K, nbr, \
-                                                         nbr_val, cap, list_cap)
+                                                         nbr_val, cap, list_cap, upper_only)
   if (K <= 32) REID_SELH(1);
   else if (K <= 64) REID_SELH(2);
   else if (K <= 128) REID_SELH(4);

@@ -183,6 +183,8 @@ class Engine:
         # N x N contraction of one rank owning every row: upper-triangle tiles only, mirrored (dist_tcgen05.cu).
         # Ranks of a multi-GPU job own strided row subsets and always run the full schedule.
         self.symmetric = True
+        self.upper_only = True      # ... and, when nobody needs the full matrix, without storing the mirrored half
+        self.upper_only_min_rows = 48_000
         self.qe_nosync_bytes = 4 << 30       # budget for sizing the query-expansion pools without a host read
         self._ubmax_pinned = torch.zeros(1, dtype=torch.int64).pin_memory()
         self._ubmax_event = torch.cuda.Event()
@@ -249,7 +251,7 @@ class Engine:
         return (n + 31) // 32 * 32
 
     def dist(self, A: Features, B: Features, metric: int = METRIC_SQEUCLIDEAN, want_rowmax: bool = False,
-             engine: int | None = None, want_chunk_min: bool = False):
+             engine: int | None = None, want_chunk_min: bool = False, upper_only: bool = False):
         """Returns (D [m, pitch] float32 — use D[:, :n] —, rowmax_key [m] int32 or None)
         [, chunk_min [m, ceil(n/32)] float32 when want_chunk_min (tensor-core engine only)]."""
         assert A.dp == B.dp
@@ -270,7 +272,7 @@ class Engine:
         else:
             if want_chunk_min:
                 cmin = self._empty((m, self.lib.reid_chunk_pitch(n)), torch.float32)[:, : (n + 31) // 32]
-            self.lib.reid_set_symmetric_contraction(int(self.symmetric))
+            self.lib.reid_set_symmetric_contraction((2 if upper_only else 1) if self.symmetric else 0)
             _lib.call("reid_dist", _ptr(A.hi), _ptr(A.lo), A.hi.stride(0), _ptr(ra), _ptr(A.amax), m, _ptr(B.hi),
                       _ptr(B.lo), B.hi.stride(0), _ptr(rb), _ptr(B.amax), n, A.dp, metric, _ptr(D), ld, _ptr(key),
                       _ptr(cmin), _stream())
@@ -298,13 +300,13 @@ class Engine:
 
     # ------------------------------------------------------------------ K5
     def topk_rows(self, D: torch.Tensor, cols: int, key: torch.Tensor, K: int, want_values=False, cap: int = 0,
-                  chunk_min: torch.Tensor | None = None):
+                  chunk_min: torch.Tensor | None = None, upper_only: bool = False):
         rows = D.shape[0]
         nbr = self._empty((rows, K), torch.int32)
         val = self._empty((rows, K), torch.float32) if want_values else None
         if chunk_min is not None:
-            _lib.call("reid_topk_rows_hinted", _ptr(D), rows, cols, D.stride(0), _ptr(key), _ptr(chunk_min), K,
-                      _ptr(nbr), _ptr(val), cap, _stream())
+            _lib.call("reid_topk_rows_hinted_tri", _ptr(D), rows, cols, D.stride(0), _ptr(key), _ptr(chunk_min), K,
+                      _ptr(nbr), _ptr(val), cap, int(upper_only), _stream())
         elif cap:
             _lib.call("reid_topk_rows_capped", _ptr(D), rows, cols, D.stride(0), _ptr(key), K, _ptr(nbr), _ptr(val),
                       cap, _stream())
@@ -325,15 +327,20 @@ class Engine:
                   _stream())
         return rfull, nfull, rhalf, nhalf
 
-    def krecip_V(self, sets, k1: int, D: torch.Tensor, key: torch.Tensor, row0=0, row_stride=1):
+    def krecip_V(self, sets, k1: int, D: torch.Tensor, key: torch.Tensor, row0=0, row_stride=1, upper_only=False):
         rfull, nfull, rhalf, nhalf = sets
         rows = D.shape[0]
         cap1 = v_row_capacity(k1)
         Vc = self._empty((rows, cap1), torch.int32)
         Vv = self._empty((rows, cap1), torch.float16)
         Vn = self._empty((rows,), torch.int32)
-        _lib.call("reid_krecip_V", _ptr(rfull), _ptr(nfull), _ptr(rhalf), _ptr(nhalf), row0, row_stride, rows, k1,
-                  _ptr(D), D.stride(0), _ptr(key), _ptr(Vc), _ptr(Vv), _ptr(Vn), _stream())
+        if upper_only:
+            assert row0 == 0 and row_stride == 1
+            _lib.call("reid_krecip_V_tri", _ptr(rfull), _ptr(nfull), _ptr(rhalf), _ptr(nhalf), rows, k1,
+                      _ptr(D), D.stride(0), _ptr(key), _ptr(Vc), _ptr(Vv), _ptr(Vn), 1, _stream())
+        else:
+            _lib.call("reid_krecip_V", _ptr(rfull), _ptr(nfull), _ptr(rhalf), _ptr(nhalf), row0, row_stride, rows, k1,
+                      _ptr(D), D.stride(0), _ptr(key), _ptr(Vc), _ptr(Vv), _ptr(Vn), _stream())
         return Vc, Vv, Vn
 
     def _qe_cap_hint(self) -> int:
@@ -494,7 +501,7 @@ class Engine:
     # ------------------------------------------------------------------ K4–K10 from a distance panel
     def rerank_from_panel(self, D: torch.Tensor, key: torch.Tensor, q: int, N: int, k1: int, k2: int, lam: float,
                           detail: dict | None = None, chunk_min: torch.Tensor | None = None,
-                          score: tuple | None = None, want_final: bool = True):
+                          score: tuple | None = None, want_final: bool = True, upper_only: bool = False):
         """D: this rank's panel [n_local, pitch(N)] (row l = probe rank + l*world), key: its row
         maxima.  Returns final[nq_local, pitch(g)] for this rank's queries (use [:, :g]).
         With score = ((q_pids_local, g_pids, q_cams_local, g_cams), max_rank) the last stage is the
@@ -506,12 +513,12 @@ class Engine:
         if N < K:
             raise NotImplementedError(f"re-ranking needs at least max(k1+1, k2) = {K} samples, got {N}")
         with self.span("select"):
-            nbr_local = self.topk_rows(D, N, key, K, chunk_min=chunk_min)
+            nbr_local = self.topk_rows(D, N, key, K, chunk_min=chunk_min, upper_only=upper_only)
         with self.span("x_nbr"):
             nbr = cm.gather_rows(nbr_local, N)
         with self.span("krecip"):
             sets = self.krecip_sets(nbr, k1)
-            Vc_l, Vv_l, Vn_l = self.krecip_V(sets, k1, D, key, r, P)
+            Vc_l, Vv_l, Vn_l = self.krecip_V(sets, k1, D, key, r, P, upper_only=upper_only)
         if P == 1:
             Vc, Vv, Vn = Vc_l, Vv_l, Vn_l
             if k2 != 1:
@@ -582,14 +589,24 @@ class Engine:
             allf = self.prepare(feats, normalize)
             mine = allf if cm.world == 1 else allf.rows(slice(cm.rank, N, cm.world))
         with self.span("dist"):
+            tri = False
             if self.engine == ENGINES["simt"]:
                 (D, key), cmin = self.dist(mine, allf, METRIC_SQEUCLIDEAN, want_rowmax=True), None
             else:
-                D, key, cmin = self.dist(mine, allf, METRIC_SQEUCLIDEAN, want_rowmax=True, want_chunk_min=True)
+                # One rank, symmetric schedule, nobody asked to see D: the mirrored half of the matrix is not written
+                # at all (half the 4 N^2-byte output stream); the two consumers that look left of a row's diagonal block
+                # -- selection and the V weights -- read the mirror image instead.  Queries only ever need gallery
+                # columns, which lie right of their diagonal block.
+                # Those mirror reads are 32-byte sector gathers (8x amplification), ~1e-5 ms per row, against ~2.5e-10 ms
+                # per matrix element saved in the contraction: worth it above N ~ 42 k (MSMT17 scale: -0.8 ms), not below.
+                tri = (self.upper_only and cm.world == 1 and self.symmetric and detail is None
+                       and N >= self.upper_only_min_rows)
+                D, key, cmin = self.dist(mine, allf, METRIC_SQEUCLIDEAN, want_rowmax=True, want_chunk_min=True,
+                                         upper_only=tri)
         if detail is not None:
             detail.update(D=D, key=key)
         return self.rerank_from_panel(D, key, q, N, k1, k2, lam, detail, chunk_min=cmin, score=score,
-                                      want_final=want_final)
+                                      want_final=want_final, upper_only=tri)
 
     def evaluate_reranked(self, feats: torch.Tensor, q: int, pids: torch.Tensor, cams: torch.Tensor, k1: int, k2: int,
                           lam: float, normalize: bool, max_rank: int = 50):

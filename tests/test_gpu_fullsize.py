@@ -66,7 +66,22 @@ def test_full_size_properties(eng, engine_mod, synth, name):
     # the full tile schedule (what a rank of a multi-GPU job runs) agrees to float32 rounding
     sym_rows = D[rt, :N].clone()
     sym_key = key.clone()
-    del D, cmin, key, a, b, padded, got, ref, err
+    # upper-only form (mirrored tiles not stored; selection and the V weights read the mirror image): same bits
+    K = max(sh.k1 + 1, sh.k2)
+    nbr1 = eng.topk_rows(D, N, key, K, chunk_min=cmin)
+    sets1 = eng.krecip_sets(nbr1, sh.k1)
+    V1 = eng.krecip_V(sets1, sh.k1, D, key)
+    del D, cmin, a, b, padded, got, ref, err
+    D3, key3, cmin3 = eng.dist(f, f, engine_mod.METRIC_SQEUCLIDEAN, want_rowmax=True, want_chunk_min=True,
+                               upper_only=True)
+    assert torch.equal(key3, key)
+    nbr3 = eng.topk_rows(D3, N, key3, K, chunk_min=cmin3, upper_only=True)
+    assert torch.equal(nbr3, nbr1), f"{name}: neighbour lists differ in upper-only form"
+    V3 = eng.krecip_V(eng.krecip_sets(nbr3, sh.k1), sh.k1, D3, key3, upper_only=True)
+    for u, v, what in zip(V1, V3, ("Vc", "Vv", "Vn")):
+        used = torch.arange(u.shape[1], device=dev)[None, :] < V1[2][:, None] if u.dim() == 2 else None
+        assert torch.equal(u[used], v[used]) if used is not None else torch.equal(u, v), f"{name}: {what} differs"
+    del D3, cmin3, key3, nbr1, nbr3, V1, V3, sets1, key
     eng.symmetric = False
     D2, key2, cmin2 = eng.dist(f, f, engine_mod.METRIC_SQEUCLIDEAN, want_rowmax=True, want_chunk_min=True)
     eng.symmetric = True
@@ -74,7 +89,6 @@ def test_full_size_properties(eng, engine_mod, synth, name):
     assert float((eng.rowmax_values(key2) - eng.rowmax_values(sym_key)).abs().max()) <= 4e-6
 
     # ---------------------------------------------------------------- selection == stable sort of O = D / rowmax
-    K = max(sh.k1 + 1, sh.k2)
     nbr = eng.topk_rows(D2, N, key2, K, chunk_min=cmin2)
     O = D2[rt, :N] / eng.rowmax_values(key2)[rt, None]
     O = O + 0.0                                                            # -0 ties with +0 like numpy's sort
@@ -84,10 +98,17 @@ def test_full_size_properties(eng, engine_mod, synth, name):
     del D2, cmin2, O, want, nbr
 
     # ---------------------------------------------------------------- evaluator: fused == materialised, deterministic
+    saved_min_rows, eng.upper_only_min_rows = eng.upper_only_min_rows, 0     # upper-only form at every size here
     r1 = eng.evaluate_reranked(X, q, pids, cams, sh.k1, sh.k2, sh.lam, normalize=True, max_rank=50)
     r1b = eng.evaluate_reranked(X, q, pids, cams, sh.k1, sh.k2, sh.lam, normalize=True, max_rank=50)
     for u, v, what in zip(r1, r1b, ("cmc", "mAP", "n_valid", "ap", "first_hit")):
         assert torch.equal(u, v), f"{name}: {what} differs between two runs"
+    eng.upper_only = False                                                 # mirrored half stored: identical results
+    r1c = eng.evaluate_reranked(X, q, pids, cams, sh.k1, sh.k2, sh.lam, normalize=True, max_rank=50)
+    eng.upper_only = True
+    eng.upper_only_min_rows = saved_min_rows
+    for u, v, what in zip(r1, r1c, ("cmc", "mAP", "n_valid", "ap", "first_hit")):
+        assert torch.equal(u, v), f"{name}: {what} differs between the upper-only and the full symmetric form"
     final = eng.rerank_features(X, q, sh.k1, sh.k2, sh.lam, normalize=True)
     assert final.shape[0] == q and bool(torch.isfinite(final[:, :g]).all())
     ids = (pids[:q].contiguous(), pids[q:].contiguous(), cams[:q].contiguous(), cams[q:].contiguous())
