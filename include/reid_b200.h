@@ -123,6 +123,13 @@ REID_API int reid_topk_rows_hinted(const float* D, int rows, int cols, int64_t l
 REID_API int reid_topk_rows_hinted_tri(const float* D, int rows, int cols, int64_t ld, const int32_t* rowmax_key,
                               const float* chunk_min, int K, int32_t* nbr, float* nbr_val, int cap, int upper_only,
                               void* stream);
+/* same result for the upper-only matrix in scatter form: every stored element is offered to both rows it belongs to
+ * (candidate records through `workspace`, reid_topk_scatter_workspace_bytes(n, cap) bytes, 16-byte aligned), so the
+ * unstored half is never gathered; three launches (thresholds, push, merge) */
+REID_API int64_t reid_topk_scatter_workspace_bytes(int n, int cap);
+REID_API int reid_topk_rows_scatter(const float* D, int n, int64_t ld, const int32_t* rowmax_key, const float* chunk_min,
+                           int K, int32_t* nbr, float* nbr_val, int cap, void* workspace, int64_t workspace_bytes,
+                           void* stream);
 /* test hook: same, with the candidate buffer capped so the exact fallback path is exercised */
 REID_API int reid_topk_rows_capped(const float* D, int rows, int cols, int64_t ld, const int32_t* rowmax_key,
                           int K, int32_t* nbr, float* nbr_val, int cap, void* stream);

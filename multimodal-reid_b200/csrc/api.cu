@@ -216,6 +216,18 @@ int reid_topk_rows_hinted_tri(const float* D, int rows, int cols, int64_t ld, co
                                    S(stream));
 }
 
+int64_t reid_topk_scatter_workspace_bytes(int n, int cap) { return (int64_t)select_scatter_workspace_bytes(n, cap); }
+
+int reid_topk_rows_scatter(const float* D, int n, int64_t ld, const int32_t* rowmax_key, const float* chunk_min, int K,
+                           int32_t* nbr, float* nbr_val, int cap, void* workspace, int64_t workspace_bytes,
+                           void* stream) {
+  ENTER();
+  REID_REQUIRE(chunk_min != nullptr, "topk_rows_scatter: chunk_min is NULL");
+  REID_REQUIRE(workspace_bytes >= 0, "topk_rows_scatter: negative workspace size");
+  return launch_select_topk_scatter(D, n, ld, rowmax_key, chunk_min, K, nbr, nbr_val, cap, workspace,
+                                    (size_t)workspace_bytes, S(stream));
+}
+
 int reid_topk_rows_capped(const float* D, int rows, int cols, int64_t ld, const int32_t* rowmax_key, int K,
                           int32_t* nbr, float* nbr_val, int cap, void* stream) {
   ENTER();

@@ -38,6 +38,10 @@ int launch_select_topk_hinted(const float* D, int rows, int cols, long long ld, 
                               const float* chunk_min, int K, int* nbr, float* nbr_val, int cap_override,
                               int upper_only, cudaStream_t s);
 int launch_rowmax(const float* D, int rows, int cols, long long ld, int* key, cudaStream_t s);
+size_t select_scatter_workspace_bytes(int n, int cap_override);
+int launch_select_topk_scatter(const float* D, int n, long long ld, const int* rowmax_key, const float* chunk_min,
+                               int K, int* nbr, float* nbr_val, int cap_override, void* workspace,
+                               size_t workspace_bytes, cudaStream_t s);
 int launch_select_topk(const float* D, int rows, int cols, long long ld, const int* rowmax_key, int K,
                        int* nbr, float* nbr_val, int cap_override, cudaStream_t s);
 int launch_reciprocal_sets(const int* nbr, int N, int K, int k1, int* rfull, int* nfull, int* rhalf,

@@ -259,27 +259,11 @@ __device__ __forceinline__ void warp_bitonic_u64_sel(unsigned long long* a, int 
   }
 }
 
+// Pass 1 + bound of the hinted selection for one row (one warp): the raw-D threshold D* such that the row's K nearest
+// (in O = D / m order) all have D <= D*; INFINITY when no monotone filter applies.
 template <int S>
-__global__ void __launch_bounds__(SELH_WPB * 32)
-select_topk_hinted_kernel(const float* __restrict__ D, int rows, int cols, long long ld,
-                          const int* __restrict__ rowmax_key, const float* __restrict__ chunk_min, int nch,
-                          int cm_pitch, int K, int* __restrict__ nbr, float* __restrict__ nbr_val, int cap, int list_cap,
-                          int upper_only) {
-  __shared__ unsigned long long cand_s[SELH_WPB][SELH_CAND];
-  __shared__ int list_s[SELH_WPB][SELH_LIST];
-  const int w = threadIdx.x >> 5, lane = lane_id();
-  const int row = blockIdx.x * SELH_WPB + w;
-  if (row >= rows) return;
-  unsigned long long* cand = cand_s[w];
-  int* list = list_s[w];
-  const float* p = D + (long long)row * ld;
-  // upper_only: D is the symmetric N x N matrix with only the tiles on and above the 256-wide diagonal blocks stored;
-  // an entry left of this row's diagonal block is read from its mirror image D[col, row] (bit-identical by construction)
-  const int tri0 = upper_only ? (row & ~255) : 0;
-  auto ldD = [&](int col) { return col < tri0 ? __ldg(D + (long long)col * ld + row) : __ldg(p + col); };
-  const float* cm = chunk_min + (long long)row * cm_pitch;
-  const float m = ordered_int2f(rowmax_key[row]);
-
+__device__ __forceinline__ float row_dstar(const float* __restrict__ cm, int nch, int K, float m) {
+  const int lane = lane_id();
   // pass 1: the S smallest chunk minima of this lane's share, ascending in keep[]
   float keep[S];
 #pragma unroll
@@ -332,6 +316,32 @@ select_topk_hinted_kernel(const float* __restrict__ D, int rows, int cols, long 
   } else {
     dstar = INFINITY;                                   // degenerate maximum: no monotone filter, take everything
   }
+
+  return dstar;
+}
+
+template <int S>
+__global__ void __launch_bounds__(SELH_WPB * 32)
+select_topk_hinted_kernel(const float* __restrict__ D, int rows, int cols, long long ld,
+                          const int* __restrict__ rowmax_key, const float* __restrict__ chunk_min, int nch,
+                          int cm_pitch, int K, int* __restrict__ nbr, float* __restrict__ nbr_val, int cap, int list_cap,
+                          int upper_only) {
+  __shared__ unsigned long long cand_s[SELH_WPB][SELH_CAND];
+  __shared__ int list_s[SELH_WPB][SELH_LIST];
+  const int w = threadIdx.x >> 5, lane = lane_id();
+  const int row = blockIdx.x * SELH_WPB + w;
+  if (row >= rows) return;
+  unsigned long long* cand = cand_s[w];
+  int* list = list_s[w];
+  const float* p = D + (long long)row * ld;
+  // upper_only: D is the symmetric N x N matrix with only the tiles on and above the 256-wide diagonal blocks stored;
+  // an entry left of this row's diagonal block is read from its mirror image D[col, row] (bit-identical by construction)
+  const int tri0 = upper_only ? (row & ~255) : 0;
+  auto ldD = [&](int col) { return col < tri0 ? __ldg(D + (long long)col * ld + row) : __ldg(p + col); };
+  const float* cm = chunk_min + (long long)row * cm_pitch;
+  const float m = ordered_int2f(rowmax_key[row]);
+
+  const float dstar = row_dstar<S>(cm, nch, K, m);
 
   // pass 2a: list the qualifying chunks
   int nlist = 0;
@@ -425,6 +435,263 @@ int launch_select_topk_hinted(const float* D, int rows, int cols, long long ld, 
 #undef REID_SELH
   return check_launch("select_topk_hinted_kernel");
 }
+
+// ---------------------------------------------------------------------------------------------
+// Scatter form of the hinted selection for the upper-only symmetric matrix (reid_set_symmetric_contraction(2)): only the
+// tiles on and above the 256-wide diagonal blocks of D are stored.  Reading the missing left part of a row through
+// its mirror image is a sector gather (32 B fetched per 4 B used); instead every stored element is offered to BOTH
+// rows it belongs to:
+//   select_thr_kernel    one warp per row: D*[row] from the chunk minima (which the contraction records for the whole
+//                        row, mirrored part included); the largest D* of every 32-row group -> cthr[group]
+//   select_push_kernel   one warp per row c over its stored chunks (right of the diagonal block's left edge): a chunk
+//                        is read if its minimum can matter to row c (<= D*[c]) or to one of its 32 columns
+//                        (<= cthr[chunk]); element (c, j) becomes a candidate of row c if <= D*[c], and of row j
+//                        (as column c) if j lies right of c's diagonal block and the value is <= D*[j]
+//   select_merge_kernel  one warp per row: (O, column) keys of the row's candidates, sorted, first K emitted
+// Candidate records are (raw D bits, column); their arrival order does not matter (the sort is total).  A row with
+// more candidates than slots takes the exact arg-min rounds with mirror reads, as in the pull form.
+// ---------------------------------------------------------------------------------------------
+constexpr int SELP_LIST = 1024;     // listed chunks per warp (16-bit entries)
+constexpr int SELP_STEP = 4 * 128;  // chunk minima examined per listing step: four float4 per lane
+
+// threshold in the ordered-int domain; an unbounded row (D* = +inf) admits everything, NaN minima included
+__device__ __forceinline__ int thr_key(float t) { return t == INFINITY ? 0x7fffffff : f2ordered_int(t); }
+
+
+template <int S>
+__global__ void __launch_bounds__(SELH_WPB * 32)
+select_thr_kernel(int rows, const int* __restrict__ rowmax_key, const float* __restrict__ chunk_min, int nch,
+                  int cm_pitch, int K, float* __restrict__ dstar_out, int* __restrict__ cthr_key,
+                  int* __restrict__ count) {
+  const int w = threadIdx.x >> 5, lane = lane_id();
+  const int row = blockIdx.x * SELH_WPB + w;
+  if (row >= rows) return;
+  const float m = ordered_int2f(rowmax_key[row]);
+  const float ds = row_dstar<S>(chunk_min + (long long)row * cm_pitch, nch, K, m);
+  if (lane == 0) {
+    dstar_out[row] = ds;
+    count[row] = 0;
+    atomicMax(cthr_key + (row >> 5), thr_key(ds));
+  }
+}
+
+__global__ void __launch_bounds__(SELH_WPB * 32, 5)
+select_push_kernel(const float* __restrict__ D, int n, long long ld, const float* __restrict__ chunk_min, int nch,
+                   int cm_pitch, const float* __restrict__ dstar, const int* __restrict__ cthr_key,
+                   int* __restrict__ count, unsigned long long* __restrict__ pbuf, int cap, int pf) {
+  __shared__ unsigned short list_s[SELH_WPB][SELP_LIST];
+  __shared__ unsigned long long own_s[SELH_WPB][SELH_CAND];
+  __shared__ int nlist_s[SELH_WPB];
+  const int w = threadIdx.x >> 5, lane = lane_id();
+  const int row = blockIdx.x * SELH_WPB + w;
+  if (row >= n) return;
+  unsigned short* list = list_s[w];
+  unsigned long long* own = own_s[w];         // this row's own candidates: staged, appended with one atomic at the end
+  const float* p = D + (long long)row * ld;
+  const float* cm = chunk_min + (long long)row * cm_pitch;
+  const float ds = dstar[row];
+  const int dsk = thr_key(ds);
+  const int tri0 = row & ~255;                // first stored column of this row
+  const int push0 = tri0 + 256;               // columns from here on have this row in their unstored part
+  const int pc0 = push0 >> 5;                 // first chunk whose columns take pushes (a multiple of 8)
+  int nown = 0;
+  if (lane == 0) nlist_s[w] = 0;
+  __syncwarp();
+
+  int c0 = tri0 >> 5;                         // a multiple of 8: float4 loads of chunk minima / thresholds are aligned
+  while (c0 < nch) {
+    // list the chunks that can matter to this row or to one of their columns: four consecutive chunks per lane and
+    // load, four loads in flight; order within the list is irrelevant (the merge sorts)
+    int nlist = 0;
+    for (; c0 < nch && nlist <= SELP_LIST - SELP_STEP; c0 += SELP_STEP) {
+      float4 cmv[4];
+      int4 th[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int c4 = c0 + (u * 32 + lane) * 4;
+        cmv[u] = c4 < nch ? __ldg(reinterpret_cast<const float4*>(cm + c4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        th[u] = (c4 < nch && c4 >= pc0) ? __ldg(reinterpret_cast<const int4*>(cthr_key + c4))
+                                         : make_int4(dsk, dsk, dsk, dsk);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int c4 = c0 + (u * 32 + lane) * 4;
+        unsigned h = (f2ordered_int(cmv[u].x) <= max(dsk, th[u].x) ? 1u : 0u) |
+                     (f2ordered_int(cmv[u].y) <= max(dsk, th[u].y) ? 2u : 0u) |
+                     (f2ordered_int(cmv[u].z) <= max(dsk, th[u].z) ? 4u : 0u) |
+                     (f2ordered_int(cmv[u].w) <= max(dsk, th[u].w) ? 8u : 0u);
+        const int left = nch - c4;            // chunks of this float4 inside the row
+        h = left >= 4 ? h : (left > 0 ? h & ((1u << left) - 1) : 0u);
+        if (h) {
+          int at = atomicAdd(&nlist_s[w], __popc(h));
+          while (h) {
+            const int c = c4 + __ffs(h) - 1;
+            h &= h - 1;
+            list[at++] = (unsigned short)c;
+            // the chunk's line is needed a few microseconds from now: start the fetch
+            if (pf == 1) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + (long long)c * 32));
+            else if (pf == 2) asm volatile("prefetch.global.L1 [%0];" ::"l"(p + (long long)c * 32));
+          }
+        }
+      }
+      __syncwarp();
+      nlist = nlist_s[w];
+    }
+    __syncwarp();
+    if (lane == 0) nlist_s[w] = 0;
+    __syncwarp();
+    // fetch the listed lines eight at a time
+    for (int l0 = 0; l0 < nlist; l0 += 8) {
+      float v[8], tj[8];
+      int col[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        col[u] = l0 + u < nlist ? list[l0 + u] * 32 + lane : n;
+        const bool in = col[u] < n;
+        v[u] = in ? __ldg(p + col[u]) : INFINITY;
+        tj[u] = (in && col[u] >= push0) ? __ldg(dstar + col[u]) : -INFINITY;
+      }
+      // pushes first: independent atomics, all in flight before the first returned slot is used
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const bool push = col[u] < n && col[u] >= push0 && (v[u] <= tj[u] || tj[u] == INFINITY);
+        tj[u] = __int_as_float(push ? atomicAdd(count + col[u], 1) : cap);
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const bool take = col[u] < n && (v[u] <= ds || ds == INFINITY);
+        const unsigned bt = __ballot_sync(FULL, take);
+        const int at = nown + __popc(bt & ((1u << lane) - 1));
+        if (take && at < cap) own[at] = ((unsigned long long)__float_as_uint(v[u]) << 32) | (unsigned)col[u];
+        nown += __popc(bt);
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int pos = __float_as_int(tj[u]);
+        if (pos < cap)
+          pbuf[(long long)col[u] * cap + pos] = ((unsigned long long)__float_as_uint(v[u]) << 32) | (unsigned)row;
+      }
+    }
+    __syncwarp();
+  }
+  // append the staged candidates to this row's records (other rows' pushes land in the same list concurrently)
+  if (nown > 0) {
+    int base = 0;
+    if (lane == 0) base = atomicAdd(count + row, nown);
+    base = __shfl_sync(FULL, base, 0);
+    if (nown <= cap) {
+      unsigned long long* dst = pbuf + (long long)row * cap;
+      for (int i = lane; i < nown; i += 32)
+        if (base + i < cap) dst[base + i] = own[i];
+    }
+  }
+}
+
+__global__ void __launch_bounds__(SELH_WPB * 32)
+select_merge_kernel(const float* __restrict__ D, int n, long long ld, const int* __restrict__ rowmax_key,
+                    const float* __restrict__ chunk_min, int nch, int cm_pitch, const float* __restrict__ dstar_in,
+                    const int* __restrict__ count, const unsigned long long* __restrict__ pbuf, int cap, int K,
+                    int* __restrict__ nbr, float* __restrict__ nbr_val) {
+  __shared__ unsigned long long cand_s[SELH_WPB][SELH_CAND];
+  const int w = threadIdx.x >> 5, lane = lane_id();
+  const int row = blockIdx.x * SELH_WPB + w;
+  if (row >= n) return;
+  unsigned long long* cand = cand_s[w];
+  const float m = ordered_int2f(rowmax_key[row]);
+  const int cnt = count[row];
+  if (cnt <= cap && cnt >= K) {
+    const unsigned long long* src = pbuf + (long long)row * cap;
+    for (int i = lane; i < cnt; i += 32) {
+      const unsigned long long e = src[i];
+      cand[i] = make_ck(__uint_as_float((unsigned)(e >> 32)), m, (int)(unsigned)(e & 0xffffffffu));
+    }
+    int P = 32;
+    while (P < cnt) P <<= 1;
+    for (int i = cnt + lane; i < P; i += 32) cand[i] = ~0ull;
+    __syncwarp();
+    warp_bitonic_u64_sel(cand, P, lane);
+    for (int i = lane; i < K; i += 32) {
+      const unsigned long long k0 = cand[i];
+      nbr[(long long)row * K + i] = (int)(unsigned)(k0 & 0xffffffffu);
+      if (nbr_val) nbr_val[(long long)row * K + i] = key2f((uint32_t)(k0 >> 32));
+    }
+    return;
+  }
+  // more candidates than slots (massive ties): K rounds of warp-wide arg-min, each strictly above the previous pick
+  const float* p = D + (long long)row * ld;
+  const float* cm = chunk_min + (long long)row * cm_pitch;
+  const float dstar = dstar_in[row];
+  const int tri0 = row & ~255;
+  auto ldD = [&](int col) { return col < tri0 ? __ldg(D + (long long)col * ld + row) : __ldg(p + col); };
+  unsigned long long last = 0;
+  for (int r = 0; r < K; ++r) {
+    unsigned long long mine = ~0ull;
+    for (int cc = 0; cc < nch; ++cc) {
+      if (!(__ldg(cm + cc) <= dstar || dstar == INFINITY)) continue;
+      const int col = cc * 32 + lane;
+      if (col < n) {
+        const unsigned long long k0 = make_ck(ldD(col), m, col);
+        if ((r == 0 || k0 > last) && k0 < mine) mine = k0;
+      }
+    }
+    mine = warp_min_u64(mine);
+    last = mine;
+    if (lane == 0) {
+      nbr[(long long)row * K + r] = (int)(unsigned)(last & 0xffffffffu);
+      if (nbr_val) nbr_val[(long long)row * K + r] = key2f((uint32_t)(last >> 32));
+    }
+  }
+}
+
+// workspace: D*[n] f32 | count[n] i32 | (16-byte aligned) cthr[chunk_pitch(n)] i32 | (16-byte aligned) records[n * cap] u64
+static inline size_t scatter_align16(size_t x) { return (x + 15) & ~(size_t)15; }
+static inline size_t scatter_cthr_offset(int n) { return scatter_align16((size_t)8 * n); }
+static inline size_t scatter_records_offset(int n) {
+  return scatter_align16(scatter_cthr_offset(n) + (size_t)4 * chunk_pitch(n));
+}
+size_t select_scatter_workspace_bytes(int n, int cap_override) {
+  const int cap = cap_override > 0 ? (cap_override < SELH_CAND ? cap_override : SELH_CAND) : SELH_CAND;
+  return scatter_records_offset(n) + (size_t)8 * n * cap;
+}
+
+int launch_select_topk_scatter(const float* D, int n, long long ld, const int* rowmax_key, const float* chunk_min,
+                               int K, int* nbr, float* nbr_val, int cap_override, void* workspace,
+                               size_t workspace_bytes, cudaStream_t s) {
+  if (n == 0) return REID_OK;
+  REID_REQUIRE(K >= 1 && K <= 256, "select_topk: K=%d outside [1,256]", K);
+  REID_REQUIRE(n >= K, "select_topk: row length %d is shorter than K=%d", n, K);
+  const int cap = cap_override > 0 ? (cap_override < SELH_CAND ? cap_override : SELH_CAND) : SELH_CAND;
+  REID_REQUIRE(cap >= K || cap_override > 0, "select_topk: K=%d exceeds the candidate buffer", K);
+  REID_REQUIRE(workspace != nullptr && workspace_bytes >= select_scatter_workspace_bytes(n, cap_override),
+               "select_topk_scatter: workspace of %zu bytes, %zu needed", workspace_bytes,
+               select_scatter_workspace_bytes(n, cap_override));
+  REID_REQUIRE(((uintptr_t)workspace & 15) == 0, "select_topk_scatter: workspace must be 16-byte aligned");
+  const int nch = cdiv(n, 32), pitch = chunk_pitch(n);
+  unsigned char* ws = static_cast<unsigned char*>(workspace);
+  float* dstar = reinterpret_cast<float*>(ws);
+  int* count = reinterpret_cast<int*>(ws + (size_t)4 * n);
+  int* cthr = reinterpret_cast<int*>(ws + scatter_cthr_offset(n));
+  unsigned long long* pbuf = reinterpret_cast<unsigned long long*>(ws + scatter_records_offset(n));
+  REID_REQUIRE(nch <= 65535, "select_topk_scatter: %d rows exceed the 16-bit chunk list", n);
+  REID_CUDA(cudaMemsetAsync(cthr, 0x80, (size_t)4 * pitch, s));      // below every ordered float key
+  const int grid = cdiv(n, SELH_WPB), threads = SELH_WPB * 32;
+#define REID_SELT(SS) \
+  select_thr_kernel<SS><<<grid, threads, 0, s>>>(n, rowmax_key, chunk_min, nch, pitch, K, dstar, cthr, count)
+  if (K <= 32) REID_SELT(1);
+  else if (K <= 64) REID_SELT(2);
+  else if (K <= 128) REID_SELT(4);
+  else REID_SELT(8);
+#undef REID_SELT
+  if (int rc = check_launch("select_thr_kernel")) return rc;
+  const char* pfe = getenv("REID_SEL_PF");
+  select_push_kernel<<<grid, threads, 0, s>>>(D, n, ld, chunk_min, nch, pitch, dstar, cthr, count, pbuf, cap,
+                                              pfe ? atoi(pfe) : 1);
+  if (int rc = check_launch("select_push_kernel")) return rc;
+  select_merge_kernel<<<grid, threads, 0, s>>>(D, n, ld, rowmax_key, chunk_min, nch, pitch, dstar, count, pbuf, cap, K,
+                                               nbr, nbr_val);
+  return check_launch("select_merge_kernel");
+}
+
 
 int launch_select_topk(const float* D, int rows, int cols, long long ld, const int* rowmax_key, int K,
                        int* nbr, float* nbr_val, int cap_override, cudaStream_t s) {

@@ -184,7 +184,8 @@ class Engine:
         # Ranks of a multi-GPU job own strided row subsets and always run the full schedule.
         self.symmetric = True
         self.upper_only = True      # ... and, when nobody needs the full matrix, without storing the mirrored half
-        self.upper_only_min_rows = 48_000
+        self.upper_only_min_rows = 0
+        self.scatter_select = True          # upper-only selection in scatter form (reid_topk_rows_scatter)
         self.qe_nosync_bytes = 4 << 30       # budget for sizing the query-expansion pools without a host read
         self._ubmax_pinned = torch.zeros(1, dtype=torch.int64).pin_memory()
         self._ubmax_event = torch.cuda.Event()
@@ -304,7 +305,14 @@ class Engine:
         rows = D.shape[0]
         nbr = self._empty((rows, K), torch.int32)
         val = self._empty((rows, K), torch.float32) if want_values else None
-        if chunk_min is not None:
+        if chunk_min is not None and upper_only and self.scatter_select:
+            # scatter form: every stored element is offered to both of its rows, the unstored half is never gathered
+            assert rows == cols
+            nbytes = int(self.lib.reid_topk_scatter_workspace_bytes(rows, cap))
+            ws = self._empty(((nbytes + 15) // 16 * 2,), torch.int64)
+            _lib.call("reid_topk_rows_scatter", _ptr(D), rows, D.stride(0), _ptr(key), _ptr(chunk_min), K,
+                      _ptr(nbr), _ptr(val), cap, _ptr(ws), ws.numel() * 8, _stream())
+        elif chunk_min is not None:
             _lib.call("reid_topk_rows_hinted_tri", _ptr(D), rows, cols, D.stride(0), _ptr(key), _ptr(chunk_min), K,
                       _ptr(nbr), _ptr(val), cap, int(upper_only), _stream())
         elif cap:
@@ -594,11 +602,10 @@ class Engine:
                 (D, key), cmin = self.dist(mine, allf, METRIC_SQEUCLIDEAN, want_rowmax=True), None
             else:
                 # One rank, symmetric schedule, nobody asked to see D: the mirrored half of the matrix is not written
-                # at all (half the 4 N^2-byte output stream); the two consumers that look left of a row's diagonal block
-                # -- selection and the V weights -- read the mirror image instead.  Queries only ever need gallery
-                # columns, which lie right of their diagonal block.
-                # Those mirror reads are 32-byte sector gathers (8x amplification), ~1e-5 ms per row, against ~2.5e-10 ms
-                # per matrix element saved in the contraction: worth it above N ~ 42 k (MSMT17 scale: -0.8 ms), not below.
+                # at all (half the 4 N^2-byte output stream).  Selection runs in scatter form (every stored element is
+                # offered to both rows it belongs to: reid_topk_rows_scatter) and the V weights read the few mirrored
+                # entries they need as D[col, row].  Queries only ever need gallery columns, which lie right of their
+                # diagonal block.  A win at every size (Duke: contraction -0.10 ms, selection +0.01 ms).
                 tri = (self.upper_only and cm.world == 1 and self.symmetric and detail is None
                        and N >= self.upper_only_min_rows)
                 D, key, cmin = self.dist(mine, allf, METRIC_SQEUCLIDEAN, want_rowmax=True, want_chunk_min=True,

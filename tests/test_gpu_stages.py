@@ -260,6 +260,33 @@ def test_select_fallback_and_ties(eng, engine_mod, oracle):
             np.testing.assert_array_equal(val.cpu().numpy(), np.take_along_axis(O, want.astype(np.int64), 1))
 
 
+@pytest.mark.parametrize("n,dup,K", [(1500, 1, 21), (700, 7, 21), (1100, 1, 70), (300, 1, 9)])
+def test_select_scatter_form_matches_pull_form(eng, engine_mod, n, dup, K):
+    """Upper-only matrix: the scatter form (thresholds, push, merge) == the pull form with mirror reads == the
+    selection on the fully stored matrix, bit for bit, including rows whose candidates overflow the slots."""
+    g = torch.Generator().manual_seed(n)
+    X = torch.randn(n, 48, generator=g).repeat(dup, 1)
+    X = X[torch.randperm(X.shape[0], generator=g)].to(eng.device)      # duplicates spread over the diagonal blocks
+    N = X.shape[0]
+    f = eng.prepare(X, True)
+    saved = eng.symmetric, eng.scatter_select
+    eng.symmetric = True
+    try:
+        D, key, cmin = eng.dist(f, f, engine_mod.METRIC_SQEUCLIDEAN, want_rowmax=True, want_chunk_min=True)
+        want, wval = eng.topk_rows(D, N, key, K, want_values=True, chunk_min=cmin)
+        D3, key3, cmin3 = eng.dist(f, f, engine_mod.METRIC_SQEUCLIDEAN, want_rowmax=True, want_chunk_min=True,
+                                   upper_only=True)
+        assert torch.equal(key3, key) and torch.equal(cmin3, cmin)
+        for cap in (0, 12):
+            for scatter in (True, False):
+                eng.scatter_select = scatter
+                nbr, val = eng.topk_rows(D3, N, key3, K, want_values=True, cap=cap, chunk_min=cmin3, upper_only=True)
+                assert torch.equal(nbr, want), f"cap={cap} scatter={scatter}"
+                assert torch.equal(val, wval), f"cap={cap} scatter={scatter}"
+    finally:
+        eng.symmetric, eng.scatter_select = saved
+
+
 def test_qe_merge_fallback(eng, engine_mod, synth, oracle):
     """A tiny per-warp sort buffer forces the k2-way merge path; results must not change."""
     sh, X, *_ = _features(synth, "tiny", 3, eng.device)
