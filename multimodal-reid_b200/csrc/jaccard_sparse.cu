@@ -207,6 +207,7 @@ constexpr int SS_T = 256;
 constexpr int SS_CAP = 512;     // identity-group entries staged / matches ranked per pass over the row
 constexpr int SS_QSLOTS = 64;   // per-warp queue capacity: untouched entries before the second-worst match (8 B)
 constexpr int SS_QA = 128;      // per-warp queue capacity: overlapping entries (4 B; shares SS_QSLOTS * 8 bytes)
+constexpr int SS_NB = 2048;     // cells of the raw-D histogram of untouched entries below the worst match's threshold
 
 struct SsLayout {               // after bitmap + prefix
   static constexpr size_t mk = 0;                                      // u64[SS_CAP]
@@ -217,7 +218,8 @@ struct SsLayout {               // after bitmap + prefix
   static constexpr size_t thrA = hp + (SS_CAP + 1) * 4;                // float[SS_CAP]
   static constexpr size_t thrB = thrA + SS_CAP * 4;                    // float[SS_CAP]
   static constexpr size_t queue = (thrB + SS_CAP * 4 + 15) & ~(size_t)15;
-  static constexpr size_t bytes = queue + (size_t)(SS_T / 32) * 2 * SS_QSLOTS * 8;
+  static constexpr size_t hist = queue + (size_t)(SS_T / 32) * 2 * SS_QSLOTS * 8;   // int[SS_NB]
+  static constexpr size_t bytes = hist + (size_t)SS_NB * 4;
 };
 
 // overlap value of probe g from the packed record (0 when the query does not touch g)
@@ -246,25 +248,30 @@ static __device__ __noinline__ void sp_drain_overlap(const int* qa, int cnt, con
   }
   __syncwarp();
 }
-static __device__ __noinline__ void sp_drain_zero(const unsigned long long* qz, int cnt, const float* thrA,
-                                                  const float* thrB, const unsigned long long* mk, int P, int* hv) {
-  const int lane = threadIdx.x & 31;
-  if (lane < cnt) {
-    const unsigned long long e = qz[lane];
-    const int col = (int)(unsigned)(e & 0xffffffffu);
-    const float d = __uint_as_float((unsigned)(e >> 32));
-    int lo = 0, hi = P;                                   // #{i : d > thrB[i]}; < P because d <= thrB[P-1]
-    while (lo < hi) {
-      const int mid = (lo + hi) >> 1;
-      if (d > thrB[mid]) lo = mid + 1; else hi = mid;
-    }
-    int bin = lo;
-    for (int i = lo; i < P && thrA[i] < d; ++i) {         // exact ties in final: the smaller column first
-      if ((int)(unsigned)(mk[i] & 0xffffffffu) < col) bin = i + 1; else break;
-    }
-    if (bin < P) bin_add(hv, bin);
+// Untouched entries (overlap 0) rank by raw D alone.  Those at or below the worst match's threshold are counted in a
+// histogram of SS_NB cells over [0, threshold]: cell(d) is monotone in d, so an entry in a cell that holds no match
+// threshold lies on the same side of every threshold as the whole cell.  Cells that do hold one are marked (sign bit);
+// their entries are ranked exactly by ss_zero_bin.
+__device__ __forceinline__ int ss_cell(float d, float scale) {
+  return (int)min(__float2uint_rz(__fmul_rn(d, scale)), (unsigned)(SS_NB - 1));     // negative, NaN -> 0
+}
+__device__ __forceinline__ int ss_zero_bin(float d, int col, const float* thrA, const float* thrB,
+                                           const unsigned long long* mk, int P) {
+  int lo = 0, hi = P;                                     // #{i : d > thrB[i]}; < P because d <= thrB[P-1]
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (d > thrB[mid]) lo = mid + 1; else hi = mid;
   }
-  __syncwarp();
+  int bin = lo;
+  for (int i = lo; i < P && thrA[i] < d; ++i) {           // exact ties in final: the smaller column first
+    if ((int)(unsigned)(mk[i] & 0xffffffffu) < col) bin = i + 1; else break;
+  }
+  return bin;
+}
+__device__ __forceinline__ float ss_pick8(const float4& a, const float4& b, int e) {
+  const float lo = (e & 2) ? ((e & 1) ? a.w : a.z) : ((e & 1) ? a.y : a.x);
+  const float hi = (e & 2) ? ((e & 1) ? b.w : b.z) : ((e & 1) ? b.y : b.x);
+  return (e & 4) ? hi : lo;
 }
 
 __global__ void __launch_bounds__(SS_T, 4)
@@ -286,6 +293,7 @@ score_sparse_kernel(const unsigned char* __restrict__ recs, const int* __restric
   int* hp = reinterpret_cast<int*>(aux + SsLayout::hp);
   float* thrA = reinterpret_cast<float*>(aux + SsLayout::thrA);
   float* thrB = reinterpret_cast<float*>(aux + SsLayout::thrB);
+  int* hist = reinterpret_cast<int*>(aux + SsLayout::hist);
   __shared__ int s_lo, s_len, s_total, s_cnt, s_first, s_zfast;
 
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
@@ -429,6 +437,20 @@ score_sparse_kernel(const unsigned char* __restrict__ recs, const int* __restric
     __syncthreads();
     const bool zfast = s_zfast != 0;
     const unsigned long long maxkey = mk[P - 1];
+    const bool use_hist = zfast && !(out && !wrote);
+    float hscale = 0.0f;
+    if (use_hist) {
+      const float top = thrB[P - 1];
+      if (top > 0.0f && top < INFINITY) hscale = __fdiv_rn((float)SS_NB, top);
+      if (!(hscale < INFINITY)) hscale = 0.0f;                      // degenerate: one cell, every entry ranked exactly
+      for (int x = tid; x < SS_NB; x += T) hist[x] = 0;
+      __syncthreads();
+      for (int i = tid; i < P; i += T) {                           // cells holding a threshold (or a tie range)
+        const int hi = ss_cell(thrB[i], hscale);
+        for (int x = ss_cell(thrA[i], hscale); x <= hi; ++x) hist[x] = (int)0x80000000;
+      }
+      __syncthreads();
+    }
 
     // ---------------------------------------------------------------- one pass over the row
     if (out && !wrote) {
@@ -451,12 +473,8 @@ score_sparse_kernel(const unsigned char* __restrict__ recs, const int* __restric
       wrote = true;
     } else {
       const float dthr = zfast ? thrB[P - 1] : -INFINITY;          // untouched and D > dthr: after every match
-      const float bsec = P >= 2 ? thrB[P - 2] : -INFINITY;
-      const float atop = zfast ? thrA[P - 1] : -INFINITY;
-      int cnt_top = 0;
       int* qa = reinterpret_cast<int*>(wq);                        // SS_QA slots of 4 bytes
-      unsigned long long* qz = wq + SS_QSLOTS;
-      int na = 0, nzq = 0;
+      int na = 0;
       const float4* d4 = reinterpret_cast<const float4*>(drow);
       auto ldg8 = [&](int g, float4& x0, float4& x1) {
         if (g < N) { x0 = __ldg(d4 + (g >> 2)); x1 = __ldg(d4 + (g >> 2) + 1); }
@@ -481,15 +499,12 @@ score_sparse_kernel(const unsigned char* __restrict__ recs, const int* __restric
         const float dmin = fminf(fminf(fminf(c0.x, c0.y), fminf(c0.z, c0.w)), fminf(fminf(c1v.x, c1v.y), fminf(c1v.z, c1v.w)));
         unsigned ma = zfast ? tb : vm;
         unsigned mz = 0;
-        if (zfast && vm != 0 && dmin <= dthr) {                   // rare: something untouched ranks before the worst match
+        if (zfast && vm != 0 && dmin <= dthr) {                   // something untouched ranks before the worst match
           const float dv[8] = {c0.x, c0.y, c0.z, c0.w, c1v.x, c1v.y, c1v.z, c1v.w};
 #pragma unroll
           for (int e = 0; e < 8; ++e) {
-            if (((vm & ~tb) >> e) & 1u) {
-              const float d = dv[e];
-              if (d <= dthr) {
-                if (d > bsec && d <= atop) ++cnt_top; else mz |= 1u << e;
-              }
+            if ((((vm & ~tb) >> e) & 1u) && dv[e] <= dthr) {
+              if (atomicAdd(hist + ss_cell(dv[e], hscale), 1) < 0) mz |= 1u << e;     // a cell that holds a threshold
             }
           }
         }
@@ -530,31 +545,42 @@ score_sparse_kernel(const unsigned char* __restrict__ recs, const int* __restric
             }
           }
         }
-        if (__any_sync(FULL, mz != 0)) {
-          const float dv[8] = {c0.x, c0.y, c0.z, c0.w, c1v.x, c1v.y, c1v.z, c1v.w};
-#pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const bool on = (mz >> e) & 1u;
-            const unsigned act = __ballot_sync(FULL, on);
-            if (act) {
-              if (nzq + __popc(act) > SS_QSLOTS) { sp_drain_zero(qz, nzq, thrA, thrB, mk, P, hv); nzq = 0; }
-              if (on) qz[nzq + __popc(act & ((1u << lane) - 1))] =
-                  ((unsigned long long)__float_as_uint(dv[e]) << 32) | (unsigned)(gb + e - q);
-              nzq += __popc(act);
-              __syncwarp();
-              while (nzq >= 32) { nzq -= 32; sp_drain_zero(qz + nzq, 32, thrA, thrB, mk, P, hv); }
-            }
-          }
+        while (mz) {                                              // divergent, rare: ranked against the thresholds
+          const int e = __ffs(mz) - 1;
+          mz &= mz - 1;
+          const int bin = ss_zero_bin(ss_pick8(c0, c1v, e), gb + e - q, thrA, thrB, mk, P);
+          if (bin < P) bin_add(hv, bin);
         }
+        __syncwarp();
         c0 = n0; c1v = n1; n0 = f0; n1 = f1;
       }
       if (na > 0) sp_drain_overlap(qa, na, bm, pre, vals, drow, m, c1h, c2, q, mk, P, maxkey, hv);
-      if (nzq > 0) sp_drain_zero(qz, nzq, thrA, thrB, mk, P, hv);
-#pragma unroll
-      for (int off = 16; off > 0; off >>= 1) cnt_top += __shfl_xor_sync(FULL, cnt_top, off);
-      if (lane == 0 && cnt_top) atomicAdd(hv + (P - 1), cnt_top);
     }
     __syncthreads();
+    if (use_hist) {
+      // fold the histogram into the match bins: a clean cell x belongs to bin #{i : cell(thrB[i]) < x}; every thread
+      // walks SS_NB / T consecutive cells (bins are non-decreasing along them), then equal bins combine per warp
+      constexpr int PER = SS_NB / T;
+      int x = tid * PER;
+      int lo = 0, hi = P;
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (ss_cell(thrB[mid], hscale) < x) lo = mid + 1; else hi = mid;
+      }
+      int bin = lo, sum = 0;
+      for (int k = 0; k < PER; ++k, ++x) {
+        const int h = hist[x];
+        if (h <= 0) continue;                                       // empty, or marked: its entries were ranked exactly
+        while (bin < P && ss_cell(thrB[bin], hscale) < x) {
+          if (sum) { atomicAdd(hv + bin, sum); sum = 0; }
+          ++bin;
+        }
+        sum += h;
+      }
+      const unsigned peers = __match_any_sync(FULL, bin);
+      const int tot = __reduce_add_sync(peers, sum);
+      if (tot && lane == __ffs(peers) - 1 && bin < P) atomicAdd(hv + bin, tot);
+    }
     // the whole identity group: junk leaves the kept bins, every match enters the match bins
     for (int e = tid; e < L; e += T) {
       int j;
