@@ -20,12 +20,13 @@ __global__ void qe_bound_kernel(const int* __restrict__ nbr, int K, int k2, cons
 }
 
 // Exclusive scan int32 -> int64 offsets (+ total at out[n]); n is 2e4 .. 2e6 (row counts, identity-index slots).
-// Every CTA scans 16 K entries (16 per thread) and chains its total to the next CTA through a per-launch epoch flag:
-// at most 128 CTAs, all resident at once (one per SM), so the chain cannot deadlock.
-constexpr int SCAN_ITEMS = 16;
+// Every CTA scans tiles of 4 K entries (4 per thread).  With several CTAs each publishes its own total first (epoch
+// flag per launch) and then adds up the totals of all CTAs before it, 32 at a time -- one hop instead of a chain.
+// At most 128 CTAs, all resident at once, and no CTA waits for a later one, so the look-back cannot deadlock.
+constexpr int SCAN_ITEMS = 4;
 constexpr int SCAN_TILE = 1024 * SCAN_ITEMS;
 constexpr int SCAN_MAX_CTAS = 128;
-__device__ unsigned long long g_scan_sum[SCAN_MAX_CTAS];      // inclusive total up to and including CTA b
+__device__ unsigned long long g_scan_sum[SCAN_MAX_CTAS];      // total of CTA b alone
 __device__ unsigned int g_scan_epoch[SCAN_MAX_CTAS];
 
 __global__ void __launch_bounds__(1024)
@@ -51,18 +52,23 @@ exclusive_scan_kernel(const int* __restrict__ in, int n, long long* __restrict__
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(FULL, t, o);
       if (lane == 0) {
-        long long before = 0;
-        if (blockIdx.x > 0) {
-          volatile unsigned int* ep = g_scan_epoch + (blockIdx.x - 1);
-          while (*ep != epoch) __nanosleep(20);
-          __threadfence();
-          before = (long long)*(volatile unsigned long long*)(g_scan_sum + blockIdx.x - 1);
-        }
-        *(volatile unsigned long long*)(g_scan_sum + blockIdx.x) = (unsigned long long)(before + t);
+        *(volatile unsigned long long*)(g_scan_sum + blockIdx.x) = (unsigned long long)t;
         __threadfence();
         *(volatile unsigned int*)(g_scan_epoch + blockIdx.x) = epoch;
-        s_prefix = before;
       }
+      long long before = 0;
+      for (int j0 = 0; j0 < (int)blockIdx.x; j0 += 32) {          // totals of the CTAs before this one
+        const int j = j0 + lane;
+        if (j < (int)blockIdx.x) {
+          volatile unsigned int* ep = g_scan_epoch + j;
+          while (*ep != epoch) __nanosleep(20);
+          __threadfence();
+          before += (long long)*(volatile unsigned long long*)(g_scan_sum + j);
+        }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) before += __shfl_xor_sync(FULL, before, o);
+      if (lane == 0) s_prefix = before;
     }
     __syncthreads();
     prefix = s_prefix;

@@ -268,21 +268,15 @@ __device__ __forceinline__ float row_dstar(const float* __restrict__ cm, int nch
   float keep[S];
 #pragma unroll
   for (int s = 0; s < S; ++s) keep[s] = INFINITY;
-  {
-    int c = lane;
-    for (; c + 7 * 32 < nch; c += 8 * 32) {
-      float v[8];
+  // lane l takes chunks l, l + 32, ...: neighbours cluster in adjacent chunks when the gallery is ordered by identity,
+  // and a lane keeps only S values, so adjacent chunks must go to different lanes for the bound to stay tight
+  for (int c = lane; c < nch; c += 8 * 32) {
+    float v[8];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) v[u] = __ldg(cm + c + u * 32);
+    for (int u = 0; u < 8; ++u) v[u] = c + u * 32 < nch ? __ldg(cm + c + u * 32) : INFINITY;
 #pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        float x = v[u];
-#pragma unroll
-        for (int s = 0; s < S; ++s) { const float lo = fminf(keep[s], x); x = fmaxf(keep[s], x); keep[s] = lo; }
-      }
-    }
-    for (; c < nch; c += 32) {
-      float x = __ldg(cm + c);
+    for (int u = 0; u < 8; ++u) {
+      float x = v[u];
 #pragma unroll
       for (int s = 0; s < S; ++s) { const float lo = fminf(keep[s], x); x = fmaxf(keep[s], x); keep[s] = lo; }
     }
@@ -420,6 +414,7 @@ int launch_select_topk_hinted(const float* D, int rows, int cols, long long ld, 
   REID_REQUIRE(K >= 1 && K <= 256, "select_topk: K=%d outside [1,256]", K);
   REID_REQUIRE(cols >= K, "select_topk: row length %d is shorter than K=%d", cols, K);
   REID_REQUIRE(!upper_only || rows == cols, "select_topk: upper_only needs the square N x N matrix (%d x %d)", rows, cols);
+  REID_REQUIRE(((uintptr_t)chunk_min & 15) == 0, "select_topk: chunk_min must be 16-byte aligned");
   const int nch = cdiv(cols, 32);
   const int cap = cap_override > 0 ? (cap_override < SELH_CAND ? cap_override : SELH_CAND) : SELH_CAND;
   const int list_cap = cap_override > 0 ? (cap_override < SELH_LIST ? cap_override : SELH_LIST) : SELH_LIST;
@@ -666,6 +661,7 @@ int launch_select_topk_scatter(const float* D, int n, long long ld, const int* r
                "select_topk_scatter: workspace of %zu bytes, %zu needed", workspace_bytes,
                select_scatter_workspace_bytes(n, cap_override));
   REID_REQUIRE(((uintptr_t)workspace & 15) == 0, "select_topk_scatter: workspace must be 16-byte aligned");
+  REID_REQUIRE(((uintptr_t)chunk_min & 15) == 0, "select_topk_scatter: chunk_min must be 16-byte aligned");
   const int nch = cdiv(n, 32), pitch = chunk_pitch(n);
   unsigned char* ws = static_cast<unsigned char*>(workspace);
   float* dstar = reinterpret_cast<float*>(ws);
