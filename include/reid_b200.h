@@ -72,6 +72,10 @@ REID_API int reid_chunk_pitch(int n);
 REID_API int reid_prepare_features(const float* X, int n, int d, int64_t ld_x, int normalize, float* x32,
                           reid_half* hi, reid_half* lo, int dpad, float* sq, float* nrm, uint32_t* amax,
                           void* stream);
+/* the same for a range of rows of a larger matrix.  preset_amax != 0: *amax already holds (the float bits of) a bound on
+ * max|x| over the WHOLE matrix and is used as is -- rows prepared in separate calls then share one scaling exponent */
+REID_API int reid_prepare_rows(const float* X, int n, int d, int64_t ld_x, int normalize, float* x32, reid_half* hi,
+                      reid_half* lo, int dpad, float* sq, float* nrm, uint32_t* amax, int preset_amax, void* stream);
 
 /* K1/K2/K3  evaluate.py:7-26, reranking.py:36-41.  out[i, j] for A rows i < m, B rows j < n.
  * metric 0: (ra[i] + rb[j]) - 2 a.b with ra/rb = squared norms; metric 1: arccos(clip(a.b *
@@ -98,6 +102,20 @@ REID_API int reid_dist(const reid_half* Ahi, const reid_half* Alo, int64_t lda, 
               const uint32_t* a_amax, int m, const reid_half* Bhi, const reid_half* Blo, int64_t ldb,
               const float* rb, const uint32_t* b_amax, int n, int dpad, int metric, float* out,
               int64_t ld_out, int32_t* rowmax_key, float* chunk_min, void* stream);
+/* One block of a larger symmetric distance matrix, for callers that compute it chunk by chunk (the streamed evaluator:
+ * the features of evaluate.py:110 are still arriving over PCIe while the first blocks are contracted).  Block origins
+ * must be multiples of 256 rows / columns of the enclosing matrix; out, rowmax_key and chunk_min point at the block's
+ * origin inside the enclosing arrays; cm_pitch is the enclosing chunk-minimum row pitch (reid_chunk_pitch(N)).
+ *   mode 0  plain rectangle
+ *   mode 2  square diagonal block (same rows on both sides), upper-only form as reid_set_symmetric_contraction(2)
+ *   mode 3  rectangle strictly above the diagonal: stored as is; its mirror image's row maxima / chunk minima go to
+ *           rowmax_key_cols[block column] and chunk_min_cols[block column * cm_pitch + block row / 32]
+ * The blocks of one matrix give bit for bit the matrix a single reid_dist call gives. */
+REID_API int reid_dist_block(const reid_half* Ahi, const reid_half* Alo, int64_t lda, const float* ra, const uint32_t* a_amax,
+                    int m, const reid_half* Bhi, const reid_half* Blo, int64_t ldb, const float* rb,
+                    const uint32_t* b_amax, int n, int dpad, int metric, float* out, int64_t ld_out,
+                    int32_t* rowmax_key, float* chunk_min, int cm_pitch, int mode, int32_t* rowmax_key_cols,
+                    float* chunk_min_cols, void* stream);
 REID_API int reid_dist_fp32(const float* A, int64_t lda, const float* ra, int m, const float* B, int64_t ldb,
                    const float* rb, int n, int dpad, int metric, float* out, int64_t ld_out,
                    int32_t* rowmax_key, void* stream);

@@ -139,6 +139,15 @@ int reid_prepare_features(const float* X, int n, int d, int64_t ld_x, int normal
   return launch_prep(X, n, d, ld_x, normalize, x32, H(hi), H(lo), dpad, sq, nrm, amax, S(stream));
 }
 
+int reid_prepare_rows(const float* X, int n, int d, int64_t ld_x, int normalize, float* x32, reid_half* hi,
+                      reid_half* lo, int dpad, float* sq, float* nrm, uint32_t* amax, int preset_amax, void* stream) {
+  ENTER();
+  REID_REQUIRE(n >= 0 && d >= 1 && ld_x >= d, "prepare_rows: bad shape n=%d d=%d ld=%lld", n, d, (long long)ld_x);
+  REID_REQUIRE(dpad >= d && dpad % 64 == 0, "prepare_rows: dpad=%d must be a multiple of 64 >= d=%d", dpad, d);
+  return launch_prep_rows(X, n, d, ld_x, normalize, x32, H(hi), H(lo), dpad, sq, nrm, amax, preset_amax ? 1 : 0,
+                          S(stream));
+}
+
 int reid_dist_clock_probe(int64_t* host_out4) {
   ENTER();
   return dist_clock_probe(reinterpret_cast<long long*>(host_out4));
@@ -158,6 +167,21 @@ int reid_dist(const reid_half* Ahi, const reid_half* Alo, int64_t lda, const flo
   REID_REQUIRE(m >= 0 && n >= 0 && dpad > 0 && ld_out >= n && lda >= dpad && ldb >= dpad, "dist: bad shape");
   return launch_dist_tc(HC(Ahi), HC(Alo), lda, ra, a_amax, m, HC(Bhi), HC(Blo), ldb, rb, b_amax, n, dpad, metric,
                         out, ld_out, rowmax_key, chunk_min, S(stream));
+}
+
+int reid_dist_block(const reid_half* Ahi, const reid_half* Alo, int64_t lda, const float* ra, const uint32_t* a_amax,
+                    int m, const reid_half* Bhi, const reid_half* Blo, int64_t ldb, const float* rb,
+                    const uint32_t* b_amax, int n, int dpad, int metric, float* out, int64_t ld_out,
+                    int32_t* rowmax_key, float* chunk_min, int cm_pitch, int mode, int32_t* rowmax_key_cols,
+                    float* chunk_min_cols, void* stream) {
+  ENTER();
+  REID_REQUIRE(metric == 0 || metric == 1, "dist_block: unknown metric %d", metric);
+  REID_REQUIRE(m >= 0 && n >= 0 && dpad > 0 && ld_out >= n && lda >= dpad && ldb >= dpad, "dist_block: bad shape");
+  REID_REQUIRE(mode == 0 || mode == 2 || mode == 3, "dist_block: mode %d (0 rectangle, 2 upper-only square, 3 above the diagonal)", mode);
+  REID_REQUIRE(cm_pitch >= 0, "dist_block: negative chunk-minimum pitch");
+  return launch_dist_tc_block(HC(Ahi), HC(Alo), lda, ra, a_amax, m, HC(Bhi), HC(Blo), ldb, rb, b_amax, n, dpad, metric,
+                              out, ld_out, rowmax_key, chunk_min, cm_pitch, mode,
+                              mode == 3 ? rowmax_key_cols : rowmax_key, mode == 3 ? chunk_min_cols : chunk_min, S(stream));
 }
 
 int reid_dist_fp32(const float* A, int64_t lda, const float* ra, int m, const float* B, int64_t ldb,

@@ -238,7 +238,8 @@ dist_tc2_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant
                 const float* __restrict__ rb, const uint32_t* __restrict__ a_amax,
                 const uint32_t* __restrict__ b_amax, int m, int n, int kblocks, int metric,
                 int* __restrict__ rowmax_key, float* __restrict__ chunk_min, int nchunks, int symmetric,
-                int ntiles, float* __restrict__ out, long long ld_out, int dbg) {
+                int ntiles, float* __restrict__ out, long long ld_out, int dbg,
+                int* __restrict__ rowmax_key_m, float* __restrict__ chunk_min_m) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* epi_base = smem + STAGES * STAGE_BYTES;
   float* rb_s = reinterpret_cast<float*>(epi_base + EPI_BYTES);
@@ -255,6 +256,7 @@ dist_tc2_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
   const int mblocks = (m + BM - 1) / BM, nblocks = (n + BN - 1) / BN;
+  const int sym_cursor = symmetric == 3 ? 0 : symmetric;      // mode 3 walks the plain rectangle
   const int tile0 = (int)cluster_id_x(), tile_step = (int)n_clusters_x();
 
   if ((dbg & 64) && blockIdx.x == 0 && threadIdx.x == 0) { g_probe[0] = clock64(); g_probe[1] = globaltimer_ns(); }
@@ -286,7 +288,7 @@ dist_tc2_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant
       const uint64_t pol_ld = l2_policy_evict_last();
       for (int t = tile0; t < ntiles; t += tile_step) {
         int mb, nb;
-        cur.locate(t, symmetric, mblocks, nblocks, mb, nb);
+        cur.locate(t, sym_cursor, mblocks, nblocks, mb, nb);
         const int m0 = mb * BM + (int)rank * CM, n0 = nb * BN + (int)rank * HB;
         for (int kb = 0; kb < kblocks; ++kb) {
           mbar_wait(EMPTY_B(stage), phase ^ 1);
@@ -344,14 +346,14 @@ dist_tc2_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant
     int it = 0, nstore = 0;
     TileCursor cur;
     int mb = 0, nb = 0;
-    if (tile0 < ntiles) cur.locate(tile0, symmetric, mblocks, nblocks, mb, nb);
+    if (tile0 < ntiles) cur.locate(tile0, sym_cursor, mblocks, nblocks, mb, nb);
     // the row / column norms of a tile are fetched one tile ahead
     float rb_next = (nb * BN + et < n) ? rb[nb * BN + et] : 0.0f;
     float ra_next = (mb * BM + row_in_tile + lane < m) ? ra[mb * BM + row_in_tile + lane] : 0.0f;
     for (int t = tile0; t < ntiles; t += tile_step, ++it) {
       const int r0 = mb * BM + row_in_tile;    // first row of this warp's 32
       const int n0 = nb * BN;
-      const bool mirror = symmetric && mb < nb;
+      const bool mirror = symmetric == 3 || (symmetric && mb < nb);
       const bool store_mirror = symmetric == 1;   // mode 2: consumers read the lower triangle transposed
       const int as = it & 1, aph = (it >> 1) & 1;
       float* rbt = rb_s + (it & 1) * BN;
@@ -363,7 +365,7 @@ dist_tc2_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant
       {
         const int tn = t + tile_step;
         if (tn < ntiles) {
-          cur.locate(tn, symmetric, mblocks, nblocks, mb, nb);
+          cur.locate(tn, sym_cursor, mblocks, nblocks, mb, nb);
           rb_next = (nb * BN + et < n) ? rb[nb * BN + et] : 0.0f;
           ra_next = (mb * BM + row_in_tile + lane < m) ? ra[mb * BM + row_in_tile + lane] : 0.0f;
         }
@@ -480,8 +482,8 @@ dist_tc2_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant
           }
           const int trow = col0 + lane;
           if (trow < n) {
-            if (chunk_min) chunk_min[(long long)trow * nchunks + (r0 >> 5)] = tmn;
-            if (rowmax_key) atomicMax(rowmax_key + trow, f2ordered_int(tmx));
+            if (chunk_min_m) chunk_min_m[(long long)trow * nchunks + (r0 >> 5)] = tmn;
+            if (rowmax_key_m) atomicMax(rowmax_key_m + trow, f2ordered_int(tmx));
           }
         }
       }
@@ -558,9 +560,25 @@ int launch_dist_tc(const __half* Ahi, const __half* Alo, long long lda, const fl
                    int m, const __half* Bhi, const __half* Blo, long long ldb, const float* rb,
                    const uint32_t* b_amax, int n, int dp, int metric, float* out, long long ld_out,
                    int* rowmax_key, float* chunk_min, cudaStream_t s) {
+  return launch_dist_tc_block(Ahi, Alo, lda, ra, a_amax, m, Bhi, Blo, ldb, rb, b_amax, n, dp, metric, out, ld_out,
+                              rowmax_key, chunk_min, 0, -1, rowmax_key, chunk_min, s);
+}
+
+// One block of a larger distance matrix (the streamed evaluator computes D chunk by chunk while the features are still
+// arriving).  mode -1: as launch_dist_tc (symmetric schedule when both operands are the same rows, per
+// reid_set_symmetric_contraction); 0: plain rectangle; 2: square diagonal block, upper-only form; 3: rectangle that lies
+// strictly above the diagonal of the enclosing symmetric matrix -- stored as is, and every tile also contributes the
+// row maxima / chunk minima of its mirror image through rowmax_key_m / chunk_min_m (indexed by the block's columns).
+// cm_pitch: row pitch of the chunk-minimum arrays (0: chunk_pitch(n)); all block origins must be multiples of 256.
+int launch_dist_tc_block(const __half* Ahi, const __half* Alo, long long lda, const float* ra, const uint32_t* a_amax,
+                         int m, const __half* Bhi, const __half* Blo, long long ldb, const float* rb,
+                         const uint32_t* b_amax, int n, int dp, int metric, float* out, long long ld_out,
+                         int* rowmax_key, float* chunk_min, int cm_pitch, int mode, int* rowmax_key_m,
+                         float* chunk_min_m, cudaStream_t s) {
   using namespace tc2;
   if (m == 0 || n == 0) return REID_OK;
   static const int pair = getenv("REID_TC_PAIR") ? atoi(getenv("REID_TC_PAIR")) : 1;
+  REID_REQUIRE(pair || (mode == -1 && cm_pitch == 0), "dist_tc: block modes need the CTA-pair kernel (REID_TC_PAIR=0 is set)");
   if (!pair)
     return launch_dist_tc1(Ahi, Alo, lda, ra, a_amax, m, Bhi, Blo, ldb, rb, b_amax, n, dp, metric, out, ld_out,
                            rowmax_key, chunk_min, s);
@@ -580,11 +598,15 @@ int launch_dist_tc(const __half* Ahi, const __half* Alo, long long lda, const fl
   REID_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   REID_CUDA(cudaFuncSetAttribute(dist_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
   // same rows on both sides and a square output: compute the upper triangle only and mirror it
-  const int symmetric = (Ahi == Bhi && Alo == Blo && lda == ldb && ra == rb && a_amax == b_amax && m == n &&
-                         g_symmetric_enabled) ? g_symmetric_enabled : 0;
+  const bool same = Ahi == Bhi && Alo == Blo && lda == ldb && ra == rb && a_amax == b_amax && m == n;
+  REID_REQUIRE(mode >= -1 && mode <= 3 && mode != 1, "dist_tc: unknown block mode %d", mode);
+  REID_REQUIRE(mode != 2 || same, "dist_tc: the upper-only form needs the same rows on both sides");
+  const int symmetric = mode >= 0 ? mode : ((same && g_symmetric_enabled) ? g_symmetric_enabled : 0);
+  const int pitch = cm_pitch > 0 ? cm_pitch : chunk_pitch(n);
+  REID_REQUIRE(pitch % 4 == 0 && ((uintptr_t)chunk_min & 15) == 0, "dist_tc: chunk minima must be 16-byte aligned");
   const int mblocks = cdiv(m, BM), nblocks = cdiv(n, BN);
   long long ntiles = (long long)mblocks * nblocks;
-  if (symmetric) {
+  if (symmetric == 1 || symmetric == 2) {
     ntiles = 0;
     for (int g = 0; g * RASTER_GROUP < nblocks; ++g) ntiles += sym_group_tiles(g, nblocks);
   }
@@ -594,8 +616,9 @@ int launch_dist_tc(const __half* Ahi, const __half* Alo, long long lda, const fl
   const char* dbg_env = getenv("REID_TC_DBG");          // diagnostics only (scratch/dist_knobs.py)
   const int dbg = dbg_env ? atoi(dbg_env) : 0;
   dist_tc2_kernel<<<2 * clusters, THREADS, SMEM_BYTES, s>>>(mAhi, mAlo, mBhi, mBlo, mOut, ra, rb, a_amax, b_amax, m, n,
-                                                            dp / BK, metric, rowmax_key, chunk_min, chunk_pitch(n),
-                                                            symmetric, (int)ntiles, out, ld_out, dbg);
+                                                            dp / BK, metric, rowmax_key, chunk_min, pitch,
+                                                            symmetric, (int)ntiles, out, ld_out, dbg, rowmax_key_m,
+                                                            chunk_min_m);
   return check_launch("dist_tc2_kernel");
 }
 

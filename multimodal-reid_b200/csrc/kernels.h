@@ -18,11 +18,18 @@ static inline int padded_width(int d) { return (d + 63) / 64 * 64; }   // tensor
 // row pitch of the 32-column chunk minima: 8 slots per 256-column tile, so a tile's slots are 16-byte aligned groups
 static inline int chunk_pitch(int n) { return 8 * ((n + 255) / 256); }
 
+int launch_prep_rows(const float* X, int n, int d, long long ld_x, int normalize, float* x32, __half* hi,
+                     __half* lo, int dp, float* sq, float* nrm, uint32_t* amax, int preset_amax, cudaStream_t s);
 int launch_prep(const float* X, int n, int d, long long ld_x, int normalize, float* x32, __half* hi, __half* lo,
                 int dp, float* sq, float* nrm, uint32_t* amax, cudaStream_t s);
 int launch_dist_simt(const float* A, long long lda, const float* ra, int m, const float* B, long long ldb,
                      const float* rb, int n, int dp, int metric, float* out, long long ld_out,
                      int* rowmax_key, cudaStream_t s);
+int launch_dist_tc_block(const __half* Ahi, const __half* Alo, long long lda, const float* ra, const uint32_t* a_amax,
+                         int m, const __half* Bhi, const __half* Blo, long long ldb, const float* rb,
+                         const uint32_t* b_amax, int n, int dp, int metric, float* out, long long ld_out,
+                         int* rowmax_key, float* chunk_min, int cm_pitch, int mode, int* rowmax_key_m,
+                         float* chunk_min_m, cudaStream_t s);
 int launch_dist_tc(const __half* Ahi, const __half* Alo, long long lda, const float* ra, const uint32_t* a_amax,
                    int m, const __half* Bhi, const __half* Blo, long long ldb, const float* rb,
                    const uint32_t* b_amax, int n, int dp, int metric, float* out, long long ld_out,

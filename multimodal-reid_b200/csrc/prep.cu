@@ -46,7 +46,7 @@ __global__ void __launch_bounds__(256) prep_rows_kernel(const float* __restrict_
   if (lane == 0) {
     sq[row] = ss2;
     nrm[row] = sqrtf(ss2);
-    if (mx == mx && mx < INFINITY) atomicMax(amax, __float_as_uint(mx));   // non-negative floats order as uints
+    if (amax && mx == mx && mx < INFINITY) atomicMax(amax, __float_as_uint(mx));   // non-negative floats order as uints
   }
 }
 
@@ -84,10 +84,18 @@ __global__ void __launch_bounds__(256) split_f16_kernel(const float* __restrict_
 
 int launch_prep(const float* X, int n, int d, long long ld_x, int normalize, float* x32, __half* hi,
                 __half* lo, int dp, float* sq, float* nrm, uint32_t* amax, cudaStream_t s) {
-  REID_CUDA(cudaMemsetAsync(amax, 0, sizeof(uint32_t), s));
+  return launch_prep_rows(X, n, d, ld_x, normalize, x32, hi, lo, dp, sq, nrm, amax, 0, s);
+}
+
+// preset_amax: *amax already holds the bits of a bound on max|x| of the WHOLE matrix these rows belong to (the streamed
+// evaluator prepares the rows chunk by chunk, so the matrix-wide maximum is not known yet); it is used as is.
+int launch_prep_rows(const float* X, int n, int d, long long ld_x, int normalize, float* x32, __half* hi,
+                     __half* lo, int dp, float* sq, float* nrm, uint32_t* amax, int preset_amax, cudaStream_t s) {
+  if (!preset_amax) REID_CUDA(cudaMemsetAsync(amax, 0, sizeof(uint32_t), s));
   if (n == 0) return REID_OK;
   const int wpb = 8;
-  prep_rows_kernel<<<cdiv(n, wpb), wpb * 32, 0, s>>>(X, n, d, ld_x, normalize, x32, dp, sq, nrm, amax);
+  prep_rows_kernel<<<cdiv(n, wpb), wpb * 32, 0, s>>>(X, n, d, ld_x, normalize, x32, dp, sq, nrm,
+                                                     preset_amax ? nullptr : amax);
   int rc = check_launch("prep_rows_kernel");
   if (rc) return rc;
   const long long total4 = (long long)n * dp / 4;

@@ -40,6 +40,9 @@ def v_row_capacity(k1: int) -> int:
     return _lib.load().reid_v_row_capacity(int(k1))
 
 
+_ONE_BITS = 0x3F800000      # float32 1.0
+
+
 @dataclasses.dataclass
 class Features:
     """Prepared feature rows (engine.prepare): float32 rows padded to dp, their float16 hi/lo split
@@ -185,6 +188,8 @@ class Engine:
         self.symmetric = True
         self.upper_only = True      # ... and, when nobody needs the full matrix, without storing the mirrored half
         self.upper_only_min_rows = 0
+        self.stream_h2d = True              # evaluator: copy host features chunk by chunk under the contraction
+        self._copy_stream = None
         self.scatter_select = True          # upper-only selection in scatter form (reid_topk_rows_scatter)
         self.qe_nosync_bytes = 4 << 30       # budget for sizing the query-expansion pools without a host read
         self._ubmax_pinned = torch.zeros(1, dtype=torch.int64).pin_memory()
@@ -241,10 +246,109 @@ class Engine:
         lo = self._empty((n, dp), torch.float16)
         sq = self._empty((n,), torch.float32)
         nrm = self._empty((n,), torch.float32)
-        amax = self._empty((1,), torch.int32)
-        _lib.call("reid_prepare_features", _ptr(X), n, d, X.stride(0), int(normalize), _ptr(x32), _ptr(hi), _ptr(lo),
-                  dp, _ptr(sq), _ptr(nrm), _ptr(amax), _stream())
+        if normalize:
+            # L2-normalised rows are bounded by 1: the split's power-of-two scale is fixed up front instead of taken from
+            # the measured matrix-wide maximum, so a row's operands do not depend on which other rows it is prepared
+            # with (the streamed evaluator prepares the rows chunk by chunk and must produce the same bits)
+            amax = torch.full((1,), _ONE_BITS, dtype=torch.int32, device=self.device)
+            _lib.call("reid_prepare_rows", _ptr(X), n, d, X.stride(0), 1, _ptr(x32), _ptr(hi), _ptr(lo), dp, _ptr(sq),
+                      _ptr(nrm), _ptr(amax), 1, _stream())
+        else:
+            amax = self._empty((1,), torch.int32)
+            _lib.call("reid_prepare_features", _ptr(X), n, d, X.stride(0), 0, _ptr(x32), _ptr(hi), _ptr(lo),
+                      dp, _ptr(sq), _ptr(nrm), _ptr(amax), _stream())
         return Features(x32, hi, lo, sq, nrm, amax, d)
+
+    # ------------------------------------------------------------------ K13 + K1, streamed from host memory
+    @staticmethod
+    def stream_bounds(N: int) -> list[int]:
+        """Row boundaries (multiples of 256) of the chunks the streamed path works in.  The contraction of a chunk
+        needs the rows before it, so its cost grows with the chunk's position; later chunks are smaller so that little
+        work is left when the last byte has arrived."""
+        if N < 4096:
+            return [0, N]
+        b = [0]
+        for f in (0.40, 0.65, 0.80, 0.90):
+            r = int(N * f) // 256 * 256
+            if r > b[-1]:
+                b.append(r)
+        b.append(N)
+        return b
+
+    def prepare_dist_streamed(self, parts, normalize: bool = True):
+        """parts: host float32 [n_i, d] tensors (pinned for a truly asynchronous copy), rows in order.  Copies them to
+        the device chunk by chunk on a side stream and, as each chunk lands, prepares its rows and contracts the blocks
+        of the symmetric distance matrix that have become computable (the diagonal block in upper-only form, and the
+        rectangle above it with the mirrored statistics).  Same bits as prepare() + dist(upper_only=True) on the
+        whole matrix.  Returns (D, rowmax_key, chunk_min, N)."""
+        assert normalize and self.comm.world == 1 and self.engine != ENGINES["simt"]
+        N = sum(int(p.shape[0]) for p in parts)
+        d = int(parts[0].shape[1])
+        dp = self.lib.reid_padded_width(d)
+        X = self._empty((N, d), torch.float32)
+        x32 = self._empty((N, dp), torch.float32)
+        hi = self._empty((N, dp), torch.float16)
+        lo = self._empty((N, dp), torch.float16)
+        sq = self._empty((N,), torch.float32)
+        nrm = self._empty((N,), torch.float32)
+        amax = torch.full((1,), _ONE_BITS, dtype=torch.int32, device=self.device)
+        ld = self.pitch(N)
+        D = self._empty((N, ld), torch.float32)
+        key = self._empty((N,), torch.int32)
+        _lib.call("reid_rowmax_init", _ptr(key), N, _stream())
+        cpitch = self.lib.reid_chunk_pitch(N)
+        cmin = self._empty((N, cpitch), torch.float32)
+        bounds = self.stream_bounds(N)
+        cur = torch.cuda.current_stream(self.device)
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(self.device)
+        cs = self._copy_stream
+        cs.wait_stream(cur)                       # X was allocated on the compute stream
+        events = []
+        with torch.cuda.stream(cs):
+            r, ci = 0, 0
+            for p in parts:
+                assert p.dtype == torch.float32 and p.dim() == 2 and p.shape[1] == d
+                off, n_p = 0, int(p.shape[0])
+                while off < n_p:
+                    take = min(n_p - off, bounds[ci + 1] - r)
+                    X[r: r + take].copy_(p[off: off + take], non_blocking=True)
+                    r += take
+                    off += take
+                    if r == bounds[ci + 1]:
+                        ev = torch.cuda.Event()
+                        ev.record(cs)
+                        events.append(ev)
+                        ci += 1
+        st = _stream()
+        for c in range(len(bounds) - 1):
+            b0, b1 = bounds[c], bounds[c + 1]
+            cur.wait_event(events[c])
+            _lib.call("reid_prepare_rows", _ptr(X[b0:b1]), b1 - b0, d, X.stride(0), 1, _ptr(x32[b0:b1]), _ptr(hi[b0:b1]),
+                      _ptr(lo[b0:b1]), dp, _ptr(sq[b0:b1]), _ptr(nrm[b0:b1]), _ptr(amax), 1, st)
+            # diagonal block of this chunk: upper-only form inside the block
+            _lib.call("reid_dist_block", _ptr(hi[b0:b1]), _ptr(lo[b0:b1]), hi.stride(0), _ptr(sq[b0:b1]), _ptr(amax),
+                      b1 - b0, _ptr(hi[b0:b1]), _ptr(lo[b0:b1]), hi.stride(0), _ptr(sq[b0:b1]), _ptr(amax), b1 - b0,
+                      dp, METRIC_SQEUCLIDEAN, _ptr(D[b0:b1, b0:]), ld, _ptr(key[b0:b1]), _ptr(cmin[b0:b1, b0 // 32:]),
+                      cpitch, 2, None, None, st)
+            if b0 > 0:
+                # rows before the chunk x the chunk's columns: above the diagonal, mirrored statistics to the chunk's rows
+                _lib.call("reid_dist_block", _ptr(hi[:b0]), _ptr(lo[:b0]), hi.stride(0), _ptr(sq[:b0]), _ptr(amax), b0,
+                          _ptr(hi[b0:b1]), _ptr(lo[b0:b1]), hi.stride(0), _ptr(sq[b0:b1]), _ptr(amax), b1 - b0, dp,
+                          METRIC_SQEUCLIDEAN, _ptr(D[:b0, b0:]), ld, _ptr(key), _ptr(cmin[:, b0 // 32:]), cpitch, 3,
+                          _ptr(key[b0:b1]), _ptr(cmin[b0:b1]), st)
+        return D, key, cmin[:, : (N + 31) // 32], N
+
+    def evaluate_reranked_host(self, parts, q: int, pids: torch.Tensor, cams: torch.Tensor, k1: int, k2: int,
+                               lam: float, max_rank: int = 50):
+        """evaluate_reranked for features still in host memory (what evaluate.R1_mAP_eval.compute() holds): the copy
+        overlaps the contraction.  One rank, normalised features, tensor-core engine."""
+        with self.span("dist"):
+            D, key, cmin, N = self.prepare_dist_streamed(parts, True)
+        ids = (pids[:q].contiguous(), pids[q:].contiguous(), cams[:q].contiguous(), cams[q:].contiguous())
+        _, res = self.rerank_from_panel(D, key, q, N, k1, k2, lam, None, chunk_min=cmin, score=(ids, max_rank),
+                                        want_final=False, upper_only=True)
+        return res
 
     # ------------------------------------------------------------------ K1/K2/K3
     @staticmethod

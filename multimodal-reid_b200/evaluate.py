@@ -160,11 +160,22 @@ class R1_mAP_eval():
     def compute(self):  # called after each epoch
         eng = _engine.default_engine()
         dev = eng.device
-        feats = torch.cat([_to_device_f32(f, dev) for f in self.feats], dim=0)
+        # Features still in host memory + re-ranking on one rank: the copy is streamed under the contraction
+        # (engine.prepare_dist_streamed) instead of being finished first.  Same bits either way.
+        streamed = (self.reranking and self.feat_norm and eng.stream_h2d and eng.comm.world == 1
+                    and eng.engine != _engine.ENGINES["simt"] and eng.symmetric and eng.upper_only
+                    and len(self.feats) > 0
+                    and all(isinstance(f, torch.Tensor) and not f.is_cuda and f.dtype == torch.float32 and f.dim() == 2
+                            and f.shape[1] == self.feats[0].shape[1] for f in self.feats))
+        if streamed:
+            feats = None
+            N = sum(int(f.shape[0]) for f in self.feats)
+        else:
+            feats = torch.cat([_to_device_f32(f, dev) for f in self.feats], dim=0)
+            N = feats.shape[0]
         if self.feat_norm:
             print("The test feature is normalized")
         q = self.num_query
-        N = feats.shape[0]
         g = N - q
         pids = self._pid_store.to_device(dev)
         camids = self._cam_store.to_device(dev)
@@ -176,7 +187,11 @@ class R1_mAP_eval():
             if g < max_rank:
                 max_rank = g
                 print("Note: number of gallery samples is quite small, got {}".format(g))
-            cmc, mAP, nvalid, _, _ = eng.evaluate_reranked(feats, q, pids, camids, k1, k2, lam, self.feat_norm, max_rank)
+            if streamed:
+                cmc, mAP, nvalid, _, _ = eng.evaluate_reranked_host(self.feats, q, pids, camids, k1, k2, lam, max_rank)
+            else:
+                cmc, mAP, nvalid, _, _ = eng.evaluate_reranked(feats, q, pids, camids, k1, k2, lam, self.feat_norm,
+                                                               max_rank)
             assert int(nvalid.item()) > 0, "Error: all query identities do not appear in gallery"
             cmc, mAP = cmc.cpu().numpy(), np.float64(mAP.item())
             print("Rank@{:d}:{:.1%}, Rank@{:d}:{:.1%}, Rank@{:d}:{:.1%}, mAP:{:.1%}".format(1, cmc[0], 5, cmc[4], 10, cmc[9], mAP))

@@ -28,19 +28,23 @@ def test_prepare_matches_normalize(eng, synth, oracle):
     assert f.dp % 64 == 0 and torch.all(f.x32[:, sh.d:] == 0)
     assert torch.all(f.hi[:, sh.d:] == 0) and torch.all(f.lo[:, sh.d:] == 0)
     np.testing.assert_allclose(f.sq.cpu().numpy(), (want.astype(np.float64) ** 2).sum(1), rtol=1e-5)
-    # float16 split: x * 2^e = hi + lo to ~22 bits, with max|x| * 2^e in [2^14, 2^15)
-    amax = f.amax.cpu().numpy().view(np.float32)[0]
-    assert amax == np.abs(got).max()
-    e = 14 - int(np.floor(np.log2(amax)))
-    hi = f.hi.cpu().numpy().astype(np.float64)
-    lo = f.lo.cpu().numpy().astype(np.float64)
-    assert 2.0 ** 14 <= np.abs(hi).max() < 2.0 ** 15
-    x = f.x32.cpu().numpy().astype(np.float64) * 2.0 ** e
-    assert np.abs(hi + lo - x).max() <= 2.0 ** -11 * np.abs(lo).max() + 2.0 ** -25
-    assert np.all(np.abs(lo) <= 2.0 ** -11 * np.abs(hi) + 2.0 ** -24)
+    # float16 split: x * 2^e = hi + lo to ~22 bits.  Normalised rows are bounded by 1, so the scale is fixed up front
+    # (e = 14, independent of the other rows); raw rows take it from the measured maximum: max|x| * 2^e in [2^14, 2^15)
+    def check_split(ff, e):
+        hi = ff.hi.cpu().numpy().astype(np.float64)
+        lo = ff.lo.cpu().numpy().astype(np.float64)
+        x = ff.x32.cpu().numpy().astype(np.float64) * 2.0 ** e
+        assert np.abs(hi + lo - x).max() <= 2.0 ** -11 * np.abs(lo).max() + 2.0 ** -25
+        assert np.all(np.abs(lo) <= 2.0 ** -11 * np.abs(hi) + 2.0 ** -24)
+        return np.abs(hi).max()
+    assert f.amax.cpu().numpy().view(np.float32)[0] == 1.0
+    assert check_split(f, 14) < 2.0 ** 15
     # raw (un-normalised) preparation reproduces the input exactly
     f2 = eng.prepare(X, False)
     assert torch.equal(f2.x32[:, : sh.d], X)
+    amax = f2.amax.cpu().numpy().view(np.float32)[0]
+    assert amax == np.abs(X.cpu().numpy()).max()
+    assert 2.0 ** 14 <= check_split(f2, 14 - int(np.floor(np.log2(amax)))) < 2.0 ** 15
 
 
 @pytest.mark.parametrize("engine_name", ["simt", "tcgen05"])
@@ -349,3 +353,42 @@ def test_exclusive_scan_matches_numpy(eng, n):
                       C.c_void_p(torch.cuda.current_stream().cuda_stream))
         want = np.concatenate([[0], np.cumsum(x.astype(np.int64))])
         assert np.array_equal(out.cpu().numpy(), want)
+
+
+@pytest.mark.parametrize("name,batch", [("duke", 0), ("mid", 300), ("small", 64)])
+def test_streamed_blocks_match_single_launch(eng, engine_mod, synth, name, batch):
+    """Host features copied chunk by chunk under the contraction (diagonal blocks in upper-only form + the rectangles
+    above them with mirrored statistics) == prepare() + dist(upper_only=True) on the whole matrix, bit for bit: the
+    stored half of D, the row maxima, the chunk minima, and everything downstream (CMC, mAP, AP, first hits)."""
+    sh = synth.SHAPES[name]
+    qf, gf, qp, gp, qc, gc = synth.make(sh, 1)
+    Xh = torch.cat([qf, gf]).pin_memory()
+    N, q = Xh.shape[0], sh.q
+    parts = [Xh] if batch == 0 else [Xh[i: i + batch] for i in range(0, N, batch)]
+    dev = eng.device
+    pids, cams = torch.cat([qp, gp]).to(dev), torch.cat([qc, gc]).to(dev)
+    saved = eng.symmetric
+    eng.symmetric = True
+    try:
+        f = eng.prepare(Xh.to(dev), True)
+        D, key, cmin = eng.dist(f, f, engine_mod.METRIC_SQEUCLIDEAN, want_rowmax=True, want_chunk_min=True,
+                                upper_only=True)
+        old_bounds = engine_mod.Engine.stream_bounds
+        if N < 4096:                                   # small shapes: force several (uneven) chunks anyway
+            engine_mod.Engine.stream_bounds = staticmethod(
+                lambda n: sorted({0, min(n, 256), min(n, 768), n}))
+        try:
+            D2, key2, cmin2, N2 = eng.prepare_dist_streamed(parts, True)
+            res2 = eng.evaluate_reranked_host(parts, q, pids, cams, sh.k1, sh.k2, sh.lam, 50)
+        finally:
+            engine_mod.Engine.stream_bounds = staticmethod(old_bounds)
+        assert N2 == N and torch.equal(key2, key) and torch.equal(cmin2, cmin)
+        rows = torch.arange(N, device=dev)[:, None]
+        cols = torch.arange(D.shape[1], device=dev)[None, :]
+        stored = (cols >= (rows // 256) * 256) & (cols < N)
+        assert torch.equal(D2[stored], D[stored])
+        res = eng.evaluate_reranked(Xh.to(dev), q, pids, cams, sh.k1, sh.k2, sh.lam, normalize=True, max_rank=50)
+        for u, v, what in zip(res, res2, ("cmc", "mAP", "n_valid", "ap", "first_hit")):
+            assert torch.equal(u, v), f"{name}: {what} differs between the streamed and the resident evaluation"
+    finally:
+        eng.symmetric = saved
