@@ -257,6 +257,27 @@ REID_API int reid_score_dist(const float* dist, int q, int g, int64_t ld, const 
 REID_API int reid_score_finalize(const double* ap, int q, const int32_t* cmc_hist, int max_rank,
                         const int32_t* n_valid, float* cmc, double* mAP, void* stream);
 
+/* ---- training-side distance ops: batch scale, float32 CUDA cores, fixed summation order ---- */
+/* losses.py:14-28 `euclidean_dist`.  out[i, j] = sqrt(max(|x_i|^2 + |y_j|^2 - 2 x_i.y_j, 1e-12)); the squared norms are
+ * accumulated in the same pass (no prepared operands, any d, any pitch >= d). */
+REID_API int reid_pair_dist(const float* x, int64_t ldx, int m, const float* y, int64_t ldy, int n, int d, float* out,
+                   int64_t ld_out, void* stream);
+/* losses.py:31-83 `hard_example_mining` (and the masks of losses.py:126-139).  Per anchor row i of dist[m, n]:
+ * dist_ap / p_ind = the largest entry among columns with lab_c == lab_r[i] (the anchor's own column i is left out when
+ * skip_diag), dist_an / n_ind = the smallest among the others; ties keep the lowest column.  A row without a positive
+ * (negative) gets -inf (+inf) and index -1 where the reference's view(N, -1) raises.  p_ind / n_ind may be NULL. */
+REID_API int reid_hard_mine(const float* dist, int64_t ld, int m, int n, const int64_t* lab_r, const int64_t* lab_c,
+                   int skip_diag, float* dist_ap, float* dist_an, int64_t* p_ind, int64_t* n_ind, void* stream);
+/* autograd of reid_hard_mine: G[i, j] = g_ap[i] [j == p_ind[i]] + g_an[i] [j == n_ind[i]], every element written. */
+REID_API int reid_hard_mine_grad(const float* g_ap, const float* g_an, const int64_t* p_ind, const int64_t* n_ind, int m,
+                        int n, float* G, int64_t ldg, void* stream);
+/* autograd of reid_pair_dist (sqrt, clamp, matmul and both norm terms of losses.py:22-27):
+ * gx_i = sum_j W_ij (x_i - y_j), gy_j (+)= sum_i W_ij (y_j - x_i), W = G / dist where dist > 1e-6 (clamp inactive), else 0.
+ * gx or gy may be NULL; accumulate_gy adds into gy (x and y the same tensor: pass gy = gx). */
+REID_API int reid_pair_dist_grad(const float* x, int64_t ldx, int m, const float* y, int64_t ldy, int n, int d,
+                        const float* dist, int64_t ldd, const float* G, int64_t ldg, float* gx, int64_t ldgx,
+                        float* gy, int64_t ldgy, int accumulate_gy, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

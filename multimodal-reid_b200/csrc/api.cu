@@ -417,4 +417,38 @@ int reid_score_finalize(const double* ap, int q, const int32_t* cmc_hist, int ma
   return launch_score_finalize(ap, q, cmc_hist, max_rank, n_valid, cmc, mAP, S(stream));
 }
 
+// ---- training-side distance ops
+int reid_pair_dist(const float* x, int64_t ldx, int m, const float* y, int64_t ldy, int n, int d, float* out,
+                   int64_t ld_out, void* stream) {
+  ENTER();
+  REID_REQUIRE(m >= 0 && n >= 0 && d >= 1 && ldx >= d && ldy >= d && ld_out >= n, "pair_dist: bad shape m=%d n=%d d=%d",
+               m, n, d);
+  return launch_pair_dist(x, ldx, m, y, ldy, n, d, out, ld_out, S(stream));
+}
+
+int reid_hard_mine(const float* dist, int64_t ld, int m, int n, const int64_t* lab_r, const int64_t* lab_c,
+                   int skip_diag, float* dist_ap, float* dist_an, int64_t* p_ind, int64_t* n_ind, void* stream) {
+  ENTER();
+  REID_REQUIRE(m >= 0 && n >= 1 && ld >= n, "hard_mine: bad shape m=%d n=%d ld=%lld", m, n, (long long)ld);
+  return launch_hard_mine(dist, ld, m, n, lab_r, lab_c, skip_diag ? 1 : 0, dist_ap, dist_an, p_ind, n_ind, S(stream));
+}
+
+int reid_hard_mine_grad(const float* g_ap, const float* g_an, const int64_t* p_ind, const int64_t* n_ind, int m, int n,
+                        float* G, int64_t ldg, void* stream) {
+  ENTER();
+  REID_REQUIRE(m >= 0 && n >= 0 && ldg >= n && m <= 65535, "hard_mine_grad: bad shape m=%d n=%d", m, n);
+  return launch_mine_grad(g_ap, g_an, p_ind, n_ind, m, n, G, ldg, S(stream));
+}
+
+int reid_pair_dist_grad(const float* x, int64_t ldx, int m, const float* y, int64_t ldy, int n, int d,
+                        const float* dist, int64_t ldd, const float* G, int64_t ldg, float* gx, int64_t ldgx,
+                        float* gy, int64_t ldgy, int accumulate_gy, void* stream) {
+  ENTER();
+  REID_REQUIRE(m >= 0 && n >= 0 && d >= 1 && ldx >= d && ldy >= d && ldd >= n && ldg >= n,
+               "pair_dist_grad: bad shape m=%d n=%d d=%d", m, n, d);
+  REID_REQUIRE((!gx || ldgx >= d) && (!gy || ldgy >= d), "pair_dist_grad: gradient pitch below d=%d", d);
+  return launch_pair_grad(x, ldx, m, y, ldy, n, d, dist, ldd, G, ldg, gx, ldgx, gy, ldgy, accumulate_gy ? 1 : 0,
+                          S(stream));
+}
+
 }  // extern "C"

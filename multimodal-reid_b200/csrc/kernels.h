@@ -96,4 +96,15 @@ int launch_score_finalize(const double* ap, int q, const int* cmc_hist, int max_
 int launch_transpose_add(const float* src, int n, long long ld_src, float* dst, long long ld_dst, int accumulate,
                          cudaStream_t s);
 
+// train.cu
+int launch_pair_dist(const float* X, long long ldx, int m, const float* Y, long long ldy, int n, int d, float* out,
+                     long long ldo, cudaStream_t s);
+int launch_hard_mine(const float* D, long long ld, int m, int n, const int64_t* lab_r, const int64_t* lab_c,
+                     int skip_diag, float* dist_ap, float* dist_an, int64_t* p_ind, int64_t* n_ind, cudaStream_t s);
+int launch_mine_grad(const float* g_ap, const float* g_an, const int64_t* p_ind, const int64_t* n_ind, int m, int n,
+                     float* G, long long ldg, cudaStream_t s);
+int launch_pair_grad(const float* X, long long ldx, int m, const float* Y, long long ldy, int n, int d,
+                     const float* dist, long long ldd, const float* G, long long ldg, float* gx, long long ldgx,
+                     float* gy, long long ldgy, int accumulate_gy, cudaStream_t s);
+
 }  // namespace reid

@@ -1,0 +1,211 @@
+// Training-side distance ops, batch scale: m, n = 64 .. a few thousand rows, d <= 3072.
+//   pair_dist_kernel    losses.py:14-28   dist = sqrt(clamp(|x|^2 + |y|^2 - 2 x.y, 1e-12)), norms fused (no prep pass)
+//   hard_mine_kernel    losses.py:31-83   per anchor: farthest same-label column, nearest other-label column
+//   mine_grad_kernel    autograd of the two selections: the gradient w.r.t. the distance matrix (two entries per row)
+//   pair_grad_kernel    autograd of pair_dist: gx_i = sum_j W_ij (x_i - y_j), W = G / dist where the clamp is inactive
+// These matrices are KBs to a few MB: every kernel here is latency-bound, so the design goal is few launches, enough
+// CTAs to cover the SMs at B = 64 already, and fixed summation orders (no float atomics: results are run-to-run
+// deterministic, which the reference's CUDA path is not).
+#include "common.cuh"
+#include "kernels.h"
+
+namespace reid {
+
+constexpr int PT = 32;     // output tile edge
+constexpr int PK = 32;     // K slab
+
+// 256 threads, 32 x 32 outputs, 2 x 2 per thread; rows/columns past the edge are staged as zeros.
+__global__ void __launch_bounds__(256)
+pair_dist_kernel(const float* __restrict__ X, long long ldx, int m, const float* __restrict__ Y, long long ldy, int n,
+                 int d, float* __restrict__ out, long long ldo) {
+  __shared__ float Xs[PK][PT + 1];
+  __shared__ float Ys[PK][PT + 1];
+  const int tid = threadIdx.x;
+  const int tx = tid & 15, ty = tid >> 4;
+  const int m0 = blockIdx.y * PT, n0 = blockIdx.x * PT;
+  const int lr = tid >> 3, lk = (tid & 7) * 4;       // staging: row lr, 4 consecutive k
+  float acc[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
+  float xx[2] = {0.f, 0.f}, yy[2] = {0.f, 0.f};
+  for (int k0 = 0; k0 < d; k0 += PK) {
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int k = k0 + lk + e;
+      const int r = m0 + lr, c = n0 + lr;
+      Xs[lk + e][lr] = (r < m && k < d) ? X[(long long)r * ldx + k] : 0.f;
+      Ys[lk + e][lr] = (c < n && k < d) ? Y[(long long)c * ldy + k] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < PK; ++k) {
+      const float a0 = Xs[k][ty], a1 = Xs[k][ty + 16], b0 = Ys[k][tx], b1 = Ys[k][tx + 16];
+      acc[0][0] = __fmaf_rn(a0, b0, acc[0][0]);
+      acc[0][1] = __fmaf_rn(a0, b1, acc[0][1]);
+      acc[1][0] = __fmaf_rn(a1, b0, acc[1][0]);
+      acc[1][1] = __fmaf_rn(a1, b1, acc[1][1]);
+      xx[0] = __fmaf_rn(a0, a0, xx[0]);
+      xx[1] = __fmaf_rn(a1, a1, xx[1]);
+      yy[0] = __fmaf_rn(b0, b0, yy[0]);
+      yy[1] = __fmaf_rn(b1, b1, yy[1]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int r = m0 + ty + 16 * i, c = n0 + tx + 16 * j;
+      if (r < m && c < n) {
+        // (xx + yy) - 2 * matmul: the doubling is exact, so one fma rounds like the reference's subtract
+        const float v = __fmaf_rn(-2.0f, acc[i][j], __fadd_rn(xx[i], yy[j]));
+        out[(long long)r * ldo + c] = __fsqrt_rn(fmaxf(v, 1e-12f));
+      }
+    }
+}
+
+// One warp per anchor row.  Positives: label equal (the anchor's own column included, as in the reference, unless
+// skip_diag); negatives: label different.  Ties go to the lowest column (torch.max / torch.min on CPU keep the first).
+__global__ void __launch_bounds__(256)
+hard_mine_kernel(const float* __restrict__ D, long long ld, int m, int n, const int64_t* __restrict__ lab_r,
+                 const int64_t* __restrict__ lab_c, int skip_diag, float* __restrict__ dist_ap,
+                 float* __restrict__ dist_an, int64_t* __restrict__ p_ind, int64_t* __restrict__ n_ind) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= m) return;
+  const int lane = lane_id();
+  const int64_t me = lab_r[row];
+  // keys: (ordered distance << 32) | tie-break, so that one 64-bit max / min decides value and column together
+  unsigned long long best_p = 0ull, best_n = ~0ull;
+  for (int c = lane; c < n; c += 32) {
+    const float v = D[(long long)row * ld + c];
+    const unsigned long long k = (unsigned long long)f2key(v + 0.0f) << 32;
+    if (lab_c[c] == me) {
+      if (!(skip_diag && c == row)) {
+        const unsigned long long kp = k | (0xffffffffu - (unsigned)c);
+        best_p = kp > best_p ? kp : best_p;
+      }
+    } else {
+      const unsigned long long kn = k | (unsigned)c;
+      best_n = kn < best_n ? kn : best_n;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const unsigned long long p = __shfl_xor_sync(FULL, best_p, o), q = __shfl_xor_sync(FULL, best_n, o);
+    best_p = p > best_p ? p : best_p;
+    best_n = q < best_n ? q : best_n;
+  }
+  if (lane == 0) {
+    const bool hp = best_p != 0ull, hn = best_n != ~0ull;
+    dist_ap[row] = hp ? key2f((uint32_t)(best_p >> 32)) : -INFINITY;
+    dist_an[row] = hn ? key2f((uint32_t)(best_n >> 32)) : INFINITY;
+    if (p_ind) p_ind[row] = hp ? (int64_t)(0xffffffffu - (uint32_t)best_p) : -1;
+    if (n_ind) n_ind[row] = hn ? (int64_t)(uint32_t)best_n : -1;
+  }
+}
+
+// G[i, j] = g_ap[i] [j == p_i] + g_an[i] [j == n_i]; every element written once (no memset, no atomics)
+__global__ void __launch_bounds__(256)
+mine_grad_kernel(const float* __restrict__ g_ap, const float* __restrict__ g_an, const int64_t* __restrict__ p_ind,
+                 const int64_t* __restrict__ n_ind, int m, int n, float* __restrict__ G, long long ldg) {
+  const int row = blockIdx.y;
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= n) return;
+  float v = 0.f;
+  if (p_ind[row] == c) v += g_ap[row];
+  if (n_ind[row] == c) v += g_an[row];
+  G[(long long)row * ldg + c] = v;
+}
+
+// out[r, c] (+)= sum_t W(r,t) (P[r,c] - Q[t,c]),  W(r,t) = G(r,t) / dist(r,t) where dist > 1e-6 (clamp inactive), else 0.
+// (r,t) addresses G and dist through two strides, so the same kernel serves gx (r = anchor) and gy (r = column).
+// CTA = 8 rows x 128 feature columns, 128 threads; t walks in order: fixed summation order.
+constexpr int GR = 8, GT = 64;
+__global__ void __launch_bounds__(128)
+pair_grad_kernel(const float* __restrict__ P, long long ldp, int rows, const float* __restrict__ Q, long long ldq,
+                 int others, int d, const float* __restrict__ dist, const float* __restrict__ G, long long s_r,
+                 long long s_t, long long g_r, long long g_t, float* __restrict__ out, long long ld_out,
+                 int accumulate) {
+  __shared__ float Ws[GR][GT];
+  const int r0 = blockIdx.x * GR;
+  const int c = blockIdx.y * 128 + threadIdx.x;
+  float acc[GR], sw[GR];
+#pragma unroll
+  for (int i = 0; i < GR; ++i) acc[i] = 0.f, sw[i] = 0.f;
+  for (int t0 = 0; t0 < others; t0 += GT) {
+    for (int e = threadIdx.x; e < GR * GT; e += 128) {
+      const int i = e / GT, t = e % GT;
+      float w = 0.f;
+      if (r0 + i < rows && t0 + t < others) {
+        const float dv = dist[(long long)(r0 + i) * s_r + (long long)(t0 + t) * s_t];
+        const float gv = G[(long long)(r0 + i) * g_r + (long long)(t0 + t) * g_t];
+        w = dv > 1e-6f ? __fdiv_rn(gv, dv) : 0.f;
+      }
+      Ws[i][t] = w;
+    }
+    __syncthreads();
+    const int tn = min(GT, others - t0);
+    for (int t = 0; t < tn; ++t) {
+      const float qv = c < d ? Q[(long long)(t0 + t) * ldq + c] : 0.f;
+#pragma unroll
+      for (int i = 0; i < GR; ++i) {
+        const float w = Ws[i][t];
+        acc[i] = __fmaf_rn(w, qv, acc[i]);
+        sw[i] += w;
+      }
+    }
+    __syncthreads();
+  }
+  if (c < d) {
+#pragma unroll
+    for (int i = 0; i < GR; ++i) {
+      const int r = r0 + i;
+      if (r < rows) {
+        const float v = __fmaf_rn(sw[i], P[(long long)r * ldp + c], -acc[i]);
+        float* o = out + (long long)r * ld_out + c;
+        *o = accumulate ? *o + v : v;
+      }
+    }
+  }
+}
+
+int launch_pair_dist(const float* X, long long ldx, int m, const float* Y, long long ldy, int n, int d, float* out,
+                     long long ldo, cudaStream_t s) {
+  if (m == 0 || n == 0) return REID_OK;
+  dim3 grid(cdiv(n, PT), cdiv(m, PT));
+  pair_dist_kernel<<<grid, 256, 0, s>>>(X, ldx, m, Y, ldy, n, d, out, ldo);
+  return check_launch("pair_dist_kernel");
+}
+
+int launch_hard_mine(const float* D, long long ld, int m, int n, const int64_t* lab_r, const int64_t* lab_c,
+                     int skip_diag, float* dist_ap, float* dist_an, int64_t* p_ind, int64_t* n_ind, cudaStream_t s) {
+  if (m == 0) return REID_OK;
+  hard_mine_kernel<<<cdiv(m, 8), 256, 0, s>>>(D, ld, m, n, lab_r, lab_c, skip_diag, dist_ap, dist_an, p_ind, n_ind);
+  return check_launch("hard_mine_kernel");
+}
+
+int launch_mine_grad(const float* g_ap, const float* g_an, const int64_t* p_ind, const int64_t* n_ind, int m, int n,
+                     float* G, long long ldg, cudaStream_t s) {
+  if (m == 0 || n == 0) return REID_OK;
+  dim3 grid(cdiv(n, 256), m);
+  mine_grad_kernel<<<grid, 256, 0, s>>>(g_ap, g_an, p_ind, n_ind, m, n, G, ldg);
+  return check_launch("mine_grad_kernel");
+}
+
+int launch_pair_grad(const float* X, long long ldx, int m, const float* Y, long long ldy, int n, int d,
+                     const float* dist, long long ldd, const float* G, long long ldg, float* gx, long long ldgx,
+                     float* gy, long long ldgy, int accumulate_gy, cudaStream_t s) {
+  if (d == 0) return REID_OK;
+  if (gx && m > 0) {
+    dim3 grid(cdiv(m, GR), cdiv(d, 128));
+    pair_grad_kernel<<<grid, 128, 0, s>>>(X, ldx, m, Y, ldy, n, d, dist, G, ldd, 1, ldg, 1, gx, ldgx, 0);
+    int rc = check_launch("pair_grad_kernel");
+    if (rc != REID_OK) return rc;
+  }
+  if (gy && n > 0) {
+    dim3 grid(cdiv(n, GR), cdiv(d, 128));
+    pair_grad_kernel<<<grid, 128, 0, s>>>(Y, ldy, n, X, ldx, m, d, dist, G, 1, ldd, 1, ldg, gy, ldgy, accumulate_gy);
+    return check_launch("pair_grad_kernel");
+  }
+  return REID_OK;
+}
+
+}  // namespace reid

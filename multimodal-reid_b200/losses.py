@@ -1,0 +1,149 @@
+"""Drop-in for the distance / hard-mining part of the reference's ``losses.py``.
+
+``euclidean_dist`` (losses.py:14-28), ``hard_example_mining`` (:31-83) and the two triplet losses built on
+them (``WeightedRegularizedTriplet`` :86-108, ``WeightedRegularizedTripletXBM`` :111-152) keep their names,
+arguments and return values; forward and backward run as sm_100a kernels of libreid_b200.so (train.cu).
+torch is used for device buffers, autograd bookkeeping and the final N-element ranking loss, as in the
+reference.  No CPU path: CPU tensors raise."""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+from torch.nn import functional as F
+
+from . import _lib
+from .engine import _ptr, _stream
+
+
+def _dev_f32(t: torch.Tensor, what: str) -> torch.Tensor:
+    if not t.is_cuda:
+        raise _lib.ReidError(f"{what} must be a CUDA tensor: reid_b200 has no CPU path")
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t if t.stride(-1) == 1 else t.contiguous()
+
+
+def _labels(t: torch.Tensor, device) -> torch.Tensor:
+    return t.to(device=device, dtype=torch.int64).contiguous()
+
+
+class _PairDist(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, y):
+        xs, ys = _dev_f32(x, "x"), _dev_f32(y, "y")
+        m, d = xs.shape
+        n = ys.shape[0]
+        if ys.shape[1] != d:
+            raise ValueError(f"feature widths differ: {d} vs {ys.shape[1]}")
+        out = torch.empty((m, n), dtype=torch.float32, device=xs.device)
+        with torch.cuda.device(xs.device):
+            _lib.call("reid_pair_dist", _ptr(xs), xs.stride(0), m, _ptr(ys), ys.stride(0), n, d, _ptr(out), n,
+                      _stream())
+        ctx.save_for_backward(xs, ys, out)
+        ctx.same = x is y
+        ctx.dtypes = (x.dtype, y.dtype)
+        return out
+
+    @staticmethod
+    def backward(ctx, G):
+        xs, ys, dist = ctx.saved_tensors
+        G = _dev_f32(G, "grad").contiguous()
+        m, d = xs.shape
+        n = ys.shape[0]
+        need_x, need_y = ctx.needs_input_grad
+        gx = torch.empty_like(xs, memory_format=torch.contiguous_format) if need_x else None
+        gy = torch.empty_like(ys, memory_format=torch.contiguous_format) if need_y else None
+        with torch.cuda.device(xs.device):
+            _lib.call("reid_pair_dist_grad", _ptr(xs), xs.stride(0), m, _ptr(ys), ys.stride(0), n, d, _ptr(dist), n,
+                      _ptr(G), n, _ptr(gx), d, _ptr(gy), d, 0, _stream())
+        gx = gx.to(ctx.dtypes[0]) if gx is not None else None
+        gy = gy.to(ctx.dtypes[1]) if gy is not None else None
+        return gx, gy
+
+
+def euclidean_dist(x, y):
+    """losses.py:14-28 — [m, d], [n, d] -> [m, n] Euclidean distances (sqrt of the clamped squared form)."""
+    return _PairDist.apply(x, y)
+
+
+class _HardMine(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, dist_mat, lab_r, lab_c, skip_diag):
+        D = _dev_f32(dist_mat, "dist_mat")
+        m, n = D.shape
+        dev = D.device
+        ap = torch.empty(m, dtype=torch.float32, device=dev)
+        an = torch.empty(m, dtype=torch.float32, device=dev)
+        pi = torch.empty(m, dtype=torch.int64, device=dev)
+        ni = torch.empty(m, dtype=torch.int64, device=dev)
+        with torch.cuda.device(dev):
+            _lib.call("reid_hard_mine", _ptr(D), D.stride(0), m, n, _ptr(lab_r), _ptr(lab_c), int(skip_diag), _ptr(ap),
+                      _ptr(an), _ptr(pi), _ptr(ni), _stream())
+        ctx.save_for_backward(pi, ni)
+        ctx.shape = (m, n)
+        ctx.mark_non_differentiable(pi, ni)
+        return ap, an, pi, ni
+
+    @staticmethod
+    def backward(ctx, g_ap, g_an, _gp, _gn):
+        pi, ni = ctx.saved_tensors
+        m, n = ctx.shape
+        g_ap = g_ap.contiguous().float()
+        g_an = g_an.contiguous().float()
+        G = torch.empty((m, n), dtype=torch.float32, device=pi.device)
+        with torch.cuda.device(pi.device):
+            _lib.call("reid_hard_mine_grad", _ptr(g_ap), _ptr(g_an), _ptr(pi), _ptr(ni), m, n, _ptr(G), n, _stream())
+        return G, None, None, None
+
+
+def hard_example_mining(dist_mat, labels, return_inds=False):
+    """losses.py:31-83 — hardest positive (farthest same-label sample, the anchor itself included) and hardest
+    negative (nearest other-label sample) of every anchor.  Unlike the reference, identities need not have
+    the same number of samples (its ``view(N, -1)`` requires that)."""
+    assert len(dist_mat.size()) == 2
+    assert dist_mat.size(0) == dist_mat.size(1)
+    lab = _labels(labels, dist_mat.device)
+    dist_ap, dist_an, p_inds, n_inds = _HardMine.apply(dist_mat, lab, lab, False)
+    if return_inds:
+        return dist_ap, dist_an, p_inds, n_inds
+    return dist_ap, dist_an
+
+
+class WeightedRegularizedTriplet(object):
+    """losses.py:86-108 (margin ranking loss, or soft-margin when ``margin`` is None)."""
+
+    def __init__(self, margin=None):
+        if margin is not None:
+            self.ranking_loss = nn.MarginRankingLoss(margin=margin)
+        else:
+            self.ranking_loss = nn.SoftMarginLoss()
+        self.margin = margin
+
+    def _rank(self, dist_ap, dist_an):
+        y = torch.ones_like(dist_an)
+        if self.margin is not None:
+            return self.ranking_loss(dist_an, dist_ap, y)
+        return self.ranking_loss(dist_an - dist_ap, y)
+
+    def __call__(self, global_feat, labels, normalize_feature=False):
+        if normalize_feature:
+            global_feat = F.normalize(global_feat, dim=-1)
+        dist_mat = euclidean_dist(global_feat, global_feat)
+        dist_ap, dist_an = hard_example_mining(dist_mat, labels)
+        return self._rank(dist_ap, dist_an)
+
+
+class WeightedRegularizedTripletXBM(WeightedRegularizedTriplet):
+    """losses.py:111-152 with the masks the code sets up (:126-128): positives = same label in the memory
+    bank minus the anchor's own slot (the first N bank entries are the batch), negatives = different label.
+    NOTE the reference then indexes ``dist_mat[is_pos]`` with a *long* 0/1 tensor (:132, :137), which selects
+    rows 0 and 1 of the matrix instead of masking; that indexing slip is not reproduced."""
+
+    def __call__(self, global_feat, labels, global_feat_xbm, labels_xbm, normalize_feature=False):
+        if normalize_feature:
+            global_feat = F.normalize(global_feat, dim=-1)
+            global_feat_xbm = F.normalize(global_feat_xbm, dim=-1)
+        dist_mat = euclidean_dist(global_feat, global_feat_xbm)
+        dev = dist_mat.device
+        dist_ap, dist_an, _, _ = _HardMine.apply(dist_mat, _labels(labels, dev), _labels(labels_xbm, dev), True)
+        return self._rank(dist_ap, dist_an)

@@ -1,0 +1,170 @@
+"""GPU: the training-side distance ops (losses.py drop-in) through the C-ABI against golden vectors
+frozen from the unmodified reference (forward, mined pairs, loss, autograd gradients) and against the oracle.
+Tolerances (float32 path): distances 2e-5 relative off the diagonal; mined values 2e-5 relative with indices exact
+where the runner-up is farther than that away; loss 1e-5; gradients 1e-4 of the largest gradient entry."""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import losses_oracle as lo
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "losses", "*.npz")))
+IDS = [os.path.basename(p)[:-4] for p in GOLDEN]
+
+
+@pytest.fixture(scope="module")
+def L():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import losses
+    return losses
+
+
+def _offdiag(a):
+    return ~np.eye(a.shape[0], a.shape[1], dtype=bool)
+
+
+def _check_mined(dist, lab_r, lab_c, ap, an, pi, ni, skip_diag=False):
+    """exact consistency with the matrix the kernel was given (bit-exact values, first-index ties)"""
+    o = lo.hard_example_mining(dist, lab_r, lab_c, skip_diag)
+    np.testing.assert_array_equal(ap.view(np.uint32), o[0].view(np.uint32))
+    np.testing.assert_array_equal(an.view(np.uint32), o[1].view(np.uint32))
+    np.testing.assert_array_equal(pi, o[2])
+    np.testing.assert_array_equal(ni, o[3])
+
+
+@pytest.mark.parametrize("path", GOLDEN, ids=IDS)
+def test_forward_golden(L, path):
+    z = np.load(path)
+    x, y = torch.from_numpy(z["x"]).cuda(), torch.from_numpy(z["y"]).cuda()
+    dxx = L.euclidean_dist(x, x)
+    dxy = L.euclidean_dist(x, y)
+    assert dxx.dtype == torch.float32 and dxx.shape == z["dist_xx"].shape and dxx.is_cuda
+    m = _offdiag(z["dist_xx"])
+    np.testing.assert_allclose(dxx.cpu().numpy()[m], z["dist_xx"][m], rtol=2e-5)
+    np.testing.assert_allclose(dxy.cpu().numpy(), z["dist_xy"], rtol=2e-5)
+    assert (dxx.diagonal() >= 1e-6).all()             # the clamp (losses.py:27)
+    # mining on the REFERENCE's matrix: bit-exact values and indices
+    lab = torch.from_numpy(z["labels"])
+    ap, an, pi, ni = L.hard_example_mining(torch.from_numpy(z["dist_xx"]).cuda(), lab, return_inds=True)
+    assert pi.dtype == torch.int64 and ap.dtype == torch.float32
+    np.testing.assert_array_equal(ap.cpu().numpy().view(np.uint32), z["dist_ap"].view(np.uint32))
+    np.testing.assert_array_equal(an.cpu().numpy().view(np.uint32), z["dist_an"].view(np.uint32))
+    np.testing.assert_array_equal(pi.cpu().numpy(), z["p_inds"])
+    np.testing.assert_array_equal(ni.cpu().numpy(), z["n_inds"])
+    # mining on our own matrix: consistent with it, and within tolerance of the reference
+    ap2, an2 = L.hard_example_mining(dxx, lab.cuda())
+    np.testing.assert_allclose(ap2.cpu().numpy(), z["dist_ap"], rtol=2e-5)
+    np.testing.assert_allclose(an2.cpu().numpy(), z["dist_an"], rtol=2e-5)
+
+
+@pytest.mark.parametrize("path", GOLDEN, ids=IDS)
+@pytest.mark.parametrize("tag,margin,norm", [("m03", 0.3, False), ("soft", None, False), ("m03n", 0.3, True)])
+def test_triplet_golden(L, path, tag, margin, norm):
+    z = np.load(path)
+    x = torch.from_numpy(z["x"]).cuda().requires_grad_(True)
+    loss = L.WeightedRegularizedTriplet(margin)(x, torch.from_numpy(z["labels"]).cuda(), normalize_feature=norm)
+    loss.backward()
+    ref_l, ref_g = float(z[f"loss_{tag}"]), z[f"grad_{tag}"]
+    assert abs(loss.item() - ref_l) <= 1e-5 * max(1.0, abs(ref_l))
+    np.testing.assert_allclose(x.grad.cpu().numpy(), ref_g, rtol=1e-4, atol=1e-4 * max(np.abs(ref_g).max(), 1e-30))
+
+
+@pytest.mark.parametrize("path", GOLDEN, ids=IDS)
+def test_dense_gradient_golden(L, path):
+    z = np.load(path)
+    x = torch.from_numpy(z["x"]).cuda().requires_grad_(True)
+    y = torch.from_numpy(z["y"]).cuda().requires_grad_(True)
+    (L.euclidean_dist(x, y) * torch.from_numpy(z["R"]).cuda()).sum().backward()
+    for got, ref in ((x.grad, z["gx_dense"]), (y.grad, z["gy_dense"])):
+        np.testing.assert_allclose(got.cpu().numpy(), ref, rtol=1e-4, atol=1e-4 * np.abs(ref).max())
+
+
+@pytest.mark.parametrize("m,n,d", [(1, 1, 1), (33, 65, 31), (64, 64, 2048), (257, 1000, 100), (512, 512, 1280)])
+def test_shapes_vs_oracle(L, m, n, d):
+    g = torch.Generator().manual_seed(m * 131 + n)
+    x = torch.randn(m, d, generator=g)
+    y = torch.randn(n, d, generator=g)
+    lab_r = torch.randint(0, 7, (m,), generator=g)
+    lab_c = torch.randint(0, 7, (n,), generator=g)
+    xd = x.cuda().requires_grad_(True)
+    yd = y.cuda().requires_grad_(True)
+    dist = L.euclidean_dist(xd, yd)
+    want = lo.euclidean_dist(x.numpy(), y.numpy())
+    np.testing.assert_allclose(dist.detach().cpu().numpy(), want, rtol=3e-5, atol=1e-5)
+    mod = __import__("importlib").import_module("multimodal-reid_b200.losses")
+    ap, an, pi, ni = mod._HardMine.apply(dist, lab_r.cuda(), lab_c.cuda(), False)
+    _check_mined(dist.detach().cpu().numpy(), lab_r.numpy(), lab_c.numpy(), ap.detach().cpu().numpy(),
+                 an.detach().cpu().numpy(), pi.cpu().numpy(), ni.cpu().numpy())
+    R = torch.rand(m, n, generator=g) - 0.5
+    (dist * R.cuda()).sum().backward()
+    gx, gy = lo.euclidean_dist_grad(x.numpy(), y.numpy(), dist.detach().cpu().numpy(), R.numpy())
+    np.testing.assert_allclose(xd.grad.cpu().numpy(), gx, rtol=1e-4, atol=1e-4 * max(np.abs(gx).max(), 1e-30))
+    np.testing.assert_allclose(yd.grad.cpu().numpy(), gy, rtol=1e-4, atol=1e-4 * max(np.abs(gy).max(), 1e-30))
+
+
+def test_strided_and_half_inputs(L):
+    g = torch.Generator().manual_seed(5)
+    big = torch.randn(48, 200, generator=g).cuda()
+    x = big[:, :150]                                  # pitch 200 > d
+    want = lo.euclidean_dist(x.cpu().numpy(), x.cpu().numpy())
+    got = L.euclidean_dist(x, x).cpu().numpy()
+    m = _offdiag(want)
+    np.testing.assert_allclose(got[m], want[m], rtol=3e-5)
+    h = x.half()
+    got16 = L.euclidean_dist(h, h)                    # fp16 embeddings are up-cast once, result float32
+    assert got16.dtype == torch.float32
+    want16 = lo.euclidean_dist(h.float().cpu().numpy(), h.float().cpu().numpy())
+    np.testing.assert_allclose(got16.cpu().numpy()[m], want16[m], rtol=3e-5)
+
+
+def test_xbm_variant_and_edge_rows(L):
+    """losses.py:111-152 with the masks of :126-128 (own slot excluded from the positives)."""
+    g = torch.Generator().manual_seed(9)
+    N, M, d = 32, 160, 64
+    lab_b = torch.arange(8).repeat_interleave(4)
+    lab_m = torch.cat([lab_b, torch.randint(0, 12, (M - N,), generator=g)])
+    xb = torch.randn(N, d, generator=g)
+    xm = torch.cat([xb, torch.randn(M - N, d, generator=g)])
+    xv = xb.clone().cuda().requires_grad_(True)
+    loss = L.WeightedRegularizedTripletXBM(0.3)(xv, lab_b.cuda(), xm.cuda(), lab_m.cuda())
+    loss.backward()
+    dist = lo.euclidean_dist(xb.numpy(), xm.numpy())
+    ap, an, pi, ni = lo.hard_example_mining(dist, lab_b.numpy(), lab_m.numpy(), skip_diag=True)
+    t = ap.astype(np.float64) - an + 0.3
+    assert abs(loss.item() - np.maximum(t, 0).mean()) < 1e-5
+    assert (pi != np.arange(N)).all()
+    G = np.zeros_like(dist, dtype=np.float64)
+    act = (t > 0) / N
+    np.add.at(G, (np.arange(N), pi), act)
+    np.add.at(G, (np.arange(N), ni), -act)
+    gx, _ = lo.euclidean_dist_grad(xb.numpy(), xm.numpy(), dist, G)
+    np.testing.assert_allclose(xv.grad.cpu().numpy(), gx, rtol=1e-4, atol=1e-4 * np.abs(gx).max())
+    # rows without negatives / positives
+    same = torch.zeros(6, dtype=torch.int64).cuda()
+    dm = L.euclidean_dist(xb[:6].cuda(), xb[:6].cuda())
+    ap, an, pi, ni = L.hard_example_mining(dm, same, return_inds=True)
+    assert torch.isinf(an).all() and (ni == -1).all() and (pi >= 0).all()
+
+
+def test_cpu_tensors_raise(L):
+    mod = __import__("importlib").import_module("multimodal-reid_b200._lib")
+    with pytest.raises(mod.ReidError):
+        L.euclidean_dist(torch.randn(4, 8), torch.randn(4, 8))
+
+
+def test_deterministic(L):
+    g = torch.Generator().manual_seed(2)
+    x = torch.randn(128, 768, generator=g).cuda()
+    lab = torch.arange(32).repeat_interleave(4).cuda()
+    outs = []
+    for _ in range(3):
+        xv = x.clone().requires_grad_(True)
+        L.WeightedRegularizedTriplet(None)(xv, lab).backward()
+        outs.append(xv.grad.clone())
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])

@@ -1,0 +1,94 @@
+"""CPU: the training-side oracle (oracle/losses_oracle.py) against golden vectors frozen from the unmodified
+reference losses.py (oracle/make_golden_losses.py), and — in the build container — against the live reference."""
+import glob
+import importlib.util
+import os
+
+import numpy as np
+import pytest
+
+from oracle import losses_oracle as lo
+
+GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "losses", "*.npz")))
+IDS = [os.path.basename(p)[:-4] for p in GOLDEN]
+
+
+def _offdiag_close(a, b, rtol):
+    """Diagonal entries of dist(x, x) are sqrt of a cancellation residue (1e-6 .. 1e-3): noise in both."""
+    mask = ~np.eye(a.shape[0], a.shape[1], dtype=bool) if a.shape[0] == a.shape[1] else np.ones(a.shape, bool)
+    np.testing.assert_allclose(a[mask], b[mask], rtol=rtol, atol=0)
+
+
+def test_golden_files_exist():
+    assert len(GOLDEN) == 4
+
+
+@pytest.mark.parametrize("path", GOLDEN, ids=IDS)
+def test_euclidean_dist(path):
+    z = np.load(path)
+    _offdiag_close(lo.euclidean_dist(z["x"], z["x"]), z["dist_xx"], 2e-5)
+    np.testing.assert_allclose(lo.euclidean_dist(z["x"], z["y"]), z["dist_xy"], rtol=2e-5)
+
+
+@pytest.mark.parametrize("path", GOLDEN, ids=IDS)
+def test_hard_example_mining_exact_on_the_reference_matrix(path):
+    z = np.load(path)
+    ap, an, pi, ni = lo.hard_example_mining(z["dist_xx"], z["labels"])
+    np.testing.assert_array_equal(ap.view(np.uint32), z["dist_ap"].view(np.uint32))
+    np.testing.assert_array_equal(an.view(np.uint32), z["dist_an"].view(np.uint32))
+    np.testing.assert_array_equal(pi, z["p_inds"])
+    np.testing.assert_array_equal(ni, z["n_inds"])
+
+
+@pytest.mark.parametrize("path", GOLDEN, ids=IDS)
+def test_dense_gradient(path):
+    z = np.load(path)
+    gx, gy = lo.euclidean_dist_grad(z["x"], z["y"], z["dist_xy"], z["R"])
+    np.testing.assert_allclose(gx, z["gx_dense"], rtol=1e-4, atol=1e-4 * np.abs(z["gx_dense"]).max())
+    np.testing.assert_allclose(gy, z["gy_dense"], rtol=1e-4, atol=1e-4 * np.abs(z["gy_dense"]).max())
+
+
+@pytest.mark.parametrize("path", GOLDEN, ids=IDS)
+@pytest.mark.parametrize("tag,margin", [("m03", 0.3), ("soft", None)])
+def test_triplet_loss_and_gradient(path, tag, margin):
+    z = np.load(path)
+    loss, grad, _ = lo.triplet(z["x"], z["labels"], margin)
+    assert abs(loss - float(z[f"loss_{tag}"])) <= 1e-5 * max(1.0, abs(loss))
+    ref = z[f"grad_{tag}"]
+    np.testing.assert_allclose(grad, ref, rtol=1e-4, atol=1e-5 * max(np.abs(ref).max(), 1e-30))
+
+
+def test_mining_edge_cases():
+    d = np.array([[0.0, 2.0, 2.0, 1.0], [2.0, 0.0, 1.0, 1.0], [2.0, 1.0, 0.0, 3.0], [1.0, 1.0, 3.0, 0.0]], np.float32)
+    lab = np.array([5, 5, 9, 9])
+    ap, an, pi, ni = lo.hard_example_mining(d, lab)
+    assert pi.tolist() == [1, 0, 3, 2] and ni.tolist() == [3, 2, 1, 0]      # ties keep the first column
+    ap, an, pi, ni = lo.hard_example_mining(d, np.array([1, 1, 1, 1]))
+    assert np.isinf(an).all() and (ni == -1).all()
+    ap, an, pi, ni = lo.hard_example_mining(d, np.array([1, 2, 3, 4]), skip_diag=True)
+    assert np.isneginf(ap).all() and (pi == -1).all()
+
+
+@pytest.mark.skipif(not os.path.isfile("/root/reference/losses.py"), reason="reference tree not mounted")
+def test_oracle_vs_live_reference():
+    import torch
+    spec = importlib.util.spec_from_file_location("_ref_losses", "/root/reference/losses.py")
+    L = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(L)
+    g = torch.Generator().manual_seed(11)
+    lab = torch.arange(10).repeat_interleave(4)[torch.randperm(40, generator=g)]
+    x = torch.randn(10, 96, generator=g)[lab] + 0.7 * torch.randn(40, 96, generator=g)
+    d = L.euclidean_dist(x, x)
+    _offdiag_close(lo.euclidean_dist(x.numpy(), x.numpy()), d.numpy(), 2e-5)
+    ap, an, pi, ni = L.hard_example_mining(d, lab, return_inds=True)
+    o = lo.hard_example_mining(d.numpy(), lab.numpy())
+    np.testing.assert_array_equal(o[0], ap.numpy())
+    np.testing.assert_array_equal(o[1], an.numpy())
+    np.testing.assert_array_equal(o[2], pi.numpy())
+    np.testing.assert_array_equal(o[3], ni.numpy())
+    xv = x.clone().requires_grad_(True)
+    loss = L.WeightedRegularizedTriplet(0.3)(xv, lab)
+    loss.backward()
+    l2, g2, _ = lo.triplet(x.numpy(), lab.numpy(), 0.3)
+    assert abs(l2 - loss.item()) < 1e-5
+    np.testing.assert_allclose(g2, xv.grad.numpy(), rtol=1e-4, atol=1e-5 * xv.grad.abs().max().item())
