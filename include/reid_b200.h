@@ -277,6 +277,14 @@ REID_API int reid_hard_mine_grad(const float* g_ap, const float* g_an, const int
 REID_API int reid_pair_dist_grad(const float* x, int64_t ldx, int m, const float* y, int64_t ldy, int n, int d,
                         const float* dist, int64_t ldd, const float* G, int64_t ldg, float* gx, int64_t ldgx,
                         float* gy, int64_t ldgy, int accumulate_gy, void* stream);
+/* reid_hard_mine_grad + reid_pair_dist_grad taken together for losses that only use the mined pairs (losses.py:96-108,
+ * :141-151): gx_i = wp_i (x_i - y_p) + wn_i (x_i - y_n) with wp = g_ap / dist_ap, wn = g_an / dist_an (0 where the clamp
+ * was active or the index is -1); gy_j (+)= the same terms seen from the selected columns, anchors in ascending order.
+ * O((m + n) d) instead of O(m n d); no float atomics. */
+REID_API int reid_triplet_grad(const float* x, int64_t ldx, int m, const float* y, int64_t ldy, int n, int d,
+                      const float* dist_ap, const float* dist_an, const int64_t* p_ind, const int64_t* n_ind,
+                      const float* g_ap, const float* g_an, float* gx, int64_t ldgx, float* gy, int64_t ldgy,
+                      int accumulate_gy, void* stream);
 
 #ifdef __cplusplus
 }

@@ -451,4 +451,16 @@ int reid_pair_dist_grad(const float* x, int64_t ldx, int m, const float* y, int6
                           S(stream));
 }
 
+int reid_triplet_grad(const float* x, int64_t ldx, int m, const float* y, int64_t ldy, int n, int d,
+                      const float* dist_ap, const float* dist_an, const int64_t* p_ind, const int64_t* n_ind,
+                      const float* g_ap, const float* g_an, float* gx, int64_t ldgx, float* gy, int64_t ldgy,
+                      int accumulate_gy, void* stream) {
+  ENTER();
+  REID_REQUIRE(m >= 0 && n >= 0 && d >= 1 && ldx >= d && ldy >= d && m <= 0x7fffffff / 2,
+               "triplet_grad: bad shape m=%d n=%d d=%d", m, n, d);
+  REID_REQUIRE((!gx || ldgx >= d) && (!gy || ldgy >= d), "triplet_grad: gradient pitch below d=%d", d);
+  return launch_triplet_grad(x, ldx, m, y, ldy, n, d, dist_ap, dist_an, p_ind, n_ind, g_ap, g_an, gx, ldgx, gy, ldgy,
+                             accumulate_gy ? 1 : 0, S(stream));
+}
+
 }  // extern "C"

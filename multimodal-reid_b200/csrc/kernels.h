@@ -107,4 +107,9 @@ int launch_pair_grad(const float* X, long long ldx, int m, const float* Y, long 
                      const float* dist, long long ldd, const float* G, long long ldg, float* gx, long long ldgx,
                      float* gy, long long ldgy, int accumulate_gy, cudaStream_t s);
 
+int launch_triplet_grad(const float* X, long long ldx, int m, const float* Y, long long ldy, int n, int d,
+                        const float* dist_ap, const float* dist_an, const int64_t* p_ind, const int64_t* n_ind,
+                        const float* g_ap, const float* g_an, float* gx, long long ldgx, float* gy, long long ldgy,
+                        int accumulate_gy, cudaStream_t s);
+
 }  // namespace reid

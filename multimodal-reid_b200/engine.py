@@ -129,6 +129,35 @@ class Comm:
     def nmax(self, n: int) -> int:
         return (n + self.world - 1) // self.world
 
+    def block_bounds(self, n: int, rank: int | None = None) -> tuple[int, int]:
+        """Contiguous block [lo, hi) of n rows that rank uploads in upload_sharded (ceil(n / world) rows each)."""
+        r = self.rank if rank is None else rank
+        nm = self.nmax(n)
+        return min(n, r * nm), min(n, (r + 1) * nm)
+
+    def upload_sharded(self, parts, device) -> torch.Tensor:
+        """Host feature batches (the list R1_mAP_eval.update() collected, evaluate.py:104-106) -> the full [N, d]
+        matrix on every rank, with each rank copying only ITS contiguous 1/world block over PCIe and the blocks
+        all-gathered over NVLink: host->device bytes per rank fall by the factor world (at 8 ranks the replicated
+        upload of MSMT17's 192 MB shared one host's PCIe/DRAM bandwidth eight ways)."""
+        n = sum(int(f.shape[0]) for f in parts)
+        d = int(parts[0].shape[1])
+        nm = self.nmax(n)
+        lo, hi = self.block_bounds(n)
+        mine = torch.empty((nm, d), dtype=torch.float32, device=device)
+        off = 0
+        for f in parts:
+            rows = int(f.shape[0])
+            a, b = max(lo, off), min(hi, off + rows)
+            if a < b:
+                mine[a - lo: b - lo].copy_(f[a - off: b - off], non_blocking=True)
+            off += rows
+        if hi - lo < nm:
+            mine[hi - lo:].zero_()
+        if self.world == 1:
+            return mine[:n]
+        return self._all_gather(mine).view(self.world * nm, d)[:n]
+
     def pad_rows(self, local: torch.Tensor, n: int) -> torch.Tensor:
         """Zero-pads this rank's rows to ceil(n / world) so that every rank contributes the same shape."""
         nm = self.nmax(n)
@@ -189,6 +218,7 @@ class Engine:
         self.upper_only = True      # ... and, when nobody needs the full matrix, without storing the mirrored half
         self.upper_only_min_rows = 0
         self.stream_h2d = True              # evaluator: copy host features chunk by chunk under the contraction
+        self.shard_h2d = True               # evaluator on several ranks: each uploads 1/world of the host rows, all-gather over NVLink
         self._copy_stream = None
         self.scatter_select = True          # upper-only selection in scatter form (reid_topk_rows_scatter)
         self.qe_nosync_bytes = 4 << 30       # budget for sizing the query-expansion pools without a host read

@@ -167,9 +167,16 @@ class R1_mAP_eval():
                     and len(self.feats) > 0
                     and all(isinstance(f, torch.Tensor) and not f.is_cuda and f.dtype == torch.float32 and f.dim() == 2
                             and f.shape[1] == self.feats[0].shape[1] for f in self.feats))
+        host_f32 = (len(self.feats) > 0
+                    and all(isinstance(f, torch.Tensor) and not f.is_cuda and f.dtype == torch.float32 and f.dim() == 2
+                            and f.shape[1] == self.feats[0].shape[1] for f in self.feats))
         if streamed:
             feats = None
             N = sum(int(f.shape[0]) for f in self.feats)
+        elif host_f32 and eng.comm.world > 1 and eng.shard_h2d:
+            # several ranks, features in host memory: every rank uploads 1/world of the rows, NCCL all-gather does the rest
+            feats = eng.comm.upload_sharded(self.feats, dev)
+            N = feats.shape[0]
         else:
             feats = torch.cat([_to_device_f32(f, dev) for f in self.feats], dim=0)
             N = feats.shape[0]

@@ -40,7 +40,6 @@ class _PairDist(torch.autograd.Function):
             _lib.call("reid_pair_dist", _ptr(xs), xs.stride(0), m, _ptr(ys), ys.stride(0), n, d, _ptr(out), n,
                       _stream())
         ctx.save_for_backward(xs, ys, out)
-        ctx.same = x is y
         ctx.dtypes = (x.dtype, y.dtype)
         return out
 
@@ -109,6 +108,49 @@ def hard_example_mining(dist_mat, labels, return_inds=False):
     return dist_ap, dist_an
 
 
+class _MinedPairs(torch.autograd.Function):
+    """euclidean_dist + hard mining as ONE autograd node for the losses that only use the mined pairs
+    (losses.py:96-98, :121-139): forward = reid_pair_dist + reid_hard_mine, backward = reid_triplet_grad
+    (O((m + n) d), no m x n gradient matrix)."""
+
+    @staticmethod
+    def forward(ctx, x, y, lab_r, lab_c, skip_diag):
+        xs, ys = _dev_f32(x, "x"), _dev_f32(y, "y")
+        m, d = xs.shape
+        n = ys.shape[0]
+        dev = xs.device
+        dist = torch.empty((m, n), dtype=torch.float32, device=dev)
+        ap = torch.empty(m, dtype=torch.float32, device=dev)
+        an = torch.empty(m, dtype=torch.float32, device=dev)
+        pi = torch.empty(m, dtype=torch.int64, device=dev)
+        ni = torch.empty(m, dtype=torch.int64, device=dev)
+        with torch.cuda.device(dev):
+            s = _stream()
+            _lib.call("reid_pair_dist", _ptr(xs), xs.stride(0), m, _ptr(ys), ys.stride(0), n, d, _ptr(dist), n, s)
+            _lib.call("reid_hard_mine", _ptr(dist), n, m, n, _ptr(lab_r), _ptr(lab_c), int(skip_diag), _ptr(ap),
+                      _ptr(an), _ptr(pi), _ptr(ni), s)
+        ctx.save_for_backward(xs, ys, ap, an, pi, ni)
+        ctx.dtypes = (x.dtype, y.dtype)
+        return ap, an
+
+    @staticmethod
+    def backward(ctx, g_ap, g_an):
+        xs, ys, ap, an, pi, ni = ctx.saved_tensors
+        m, d = xs.shape
+        n = ys.shape[0]
+        need_x, need_y = ctx.needs_input_grad[:2]
+        g_ap = g_ap.contiguous().float()
+        g_an = g_an.contiguous().float()
+        gx = torch.empty((m, d), dtype=torch.float32, device=xs.device) if need_x else None
+        gy = torch.empty((n, d), dtype=torch.float32, device=xs.device) if need_y else None
+        with torch.cuda.device(xs.device):
+            _lib.call("reid_triplet_grad", _ptr(xs), xs.stride(0), m, _ptr(ys), ys.stride(0), n, d, _ptr(ap), _ptr(an),
+                      _ptr(pi), _ptr(ni), _ptr(g_ap), _ptr(g_an), _ptr(gx), d, _ptr(gy), d, 0, _stream())
+        gx = gx.to(ctx.dtypes[0]) if gx is not None else None
+        gy = gy.to(ctx.dtypes[1]) if gy is not None else None
+        return gx, gy, None, None, None
+
+
 class WeightedRegularizedTriplet(object):
     """losses.py:86-108 (margin ranking loss, or soft-margin when ``margin`` is None)."""
 
@@ -128,8 +170,8 @@ class WeightedRegularizedTriplet(object):
     def __call__(self, global_feat, labels, normalize_feature=False):
         if normalize_feature:
             global_feat = F.normalize(global_feat, dim=-1)
-        dist_mat = euclidean_dist(global_feat, global_feat)
-        dist_ap, dist_an = hard_example_mining(dist_mat, labels)
+        lab = _labels(labels, global_feat.device)
+        dist_ap, dist_an = _MinedPairs.apply(global_feat, global_feat, lab, lab, False)
         return self._rank(dist_ap, dist_an)
 
 
@@ -143,7 +185,7 @@ class WeightedRegularizedTripletXBM(WeightedRegularizedTriplet):
         if normalize_feature:
             global_feat = F.normalize(global_feat, dim=-1)
             global_feat_xbm = F.normalize(global_feat_xbm, dim=-1)
-        dist_mat = euclidean_dist(global_feat, global_feat_xbm)
-        dev = dist_mat.device
-        dist_ap, dist_an, _, _ = _HardMine.apply(dist_mat, _labels(labels, dev), _labels(labels_xbm, dev), True)
+        dev = global_feat.device
+        dist_ap, dist_an = _MinedPairs.apply(global_feat, global_feat_xbm, _labels(labels, dev),
+                                             _labels(labels_xbm, dev), True)
         return self._rank(dist_ap, dist_an)

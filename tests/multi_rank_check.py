@@ -48,6 +48,25 @@ def main():
             assert torch.equal(a, b), f"{name}: {what} differs on rank {rank}"
         if rank == 0:
             print(f"{name} k1={k1} k2={k2}: {world}-rank result == 1-rank result, mAP {float(r2[1]):.6f}", flush=True)
+    # the drop-in evaluator on host batches: sharded upload + all-gather == replicated upload, bit for bit
+    import contextlib
+    import io
+    ev = importlib.import_module("multimodal-reid_b200.evaluate")
+    sh = synth.SHAPES["mid"]
+    qf, gf, qp, gp, qc, gc = synth.make(sh, 5)
+    feats, pids, cams = torch.cat([qf, gf]), torch.cat([qp, gp]), torch.cat([qc, gc])
+    res = []
+    for shard in (True, False):
+        engine.default_engine().shard_h2d = shard
+        e = ev.R1_mAP_eval(sh.q, feat_norm=True, reranking=True, rerank_params=(20, 6, 0.3))
+        e.reset()
+        for a in range(0, feats.shape[0], 997):          # ragged batches, like a data loader's last batch
+            e.update((feats[a:a + 997], pids[a:a + 997], cams[a:a + 997]))
+        with contextlib.redirect_stdout(io.StringIO()):
+            res.append(e.compute())
+    assert (res[0][0] == res[1][0]).all() and res[0][1] == res[1][1], "sharded upload changed the result"
+    if rank == 0:
+        print(f"evaluator on host batches: sharded upload == replicated upload, mAP {res[0][1]:.6f}", flush=True)
     dist.barrier()
     dist.destroy_process_group()
 

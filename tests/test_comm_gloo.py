@@ -53,6 +53,14 @@ def _worker(rank, world, port, n_rows, ret):
             assert np.array_equal(gn.numpy(), np.arange(n) % 5)
             assert np.array_equal(gi.numpy(), np.arange(n)[:, None] * 100 + np.arange(cw))
             assert np.array_equal(gv.numpy(), (np.arange(n)[:, None] + np.arange(cw) / 8).astype(np.float16))
+            # sharded upload: every rank copies its contiguous block of the (ragged) host batches, all-gather restores all rows
+            d = 5
+            host = torch.arange(n * d, dtype=torch.float32).reshape(n, d)
+            cuts = sorted({0, n} | {min(n, c) for c in (3, 4, 11)})
+            parts = [host[a:b] for a, b in zip(cuts[:-1], cuts[1:])]
+            lo, hi = cm.block_bounds(n)
+            assert (lo, hi) == (min(n, rank * cm.nmax(n)), min(n, (rank + 1) * cm.nmax(n)))
+            assert torch.equal(cm.upload_sharded(parts, torch.device("cpu")), host)
             # pool layout: every rank derives every rank's pool size and row offsets from the global bounds
             rng = np.random.default_rng(n)
             ub = np.zeros(cm.nmax(n) * world, np.int32)

@@ -168,3 +168,27 @@ def test_deterministic(L):
         L.WeightedRegularizedTriplet(None)(xv, lab).backward()
         outs.append(xv.grad.clone())
     assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+
+
+def test_fused_node_equals_composition(L):
+    """WeightedRegularizedTriplet (one fused autograd node, sparse backward) == euclidean_dist -> hard_example_mining
+    (two nodes, dense backward); one column chosen as hardest negative by > 512 anchors exercises the hit-list flush."""
+    g = torch.Generator().manual_seed(21)
+    m, d = 1400, 96
+    x = torch.randn(m, d, generator=g)
+    x[7] = 0.0                                        # close to everything: the nearest negative of most anchors
+    lab = torch.arange(m) % 350
+    lab[7] = 10_000
+    xd = x.cuda()
+    labd = lab.cuda()
+    a = xd.clone().requires_grad_(True)
+    loss_a = L.WeightedRegularizedTriplet(None)(a, labd)
+    loss_a.backward()
+    b = xd.clone().requires_grad_(True)
+    ap, an, pi, ni = L.hard_example_mining(L.euclidean_dist(b, b), labd, return_inds=True)
+    assert (ni == 7).sum().item() > 512
+    loss_b = torch.nn.functional.soft_margin_loss(an - ap, torch.ones_like(an))
+    loss_b.backward()
+    assert abs(loss_a.item() - loss_b.item()) < 1e-6
+    np.testing.assert_allclose(a.grad.cpu().numpy(), b.grad.cpu().numpy(), rtol=1e-4,
+                               atol=1e-5 * b.grad.abs().max().item())
