@@ -294,10 +294,15 @@ def main():
         for _ in range(2):
             step_e2e()
         e2e_ms, _, (cmc_e, map_e), _ = timed(step_e2e, args.steps)
-        h2d = feats_h.numel() * 4 + pids_h.numel() * 8 + cams_h.numel() * 8
+        # several ranks: each uploads its 1/world block of the features (Comm.upload_sharded) and all the ids
+        ids_b = pids_h.numel() * 8 + cams_h.numel() * 8
+        lo_r, hi_r = cm.block_bounds(N)
+        h2d_rank = (hi_r - lo_r) * d * 4 + ids_b if world > 1 else feats_h.numel() * 4 + ids_b
+        h2d = feats_h.numel() * 4 + world * ids_b             # whole job
         d2h = 50 * 4 + 8 + 4 + 8          # cmc, mAP, n_valid, longest-union hint (async, pinned)
         e2e = {"value": q * g * args.steps / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms / args.steps,
-               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "mAP": float(map_e),
+               "h2d_bytes_per_step": h2d, "h2d_bytes_per_step_this_rank": h2d_rank, "d2h_bytes_per_step": d2h,
+               "mAP": float(map_e),
                "api": "evaluate.R1_mAP_eval(reranking=True).update(host tensors).compute()"}
 
     clocks = sampler.stop() if rank == 0 else None
