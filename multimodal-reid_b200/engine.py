@@ -457,6 +457,65 @@ class Engine:
                       _stream())
         return (nbr, val) if want_values else nbr
 
+    # ------------------------------------------------------------------ SURVEY §8 a13, first slice: streamed retrieval
+    @staticmethod
+    def column_blocks(g: int, cols_per_pass: int, K: int) -> list[tuple[int, int]]:
+        """[c0, c1) gallery blocks of at most cols_per_pass columns (a tail shorter than K joins its predecessor:
+        the selection kernels need at least K columns per block)."""
+        starts = list(range(0, g, max(cols_per_pass, K)))
+        if len(starts) > 1 and g - starts[-1] < K:
+            starts.pop()
+        return [(c0, starts[i + 1] if i + 1 < len(starts) else g) for i, c0 in enumerate(starts)]
+
+    def retrieve_topk(self, Q: Features, G: Features, K: int, metric: int = METRIC_SQEUCLIDEAN,
+                      rows_per_pass: int = 16384, cols_per_pass: int = 65536):
+        """Exact K nearest gallery rows of every query row, ascending in stable (distance, column) order, WITHOUT the
+        q x g matrix ever existing (100k x 1M x 4 B = 400 GB): the contraction writes one [rows_per_pass, cols_per_pass]
+        panel at a time together with its 32-column chunk minima, the hinted selection reads ~K chunks per row of it,
+        and the per-block winners [rows, blocks * K] are selected once more.  Candidate position order equals global
+        column order among equal distances, so the result is bit for bit what selection over the full matrix gives.
+        Returns (idx int32 [q, K], dist float32 [q, K]); raw distances (the selection's divisor is 1)."""
+        q, g = Q.n, G.n
+        if not 1 <= K <= min(g, 256):
+            raise ValueError(f"K={K} outside [1, min(g, 256)]")
+        blocks = self.column_blocks(g, cols_per_pass, K)
+        nb = len(blocks)
+        unit = torch.full((min(q, rows_per_pass),), 0x3F800000, dtype=torch.int32, device=self.device)   # key of 1.0f
+        out_i = self._empty((q, K), torch.int32)
+        out_v = self._empty((q, K), torch.float32)
+        sym = self.symmetric
+        self.symmetric = False               # panels are rectangles of two different row sets
+        try:
+            for r0 in range(0, q, rows_per_pass):
+                r1 = min(q, r0 + rows_per_pass)
+                m = r1 - r0
+                A = Q.rows(slice(r0, r1))
+                if nb == 1:
+                    cv, ci = out_v[r0:r1], out_i[r0:r1]
+                else:
+                    cv = self._empty((m, self.pitch(nb * K)), torch.float32)
+                    ci = self._empty((m, nb * K), torch.int32)
+                for b, (c0, c1) in enumerate(blocks):
+                    with self.span("dist"):
+                        D, _, cmin = self.dist(A, G.rows(slice(c0, c1)), metric, want_rowmax=False, want_chunk_min=True)
+                    with self.span("select"):
+                        idx, val = self.topk_rows(D, c1 - c0, unit[:m], K, want_values=True, chunk_min=cmin)
+                        if nb == 1:
+                            ci.copy_(idx)
+                            cv.copy_(val)
+                        else:
+                            ci[:, b * K:(b + 1) * K] = idx + c0
+                            cv[:, b * K:(b + 1) * K] = val
+                    del D, cmin
+                if nb > 1:
+                    with self.span("merge"):
+                        pos, val = self.topk_rows(cv, nb * K, unit[:m], K, want_values=True)
+                        out_i[r0:r1] = torch.gather(ci, 1, pos.long())
+                        out_v[r0:r1] = val
+        finally:
+            self.symmetric = sym
+        return out_i, out_v
+
     # ------------------------------------------------------------------ K6
     def krecip_sets(self, nbr: torch.Tensor, k1: int):
         N, K = nbr.shape

@@ -1,0 +1,37 @@
+"""Streamed top-k retrieval (first slice; BASELINE.json config 5: 100k query x 1M gallery x 512-d).
+
+No function of the reference corresponds to this: its ``euclidean_distance`` + ``np.argsort`` (evaluate.py:7-13, :40)
+would need the 400 GB q x g matrix.  The semantics are those two calls restricted to the first ``topk`` columns of every
+row: squared L2 (or the arccos metric of evaluate.py:16-26), ascending, ties by gallery index.  With several ranks the
+queries are sharded cyclically and the lists all-gathered over NVLink.  No CPU path."""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import engine as _engine
+from .reranking import _to_device_f32
+
+
+def topk_retrieval_device(qf, gf, topk: int = 100, metric: int = _engine.METRIC_SQEUCLIDEAN, feat_norm: bool = False,
+                          eng: _engine.Engine | None = None, rows_per_pass: int = 16384, cols_per_pass: int = 65536):
+    """Returns (indices int32 [q, topk], distances float32 [q, topk]) on the device, identical on every rank."""
+    eng = eng or _engine.default_engine()
+    cm = eng.comm
+    q = int(qf.shape[0])
+    # one prepare call: queries and gallery share the power-of-two operand scale, like one call of the evaluator
+    allf = eng.prepare(torch.cat([_to_device_f32(qf, eng.device), _to_device_f32(gf, eng.device)]), feat_norm)
+    Q, G = allf.rows(slice(cm.rank, q, cm.world)), allf.rows(slice(q, allf.n))
+    idx, val = eng.retrieve_topk(Q, G, topk, metric, rows_per_pass, cols_per_pass)
+    if cm.world > 1:
+        with eng.span("x_topk"):
+            idx = cm.gather_rows(idx, q)
+            val = cm.gather_rows(val, q)
+    return idx, val
+
+
+def topk_retrieval(qf, gf, topk: int = 100, metric: str = "euclidean", feat_norm: bool = False):
+    """numpy front end: (indices int32 [q, topk], distances float32 [q, topk])."""
+    m = {"euclidean": _engine.METRIC_SQEUCLIDEAN, "cosine": _engine.METRIC_ARCCOS}[metric]
+    idx, val = topk_retrieval_device(qf, gf, topk, m, feat_norm)
+    return idx.cpu().numpy(), val.cpu().numpy()

@@ -1,0 +1,86 @@
+"""GPU: streamed top-k retrieval (first slice): never holds the q x g matrix, yet returns bit for bit what
+selection over the full matrix returns, and matches the oracle's distance + stable argsort modulo ties < 1e-6."""
+import importlib
+
+import numpy as np
+import pytest
+import torch
+
+from parity import assert_ranking_equal_mod_ties
+
+pytestmark = pytest.mark.gpu
+
+
+def _make(q, g, d, seed, dup=0):
+    gen = torch.Generator().manual_seed(seed)
+    cent = torch.randn(40, d, generator=gen)
+    qf = cent[torch.randint(0, 40, (q,), generator=gen)] + 1.5 * torch.randn(q, d, generator=gen)
+    gf = cent[torch.randint(0, 40, (g,), generator=gen)] + 1.5 * torch.randn(g, d, generator=gen)
+    if dup:                                  # exact duplicates in different column blocks: ties broken by column
+        gf[-dup:] = gf[:dup]
+    return qf, gf
+
+
+@pytest.mark.parametrize("q,g,d,K,rows,cols,norm", [
+    (300, 5000, 128, 100, 128, 1024, True),       # 5 blocks, last one short
+    (257, 4100, 64, 100, 4096, 4096, False),      # tail of 4 columns joins its predecessor
+    (64, 700, 512, 21, 50, 65536, True),          # single block
+    (100, 3000, 96, 256, 33, 300, False),         # K = 256, ragged row passes
+])
+def test_streamed_equals_full_matrix(eng, oracle, q, g, d, K, rows, cols, norm):
+    qf, gf = _make(q, g, d, q + g, dup=17)
+    allf = eng.prepare(torch.cat([qf, gf]).to(eng.device), norm)
+    Q, G = allf.rows(slice(0, q)), allf.rows(slice(q, q + g))
+    idx, val = eng.retrieve_topk(Q, G, K, rows_per_pass=rows, cols_per_pass=cols)
+    assert idx.shape == (q, K) and idx.dtype == torch.int32 and val.dtype == torch.float32
+    # the same selection over the materialised matrix
+    sym = eng.symmetric
+    eng.symmetric = False
+    try:
+        D, _ = eng.dist(Q, G)
+    finally:
+        eng.symmetric = sym
+    unit = torch.full((q,), 0x3F800000, dtype=torch.int32, device=eng.device)
+    idx_full, val_full = eng.topk_rows(D, g, unit, K, want_values=True)
+    assert torch.equal(idx, idx_full)
+    assert torch.equal(val.view(torch.int32), val_full.view(torch.int32))
+    # values are the matrix entries, ascending, ties by column
+    Dn = D[:, :g].cpu().numpy()
+    v = val.cpu().numpy()
+    i = idx.cpu().numpy().astype(np.int64)
+    np.testing.assert_array_equal(v, np.take_along_axis(Dn, i, 1) + 0.0)
+    assert (np.diff(v, axis=1) >= 0).all()
+    tie = np.diff(v, axis=1) == 0
+    assert (np.diff(i, axis=1)[tie] > 0).all()
+    # against the oracle (float32 BLAS distances + stable argsort): equal modulo ties within 1e-6
+    f = torch.cat([qf, gf])
+    if norm:
+        f = torch.nn.functional.normalize(f, dim=1, p=2)
+    want = oracle.sq_euclidean(f[:q].numpy(), f[q:].numpy())
+    order = np.argsort(want, axis=1, kind="stable")[:, :K]
+    scale = max(1.0, float(np.abs(want).max()))
+    # ties: 1e-6 on normalised features (north_star); raw features carry float32 GEMM noise of ~1e-6 of the largest distance
+    assert_ranking_equal_mod_ties(i, order, want / scale, tol=1e-6 if norm else 4e-6, what="streamed top-k vs oracle")
+    np.testing.assert_allclose(v, np.take_along_axis(want, order, 1), rtol=1e-4, atol=1e-5 * scale)
+
+
+def test_column_blocks(engine_mod):
+    cb = engine_mod.Engine.column_blocks
+    assert cb(10, 4, 2) == [(0, 4), (4, 8), (8, 10)]
+    assert cb(9, 4, 2) == [(0, 4), (4, 9)]                 # a 1-column tail joins its predecessor
+    assert cb(3, 100, 3) == [(0, 3)]
+    assert cb(1000, 10, 100) == [(i, min(1000, i + 100)) for i in range(0, 1000, 100)]
+
+
+def test_front_end_and_cosine(oracle):
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    r = importlib.import_module("multimodal-reid_b200.retrieval")
+    qf, gf = _make(50, 900, 80, 3)
+    idx, val = r.topk_retrieval(qf, gf, topk=10, metric="cosine")
+    assert idx.shape == (50, 10) and idx.dtype == np.int32 and val.dtype == np.float32
+    want = oracle.arccos_distance(qf.numpy(), gf.numpy())
+    order = np.argsort(want, axis=1, kind="stable")[:, :10]
+    assert_ranking_equal_mod_ties(idx.astype(np.int64), order, want, what="cosine top-k")
+    with pytest.raises(ValueError):
+        r.topk_retrieval(qf, gf, topk=1000)
