@@ -286,6 +286,32 @@ REID_API int reid_triplet_grad(const float* x, int64_t ldx, int m, const float* 
                       const float* g_ap, const float* g_an, float* gx, int64_t ldgx, float* gy, int64_t ldgy,
                       int accumulate_gy, void* stream);
 
+/* ---- CMC / mAP when the q x g matrix is never materialised (evaluate.py:40-88 semantics) ----
+ * The caller produces the matrix panel by panel (reid_dist on row chunks x column blocks), twice.
+ * Setup: reid_pid_index over the gallery ids; reid_stream_group_lookup -> for every query the slice [glo, glo+glen) of
+ * pid_list holding the gallery columns of its identity; goff = exclusive prefix sum of glen (caller).
+ * Sweep 1: reid_stream_group_gather on every panel fills gd[goff[i] + e] = D[i, pid_list[glo[i] + e]];
+ *          reid_stream_group_sort: per query the matches' (distance, column) keys ascending in mkeys[goff .. goff+nmatch),
+ *          the junk keys (same camera, evaluate.py:55) behind them; identities with more than 1024 gallery columns are
+ *          reported through *overflow (largest group seen; 0 = none) and their queries skipped.
+ * Sweep 2: reid_stream_count_panel on every panel adds to bins[goff[i] + b] the number of entries of the panel row with
+ *          exactly b match keys below them (entries beyond the farthest match are skipped with one compare);
+ *          bins zeroed by the caller.  rows/glo/glen/goff/nmatch pointers are those of the panel's first row.
+ * Finally reid_stream_score: kept rank of every match = prefix sum of its bins minus the junk in front of it -> AP
+ *          (float64, -1 = skipped), first-hit rank, CMC histogram and n_valid exactly like reid_score_dist. */
+REID_API int reid_stream_group_lookup(const int64_t* q_pid, int nq, const uint64_t* pid_keys, const int64_t* pid_start,
+                             int pid_T, int32_t* glo, int32_t* glen, void* stream);
+REID_API int reid_stream_group_gather(const float* panel, int64_t ld, int rows, int c0, int c1, const int32_t* glo,
+                             const int32_t* glen, const int64_t* goff, const int32_t* pid_list, float* gd, void* stream);
+REID_API int reid_stream_group_sort(int nq, const int32_t* glo, const int32_t* glen, const int64_t* goff,
+                           const int32_t* pid_list, const float* gd, const int64_t* q_cam, const int64_t* g_cam,
+                           uint64_t* mkeys, int32_t* nmatch, int32_t* overflow, void* stream);
+REID_API int reid_stream_count_panel(const float* panel, int64_t ld, int rows, int c0, int c1, const int64_t* goff,
+                            const uint64_t* mkeys, const int32_t* nmatch, int32_t* bins, void* stream);
+REID_API int reid_stream_score(int nq, const int32_t* glen, const int64_t* goff, const uint64_t* mkeys,
+                      const int32_t* nmatch, const int32_t* bins, int max_rank, double* ap, int32_t* first_hit,
+                      int32_t* cmc_hist, int32_t* n_valid, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -463,4 +463,48 @@ int reid_triplet_grad(const float* x, int64_t ldx, int m, const float* y, int64_
                              accumulate_gy ? 1 : 0, S(stream));
 }
 
+// ---- CMC / mAP over a streamed q x g problem
+#define LL(p) reinterpret_cast<const long long*>(p)
+int reid_stream_group_lookup(const int64_t* q_pid, int nq, const uint64_t* pid_keys, const int64_t* pid_start, int pid_T,
+                             int32_t* glo, int32_t* glen, void* stream) {
+  ENTER();
+  REID_REQUIRE(nq >= 0 && pid_T >= 1, "stream_group_lookup: bad shape");
+  return launch_stream_group_lookup(LL(q_pid), nq, reinterpret_cast<const unsigned long long*>(pid_keys), LL(pid_start),
+                                    pid_T, glo, glen, S(stream));
+}
+
+int reid_stream_group_gather(const float* panel, int64_t ld, int rows, int c0, int c1, const int32_t* glo,
+                             const int32_t* glen, const int64_t* goff, const int32_t* pid_list, float* gd, void* stream) {
+  ENTER();
+  REID_REQUIRE(rows >= 0 && c0 >= 0 && c1 >= c0 && ld >= c1 - c0, "stream_group_gather: bad panel");
+  return launch_stream_group_gather(panel, ld, rows, c0, c1, glo, glen, LL(goff), pid_list, gd, S(stream));
+}
+
+int reid_stream_group_sort(int nq, const int32_t* glo, const int32_t* glen, const int64_t* goff, const int32_t* pid_list,
+                           const float* gd, const int64_t* q_cam, const int64_t* g_cam, uint64_t* mkeys, int32_t* nmatch,
+                           int32_t* overflow, void* stream) {
+  ENTER();
+  REID_REQUIRE(nq >= 0, "stream_group_sort: bad shape");
+  return launch_stream_group_sort(nq, glo, glen, LL(goff), pid_list, gd, LL(q_cam), LL(g_cam),
+                                  reinterpret_cast<unsigned long long*>(mkeys), nmatch, overflow, S(stream));
+}
+
+int reid_stream_count_panel(const float* panel, int64_t ld, int rows, int c0, int c1, const int64_t* goff,
+                            const uint64_t* mkeys, const int32_t* nmatch, int32_t* bins, void* stream) {
+  ENTER();
+  REID_REQUIRE(rows >= 0 && c0 >= 0 && c1 >= c0 && ld >= c1 - c0 && ld % 4 == 0, "stream_count_panel: bad panel");
+  REID_REQUIRE(((uintptr_t)panel & 15) == 0, "stream_count_panel: panel must be 16-byte aligned");
+  return launch_stream_count_panel(panel, ld, rows, c0, c1, LL(goff), reinterpret_cast<const unsigned long long*>(mkeys),
+                                   nmatch, bins, S(stream));
+}
+
+int reid_stream_score(int nq, const int32_t* glen, const int64_t* goff, const uint64_t* mkeys, const int32_t* nmatch,
+                      const int32_t* bins, int max_rank, double* ap, int32_t* first_hit, int32_t* cmc_hist,
+                      int32_t* n_valid, void* stream) {
+  ENTER();
+  REID_REQUIRE(nq >= 0 && max_rank >= 1, "stream_score: bad shape");
+  return launch_stream_score(nq, glen, LL(goff), reinterpret_cast<const unsigned long long*>(mkeys), nmatch, bins,
+                             max_rank, ap, first_hit, cmc_hist, n_valid, S(stream));
+}
+
 }  // extern "C"

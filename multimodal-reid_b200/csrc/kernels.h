@@ -112,4 +112,18 @@ int launch_triplet_grad(const float* X, long long ldx, int m, const float* Y, lo
                         const float* g_ap, const float* g_an, float* gx, long long ldgx, float* gy, long long ldgy,
                         int accumulate_gy, cudaStream_t s);
 
+// stream_score.cu (CMC / mAP without the q x g matrix)
+int launch_stream_group_lookup(const long long* q_pid, int nq, const unsigned long long* keys, const long long* start,
+                               int T, int* glo, int* glen, cudaStream_t s);
+int launch_stream_group_gather(const float* panel, long long ld, int rows, int c0, int c1, const int* glo,
+                               const int* glen, const long long* goff, const int* list, float* gd, cudaStream_t s);
+int launch_stream_group_sort(int nq, const int* glo, const int* glen, const long long* goff, const int* list,
+                             const float* gd, const long long* q_cam, const long long* g_cam,
+                             unsigned long long* mkeys, int* nmatch, int* overflow, cudaStream_t s);
+int launch_stream_count_panel(const float* panel, long long ld, int rows, int c0, int c1, const long long* goff,
+                              const unsigned long long* mkeys, const int* nmatch, int* bins, cudaStream_t s);
+int launch_stream_score(int nq, const int* glen, const long long* goff, const unsigned long long* mkeys,
+                        const int* nmatch, const int* bins, int max_rank, double* ap, int* first_hit, int* cmc_hist,
+                        int* n_valid, cudaStream_t s);
+
 }  // namespace reid

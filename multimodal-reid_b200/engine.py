@@ -468,7 +468,7 @@ class Engine:
         return [(c0, starts[i + 1] if i + 1 < len(starts) else g) for i, c0 in enumerate(starts)]
 
     def retrieve_topk(self, Q: Features, G: Features, K: int, metric: int = METRIC_SQEUCLIDEAN,
-                      rows_per_pass: int = 16384, cols_per_pass: int = 65536):
+                      rows_per_pass: int = 16384, cols_per_pass: int = 65536, on_panel=None):
         """Exact K nearest gallery rows of every query row, ascending in stable (distance, column) order, WITHOUT the
         q x g matrix ever existing (100k x 1M x 4 B = 400 GB): the contraction writes one [rows_per_pass, cols_per_pass]
         panel at a time together with its 32-column chunk minima, the hinted selection reads ~K chunks per row of it,
@@ -506,6 +506,8 @@ class Engine:
                         else:
                             ci[:, b * K:(b + 1) * K] = idx + c0
                             cv[:, b * K:(b + 1) * K] = val
+                    if on_panel is not None:
+                        on_panel(D, r0, m, c0, c1)
                     del D, cmin
                 if nb > 1:
                     with self.span("merge"):
@@ -515,6 +517,73 @@ class Engine:
         finally:
             self.symmetric = sym
         return out_i, out_v
+
+    def evaluate_streamed(self, Q: Features, G: Features, q_pids, g_pids, q_cams, g_cams, max_rank: int = 50,
+                          K: int = 0, metric: int = METRIC_SQEUCLIDEAN, rows_per_pass: int = 16384,
+                          cols_per_pass: int = 65536, q_total: int | None = None):
+        """evaluate.py:40-88 (CMC / mAP with same-id same-camera junk removed) for a q x g problem too large to hold:
+        the contraction is swept twice over [rows_per_pass x cols_per_pass] panels (stream_score.cu) — sweep 1 collects the
+        distances of every query's same-identity columns (and, with K > 0, the exact top-K lists of retrieve_topk on
+        the same panels), sweep 2 counts the entries in front of every match.  Q / q_pids / q_cams are this rank's
+        queries.  Returns ((cmc, mAP, n_valid, ap, first_hit), (idx, dist) or None)."""
+        nq, g = Q.n, G.n
+        keys, start, lst, T = self.pid_index(g_pids)
+        glo = self._empty((nq,), torch.int32)
+        glen = self._empty((nq,), torch.int32)
+        _lib.call("reid_stream_group_lookup", _ptr(q_pids), nq, _ptr(keys), _ptr(start), T, _ptr(glo), _ptr(glen), _stream())
+        goff = self._zeros((nq + 1,), torch.int64)
+        goff[1:] = torch.cumsum(glen, 0, dtype=torch.int64)
+        total = int(goff[-1].item())                       # the evaluation's one host read before the sweeps
+        gd = self._empty((max(total, 1),), torch.float32)
+        mkeys = self._empty((max(total, 1),), torch.int64)
+        bins = self._zeros((max(total, 1),), torch.int32)
+        nmatch = self._empty((nq,), torch.int32)
+        overflow = self._zeros((1,), torch.int32)
+
+        def gather(D, r0, m, c0, c1):
+            _lib.call("reid_stream_group_gather", _ptr(D), D.stride(0), m, c0, c1, _ptr(glo[r0:]), _ptr(glen[r0:]),
+                      _ptr(goff[r0:]), _ptr(lst), _ptr(gd), _stream())
+
+        def count(D, r0, m, c0, c1):
+            _lib.call("reid_stream_count_panel", _ptr(D), D.stride(0), m, c0, c1, _ptr(goff[r0:]), _ptr(mkeys),
+                      _ptr(nmatch[r0:]), _ptr(bins), _stream())
+
+        top = None
+        with self.span("sweep1"):
+            if K > 0:
+                top = self.retrieve_topk(Q, G, K, metric, rows_per_pass, cols_per_pass, on_panel=gather)
+            else:
+                self._sweep(Q, G, metric, rows_per_pass, cols_per_pass, gather)
+            _lib.call("reid_stream_group_sort", nq, _ptr(glo), _ptr(glen), _ptr(goff), _ptr(lst), _ptr(gd), _ptr(q_cams),
+                      _ptr(g_cams), _ptr(mkeys), _ptr(nmatch), _ptr(overflow), _stream())
+        with self.span("sweep2"):
+            self._sweep(Q, G, metric, rows_per_pass, cols_per_pass, count)
+
+        def launch(ap, first, hist, nvalid):
+            _lib.call("reid_stream_score", nq, _ptr(glen), _ptr(goff), _ptr(mkeys), _ptr(nmatch), _ptr(bins), max_rank,
+                      _ptr(ap), _ptr(first), _ptr(hist), _ptr(nvalid), _stream())
+        res = self._score_common(launch, nq, max_rank, q_total, span="score")
+        big = int(overflow.item())
+        if big:
+            raise _lib.ReidError(f"an identity has {big} gallery samples; the streamed scorer holds at most 1024 per query")
+        return res, top
+
+    def _sweep(self, Q: Features, G: Features, metric: int, rows_per_pass: int, cols_per_pass: int, on_panel):
+        """One pass of the contraction over [rows_per_pass x cols_per_pass] panels of Q x G; on_panel(D, r0, m, c0, c1)."""
+        sym = self.symmetric
+        self.symmetric = False
+        try:
+            for r0 in range(0, Q.n, rows_per_pass):
+                r1 = min(Q.n, r0 + rows_per_pass)
+                A = Q.rows(slice(r0, r1))
+                for c0, c1 in self.column_blocks(G.n, cols_per_pass, 1):
+                    with self.span("dist"):
+                        D, _ = self.dist(A, G.rows(slice(c0, c1)), metric)
+                    with self.span("panel"):
+                        on_panel(D, r0, r1 - r0, c0, c1)
+                    del D
+        finally:
+            self.symmetric = sym
 
     # ------------------------------------------------------------------ K6
     def krecip_sets(self, nbr: torch.Tensor, k1: int):

@@ -10,6 +10,7 @@ import numpy as np
 import torch
 
 from . import engine as _engine
+from .evaluate import _ids
 from .reranking import _to_device_f32
 
 
@@ -35,3 +36,33 @@ def topk_retrieval(qf, gf, topk: int = 100, metric: str = "euclidean", feat_norm
     m = {"euclidean": _engine.METRIC_SQEUCLIDEAN, "cosine": _engine.METRIC_ARCCOS}[metric]
     idx, val = topk_retrieval_device(qf, gf, topk, m, feat_norm)
     return idx.cpu().numpy(), val.cpu().numpy()
+
+
+def streamed_eval(qf, gf, q_pids, g_pids, q_camids, g_camids, max_rank: int = 50, topk: int = 0,
+                  feat_norm: bool = True, rows_per_pass: int = 16384, cols_per_pass: int = 65536):
+    """``R1_mAP_eval(reranking=False)`` semantics (evaluate.py:110-135: optional L2 normalisation, squared Euclidean
+    distances, ``eval_func``) for a query / gallery pair whose distance matrix does not fit: returns
+    ``(cmc float32[max_rank], mAP float64)`` and, with ``topk > 0``, also the exact top-k lists
+    ``(indices int32 [q, topk], distances float32 [q, topk])`` computed on the same panels."""
+    eng = _engine.default_engine()
+    cm = eng.comm
+    q, g = int(qf.shape[0]), int(gf.shape[0])
+    if g < max_rank:
+        max_rank = g
+        print("Note: number of gallery samples is quite small, got {}".format(g))
+    allf = eng.prepare(torch.cat([_to_device_f32(qf, eng.device), _to_device_f32(gf, eng.device)]), feat_norm)
+    mine = slice(cm.rank, q, cm.world)
+    Q, G = allf.rows(mine), allf.rows(slice(q, q + g))
+    qp, gp = _ids(q_pids, eng.device), _ids(g_pids, eng.device)
+    qc, gc = _ids(q_camids, eng.device), _ids(g_camids, eng.device)
+    (cmc, mAP, nvalid, _, _), top = eng.evaluate_streamed(Q, G, qp[mine].contiguous(), gp, qc[mine].contiguous(), gc,
+                                                          max_rank, topk, _engine.METRIC_SQEUCLIDEAN, rows_per_pass,
+                                                          cols_per_pass, q_total=q)
+    assert int(nvalid.item()) > 0, "Error: all query identities do not appear in gallery"
+    out = (cmc.cpu().numpy(), np.float64(mAP.item()))
+    if top is None:
+        return out
+    idx, val = top
+    if cm.world > 1:
+        idx, val = cm.gather_rows(idx, q), cm.gather_rows(val, q)
+    return out + (idx.cpu().numpy(), val.cpu().numpy())

@@ -84,3 +84,63 @@ def test_front_end_and_cosine(oracle):
     assert_ranking_equal_mod_ties(idx.astype(np.int64), order, want, what="cosine top-k")
     with pytest.raises(ValueError):
         r.topk_retrieval(qf, gf, topk=1000)
+
+
+def _ids_case(q, g, n_id, n_cam, seed, absent=0):
+    gen = torch.Generator().manual_seed(seed)
+    gp = torch.randint(0, n_id, (g,), generator=gen)
+    qp = torch.randint(0, n_id, (q,), generator=gen)
+    if absent:
+        qp[:absent] = n_id + 5                      # identities that do not occur in the gallery: skipped queries
+    return qp, gp, torch.randint(0, n_cam, (q,), generator=gen), torch.randint(0, n_cam, (g,), generator=gen)
+
+
+@pytest.mark.parametrize("q,g,d,n_id,n_cam,rows,cols,K", [
+    (300, 5000, 128, 60, 6, 128, 1024, 0),         # ~80 same-identity columns per query, a few junk
+    (257, 4100, 64, 400, 2, 4096, 999, 20),        # two cameras: half of every group is junk; top-k on the same panels
+    (90, 2500, 96, 3, 3, 50, 700, 0),              # groups of ~830 columns: most of the row ranks before the farthest match
+])
+def test_streamed_cmc_map_equals_materialised(eng, oracle, q, g, d, n_id, n_cam, rows, cols, K):
+    qf, gf = _make(q, g, d, q * 7 + g, dup=25)
+    qp, gp, qc, gc = _ids_case(q, g, n_id, n_cam, q + 1, absent=7)
+    dev = eng.device
+    allf = eng.prepare(torch.cat([qf, gf]).to(dev), True)
+    Q, G = allf.rows(slice(0, q)), allf.rows(slice(q, q + g))
+    ids = [t.to(dev) for t in (qp, gp, qc, gc)]
+    (cmc, mAP, nv, ap, first), top = eng.evaluate_streamed(Q, G, ids[0], ids[1], ids[2], ids[3], 50, K,
+                                                           rows_per_pass=rows, cols_per_pass=cols)
+    sym = eng.symmetric
+    eng.symmetric = False
+    try:
+        D, _ = eng.dist(Q, G)
+    finally:
+        eng.symmetric = sym
+    cmc2, mAP2, nv2, ap2, first2 = eng.evaluate_dist(D, g, *ids, 50)
+    assert int(nv.item()) == int(nv2.item()) == q - 7
+    assert torch.equal(first, first2)
+    assert torch.equal(cmc, cmc2)
+    np.testing.assert_allclose(ap.cpu().numpy(), ap2.cpu().numpy(), rtol=0, atol=1e-13)
+    assert abs(float(mAP.item()) - float(mAP2.item())) < 1e-13
+    if K:
+        unit = torch.full((q,), 0x3F800000, dtype=torch.int32, device=dev)
+        idx_full = eng.topk_rows(D, g, unit, K)
+        assert torch.equal(top[0], idx_full)
+    # and the oracle on its own float32 distances (evaluate.py:29-88 restated)
+    f = torch.nn.functional.normalize(torch.cat([qf, gf]), dim=1, p=2)
+    want = oracle.sq_euclidean(f[:q].numpy(), f[q:].numpy())
+    c3, m3 = oracle.cmc_map(want, qp.numpy(), gp.numpy(), qc.numpy(), gc.numpy())
+    assert np.abs(cmc.cpu().numpy() - c3).max() < 1e-5 and abs(float(mAP.item()) - m3) < 1e-5
+
+
+def test_streamed_eval_front_end(oracle):
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    r = importlib.import_module("multimodal-reid_b200.retrieval")
+    qf, gf = _make(120, 1500, 64, 77)
+    qp, gp, qc, gc = _ids_case(120, 1500, 30, 4, 5)
+    cmc, mAP, idx, val = r.streamed_eval(qf, gf, qp, gp.numpy(), qc, gc, topk=10, cols_per_pass=400)
+    assert cmc.dtype == np.float32 and cmc.shape == (50,) and isinstance(mAP, np.float64) and idx.shape == (120, 10)
+    f = torch.nn.functional.normalize(torch.cat([qf, gf]), dim=1, p=2)
+    c3, m3 = oracle.cmc_map(oracle.sq_euclidean(f[:120].numpy(), f[120:].numpy()), qp.numpy(), gp.numpy(), qc.numpy(),
+                            gc.numpy())
+    assert np.abs(cmc - c3).max() < 1e-5 and abs(mAP - m3) < 1e-5
