@@ -30,6 +30,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=1)
     ap.add_argument("--rows-per-pass", type=int, default=16384)
     ap.add_argument("--cols-per-pass", type=int, default=65536)
+    ap.add_argument("--score", action="store_true", help="also CMC / mAP over the streamed problem (two sweeps)")
+    ap.add_argument("--ids", type=int, default=50_000, help="identities (gallery draws from 1.2x as many), 32 cameras")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -44,18 +46,36 @@ def main():
     cm = eng.comm
     q, g, d, K = args.q, args.g, args.d, args.topk
     gen = torch.Generator(device=dev).manual_seed(0)
-    cent = torch.randn(4096, d, generator=gen, device=dev)
+    # SURVEY 8(d) generator: identity centroids ~ N(0, I), sample = centroid + 2.5 * N(0, I); the gallery draws from
+    # 1.2x as many identities (distractors), cameras uniform over 32
+    n_gid = int(args.ids * 1.2)
+    qp = torch.randint(0, args.ids, (q,), generator=gen, device=dev)
+    gp = torch.randint(0, n_gid, (g,), generator=gen, device=dev)
+    qc = torch.randint(0, 32, (q,), generator=gen, device=dev)
+    gc = torch.randint(0, 32, (g,), generator=gen, device=dev)
+    cent = torch.randn(n_gid, d, generator=gen, device=dev)
+    pid_all = torch.cat([qp, gp])
     feats = torch.empty((q + g, d), dtype=torch.float32, device=dev)
     for a in range(0, q + g, 1 << 18):               # bounded temporaries
         b = min(q + g, a + (1 << 18))
-        ids = torch.randint(0, 4096, (b - a,), generator=gen, device=dev)
-        feats[a:b] = cent[ids] + 2.5 * torch.randn(b - a, d, generator=gen, device=dev)
+        feats[a:b] = cent[pid_all[a:b]] + 2.5 * torch.randn(b - a, d, generator=gen, device=dev)
+    del cent, pid_all
     allf = eng.prepare(feats, True)
     del feats
     Q, G = allf.rows(slice(cm.rank, q, cm.world)), allf.rows(slice(q, q + g))
 
+    mine = slice(cm.rank, q, cm.world)
+    qp_l, qc_l = qp[mine].contiguous(), qc[mine].contiguous()
+    score_out = {}
+
     def step():
-        idx, val = eng.retrieve_topk(Q, G, K, rows_per_pass=args.rows_per_pass, cols_per_pass=args.cols_per_pass)
+        if args.score:
+            (cmc, mAP, nv, _, _), (idx, val) = eng.evaluate_streamed(Q, G, qp_l, gp, qc_l, gc, 50, K,
+                                                                     rows_per_pass=args.rows_per_pass,
+                                                                     cols_per_pass=args.cols_per_pass, q_total=q)
+            score_out.update(cmc=cmc, mAP=mAP, nv=nv)
+        else:
+            idx, val = eng.retrieve_topk(Q, G, K, rows_per_pass=args.rows_per_pass, cols_per_pass=args.cols_per_pass)
         if cm.world > 1:
             idx, val = cm.gather_rows(idx, q), cm.gather_rows(val, q)
         return idx, val
@@ -90,7 +110,10 @@ def main():
         rows_local = cm.local_count(q)
         flops = 2.0 * rows_local * g * d
         dist_ms = stages.get("dist", float("nan"))
-        line = {"metric": "top-k retrieval q x g pairs/sec (distance + exact top-k, matrix never materialised)",
+        sweeps = 2 if args.score else 1
+        flops *= sweeps
+        line = {"metric": ("top-k retrieval + CMC/mAP" if args.score else "top-k retrieval")
+                          + " q x g pairs/sec (matrix never materialised)",
                 "value": q * g / (ms * 1e-3), "unit": "pairs/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
                 "dtype": "f32 (fp16-split tensor-core contraction)", "data": "synthetic",
@@ -105,6 +128,8 @@ def main():
                 "hbm_panel": {"bytes_written_per_step": 4.0 * rows_local * g * (1 + 1 / 32),
                               "GB/s_over_dist": 4.0 * rows_local * g * (1 + 1 / 32) / (dist_ms * 1e-3) / 1e9,
                               "peak": hbm},
+                "score": ({"mAP": float(score_out["mAP"].item()), "rank1": float(score_out["cmc"][0].item()),
+                           "n_valid": int(score_out["nv"].item()), "sweeps": 2} if args.score else None),
                 "first_row": {"idx": idx[0, :5].tolist(), "dist": [round(float(x), 6) for x in val[0, :5]]}}
         print(json.dumps(line))
     if world > 1:
