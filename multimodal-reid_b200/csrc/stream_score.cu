@@ -94,46 +94,84 @@ group_sort_kernel(int nq, const int* __restrict__ glo, const int* __restrict__ g
   if (tid == 0) nmatch[qi] = P;
 }
 
-// one CTA per panel row: bins[goff + b] += #{entries of this block with exactly b match keys below them}, b < P
+// one CTA per panel row: bins[goff + b] += #{entries of this block with exactly b match keys below them}, b < P.
+// Entries at or below the farthest match's distance are counted in SG_NB cells over [0, dmax] (cell(d) is monotone in d,
+// so an entry in a cell that holds no match lies on the same side of every match as the whole cell: one multiply, one
+// convert, one shared-memory add); only entries that share a cell with a match take the exact (distance, column) search.
+constexpr int SG_NB = 2048;
+__device__ __forceinline__ int sg_cell(float d, float scale) {
+  return (int)min(__float2uint_rz(__fmul_rn(d, scale)), (unsigned)(SG_NB - 1));       // negative -> 0
+}
+
 __global__ void __launch_bounds__(256)
 count_panel_kernel(const float* __restrict__ panel, long long ld, int rows, int c0, int c1,
                    const long long* __restrict__ goff, const unsigned long long* __restrict__ mkeys,
                    const int* __restrict__ nmatch, int* __restrict__ bins) {
   __shared__ unsigned long long sk[SG_CAP];
   __shared__ int hist[SG_CAP];
+  __shared__ int cells[SG_NB];
   const int row = blockIdx.x, tid = threadIdx.x;
   const int P = nmatch[row];
   if (P == 0) return;
   const long long off = goff[row];
   for (int i = tid; i < P; i += 256) { sk[i] = mkeys[off + i]; hist[i] = 0; }
+  for (int i = tid; i < SG_NB; i += 256) cells[i] = 0;
   __syncthreads();
   const unsigned long long kmax = sk[P - 1];
   const float dmax = key2f((uint32_t)(kmax >> 32));
+  const bool fast = dmax > 0.0f && dmax < INFINITY;      // otherwise (zero, inf, NaN) every entry is searched exactly
+  float scale = 0.0f;
+  if (fast) {
+    scale = __fdiv_rn((float)SG_NB, dmax);
+    if (!(scale < INFINITY)) scale = 0.0f;               // one cell: everything exact
+    for (int i = tid; i < P; i += 256) cells[sg_cell(key2f((uint32_t)(sk[i] >> 32)), scale)] = (int)0x80000000;
+  }
+  __syncthreads();
   const float* r = panel + (long long)row * ld;
   const int n = c1 - c0;
-  auto offer = [&](float d, int j) {
-    if (!(d > dmax)) {                                   // NaN falls through to the key compare
-      const unsigned long long k = dist_key(d, c0 + j);
-      if (k <= kmax) {
-        int lo = 0, hi = P;                              // #{match keys < k}
-        while (lo < hi) {
-          const int mid = (lo + hi) >> 1;
-          if (sk[mid] < k) lo = mid + 1; else hi = mid;
-        }
-        atomicAdd(&hist[lo], 1);
+  auto exact = [&](float d, int j) {
+    const unsigned long long k = dist_key(d, c0 + j);
+    if (k <= kmax) {
+      int lo = 0, hi = P;                                // #{match keys < k}
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (sk[mid] < k) lo = mid + 1; else hi = mid;
       }
+      atomicAdd(&hist[lo], 1);
+    }
+  };
+  auto offer = [&](float d, int j) {
+    if (fast) {
+      if (d <= dmax && atomicAdd(&cells[sg_cell(d, scale)], 1) < 0) exact(d, j);
+    } else if (!(d > dmax)) {
+      exact(d, j);
     }
   };
   const int n4 = n >> 2;
   const float4* r4 = reinterpret_cast<const float4*>(r);
   for (int i = tid; i < n4; i += 256) {
     const float4 v = __ldg(r4 + i);
-    if (fminf(fminf(v.x, v.y), fminf(v.z, v.w)) <= dmax || v.x != v.x || v.y != v.y || v.z != v.z || v.w != v.w) {
+    if (!fast || fminf(fminf(v.x, v.y), fminf(v.z, v.w)) <= dmax) {
       offer(v.x, 4 * i); offer(v.y, 4 * i + 1); offer(v.z, 4 * i + 2); offer(v.w, 4 * i + 3);
     }
   }
   for (int j = 4 * n4 + tid; j < n; j += 256) offer(__ldg(r + j), j);
   __syncthreads();
+  if (fast) {
+    // a cell without a match: all its entries have exactly #{matches in lower cells} match keys below them
+    for (int c = tid; c < SG_NB; c += 256) {
+      const int cnt = cells[c];
+      if (cnt > 0) {
+        int lo = 0, hi = P;
+        while (lo < hi) {
+          const int mid = (lo + hi) >> 1;
+          if (sg_cell(key2f((uint32_t)(sk[mid] >> 32)), scale) < c) lo = mid + 1; else hi = mid;
+        }
+        if (lo < P) atomicAdd(&hist[lo], cnt);
+      }
+    }
+    __syncthreads();
+  }
   for (int i = tid; i < P; i += 256)
     if (hist[i]) bins[off + i] += hist[i];               // this CTA owns the row's bins: plain adds
 }
