@@ -66,3 +66,34 @@ def test_drop_in_names():
     e = evaluate.R1_mAP_eval(5, max_rank=10, feat_norm=True, reranking=False)
     e.reset()
     assert (e.num_query, e.max_rank, e.feat_norm, e.reranking, e.feats, e.pids, e.camids) == (5, 10, True, False, [], [], [])
+
+
+def test_losses_and_retrieval_surface():
+    """losses.py drop-in names (losses.py:14, :31, :86, :111 of the reference) and the streamed-retrieval module import
+    without a GPU; compute calls on CPU tensors raise instead of falling back."""
+    import importlib
+
+    import pytest
+    import torch
+    import losses
+    for n in ("euclidean_dist", "hard_example_mining", "WeightedRegularizedTriplet", "WeightedRegularizedTripletXBM"):
+        assert hasattr(losses, n)
+    assert losses.WeightedRegularizedTriplet(0.3).margin == 0.3 and losses.WeightedRegularizedTriplet().margin is None
+    _lib = importlib.import_module("multimodal-reid_b200._lib")
+    with pytest.raises(_lib.ReidError):
+        losses.euclidean_dist(torch.randn(3, 4), torch.randn(3, 4))
+    r = importlib.import_module("multimodal-reid_b200.retrieval")
+    assert callable(r.topk_retrieval) and callable(r.streamed_eval)
+
+
+def test_column_blocks_host_logic():
+    import importlib
+    cb = importlib.import_module("multimodal-reid_b200.engine").Engine.column_blocks
+    assert cb(10, 4, 2) == [(0, 4), (4, 8), (8, 10)]
+    assert cb(9, 4, 2) == [(0, 4), (4, 9)]                 # a tail shorter than K joins its predecessor
+    assert cb(3, 100, 3) == [(0, 3)]
+    assert cb(1000, 10, 100) == [(i, min(1000, i + 100)) for i in range(0, 1000, 100)]
+    for g, c, k in ((1_000_000, 65536, 100), (200_000, 65536, 100), (17, 5, 5)):
+        b = cb(g, c, k)
+        assert b[0][0] == 0 and b[-1][1] == g and all(x[1] == y[0] for x, y in zip(b, b[1:]))
+        assert all(hi - lo >= min(k, g) for lo, hi in b)
