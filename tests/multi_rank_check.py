@@ -67,6 +67,28 @@ def main():
     assert (res[0][0] == res[1][0]).all() and res[0][1] == res[1][1], "sharded upload changed the result"
     if rank == 0:
         print(f"evaluator on host batches: sharded upload == replicated upload, mAP {res[0][1]:.6f}", flush=True)
+    # streamed retrieval + CMC/mAP: sharded queries + all-gathered lists == one rank, bit for bit
+    retrieval = importlib.import_module("multimodal-reid_b200.retrieval")
+    engine.default_engine().shard_h2d = True
+    g_ = torch.Generator().manual_seed(9)
+    qn, gn = 203, 3001
+    gp2 = torch.randint(0, 40, (gn,), generator=g_)
+    qp2 = torch.randint(0, 40, (qn,), generator=g_)
+    qc2, gc2 = torch.randint(0, 5, (qn,), generator=g_), torch.randint(0, 5, (gn,), generator=g_)
+    cent = torch.randn(40, 64, generator=g_)
+    qf2 = cent[qp2] + 1.5 * torch.randn(qn, 64, generator=g_)
+    gf2 = cent[gp2] + 1.5 * torch.randn(gn, 64, generator=g_)
+    cmc_m, map_m, idx_m, val_m = retrieval.streamed_eval(qf2, gf2, qp2, gp2, qc2, gc2, topk=30, rows_per_pass=64,
+                                                         cols_per_pass=700)
+    allf = single.prepare(torch.cat([qf2, gf2]).to(dev), True)
+    ids2 = [t.to(dev) for t in (qp2, gp2, qc2, gc2)]
+    (cmc_s, map_s, _, _, _), (idx_s, val_s) = single.evaluate_streamed(
+        allf.rows(slice(0, qn)), allf.rows(slice(qn, qn + gn)), ids2[0], ids2[1], ids2[2], ids2[3], 50, 30,
+        rows_per_pass=64, cols_per_pass=700)
+    assert (cmc_m == cmc_s.cpu().numpy()).all() and map_m == float(map_s.item()), "streamed CMC/mAP differs across ranks"
+    assert (idx_m == idx_s.cpu().numpy()).all() and (val_m == val_s.cpu().numpy()).all(), "streamed top-k differs"
+    if rank == 0:
+        print(f"streamed retrieval + CMC/mAP: {world}-rank result == 1-rank result, mAP {map_m:.6f}", flush=True)
     dist.barrier()
     dist.destroy_process_group()
 
