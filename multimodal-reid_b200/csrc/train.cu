@@ -12,7 +12,7 @@
 namespace reid {
 
 constexpr int PT = 32;     // output tile edge
-constexpr int PK = 32;     // K slab
+constexpr int PK = 128;    // K slab: 16 + 16 independent loads per thread in flight, d / 128 dependent round trips
 
 // 256 threads, 32 x 32 outputs, 2 x 2 per thread; rows/columns past the edge are staged as zeros.
 __global__ void __launch_bounds__(256)
@@ -23,19 +23,31 @@ pair_dist_kernel(const float* __restrict__ X, long long ldx, int m, const float*
   const int tid = threadIdx.x;
   const int tx = tid & 15, ty = tid >> 4;
   const int m0 = blockIdx.y * PT, n0 = blockIdx.x * PT;
-  const int lr = tid >> 3, lk = (tid & 7) * 4;       // staging: row lr, 4 consecutive k
+  const int lr = tid >> 3, lk = (tid & 7) * 4;       // staging: row lr, 4 consecutive k in each 32-wide pass
+  const int r_ld = m0 + lr, c_ld = n0 + lr;
+  const float* xrow = X + (long long)min(r_ld, m - 1) * ldx;
+  const float* yrow = Y + (long long)min(c_ld, n - 1) * ldy;
   float acc[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
   float xx[2] = {0.f, 0.f}, yy[2] = {0.f, 0.f};
   for (int k0 = 0; k0 < d; k0 += PK) {
+    float xv[PK / 8], yv[PK / 8];
 #pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      const int k = k0 + lk + e;
-      const int r = m0 + lr, c = n0 + lr;
-      Xs[lk + e][lr] = (r < m && k < d) ? X[(long long)r * ldx + k] : 0.f;
-      Ys[lk + e][lr] = (c < n && k < d) ? Y[(long long)c * ldy + k] : 0.f;
-    }
+    for (int p = 0; p < PK / 32; ++p)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int k = k0 + p * 32 + lk + e;
+        xv[p * 4 + e] = (r_ld < m && k < d) ? __ldg(xrow + k) : 0.f;
+        yv[p * 4 + e] = (c_ld < n && k < d) ? __ldg(yrow + k) : 0.f;
+      }
+#pragma unroll
+    for (int p = 0; p < PK / 32; ++p)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        Xs[p * 32 + lk + e][lr] = xv[p * 4 + e];
+        Ys[p * 32 + lk + e][lr] = yv[p * 4 + e];
+      }
     __syncthreads();
-#pragma unroll
+#pragma unroll 32
     for (int k = 0; k < PK; ++k) {
       const float a0 = Xs[k][ty], a1 = Xs[k][ty + 16], b0 = Ys[k][tx], b1 = Ys[k][tx + 16];
       acc[0][0] = __fmaf_rn(a0, b0, acc[0][0]);
