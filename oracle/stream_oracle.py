@@ -84,3 +84,17 @@ def cmc_map_counting(dist, q_pids, g_pids, q_cams, g_cams, max_rank=50, blocks=N
     assert valid.any(), "Error: all query identities do not appear in gallery"
     cmc = (np.cumsum(hist_cmc).astype(np.float32) / np.float32(valid.sum())).astype(np.float32)
     return cmc, float(np.mean(ap[valid])), ap, first
+
+
+def topk_by_blocks(dist, K, blocks):
+    """Engine.retrieve_topk's merge argument in numpy: stable top-K inside every column block, winners laid out block
+    after block, stable top-K over that candidate matrix, candidates mapped back to global columns."""
+    dist = np.asarray(dist, np.float32) + np.float32(0)
+    cv, ci = [], []
+    for c0, c1 in blocks:
+        o = np.argsort(dist[:, c0:c1], axis=1, kind="stable")[:, :K]
+        ci.append(o + c0)
+        cv.append(np.take_along_axis(dist[:, c0:c1], o, 1))
+    cv, ci = np.concatenate(cv, 1), np.concatenate(ci, 1)
+    pos = np.argsort(cv, axis=1, kind="stable")[:, :K]
+    return np.take_along_axis(ci, pos, 1), np.take_along_axis(cv, pos, 1)

@@ -46,3 +46,15 @@ def test_zero_and_negative_distances(oracle):
     np.testing.assert_array_equal(first, first2)
     np.testing.assert_array_equal(cmc, c2)
     assert abs(mAP - m2) < 1e-15
+
+
+@pytest.mark.parametrize("quant", [None, 8])
+def test_blockwise_topk_equals_global_stable_topk(quant):
+    """candidate position order == global column order among equal distances (Engine.retrieve_topk's claim)"""
+    dist, *_ = _case(11, 30, 700, 5, 2, quant)
+    K = 50
+    want = np.argsort(dist, axis=1, kind="stable")[:, :K]
+    for blocks in ([(0, 700)], [(0, 256), (256, 512), (512, 700)], [(i, min(700, i + 64)) for i in range(0, 700, 64)]):
+        idx, val = so.topk_by_blocks(dist, K, blocks)
+        np.testing.assert_array_equal(idx, want)
+        np.testing.assert_array_equal(val, np.take_along_axis(dist, want, 1))
