@@ -92,3 +92,23 @@ def test_oracle_vs_live_reference():
     l2, g2, _ = lo.triplet(x.numpy(), lab.numpy(), 0.3)
     assert abs(l2 - loss.item()) < 1e-5
     np.testing.assert_allclose(g2, xv.grad.numpy(), rtol=1e-4, atol=1e-5 * xv.grad.abs().max().item())
+
+
+def test_reference_xbm_mask_is_an_integer_index():
+    """Why WeightedRegularizedTripletXBM is NOT reproduced bit for bit: losses.py:126-132 builds the
+    positive mask as a *long* tensor, so `dist_mat[is_pos]` is integer (row) indexing — shape [N, M, M], rows 0 and 1 of
+    the matrix — not boolean masking; every anchor gets the same `dist_ap`.  (The class itself cannot run on CPU: it
+    calls `.cuda()` at :128; the three statements below are its mask arithmetic on a toy case.)  The drop-in implements
+    the masks the code builds, which the oracle restates (`hard_example_mining(..., lab_c, skip_diag=True)`)."""
+    import torch
+    N, M = 4, 6
+    dist_mat = torch.arange(N * M, dtype=torch.float32).reshape(N, M)
+    labels, labels_xbm = torch.tensor([0, 0, 1, 1]), torch.tensor([0, 0, 1, 1, 0, 1])
+    is_pos = (labels.expand(M, N).t()).eq(labels_xbm.expand(N, M)).long()
+    is_pos[:, :N] = is_pos[:, :N] - torch.eye(N, dtype=torch.long)
+    picked = dist_mat[is_pos]
+    assert is_pos.dtype == torch.int64 and tuple(picked.shape) == (N, M, M)
+    assert torch.equal(picked.contiguous().view(N, -1).max(1)[0], torch.full((N,), 11.0))     # max of rows 0 and 1
+    # the intended semantics: farthest same-label bank entry other than the anchor's own slot
+    ap, an, pi, ni = lo.hard_example_mining(dist_mat.numpy(), labels.numpy(), labels_xbm.numpy(), skip_diag=True)
+    assert pi.tolist() == [4, 4, 5, 5] and ni.tolist() == [2, 2, 0, 0]
