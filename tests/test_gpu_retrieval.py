@@ -144,3 +144,32 @@ def test_streamed_eval_front_end(oracle):
     c3, m3 = oracle.cmc_map(oracle.sq_euclidean(f[:120].numpy(), f[120:].numpy()), qp.numpy(), gp.numpy(), qc.numpy(),
                             gc.numpy())
     assert np.abs(cmc - c3).max() < 1e-5 and abs(mAP - m3) < 1e-5
+
+
+import glob as _glob
+import os as _os
+
+_GOLDEN = sorted(_glob.glob(_os.path.join(_os.path.dirname(__file__), "golden", "*.npz")))
+
+
+@pytest.mark.parametrize("path", _GOLDEN, ids=[_os.path.basename(p)[:-4] for p in _GOLDEN])
+def test_streamed_eval_vs_reference_golden(path):
+    """Pinned to the reference itself: tests/golden holds what the unmodified R1_mAP_eval(reranking=False).compute()
+    returned for these raw features (oracle/make_golden.py) and the first rows of its euclidean_distance()."""
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    r = importlib.import_module("multimodal-reid_b200.retrieval")
+    z = np.load(path)
+    q = int(z["q"])
+    raw = torch.from_numpy(z["raw"])
+    pids, cams = z["pids"], z["cams"]
+    K = 10
+    cmc, mAP, idx, val = r.streamed_eval(raw[:q], raw[q:], pids[:q], pids[q:], cams[:q], cams[q:], topk=K,
+                                         feat_norm=True, rows_per_pass=32, cols_per_pass=100)
+    np.testing.assert_allclose(cmc, z["cmc_eval"], atol=1e-5)
+    assert abs(mAP - float(z["map_eval"])) < 1e-5
+    eu = z["eu"]                                              # reference distances of the first rows
+    rows = eu.shape[0]
+    order = np.argsort(eu, axis=1, kind="stable")[:, :K]
+    assert_ranking_equal_mod_ties(idx[:rows].astype(np.int64), order, eu, what="streamed top-k vs reference distances")
+    np.testing.assert_allclose(val[:rows], np.take_along_axis(eu, order, 1), rtol=1e-4, atol=1e-5)
