@@ -100,26 +100,59 @@ class ClockSampler:
 
 
 # ----------------------------------------------------------------------------------------------
-# CPU arm / cpu_baseline: the oracle port on a bounded, down-scaled sample of the same workload
+# CPU arm / cpu_baseline: the reference's own CPU implementation of the path on the box's host cores.
+#   kind "reference": the UNMODIFIED /root/reference/{evaluate,reranking}.py, shipped by oracle/build_ref.py as
+#                     oracle/_ref (git-ignored, travels with the snapshot): re_ranking(...) + eval_func(...), the body of
+#                     R1_mAP_eval(reranking=True).compute() (evaluate.py:110-134) with the config's k1/k2/lambda
+#   kind "port":      oracle/reid_oracle.py (sparse numpy restatement, several times FASTER than the reference) -- only
+#                     when oracle/_ref did not arrive
+# The reference keeps ~24 N^2 bytes live and argsorts the full N x N matrix (reranking.py:48): 66 s at N = 19 k, ~210 GB
+# at the MSMT17 shape.  A step of the CPU arm is therefore a bounded, down-scaled sample of the workload (same generator,
+# same q:g ratio and identity density); the shape that ran is named in `sample`.
 # ----------------------------------------------------------------------------------------------
+CPU_SCALE_DEFAULT = {"msmt17": 16, "duke": 4, "market": 4, "veri": 2}
+
+
 def cpu_sample_shape(synth, shape, scale: int):
+    if scale <= 1:
+        return shape
     return synth.scaled(shape, max(8, shape.q // scale), max(64, shape.g // scale))
 
 
-def run_cpu_oracle(synth, shape, seed=0):
-    """One re-ranked evaluation by the oracle port (numpy; BLAS threads for the contraction).
-    Returns (seconds, pairs, mAP)."""
+def cpu_scale_for(args, shape) -> int:
+    return args.cpu_scale if args.cpu_scale > 0 else CPU_SCALE_DEFAULT.get(shape.name, 4)
+
+
+def cpu_kind() -> str:
+    from oracle import build_ref                      # checker / CPU baseline only
+    return "reference" if build_ref.available() else "port"
+
+
+def run_cpu_eval(synth, shape, seed=0):
+    """One re-ranked evaluation on the host cores.  Returns (seconds, pairs, mAP, kind)."""
     import torch
-    from oracle import reid_oracle as oracle          # checker / CPU baseline only
     qf, gf, qp, gp, qc, gc = synth.make(shape, seed)
-    feats = torch.cat([qf, gf]).numpy()
-    pids = torch.cat([qp, gp]).numpy()
-    cams = torch.cat([qc, gc]).numpy()
-    t0 = time.perf_counter()
-    cmc, mAP = oracle.evaluate_features(feats, pids, cams, shape.q, feat_norm=True, reranking=True,
-                                        k1=shape.k1, k2=shape.k2, lam=shape.lam)
-    dt = time.perf_counter() - t0
-    return dt, shape.q * shape.g, float(mAP)
+    kind = cpu_kind()
+    if kind == "reference":
+        from oracle import build_ref
+        ev, rr = build_ref.load()
+        t0 = time.perf_counter()
+        # evaluate.py:110-134 with reranking=True (k1/k2/lambda of the config instead of the hard-coded 50/15/0.3)
+        feats = torch.nn.functional.normalize(torch.cat([qf, gf]), dim=1, p=2)
+        with contextlib.redirect_stdout(io.StringIO()):
+            distmat = rr.re_ranking(feats[: shape.q], feats[shape.q:], k1=shape.k1, k2=shape.k2, lambda_value=shape.lam)
+            cmc, mAP = ev.eval_func(distmat, qp.numpy(), gp.numpy(), qc.numpy(), gc.numpy())
+        dt = time.perf_counter() - t0
+    else:
+        from oracle import reid_oracle as oracle
+        feats = torch.cat([qf, gf]).numpy()
+        pids = torch.cat([qp, gp]).numpy()
+        cams = torch.cat([qc, gc]).numpy()
+        t0 = time.perf_counter()
+        cmc, mAP = oracle.evaluate_features(feats, pids, cams, shape.q, feat_norm=True, reranking=True,
+                                            k1=shape.k1, k2=shape.k2, lam=shape.lam)
+        dt = time.perf_counter() - t0
+    return dt, shape.q * shape.g, float(mAP), kind
 
 
 def cpu_threads():
@@ -130,30 +163,43 @@ def cpu_threads():
         return os.cpu_count() or 1
 
 
+def cpu_sample_desc(sample, shape, scale, kind):
+    what = ("unmodified reference re_ranking + eval_func (oracle/_ref)" if kind == "reference"
+            else "oracle/reid_oracle.py (sparse numpy port; oracle/_ref absent)")
+    if scale <= 1:
+        return (f"{sample.q}x{sample.g}x{sample.d} = the full {shape.name} shape, k1={sample.k1} k2={sample.k2} "
+                f"lambda={sample.lam}; one full re-ranked eval per step by the {what}")
+    N = shape.q + shape.g
+    return (f"{sample.q}x{sample.g}x{sample.d} (1/{scale} of {shape.name} in q and g, same generator), k1={sample.k1} "
+            f"k2={sample.k2} lambda={sample.lam}; one full re-ranked eval per step by the {what}; the full shape needs "
+            f"~24*N^2 B = {24 * N * N / 1e9:.0f} GB and a full N x N argsort per step on the host")
+
+
 def reference_arm(args, synth, shape, rank):
     if rank != 0:
         return
-    sample = cpu_sample_shape(synth, shape, args.cpu_scale)
+    scale = cpu_scale_for(args, shape)
+    sample = cpu_sample_shape(synth, shape, scale)
     for _ in range(max(0, min(args.warmup, 1))):
-        run_cpu_oracle(synth, sample)
-    times, pairs = [], 0
+        run_cpu_eval(synth, sample)
+    times, pairs, kind = [], 0, "port"
     for _ in range(args.steps):
-        dt, pairs, mAP = run_cpu_oracle(synth, sample)
+        dt, pairs, mAP, kind = run_cpu_eval(synth, sample)
         times.append(dt)
     total = sum(times)
     value = pairs * len(times) / total
-    desc = (f"{sample.q}x{sample.g}x{sample.d} (1/{args.cpu_scale} of {shape.name} in q and g, same generator), "
-            f"k1={sample.k1} k2={sample.k2} lambda={sample.lam}; full re-ranked eval per step")
+    desc = cpu_sample_desc(sample, shape, scale, kind)
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times),
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": shape.name, "q": shape.q, "g": shape.g, "d": shape.d, "k1": shape.k1, "k2": shape.k2,
-                   "lambda": shape.lam, "sample": desc},
+                   "lambda": shape.lam, "sample": desc, "sample_q": sample.q, "sample_g": sample.g,
+                   "same_config": scale <= 1},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": os.cpu_count(), "threads_blas": cpu_threads(),
-                         "kind": "port", "sample": desc},
+                         "kind": kind, "sample": desc},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0,
+        "gpu_launches": 0, "mAP_sample": mAP,
     }
     print(json.dumps(line), flush=True)
 
@@ -167,9 +213,12 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="duke")
+    ap.add_argument("--workload", default="msmt17", help="msmt17 (the north-star shape, default) | duke | market | veri")
+    ap.add_argument("--k1", type=int, default=0, help="override the workload's k1 (e.g. 50, the evaluator's own value)")
+    ap.add_argument("--k2", type=int, default=0)
     ap.add_argument("--engine", default="auto", choices=["auto", "simt", "tcgen05"])
-    ap.add_argument("--cpu-scale", type=int, default=2, help="CPU sample = workload with q and g divided by this")
+    ap.add_argument("--cpu-scale", type=int, default=0,
+                    help="CPU sample = workload with q and g divided by this (0: per-workload default; 1: full shape)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--stages", action="store_true", help="print a per-stage table to stderr")
@@ -183,6 +232,9 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     synth = importlib.import_module("multimodal-reid_b200.synth")
     shape = synth.SHAPES[args.workload]
+    if args.k1 or args.k2:
+        import dataclasses
+        shape = dataclasses.replace(shape, k1=args.k1 or shape.k1, k2=args.k2 or shape.k2)
 
     if args.impl == "reference":
         reference_arm(args, synth, shape, rank)
@@ -322,26 +374,32 @@ def main():
     # what the tensor pipe is actually asked to do: 3 fp16 MMAs (hi.hi + hi.lo + lo.hi) over the 256 x 256 tiles the
     # schedule computes -- the upper triangle only when one rank owns every row (symmetric mode)
     T_n, dp = -(-N // 256), -(-d // 64) * 64
-    tiles = T_n * (T_n + 1) // 2 if (world == 1 and eng.symmetric) else -(-rows_local // 256) * T_n
+    sym_sched = eng.symmetric and (world == 1 or getattr(eng, "fabric", None) is not None)
+    tiles = eng.last_tiles if getattr(eng, "last_tiles", 0) else (
+        T_n * (T_n + 1) // 2 if sym_sched else -(-rows_local // 256) * T_n)
     issued = 3.0 * tiles * 2.0 * 256 * 256 * dp
     issued_tf = issued / (dist_ms * 1e-3) / 1e12
-    traffic = None
+    traffic_all = {}
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
-    if world == 1 and os.path.exists(tpath):
+    if os.path.exists(tpath):
         with open(tpath) as f:
-            traffic = json.load(f).get(shape.name, {}).get("dist_tc2_kernel")
-    roofline = {"kernel": "dist_tc2_kernel (N x N squared-L2 contraction, tcgen05 cta_group::2)", "bound": "tensor",
-                "achieved": achieved, "peak": tf32_peak, "unit": "TFLOP/s", "frac": achieved / tf32_peak,
-                "peak_source": f"{peaks['source']}: {which}/2 = TF32-equivalent dense ("
+            traffic_all = json.load(f).get(shape.name, {})
+    traffic = traffic_all.get("dist_tc2_kernel") if world == 1 else None
+    # frac = what the tensor pipe executes / what it can execute: issued fp16 MMA flops (3 per 256 x 256 x dp tile the
+    # schedule really computes) over the measured dense bf16 rate (kind::f16 MMAs run at the bf16 rate).  The
+    # algorithmic 2*rows*N*d figure of SURVEY 8(d) is reported beside it, against the TF32-equivalent (bf16 / 2) peak; it
+    # can exceed that peak because the symmetric schedule computes only the upper-triangle tiles.
+    roofline = {"kernel": "dist_tc2_kernel (N x N squared-L2 contraction, tcgen05 cta_group::2, fp16 hi/lo split)",
+                "bound": "tensor", "achieved": issued_tf, "peak": bf16_peak, "unit": "TFLOP/s",
+                "frac": issued_tf / bf16_peak,
+                "peak_source": f"{peaks['source']}: {which} ("
                                + ("burst: SM clocks stayed at max" if at_max else "sustained: SM clocks lowered under load")
                                + ")",
-                "frac_note": "achieved counts the 2*rows*N*d flops of the full matrix (SURVEY 8d); with one rank the "
-                             "symmetric schedule computes only the upper-triangle tiles and mirrors the rest, so frac can "
-                             "exceed 1 -- the tensor-pipe fraction is issued_frac_of_bf16_peak",
+                "achieved_is": "issued fp16 MMA flops = 3 * tiles * 2*256*256*dp per launch / live CUDA-event time",
                 "traffic": traffic, "traffic_source": "profiles/traffic.json (ncu --set full, dram read+write per launch)",
-                "ms": dist_ms, "algorithmic_flops_per_launch": flops,
-                "issued_fp16_tflops": issued_tf, "issued_frac_of_bf16_peak": issued_tf / bf16_peak,
-                "tiles_256x256": tiles, "symmetric_schedule": bool(world == 1 and eng.symmetric)}
+                "ms": dist_ms, "tiles_256x256": tiles, "symmetric_schedule": bool(sym_sched),
+                "algorithmic_flops_per_launch": flops, "algorithmic_tflops": achieved,
+                "algorithmic_frac_of_tf32_equiv_peak": achieved / tf32_peak}
     hbm = {}
     # algorithmic bytes: selection reads the chunk minima (+ ~K candidate lines per row); the fused
     # Jaccard/score kernel streams its queries' rows of D once and writes nothing q x g
@@ -356,12 +414,11 @@ def main():
     # ---- CPU baseline (rank 0, N == 1 only): oracle port on a bounded sample
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        sample = cpu_sample_shape(synth, shape, args.cpu_scale)
-        dt, pairs, m = run_cpu_oracle(synth, sample)
+        scale = cpu_scale_for(args, shape)
+        sample = cpu_sample_shape(synth, shape, scale)
+        dt, pairs, m, kind = run_cpu_eval(synth, sample)
         cpu = {"value": pairs / dt, "unit": UNIT, "cores": os.cpu_count(), "threads_blas": cpu_threads(),
-               "kind": "port", "seconds": dt,
-               "sample": f"{sample.q}x{sample.g}x{sample.d} (1/{args.cpu_scale} of {shape.name} in q and g), "
-                         f"k1={sample.k1} k2={sample.k2}; one full re-ranked eval by oracle/reid_oracle.py"}
+               "kind": kind, "seconds": dt, "sample": cpu_sample_desc(sample, shape, scale, kind)}
 
     if rank == 0:
         line = {

@@ -40,7 +40,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--steps", type=int, default=200)
     args = ap.parse_args()
-    import losses
+    import reid_losses as losses
     import importlib
     lib = importlib.import_module("multimodal-reid_b200._lib").load()
     torch.backends.cuda.matmul.allow_tf32 = False

@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define REID_ABI_VERSION 1
+#define REID_ABI_VERSION 2
 
 #define REID_OK 0
 #define REID_ERR_CUDA (-1)
@@ -48,6 +48,9 @@ extern "C" {
 typedef uint16_t reid_half; /* IEEE binary16 bit pattern */
 
 REID_API int reid_abi_version(void);
+/* hash of the sources this binary was built from (multimodal-reid_b200/build.py source_hash); the loader refuses a
+ * library whose hash differs from the sources beside it */
+REID_API const char* reid_source_hash(void);
 REID_API const char* reid_last_error(void);
 /* 0 if `device` is an sm_100 part this library can run on, REID_ERR_UNSUPPORTED otherwise. */
 REID_API int reid_device_check(int device);
@@ -90,24 +93,24 @@ REID_API int reid_prepare_rows(const float* X, int n, int d, int64_t ld_x, int n
 /* When A and B of reid_dist are the same rows (same pointers, pitches, norms; m == n) the contraction computes only
  * the tiles touching the upper triangle and stores every off-diagonal tile a second time transposed (with the
  * mirrored rows' maxima and chunk minima): outside its 256-wide diagonal blocks the N x N matrix of re-ranking is an
- * exact mirror, at half the tensor-core work.  Process-global switch: 1 (default) as described; 0 = every tile computed
- * (what a rank owning a strided subset of the rows runs anyway); 2 = upper-only: mirrored tiles are NOT stored (their row
- * maxima and chunk minima still are) -- half the output stream; entries left of a row's 256-wide diagonal block are then
- * undefined and consumers must read D[col, row] instead (the _tri entry points do). */
-REID_API int reid_set_symmetric_contraction(int on);
+ * exact mirror, at half the tensor-core work.  `sym_mode` (an argument of every call -- no process-wide state, so two
+ * engines / streams / threads cannot disturb each other): 1 as described; 0 = every tile computed; 2 = upper-only:
+ * mirrored tiles are NOT stored (their row maxima and chunk minima still are) -- half the output stream; entries left of
+ * a row's 256-wide diagonal block are then undefined and consumers must read D[col, row] instead (the _tri entry points
+ * do).  Modes 1 and 2 apply when both operands are the same rows; a rectangle of different row sets always runs in full. */
 /* Diagnostics: with the environment variable REID_TC_DBG & 64 set, block 0 of reid_dist's kernel records
  * {clock64, globaltimer ns} at entry and exit; this copies the four values to HOST memory (synchronises). */
 REID_API int reid_dist_clock_probe(int64_t* host_out4);
 REID_API int reid_dist(const reid_half* Ahi, const reid_half* Alo, int64_t lda, const float* ra,
               const uint32_t* a_amax, int m, const reid_half* Bhi, const reid_half* Blo, int64_t ldb,
               const float* rb, const uint32_t* b_amax, int n, int dpad, int metric, float* out,
-              int64_t ld_out, int32_t* rowmax_key, float* chunk_min, void* stream);
+              int64_t ld_out, int32_t* rowmax_key, float* chunk_min, int sym_mode, void* stream);
 /* One block of a larger symmetric distance matrix, for callers that compute it chunk by chunk (the streamed evaluator:
  * the features of evaluate.py:110 are still arriving over PCIe while the first blocks are contracted).  Block origins
  * must be multiples of 256 rows / columns of the enclosing matrix; out, rowmax_key and chunk_min point at the block's
  * origin inside the enclosing arrays; cm_pitch is the enclosing chunk-minimum row pitch (reid_chunk_pitch(N)).
  *   mode 0  plain rectangle
- *   mode 2  square diagonal block (same rows on both sides), upper-only form as reid_set_symmetric_contraction(2)
+ *   mode 2  square diagonal block (same rows on both sides), upper-only form as sym_mode 2
  *   mode 3  rectangle strictly above the diagonal: stored as is; its mirror image's row maxima / chunk minima go to
  *           rowmax_key_cols[block column] and chunk_min_cols[block column * cm_pitch + block row / 32]
  * The blocks of one matrix give bit for bit the matrix a single reid_dist call gives. */
@@ -136,7 +139,7 @@ REID_API int reid_topk_rows(const float* D, int rows, int cols, int64_t ld, cons
 /* same result, reading only the chunks whose recorded minimum can hold a neighbour (~K of cols/32) */
 REID_API int reid_topk_rows_hinted(const float* D, int rows, int cols, int64_t ld, const int32_t* rowmax_key,
                           const float* chunk_min, int K, int32_t* nbr, float* nbr_val, int cap, void* stream);
-/* same for the square symmetric matrix of reid_dist's upper-only mode (reid_set_symmetric_contraction(2)): entries left of
+/* same for the square symmetric matrix of reid_dist's upper-only mode (sym_mode 2): entries left of
  * a row's 256-wide diagonal block are read from their mirror image D[col, row] */
 REID_API int reid_topk_rows_hinted_tri(const float* D, int rows, int cols, int64_t ld, const int32_t* rowmax_key,
                               const float* chunk_min, int K, int32_t* nbr, float* nbr_val, int cap, int upper_only,

@@ -12,6 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libreid_b200.so")
 HEADER_PATH = os.path.join(_HERE, "..", "include", "reid_b200.h")
 
+ABI_VERSION = 2          # bumped whenever a signature in include/reid_b200.h changes
 _p = C.c_void_p
 _i = C.c_int
 _l = C.c_int64
@@ -59,19 +60,24 @@ def load(build_if_missing: bool = True) -> C.CDLL:
     global _lib
     if _lib is not None:
         return _lib
-    if not os.path.exists(LIB_PATH):
+    from . import build as _build
+    if _build.stale():
+        # missing, or built from other sources than the ones beside it (hash baked in at build time): rebuild, never
+        # run an old binary silently
         if not build_if_missing:
-            raise ReidError(f"{LIB_PATH} is missing (run `python multimodal-reid_b200/build.py`); "
+            raise ReidError(f"{LIB_PATH} is missing or stale (run `python multimodal-reid_b200/build.py`); "
                             "there is no CPU fallback")
-        from . import build as _build
         _build.build()
     lib = C.CDLL(LIB_PATH)
     for name, (restype, args) in _parse_header().items():
         fn = getattr(lib, name)
         fn.argtypes = args
         fn.restype = restype
-    if lib.reid_abi_version() != 1:
+    if lib.reid_abi_version() != ABI_VERSION:
         raise ReidError("libreid_b200.so ABI version mismatch; rebuild")
+    if lib.reid_source_hash().decode() != _build.source_hash():
+        raise ReidError("libreid_b200.so was built from different sources than the ones beside it; rebuild "
+                        "(python multimodal-reid_b200/build.py --force)")
     _lib = lib
     return lib
 

@@ -9,7 +9,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libreid_b200.so")
-SOURCES = ["api.cu", "prep.cu", "dist_simt.cu", "dist_tcgen05.cu", "dist_tc2.cu", "select.cu", "krecip.cu", "qe.cu",
+SOURCES = ["api.cu", "prep.cu", "dist_simt.cu", "dist_tc2.cu", "select.cu", "krecip.cu", "qe.cu",
            "jaccard.cu", "jaccard_score.cu", "jaccard_sparse.cu", "rank.cu", "score.cu", "train.cu", "stream_score.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "--threads", "0"]
@@ -22,13 +22,31 @@ def _nvcc() -> str:
     raise RuntimeError("nvcc not found; reid_b200 has no prebuilt or CPU fallback")
 
 
+def source_hash() -> str:
+    """sha256 over the CUDA sources and the public header; baked into the library (reid_source_hash) so that a stale
+    .so is recognised by content, not by file times (a snapshot copy does not keep them)."""
+    import hashlib
+    h = hashlib.sha256()
+    files = sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".h")))
+    files.append(os.path.join(HERE, "..", "include", "reid_b200.h"))
+    for f in files:
+        h.update(os.path.basename(f).encode())
+        with open(f, "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()[:32]
+
+
+def built_hash() -> str | None:
+    """Source hash recorded beside the library by the build that produced it."""
+    try:
+        with open(LIB + ".srchash") as f:
+            return f.read().strip()
+    except OSError:
+        return None
+
+
 def stale() -> bool:
-    if not os.path.exists(LIB):
-        return True
-    t = os.path.getmtime(LIB)
-    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)]
-    deps.append(os.path.join(HERE, "..", "include", "reid_b200.h"))
-    return any(os.path.getmtime(d) > t for d in deps)
+    return not os.path.exists(LIB) or built_hash() != source_hash()
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
@@ -37,12 +55,15 @@ def build(force: bool = False, verbose: bool = False) -> str:
     objdir = os.path.join(HERE, "build")
     os.makedirs(objdir, exist_ok=True)
     nvcc = _nvcc()
+    srchash = source_hash()
     objs = []
     procs = []
     for src in SOURCES:
         obj = os.path.join(objdir, src.replace(".cu", ".o"))
         objs.append(obj)
         cmd = [nvcc, *NVCC_FLAGS, *os.environ.get("REID_NVCC_EXTRA", "").split(), "-c", os.path.join(CSRC, src), "-o", obj]
+        if src == "api.cu":
+            cmd.insert(1, f'-DREID_SRC_HASH="{srchash}"')
         if verbose:
             cmd.insert(1, "-Xptxas")
             cmd.insert(2, "-v")
@@ -58,6 +79,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     cmd = [nvcc, "-shared", "-o", LIB, *objs, "-gencode", "arch=compute_100a,code=sm_100a",
            "-Xcompiler", "-fPIC", "-cudart", "static", "-ldl"]
     subprocess.check_call(cmd)
+    with open(LIB + ".srchash", "w") as f:
+        f.write(srchash)
     return LIB
 
 

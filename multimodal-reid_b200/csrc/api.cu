@@ -106,6 +106,10 @@ using namespace reid;
 extern "C" {
 
 int reid_abi_version(void) { return REID_ABI_VERSION; }
+#ifndef REID_SRC_HASH
+#define REID_SRC_HASH "unknown"
+#endif
+const char* reid_source_hash(void) { return REID_SRC_HASH; }
 const char* reid_last_error(void) { return g_err; }
 
 int reid_device_check(int device) {
@@ -153,20 +157,16 @@ int reid_dist_clock_probe(int64_t* host_out4) {
   return dist_clock_probe(reinterpret_cast<long long*>(host_out4));
 }
 
-int reid_set_symmetric_contraction(int on) {
-  set_symmetric_contraction(on);
-  return REID_OK;
-}
 
 int reid_dist(const reid_half* Ahi, const reid_half* Alo, int64_t lda, const float* ra, const uint32_t* a_amax,
               int m, const reid_half* Bhi, const reid_half* Blo, int64_t ldb, const float* rb,
               const uint32_t* b_amax, int n, int dpad, int metric, float* out, int64_t ld_out,
-              int32_t* rowmax_key, float* chunk_min, void* stream) {
+              int32_t* rowmax_key, float* chunk_min, int sym_mode, void* stream) {
   ENTER();
   REID_REQUIRE(metric == 0 || metric == 1, "dist: unknown metric %d", metric);
   REID_REQUIRE(m >= 0 && n >= 0 && dpad > 0 && ld_out >= n && lda >= dpad && ldb >= dpad, "dist: bad shape");
   return launch_dist_tc(HC(Ahi), HC(Alo), lda, ra, a_amax, m, HC(Bhi), HC(Blo), ldb, rb, b_amax, n, dpad, metric,
-                        out, ld_out, rowmax_key, chunk_min, S(stream));
+                        out, ld_out, rowmax_key, chunk_min, sym_mode, S(stream));
 }
 
 int reid_dist_block(const reid_half* Ahi, const reid_half* Alo, int64_t lda, const float* ra, const uint32_t* a_amax,

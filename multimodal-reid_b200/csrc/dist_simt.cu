@@ -1,5 +1,5 @@
 // Distance contraction, CUDA-core engine (fp32 FMA on the float32 rows).  Bring-up and
-// cross-check engine for the tcgen05 path in dist_tcgen05.cu; same fused epilogues:
+// cross-check engine for the tcgen05 path in dist_tc2.cu; same fused epilogues:
 //   metric 0: D = (|a|^2 + |b|^2) - 2 a.b          evaluate.py:7-13, reranking.py:36-41
 //   metric 1: arccos(clip(a.b * (1/(|a||b|))))     evaluate.py:16-26
 // plus an optional per-row running maximum (reranking.py:46 needs max_k D[k,i]).

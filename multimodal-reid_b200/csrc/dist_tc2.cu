@@ -1,7 +1,7 @@
 // Distance contraction on CTA pairs (tcgen05.mma.cta_group::2) -- K1/K2/K3: evaluate.py:7-26, reranking.py:36-41.
 //
-// Same arithmetic as dist_tcgen05.cu (float16 hi/lo split operands, hi.hi + hi.lo + lo.hi accumulated in float32 in
-// TMEM, fused distance epilogue) but one 256 x 256 output tile per PAIR of SMs.  Why: the single-CTA kernel streams
+// float16 hi/lo split operands, hi.hi + hi.lo + lo.hi accumulated in float32 in TMEM, fused distance epilogue, one
+// 256 x 256 output tile per PAIR of SMs.  Why pairs: the single-CTA predecessor (round 1, retired) streamed
 // 96 KB of operands per 64-wide K block into every SM (768 KB per 128 x 256 tile) and ncu / the store ablation showed
 // it pinned at the L2 -> SM throughput cap (~12 TB/s) -- the tensor pipe waits for operands, and the 1.6 GB output
 // stream competes for the same L2 ports.  A CTA pair shares the B operand: each CTA loads its own 128 rows of A and
@@ -545,10 +545,6 @@ static int make_map(CUtensorMap* map, CUtensorMapDataType dt, int esize, const v
 
 }  // namespace tc2
 
-static int g_symmetric_enabled = 1;     // 0 off, 1 upper triangle computed + mirrored, 2 upper triangle only
-void set_symmetric_contraction(int on) { g_symmetric_enabled = on < 0 ? 0 : (on > 2 ? 1 : on); }
-int symmetric_contraction_enabled() { return g_symmetric_enabled; }
-
 int dist_clock_probe(long long* host_out4) {
   unsigned long long v[4];
   REID_CUDA(cudaMemcpyFromSymbol(v, tc2::g_probe, sizeof(v)));
@@ -559,14 +555,17 @@ int dist_clock_probe(long long* host_out4) {
 int launch_dist_tc(const __half* Ahi, const __half* Alo, long long lda, const float* ra, const uint32_t* a_amax,
                    int m, const __half* Bhi, const __half* Blo, long long ldb, const float* rb,
                    const uint32_t* b_amax, int n, int dp, int metric, float* out, long long ld_out,
-                   int* rowmax_key, float* chunk_min, cudaStream_t s) {
+                   int* rowmax_key, float* chunk_min, int sym_mode, cudaStream_t s) {
+  // sym_mode (per call, no process state): 0 every tile; 1 upper triangle computed + mirrored stores; 2 upper triangle
+  // only.  1 and 2 apply when both operands are the same rows; a rectangle of two different row sets runs in full.
+  REID_REQUIRE(sym_mode >= 0 && sym_mode <= 2, "dist_tc: sym_mode %d outside 0..2", sym_mode);
   return launch_dist_tc_block(Ahi, Alo, lda, ra, a_amax, m, Bhi, Blo, ldb, rb, b_amax, n, dp, metric, out, ld_out,
-                              rowmax_key, chunk_min, 0, -1, rowmax_key, chunk_min, s);
+                              rowmax_key, chunk_min, 0, -1 - sym_mode, rowmax_key, chunk_min, s);
 }
 
 // One block of a larger distance matrix (the streamed evaluator computes D chunk by chunk while the features are still
-// arriving).  mode -1: as launch_dist_tc (symmetric schedule when both operands are the same rows, per
-// reid_set_symmetric_contraction); 0: plain rectangle; 2: square diagonal block, upper-only form; 3: rectangle that lies
+// arriving).  mode -1 - sym (sym = 0, 1, 2): launch_dist_tc's whole-matrix call (symmetric schedule `sym` when both
+// operands are the same rows); 0: plain rectangle; 2: square diagonal block, upper-only form; 3: rectangle that lies
 // strictly above the diagonal of the enclosing symmetric matrix -- stored as is, and every tile also contributes the
 // row maxima / chunk minima of its mirror image through rowmax_key_m / chunk_min_m (indexed by the block's columns).
 // cm_pitch: row pitch of the chunk-minimum arrays (0: chunk_pitch(n)); all block origins must be multiples of 256.
@@ -577,11 +576,6 @@ int launch_dist_tc_block(const __half* Ahi, const __half* Alo, long long lda, co
                          float* chunk_min_m, cudaStream_t s) {
   using namespace tc2;
   if (m == 0 || n == 0) return REID_OK;
-  static const int pair = getenv("REID_TC_PAIR") ? atoi(getenv("REID_TC_PAIR")) : 1;
-  REID_REQUIRE(pair || (mode == -1 && cm_pitch == 0), "dist_tc: block modes need the CTA-pair kernel (REID_TC_PAIR=0 is set)");
-  if (!pair)
-    return launch_dist_tc1(Ahi, Alo, lda, ra, a_amax, m, Bhi, Blo, ldb, rb, b_amax, n, dp, metric, out, ld_out,
-                           rowmax_key, chunk_min, s);
   REID_REQUIRE(dp % BK == 0, "dist_tc: padded width %d must be a multiple of %d", dp, BK);
   REID_REQUIRE(lda % 8 == 0 && ldb % 8 == 0 && ld_out % 4 == 0,
                "dist_tc: row pitches must keep rows 16-byte aligned (lda=%lld ldb=%lld ld_out=%lld)", lda, ldb,
@@ -599,9 +593,9 @@ int launch_dist_tc_block(const __half* Ahi, const __half* Alo, long long lda, co
   REID_CUDA(cudaFuncSetAttribute(dist_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
   // same rows on both sides and a square output: compute the upper triangle only and mirror it
   const bool same = Ahi == Bhi && Alo == Blo && lda == ldb && ra == rb && a_amax == b_amax && m == n;
-  REID_REQUIRE(mode >= -1 && mode <= 3 && mode != 1, "dist_tc: unknown block mode %d", mode);
+  REID_REQUIRE(mode >= -3 && mode <= 3 && mode != 1, "dist_tc: unknown block mode %d", mode);
   REID_REQUIRE(mode != 2 || same, "dist_tc: the upper-only form needs the same rows on both sides");
-  const int symmetric = mode >= 0 ? mode : ((same && g_symmetric_enabled) ? g_symmetric_enabled : 0);
+  const int symmetric = mode >= 0 ? mode : (same ? -1 - mode : 0);
   const int pitch = cm_pitch > 0 ? cm_pitch : chunk_pitch(n);
   REID_REQUIRE(pitch % 4 == 0 && ((uintptr_t)chunk_min & 15) == 0, "dist_tc: chunk minima must be 16-byte aligned");
   const int mblocks = cdiv(m, BM), nblocks = cdiv(n, BN);

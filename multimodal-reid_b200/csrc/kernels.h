@@ -33,13 +33,7 @@ int launch_dist_tc_block(const __half* Ahi, const __half* Alo, long long lda, co
 int launch_dist_tc(const __half* Ahi, const __half* Alo, long long lda, const float* ra, const uint32_t* a_amax,
                    int m, const __half* Bhi, const __half* Blo, long long ldb, const float* rb,
                    const uint32_t* b_amax, int n, int dp, int metric, float* out, long long ld_out,
-                   int* rowmax_key, float* chunk_min, cudaStream_t s);
-void set_symmetric_contraction(int on);
-int symmetric_contraction_enabled();
-int launch_dist_tc1(const __half* Ahi, const __half* Alo, long long lda, const float* ra, const uint32_t* a_amax,
-                    int m, const __half* Bhi, const __half* Blo, long long ldb, const float* rb,
-                    const uint32_t* b_amax, int n, int dp, int metric, float* out, long long ld_out,
-                    int* rowmax_key, float* chunk_min, cudaStream_t s);
+                   int* rowmax_key, float* chunk_min, int sym_mode, cudaStream_t s);
 int dist_clock_probe(long long* host_out4);
 int launch_select_topk_hinted(const float* D, int rows, int cols, long long ld, const int* rowmax_key,
                               const float* chunk_min, int K, int* nbr, float* nbr_val, int cap_override,

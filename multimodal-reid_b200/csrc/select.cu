@@ -227,7 +227,7 @@ select_topk_kernel(const float* __restrict__ D, int rows, int cols, long long ld
 }
 
 // ---------------------------------------------------------------------------------------------
-// Top-K with chunk minima.  The tensor-core epilogue (dist_tcgen05.cu) records the minimum of every
+// Top-K with chunk minima.  The tensor-core epilogue (dist_tc2.cu) records the minimum of every
 // 32-column chunk of D.  K chunks whose minimum is <= tau hold K elements <= tau, so the K-th smallest of
 // ANY K-or-more chunk minima bounds the K-th smallest element.  One warp per row:
 //   pass 1  every lane streams its share of the row's chunk minima (coalesced, unrolled) and keeps its S
@@ -432,7 +432,7 @@ int launch_select_topk_hinted(const float* D, int rows, int cols, long long ld, 
 }
 
 // ---------------------------------------------------------------------------------------------
-// Scatter form of the hinted selection for the upper-only symmetric matrix (reid_set_symmetric_contraction(2)): only the
+// Scatter form of the hinted selection for the upper-only symmetric matrix (reid_dist sym_mode 2): only the
 // tiles on and above the 256-wide diagonal blocks of D are stored.  Reading the missing left part of a row through
 // its mirror image is a sector gather (32 B fetched per 4 B used); instead every stored element is offered to BOTH
 // rows it belongs to:

@@ -212,7 +212,7 @@ class Engine:
         # Jaccard stage: packed per-query overlap records (jaccard_sparse.cu) with up to `sparse_cap` touched probes;
         # denser queries fall back to the dense shared-memory row (jaccard_score.cu).  sparse_cap = 0: dense only.
         self.sparse_cap = 8192
-        # N x N contraction of one rank owning every row: upper-triangle tiles only, mirrored (dist_tcgen05.cu).
+        # N x N contraction of one rank owning every row: upper-triangle tiles only, mirrored (dist_tc2.cu).
         # Ranks of a multi-GPU job own strided row subsets and always run the full schedule.
         self.symmetric = True
         self.upper_only = True      # ... and, when nobody needs the full matrix, without storing the mirrored half
@@ -407,10 +407,10 @@ class Engine:
         else:
             if want_chunk_min:
                 cmin = self._empty((m, self.lib.reid_chunk_pitch(n)), torch.float32)[:, : (n + 31) // 32]
-            self.lib.reid_set_symmetric_contraction((2 if upper_only else 1) if self.symmetric else 0)
+            sym_mode = (2 if upper_only else 1) if self.symmetric else 0      # per call: no process-wide kernel state
             _lib.call("reid_dist", _ptr(A.hi), _ptr(A.lo), A.hi.stride(0), _ptr(ra), _ptr(A.amax), m, _ptr(B.hi),
                       _ptr(B.lo), B.hi.stride(0), _ptr(rb), _ptr(B.amax), n, A.dp, metric, _ptr(D), ld, _ptr(key),
-                      _ptr(cmin), _stream())
+                      _ptr(cmin), sym_mode, _stream())
         return (D, key, cmin) if want_chunk_min else (D, key)
 
     def rowmax(self, D: torch.Tensor, cols: int) -> torch.Tensor:

@@ -75,7 +75,7 @@ def test_losses_and_retrieval_surface():
 
     import pytest
     import torch
-    import losses
+    import reid_losses as losses
     for n in ("euclidean_dist", "hard_example_mining", "WeightedRegularizedTriplet", "WeightedRegularizedTripletXBM"):
         assert hasattr(losses, n)
     assert losses.WeightedRegularizedTriplet(0.3).margin == 0.3 and losses.WeightedRegularizedTriplet().margin is None
@@ -97,3 +97,27 @@ def test_column_blocks_host_logic():
         b = cb(g, c, k)
         assert b[0][0] == 0 and b[-1][1] == g and all(x[1] == y[0] for x, y in zip(b, b[1:]))
         assert all(hi - lo >= min(k, g) for lo, hi in b)
+
+
+def test_reference_script_imports_resolve_with_repo_first(tmp_path):
+    """The five reference scripts import `R1_mAP_eval` from `evaluate` and five names from `losses`
+    (prompt_learning.py:19-21, ..._hard_sharing.py:19-21).  With this repository FIRST on sys.path, `evaluate` /
+    `reranking` must resolve to the drop-in shims and `losses` must still resolve to the reference's own module (the
+    training-side ops live in `reid_losses`, bound per symbol as INTEGRATION.md 2b shows) -- a root `losses.py` that
+    exported only the distance ops would break every training script at import time."""
+    import subprocess
+    import sys
+    ref = tmp_path / "ref"
+    ref.mkdir()
+    (ref / "losses.py").write_text("class SupConLoss: pass\nclass CrossEntropyLabelSmooth: pass\n"
+                                   "class WeightedRegularizedTriplet: pass\nclass WeightedRegularizedTripletXBM: pass\n")
+    code = ("import evaluate, reranking, losses, os;"
+            "from evaluate import R1_mAP_eval;"
+            "from losses import SupConLoss, WeightedRegularizedTriplet, CrossEntropyLabelSmooth, WeightedRegularizedTripletXBM;"
+            f"assert os.path.dirname(os.path.abspath(evaluate.__file__)) == {str(ROOT)!r};"
+            f"assert os.path.dirname(os.path.abspath(reranking.__file__)) == {str(ROOT)!r};"
+            f"assert os.path.dirname(os.path.abspath(losses.__file__)) == {str(ref)!r};"
+            "import reid_losses; assert hasattr(reid_losses, 'WeightedRegularizedTriplet')")
+    env = dict(os.environ, PYTHONPATH=f"{ROOT}{os.pathsep}{ref}")
+    r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]

@@ -27,7 +27,7 @@ def test_reference_arm_line():
               "config", "cpu_baseline", "e2e"):
         assert k in j, k
     assert j["vs_baseline"] is None and j["config"]["workload"] == "tiny"
-    assert j["cpu_baseline"]["kind"] == "port" and j["cpu_baseline"]["cores"] >= 1 and j["cpu_baseline"]["sample"]
+    assert j["cpu_baseline"]["kind"] in ("reference", "port") and j["cpu_baseline"]["cores"] >= 1 and j["cpu_baseline"]["sample"]
     assert j["cpu_baseline"]["value"] == j["value"] > 0
     assert j["e2e"] == {"value": j["value"], "unit": j["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
 

@@ -21,7 +21,7 @@ IDS = [os.path.basename(p)[:-4] for p in GOLDEN]
 def L():
     if not torch.cuda.is_available():
         pytest.skip("no CUDA device")
-    import losses
+    import reid_losses as losses
     return losses
 
 
