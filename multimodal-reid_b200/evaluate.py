@@ -46,6 +46,10 @@ def eval_func_device(dist: torch.Tensor, g: int, q_pids, g_pids, q_camids, g_cam
     """dist: device tensor [q_local, >= g] float32 (row pitch free).  Returns (cmc, mAP) like
     eval_func; only cmc[max_rank] and mAP leave the device."""
     eng = eng or _engine.default_engine()
+    if dist.dtype != torch.float32 or dist.stride(1) != 1 or dist.stride(0) % 4 != 0:
+        buf = torch.empty((dist.shape[0], _engine.Engine.pitch(g)), dtype=torch.float32, device=dist.device)
+        buf[:, :g].copy_(dist[:, :g])
+        dist = buf
     if g < max_rank:
         max_rank = g
         print("Note: number of gallery samples is quite small, got {}".format(g))
@@ -68,10 +72,11 @@ def eval_func(distmat, q_pids, g_pids, q_camids, g_camids, max_rank=50):
     mine = slice(cm.rank, num_q, cm.world)          # one process per GPU: every rank scores its share of the queries
     if cm.world > 1:
         d = d[mine]
-    d = d.to(dev, non_blocking=True)
-    if d.dtype != torch.float32:
-        d = d.float()
-    d = d.contiguous()
+    # the scoring kernel streams rows with 16-byte loads: rows are placed at a pitch that is a multiple of 4 floats (one
+    # copy either way -- the matrix has to reach the device)
+    buf = torch.empty((d.shape[0], _engine.Engine.pitch(num_g)), dtype=torch.float32, device=dev)
+    buf[:, :num_g].copy_(d, non_blocking=True)
+    d = buf
     return eval_func_device(d, num_g, _ids(q_pids, dev)[mine].contiguous(), _ids(g_pids, dev),
                             _ids(q_camids, dev)[mine].contiguous(), _ids(g_camids, dev), max_rank, eng, q_total=num_q)
 

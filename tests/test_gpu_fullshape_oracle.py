@@ -43,7 +43,7 @@ def _shape(synth, name, scale, k1, k2):
     return dataclasses.replace(sh, k1=k1, k2=k2)
 
 
-def _list_report(got, want, K, what):
+def _list_report(got, want, K, what, quanta=True):
     """Top-K lists of the re-ranked rows: positions that differ, split by the gap of the keys involved."""
     ig = np.argsort(got, axis=1, kind="stable")[:, :K]
     iw = np.argsort(want, axis=1, kind="stable")[:, :K]
@@ -53,28 +53,78 @@ def _list_report(got, want, K, what):
     n_out = int((gap > TIE_TOL).sum())
     print(f"[parity] {what}: top-{K} positions {ig.size}, differing {int(neq.sum())}, outside 1e-6 ties {n_out} "
           f"({n_out / ig.size:.2e}), largest key gap {gap.max() if gap.size else 0.0:.3e}")
-    assert np.all(gap <= 4 * FP16_QUANTUM), f"{what}: lists differ outside 4 float16 quanta (gap {gap.max():.3e})"
+    if quanta:
+        assert np.all(gap <= 4 * FP16_QUANTUM), f"{what}: lists differ outside 4 float16 quanta (gap {gap.max():.3e})"
     assert n_out <= 2e-3 * ig.size, f"{what}: {n_out} of {ig.size} list positions differ outside 1e-6 ties"
     return n_out
 
 
+def _noise_report(got, want, what, max_frac):
+    """Own contraction on both sides (tcgen05 split-fp16 here, BLAS sgemm in the oracle / reference): the two N x N
+    matrices agree to ~1e-6, which reorders neighbours tied that closely (north_star allows exactly that).  A flipped
+    neighbour at the k1 boundary changes a k-reciprocal set and with it every Jaccard term of the rows involved, by more
+    than a float16 quantum -- the reference fed two such matrices differs from ITSELF the same way (SURVEY 8a note 4).
+    Entries outside 1e-4 relative are therefore counted in two classes and bounded as a fraction; the exactness claim
+    is test (1) of test_full_shape_vs_oracle (same matrix on both sides: bit for bit)."""
+    from parity import classify_distances
+    n_bad, n_flip, mx = classify_distances(got, want)
+    frac = (n_bad + n_flip) / want.size
+    print(f"[parity] {what}: {want.size} distances; within 1e-4 relative: all but {n_bad + n_flip} ({frac:.2e}) = "
+          f"{n_flip} float16-boundary flips + {n_bad} tie-induced set changes; max rel of the rest {mx:.2e}")
+    assert frac <= max_frac, f"{what}: {n_bad + n_flip} of {want.size} entries outside 1e-4 relative"
+
+
 @pytest.mark.parametrize("name,scale,k1,k2", CASES, ids=[f"{n}-1/{s}-k{a}-{b}" for n, s, a, b in CASES])
-def test_full_shape_vs_oracle(api, synth, oracle, name, scale, k1, k2):
+def test_full_shape_vs_oracle(api, eng, engine_mod, synth, oracle, name, scale, k1, k2):
     """reranking.py:29-100 + evaluate.py:29-88 + evaluate.py:110-134 at the BASELINE shapes (configs[0..3])."""
     evaluate, reranking = api
     sh = _shape(synth, name, scale, k1, k2)
+    N = sh.q + sh.g
     qf, gf, qp, gp, qc, gc = synth.make(sh, 0)
     raw = torch.cat([qf, gf])
     f = torch.nn.functional.normalize(raw, dim=1, p=2)
-    want = oracle.re_ranking(f[: sh.q].numpy(), f[sh.q:].numpy(), k1, k2, sh.lam)
-    c_o, m_o = oracle.cmc_map(want, qp.numpy(), gp.numpy(), qc.numpy(), gc.numpy())
-    # (1) the drop-in re_ranking: q x g float32 matrix
+    ids = (qp.numpy(), gp.numpy(), qc.numpy(), gc.numpy())
+    # the product path: drop-in re_ranking -> q x g float32 matrix (upper-only contraction, scatter selection, ...)
     got = reranking.re_ranking(f[: sh.q], f[sh.q:], k1, k2, sh.lam)
-    assert got.shape == want.shape and got.dtype == np.float32
-    n_flip, mx = assert_distances_close(got, want, max_flip_frac=5e-5, what=f"{sh.name} final")
-    print(f"[parity] {sh.name} k1={k1} k2={k2}: {want.size} distances, max rel (non-flip) {mx:.2e}, fp16 flips {n_flip}")
-    _list_report(got, want, 10, f"{sh.name} k1={k1} k2={k2}")
-    # (2) eval_func on the GPU's own matrix, and the fused evaluator from raw features
+    assert got.shape == (sh.q, sh.g) and got.dtype == np.float32
+
+    # (1) SAME N x N matrix on both sides: the oracle is fed the GPU's own matrix (mirrored form; the oracle reads
+    #     column i for probe i, reranking.py:46, hence the transpose) -> everything after the contraction must agree
+    #     BIT FOR BIT at the full shape: neighbour lists, sets, weights, expansion, Jaccard chain, lambda mix
+    feats = eng.prepare(f.to(eng.device), False)
+    D, _ = eng.dist(feats, feats, engine_mod.METRIC_SQEUCLIDEAN, want_rowmax=True)
+    Dh = D[:, :N].cpu().numpy()
+    del D
+    want_same = oracle.rerank_from_dist(np.ascontiguousarray(Dh.T), sh.q, k1, k2, sh.lam)
+    np.testing.assert_array_equal(got.view(np.uint32), want_same.view(np.uint32),
+                                  err_msg=f"{sh.name}: stages after the contraction are not bit-exact at the full shape")
+    print(f"[parity] {sh.name} k1={k1} k2={k2}: final q x g matrix == oracle(GPU's N x N matrix) bit for bit "
+          f"({got.size} entries)")
+
+    # (2) the contraction itself: every entry within 1e-4 relative of the oracle's (north_star), and the neighbour
+    #     lists of the two matrices equal except at distances tied within 1e-6 (measured gap printed)
+    Do = oracle.sq_euclidean(f.numpy(), f.numpy())
+    rel = np.abs(Dh - Do) / np.maximum(np.abs(Do), 1e-3)
+    np.fill_diagonal(rel, 0.0)                       # self-distances are ~1e-7 absolute on both sides
+    assert rel.max() <= 1e-4, f"{sh.name}: contraction off by {rel.max():.2e} relative"
+    K = max(k1 + 1, k2)
+    ig = torch.topk(torch.from_numpy(Dh).to(eng.device), K, dim=1, largest=False, sorted=True).indices.cpu().numpy()
+    i_or = torch.topk(torch.from_numpy(Do).to(eng.device), K, dim=1, largest=False, sorted=True).indices.cpu().numpy()
+    neq = ig != i_or
+    r = np.nonzero(neq)[0]
+    gap = np.abs(Do[r, ig[neq]].astype(np.float64) - Do[r, i_or[neq]].astype(np.float64))
+    print(f"[parity] {sh.name}: contraction max rel {rel.max():.2e}; top-{K} neighbour lists of {N} rows differ at "
+          f"{int(neq.sum())} positions ({int(np.unique(r).size)} rows), largest key gap there {gap.max() if gap.size else 0.0:.2e}")
+    assert gap.size == 0 or gap.max() <= 4e-6, f"{sh.name}: neighbour lists differ outside near-ties (gap {gap.max():.2e})"
+    del rel
+
+    # (3) end to end with its own contraction on each side: CMC / mAP within 1e-5, distances within 1e-4 relative except
+    #     the counted tie-induced entries, top-10 lists modulo ties
+    want = oracle.rerank_from_dist(Do, sh.q, k1, k2, sh.lam)           # = oracle.re_ranking(features)
+    del Do
+    c_o, m_o = oracle.cmc_map(want, *ids)
+    _noise_report(got, want, f"{sh.name} k1={k1} k2={k2} end to end", max_frac=5e-5)
+    _list_report(got, want, 10, f"{sh.name} k1={k1} k2={k2}", quanta=False)
     with contextlib.redirect_stdout(io.StringIO()):
         cmc, mAP = evaluate.eval_func(got, qp, gp, qc, gc)
         e = evaluate.R1_mAP_eval(sh.q, feat_norm=True, reranking=True, rerank_params=(k1, k2, sh.lam))
@@ -84,6 +134,7 @@ def test_full_shape_vs_oracle(api, synth, oracle, name, scale, k1, k2):
     for c, m, what in ((cmc, mAP, "eval_func"), (cmc_e, map_e, "R1_mAP_eval")):
         assert np.abs(c - c_o).max() <= METRIC_TOL, f"{what}: CMC off by {np.abs(c - c_o).max():.2e}"       # 1e-5 abs
         assert abs(m - m_o) <= METRIC_TOL, f"{what}: mAP {m} vs oracle {m_o}"                               # 1e-5 abs
+    print(f"[parity] {sh.name} k1={k1} k2={k2}: mAP {map_e:.6f} (oracle {m_o:.6f}), Rank-1 {cmc_e[0]:.6f} ({c_o[0]:.6f})")
 
 
 def test_cosine_duke_shape(api, synth, oracle):
