@@ -374,9 +374,12 @@ def main():
     # what the tensor pipe is actually asked to do: 3 fp16 MMAs (hi.hi + hi.lo + lo.hi) over the 256 x 256 tiles the
     # schedule computes -- the upper triangle only when one rank owns every row (symmetric mode)
     T_n, dp = -(-N // 256), -(-d // 64) * 64
-    sym_sched = eng.symmetric and (world == 1 or getattr(eng, "fabric", None) is not None)
-    tiles = eng.last_tiles if getattr(eng, "last_tiles", 0) else (
-        T_n * (T_n + 1) // 2 if sym_sched else -(-rows_local // 256) * T_n)
+    fabric_path = world > 1 and eng.last_path == "fabric"
+    sym_sched = eng.symmetric and (world == 1 or fabric_path)
+    tiles = eng.last_tiles if fabric_path else (T_n * (T_n + 1) // 2 if sym_sched else -(-rows_local // 256) * T_n)
+    if fabric_path:
+        flops = 2.0 * N * N * d / world       # this rank's share of the symmetric matrix (snake tile rows)
+        achieved = flops / (dist_ms * 1e-3) / 1e12
     issued = 3.0 * tiles * 2.0 * 256 * 256 * dp
     issued_tf = issued / (dist_ms * 1e-3) / 1e12
     traffic_all = {}
@@ -426,7 +429,11 @@ def main():
             "warmup": n_warm, "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": shape.name, "q": q, "g": g, "d": d, "k1": shape.k1, "k2": shape.k2,
-                       "lambda": shape.lam, "sharding": f"probe rows cyclic over {world} rank(s)",
+                       "lambda": shape.lam,
+                       "sharding": ("one rank" if world == 1 else
+                                    f"symmetric contraction sharded by snake tile rows over {world} ranks, exchanges through "
+                                    "peer memory (CUDA IPC over NVLink), flag barriers" if fabric_path else
+                                    f"probe rows cyclic over {world} ranks, NCCL all-gathers"),
                        "l2_flush_between_steps": True, "engine": args.engine},
             "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
             "stages_ms": stages, "hbm_stages": hbm, "mAP": float(mAP.item()), "rank1": float(cmc[0].item()),

@@ -172,6 +172,72 @@ REID_API int reid_krecip_V_tri(const int32_t* rfull, const int32_t* nfull, const
                       const int32_t* rowmax_key, int32_t* Vc, reid_half* Vv, int32_t* Vn, int upper_only,
                       void* stream);
 
+/* ---- Sharded symmetric path (no reference function: the reference is single-process) ----------------
+ * One process per GPU.  Wherever an entry point takes (row0, row_stride) / (q0, q_stride), a NEGATIVE stride selects
+ * "snake block" ownership: world = -stride ranks own the 256-row tile rows of the symmetric N x N matrix in
+ * boustrophedon order (tile rows 0..P-1 -> ranks 0..P-1, P..2P-1 -> ranks P-1..0, ...), rank = row0; local row l is row
+ * (l & 255) of the rank's (l >> 8)-th tile row.  A positive stride is the cyclic-row ownership of the NCCL path.
+ *
+ * reid_dist_sharded: reranking.py:36-41 for a rank's share -- the upper-triangle tiles (tile row <= tile column) of the
+ * tile rows it owns; `tiles` = (tile row, tile column) pairs in global tile coordinates (device, int32 x 2 x ntiles).
+ * out[nloc, ld_out]: the rank's rows, upper-only form.  rowmax_key[n] (global rows, reid_rowmax_init first): maximum
+ * over the part of every row this rank computed, direct or mirrored.  chunk_min[nloc, cm_pitch]: 32-column chunk minima
+ * of the stored rows (valid from the diagonal block on).  chunk_min_m[n, cmm_pitch]: chunk minima of the mirrored tiles,
+ * entry [i, 8 * t' + k] = minimum over rows 32k..32k+31 of the rank's t'-th tile row of column i (valid for the tile
+ * rows owned above row i's). */
+REID_API int reid_dist_sharded(const reid_half* hi, const reid_half* lo, int64_t ld, const float* sq, const uint32_t* amax,
+                      int n, int dpad, const int32_t* tiles, int ntiles, int world, float* out, int64_t ld_out,
+                      int nloc, int32_t* rowmax_key, float* chunk_min, int cm_pitch, float* chunk_min_m, int cmm_pitch,
+                      void* stream);
+/* K5 (reranking.py:46,48) over the sharded matrix, in scatter form.  tau: per row, the K-th smallest chunk minimum this
+ * rank holds (ordered key; 0xffffffff = fewer than K chunks).  dstar: stats = world slots of slot_ints ints, slot p =
+ * rank p's {rowmax_key[n], tau_key[n]}; writes the global row maxima (key_g[n], and key_l[local row] for owned rows), the raw-distance
+ * thresholds, zeroed counters and the 32-row group thresholds (cthr_key[reid_chunk_pitch(n)]).  push: candidates
+ * (raw D bits << 32 | column) of ALL rows from the rank's stored elements into pbuf[n, cap].  merge_local: per row, the
+ * K best (O key << 32 | column) records -> inbox of the row's owner: peers[owner] + inbox_off, laid out
+ * [world][nloc_max][K] uint64.  merge_final: per owned row, the world x K records sorted; the first K columns are the
+ * row's neighbour list, written to the table at peers[p] + nbr_off ([n, K] int32, global rows) of EVERY rank. */
+REID_API int reid_shard_tau(int n, int rank, int world, const float* cm_d, int pitch_d, const float* cm_m, int pitch_m,
+                   int K, int32_t* tau_key, void* stream);
+REID_API int reid_shard_dstar(int n, int rank, int world, const int32_t* stats, int64_t slot_ints, int32_t* key_g,
+                     int32_t* key_l, float* dstar, int32_t* count, int32_t* cthr_key, void* stream);
+REID_API int reid_shard_push(const float* D, int nloc, int rank, int world, int n, int64_t ld, const float* cm_d,
+                    int pitch_d, const float* dstar, const int32_t* cthr_key, int32_t* count, void* pbuf, int cap,
+                    void* stream);
+REID_API int reid_shard_merge_local(const float* D, int64_t ld, int n, int rank, int world, const float* cm_d, int pitch_d,
+                           const float* cm_m, int pitch_m, const int32_t* key_g, const float* dstar,
+                           const int32_t* count, const void* pbuf, int cap, int K, void* const* peers,
+                           int64_t inbox_off, int nloc_max, void* stream);
+REID_API int reid_shard_merge_final(int nloc, int rank, int world, int K, const void* inbox, int nloc_max,
+                           void* const* peers, int64_t nbr_off, float* nbr_val, void* stream);
+/* K6b for a rank's own rows of the sharded matrix: entries left of a row's diagonal block are read from the panel of the
+ * rank owning the mirror image (panels[world] device pointers, same pitch ld everywhere).  V rows are written at their
+ * GLOBAL row index (Vc / Vv [n, cap1], Vn [n]); D and rowmax_key are indexed by local row. */
+REID_API int reid_krecip_V_sharded(const int32_t* rfull, const int32_t* nfull, const int32_t* rhalf, const int32_t* nhalf,
+                          int rank, int world, int rows, int k1, const float* D, int64_t ld,
+                          const int32_t* rowmax_key, const void* const* panels, int32_t* Vc, reid_half* Vv, int32_t* Vn,
+                          void* stream);
+/* Peer-memory fabric: an arena per rank (cudaMalloc; export -> 64-byte CUDA IPC handle; open maps a peer's arena into
+ * this process with peer access enabled), identical layout on every rank.  `peers` is a DEVICE array of world arena base
+ * pointers (own arena at index rank).  barrier: a kernel on the stream -- stores `epoch` into flags[rank] of every peer
+ * (release.sys) and waits until all of its own flags reached it; flags = world uint32 at flags_off of every arena,
+ * zero-initialised; epochs grow by one per barrier.  bcast*: copy this rank's part of a replicated table into every
+ * peer's arena at the same offset: a byte range; the owned snake blocks of an [n, row_bytes] table; owned V rows in ELL
+ * form (count + used prefix); owned rows of a CSR pool (cnt[n], int32 columns / float16 values at element offsets off[]). */
+REID_API int reid_fabric_alloc(int64_t bytes, void** out);
+REID_API int reid_fabric_free(void* p);
+REID_API int reid_fabric_export(void* p, void* handle64);
+REID_API int reid_fabric_open(const void* handle64, void** out);
+REID_API int reid_fabric_close(void* p);
+REID_API int reid_fabric_barrier(void* const* peers, int64_t flags_off, int rank, int world, int epoch, void* stream);
+REID_API int reid_fabric_bcast(void* const* peers, int rank, int world, int64_t offset, int64_t bytes, void* stream);
+REID_API int reid_fabric_bcast_rows(void* const* peers, int rank, int world, int64_t offset, int row_bytes, int n,
+                           void* stream);
+REID_API int reid_fabric_bcast_ell(void* const* peers, int rank, int world, int64_t off_cnt, int64_t off_cols,
+                          int64_t off_vals, int cap1, int n, void* stream);
+REID_API int reid_fabric_bcast_pool(void* const* peers, int rank, int world, int64_t off_cnt, int64_t off_cols,
+                           int64_t off_vals, const int64_t* off, int n, void* stream);
+
 /* K7  reranking.py:73-78.  ub[l] = upper bound of |supp V_qe[row_l]|; exclusive scan to offsets;
  * then the expansion itself into a CSR pool (Qc/Qv at qoff[l], Qn[l] entries, columns ascending).
  * V (Vc/Vv/Vn, ELL pitch cap1) and nbr are global (all N rows). */

@@ -271,7 +271,7 @@ int reid_krecip_V(const int32_t* rfull, const int32_t* nfull, const int32_t* rha
   ENTER();
   REID_REQUIRE(k1 >= 1 && row_stride >= 1 && row0 >= 0, "krecip_V: bad window");
   return launch_expand_weights(rfull, nfull, rhalf, nhalf, row0, row_stride, rows, k1, D, ld, rowmax_key,
-                               Vc, H(Vv), Vn, 0, S(stream));
+                               Vc, H(Vv), Vn, 0, nullptr, 0, S(stream));
 }
 
 int reid_krecip_V_tri(const int32_t* rfull, const int32_t* nfull, const int32_t* rhalf, const int32_t* nhalf,
@@ -280,7 +280,95 @@ int reid_krecip_V_tri(const int32_t* rfull, const int32_t* nfull, const int32_t*
   ENTER();
   REID_REQUIRE(k1 >= 1, "krecip_V: bad k1");
   return launch_expand_weights(rfull, nfull, rhalf, nhalf, 0, 1, rows, k1, D, ld, rowmax_key, Vc, H(Vv), Vn,
-                               upper_only ? 1 : 0, S(stream));
+                               upper_only ? 1 : 0, nullptr, 0, S(stream));
+}
+
+/* ---- sharded symmetric path (one process per GPU, peer memory) ---------------------------------------------- */
+#define PEERS(p) reinterpret_cast<unsigned char* const*>(p)
+
+int reid_dist_sharded(const reid_half* hi, const reid_half* lo, int64_t ld, const float* sq, const uint32_t* amax, int n,
+                      int dpad, const int32_t* tiles, int ntiles, int world, float* out, int64_t ld_out, int nloc,
+                      int32_t* rowmax_key, float* chunk_min, int cm_pitch, float* chunk_min_m, int cmm_pitch,
+                      void* stream) {
+  ENTER();
+  REID_REQUIRE(n >= 0 && dpad > 0 && ld >= dpad && ld_out >= n && world >= 1 && ntiles >= 0, "dist_sharded: bad shape");
+  return launch_dist_tc_sharded(HC(hi), HC(lo), ld, sq, amax, n, dpad, tiles, ntiles, world, out, ld_out, nloc,
+                                rowmax_key, chunk_min, cm_pitch, chunk_min_m, cmm_pitch, S(stream));
+}
+
+int reid_shard_tau(int n, int rank, int world, const float* cm_d, int pitch_d, const float* cm_m, int pitch_m, int K,
+                   int32_t* tau_key, void* stream) {
+  ENTER();
+  return launch_shard_tau(n, rank, world, cm_d, pitch_d, cm_m, pitch_m, K, reinterpret_cast<unsigned*>(tau_key),
+                          S(stream));
+}
+
+int reid_shard_dstar(int n, int rank, int world, const int32_t* stats, int64_t slot_ints, int32_t* key_g, int32_t* key_l,
+                     float* dstar, int32_t* count, int32_t* cthr_key, void* stream) {
+  ENTER();
+  return launch_shard_dstar(n, rank, world, stats, slot_ints, key_g, key_l, dstar, count, cthr_key, S(stream));
+}
+
+int reid_shard_push(const float* D, int nloc, int rank, int world, int n, int64_t ld, const float* cm_d, int pitch_d,
+                    const float* dstar, const int32_t* cthr_key, int32_t* count, void* pbuf, int cap, void* stream) {
+  ENTER();
+  return launch_shard_push(D, nloc, rank, world, n, ld, cm_d, pitch_d, dstar, cthr_key, count,
+                           static_cast<unsigned long long*>(pbuf), cap, S(stream));
+}
+
+int reid_shard_merge_local(const float* D, int64_t ld, int n, int rank, int world, const float* cm_d, int pitch_d,
+                           const float* cm_m, int pitch_m, const int32_t* key_g, const float* dstar,
+                           const int32_t* count, const void* pbuf, int cap, int K, void* const* peers,
+                           int64_t inbox_off, int nloc_max, void* stream) {
+  ENTER();
+  return launch_shard_merge_local(D, ld, n, rank, world, cm_d, pitch_d, cm_m, pitch_m, key_g, dstar, count,
+                                  static_cast<const unsigned long long*>(pbuf), cap, K, PEERS(peers), inbox_off,
+                                  nloc_max, S(stream));
+}
+
+int reid_shard_merge_final(int nloc, int rank, int world, int K, const void* inbox, int nloc_max, void* const* peers,
+                           int64_t nbr_off, float* nbr_val, void* stream) {
+  ENTER();
+  return launch_shard_merge_final(nloc, rank, world, K, static_cast<const unsigned long long*>(inbox), nloc_max,
+                                  PEERS(peers), nbr_off, nbr_val, S(stream));
+}
+
+int reid_krecip_V_sharded(const int32_t* rfull, const int32_t* nfull, const int32_t* rhalf, const int32_t* nhalf,
+                          int rank, int world, int rows, int k1, const float* D, int64_t ld, const int32_t* rowmax_key,
+                          const void* const* panels, int32_t* Vc, reid_half* Vv, int32_t* Vn, void* stream) {
+  ENTER();
+  REID_REQUIRE(k1 >= 1 && world >= 1 && rank >= 0 && rank < world && panels, "krecip_V_sharded: bad arguments");
+  return launch_expand_weights(rfull, nfull, rhalf, nhalf, rank, -world, rows, k1, D, ld, rowmax_key, Vc, H(Vv), Vn, 1,
+                               reinterpret_cast<const float* const*>(panels), 1, S(stream));
+}
+
+int reid_fabric_alloc(int64_t bytes, void** out) { ENTER(); return fabric_alloc(bytes, out); }
+int reid_fabric_free(void* p) { return fabric_free(p); }
+int reid_fabric_export(void* p, void* handle64) { ENTER(); return fabric_export(p, handle64); }
+int reid_fabric_open(const void* handle64, void** out) { ENTER(); return fabric_open(handle64, out); }
+int reid_fabric_close(void* p) { return fabric_close(p); }
+int reid_fabric_barrier(void* const* peers, int64_t flags_off, int rank, int world, int epoch, void* stream) {
+  ENTER();
+  return launch_fabric_barrier(PEERS(peers), flags_off, rank, world, (unsigned)epoch, S(stream));
+}
+int reid_fabric_bcast(void* const* peers, int rank, int world, int64_t offset, int64_t bytes, void* stream) {
+  ENTER();
+  return launch_fabric_bcast(PEERS(peers), rank, world, offset, bytes, S(stream));
+}
+int reid_fabric_bcast_rows(void* const* peers, int rank, int world, int64_t offset, int row_bytes, int n, void* stream) {
+  ENTER();
+  return launch_fabric_bcast_rows(PEERS(peers), rank, world, offset, row_bytes, n, S(stream));
+}
+int reid_fabric_bcast_ell(void* const* peers, int rank, int world, int64_t off_cnt, int64_t off_cols, int64_t off_vals,
+                          int cap1, int n, void* stream) {
+  ENTER();
+  return launch_fabric_bcast_ell(PEERS(peers), rank, world, off_cnt, off_cols, off_vals, cap1, n, S(stream));
+}
+int reid_fabric_bcast_pool(void* const* peers, int rank, int world, int64_t off_cnt, int64_t off_cols, int64_t off_vals,
+                           const int64_t* off, int n, void* stream) {
+  ENTER();
+  return launch_fabric_bcast_pool(PEERS(peers), rank, world, off_cnt, off_cols, off_vals,
+                                  reinterpret_cast<const long long*>(off), n, S(stream));
 }
 
 int reid_qe_bound(const int32_t* nbr, int K, int k2, const int32_t* Vn, int row0, int row_stride, int rows,
@@ -338,7 +426,7 @@ int reid_jaccard_mix(const int32_t* Qc, const reid_half* Qv, const int64_t* qoff
                      float c1, float c2, float* out, int64_t ld_out, reid_half* jaccard_out, int64_t ld_j,
                      void* ws, int64_t ws_bytes, int cap, void* stream) {
   ENTER();
-  REID_REQUIRE(q >= 0 && q <= N && q_stride >= 1, "jaccard_mix: bad shape q=%d N=%d", q, N);
+  REID_REQUIRE(q >= 0 && q <= N && q_stride != 0, "jaccard_mix: bad shape q=%d N=%d", q, N);
   return launch_jaccard_mix(Qc, HC(Qv), reinterpret_cast<const long long*>(qoff), Qn,
                             reinterpret_cast<const long long*>(colptr),
                             reinterpret_cast<const unsigned long long*>(csc_ent), D, ld, rowmax_key, q0, q_stride, nq,
@@ -368,7 +456,7 @@ int reid_jaccard_score(const int32_t* Qc, const reid_half* Qv, const int64_t* qo
                        const int32_t* pid_list, int pid_T, int max_rank, double* ap, int32_t* first_hit,
                        int32_t* cmc_hist, int32_t* n_valid, void* ws, int64_t ws_bytes, int cap, void* stream) {
   ENTER();
-  REID_REQUIRE(q >= 0 && q <= N && q_stride >= 1, "jaccard_score: bad shape q=%d N=%d", q, N);
+  REID_REQUIRE(q >= 0 && q <= N && q_stride != 0, "jaccard_score: bad shape q=%d N=%d", q, N);
   REID_REQUIRE(ap != nullptr, "jaccard_score: ap is NULL (use reid_jaccard_mix for the matrix alone)");
   return launch_jaccard_score(Qc, HC(Qv), reinterpret_cast<const long long*>(qoff), Qn,
                               reinterpret_cast<const long long*>(colptr),

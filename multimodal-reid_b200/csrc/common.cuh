@@ -68,6 +68,38 @@ __device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long v)
   return v;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Row ownership of a multi-rank job.  Two schemes, selected by the sign of `row_stride` wherever a kernel
+// takes (row0, row_stride):
+//   row_stride > 0   cyclic rows: local row l of rank row0 is global row row0 + l * row_stride (NCCL path, round 1)
+//   row_stride < 0   snake blocks: P = -row_stride ranks own 256-row tile rows of the symmetric N x N matrix in
+//                    boustrophedon order (tile rows 0..P-1 -> ranks 0..P-1, tile rows P..2P-1 -> ranks P-1..0, ...), so
+//                    the upper-triangle tiles (tile row t holds T - t of them) are balanced to O(P / T^2); local row
+//                    l is row (l & 255) of the rank's (l >> 8)-th tile row.  P = 1 is the identity in both schemes.
+// ---------------------------------------------------------------------------------------------
+__host__ __device__ inline int snake_owner(int t, int P) {
+  const int pos = t % (2 * P);
+  return pos < P ? pos : 2 * P - 1 - pos;
+}
+__host__ __device__ inline int snake_local_tile(int t, int P) {       // index of tile row t among its owner's tile rows
+  const int pos = t % (2 * P);
+  return 2 * (t / (2 * P)) + (pos >= P ? 1 : 0);
+}
+__host__ __device__ inline int snake_global_tile(int lt, int r, int P) {
+  return 2 * P * (lt >> 1) + ((lt & 1) ? 2 * P - 1 - r : r);
+}
+// number of tile rows t < t_end owned by rank r
+__host__ __device__ inline int snake_tiles_below(int t_end, int r, int P) {
+  const int pos = t_end % (2 * P);
+  return 2 * (t_end / (2 * P)) + (pos > r ? 1 : 0) + (pos > 2 * P - 1 - r ? 1 : 0);
+}
+__host__ __device__ inline long long own_row(int row0, int row_stride, int l) {
+  if (row_stride >= 0) return row0 + (long long)l * row_stride;
+  return (long long)snake_global_tile(l >> 8, row0, -row_stride) * 256 + (l & 255);
+}
+// local row of global row i on its owner under the snake scheme
+__host__ __device__ inline int snake_local_row(int i, int P) { return snake_local_tile(i >> 8, P) * 256 + (i & 255); }
+
 static inline int cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
 static inline long long round_up(long long a, long long b) { return (a + b - 1) / b * b; }
 

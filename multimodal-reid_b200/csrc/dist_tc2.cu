@@ -239,7 +239,8 @@ dist_tc2_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant
                 const uint32_t* __restrict__ b_amax, int m, int n, int kblocks, int metric,
                 int* __restrict__ rowmax_key, float* __restrict__ chunk_min, int nchunks, int symmetric,
                 int ntiles, float* __restrict__ out, long long ld_out, int dbg,
-                int* __restrict__ rowmax_key_m, float* __restrict__ chunk_min_m) {
+                int* __restrict__ rowmax_key_m, float* __restrict__ chunk_min_m, int cmm_pitch,
+                const int2* __restrict__ tile_list, int sh_world) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* epi_base = smem + STAGES * STAGE_BYTES;
   float* rb_s = reinterpret_cast<float*>(epi_base + EPI_BYTES);
@@ -288,7 +289,8 @@ dist_tc2_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant
       const uint64_t pol_ld = l2_policy_evict_last();
       for (int t = tile0; t < ntiles; t += tile_step) {
         int mb, nb;
-        cur.locate(t, sym_cursor, mblocks, nblocks, mb, nb);
+        if (tile_list) { const int2 tl = __ldg(tile_list + t); mb = tl.x; nb = tl.y; }
+        else cur.locate(t, sym_cursor, mblocks, nblocks, mb, nb);
         const int m0 = mb * BM + (int)rank * CM, n0 = nb * BN + (int)rank * HB;
         for (int kb = 0; kb < kblocks; ++kb) {
           mbar_wait(EMPTY_B(stage), phase ^ 1);
@@ -346,12 +348,22 @@ dist_tc2_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant
     int it = 0, nstore = 0;
     TileCursor cur;
     int mb = 0, nb = 0;
-    if (tile0 < ntiles) cur.locate(tile0, sym_cursor, mblocks, nblocks, mb, nb);
+    // sharded symmetric mode (tile_list != NULL): this rank computes the upper-triangle tiles of ITS tile rows (snake
+    // ownership, common.cuh); tile coordinates are global, A and B are all N rows, `out` / chunk_min hold only the
+    // rank's own rows (local row = snake_local_tile(mb) * 256 + row in tile), rowmax_key is indexed by global row and
+    // the mirrored rows' chunk minima go to chunk_min_m[global row, local tile row * 8 + 32-row group] (a compact prefix
+    // per row: the tile rows this rank owns above it)
+    auto locate = [&](int t, int& mb_, int& nb_) {
+      if (tile_list) { const int2 tl = __ldg(tile_list + t); mb_ = tl.x; nb_ = tl.y; }
+      else cur.locate(t, sym_cursor, mblocks, nblocks, mb_, nb_);
+    };
+    if (tile0 < ntiles) locate(tile0, mb, nb);
     // the row / column norms of a tile are fetched one tile ahead
     float rb_next = (nb * BN + et < n) ? rb[nb * BN + et] : 0.0f;
     float ra_next = (mb * BM + row_in_tile + lane < m) ? ra[mb * BM + row_in_tile + lane] : 0.0f;
     for (int t = tile0; t < ntiles; t += tile_step, ++it) {
-      const int r0 = mb * BM + row_in_tile;    // first row of this warp's 32
+      const int r0 = mb * BM + row_in_tile;    // first (global) row of this warp's 32
+      const int lr0 = tile_list ? snake_local_tile(mb, sh_world) * BM + row_in_tile : r0;   // ... and where it is stored
       const int n0 = nb * BN;
       const bool mirror = symmetric == 3 || (symmetric && mb < nb);
       const bool store_mirror = symmetric == 1;   // mode 2: consumers read the lower triangle transposed
@@ -365,7 +377,7 @@ dist_tc2_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant
       {
         const int tn = t + tile_step;
         if (tn < ntiles) {
-          cur.locate(tn, sym_cursor, mblocks, nblocks, mb, nb);
+          locate(tn, mb, nb);
           rb_next = (nb * BN + et < n) ? rb[nb * BN + et] : 0.0f;
           ra_next = (mb * BM + row_in_tile + lane < m) ? ra[mb * BM + row_in_tile + lane] : 0.0f;
         }
@@ -460,7 +472,7 @@ dist_tc2_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant
           asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
           __syncwarp();
           if (lane == 0) {
-            tma_store_2d(&tmOut, smem_u32(buf), col0, r0);
+            tma_store_2d(&tmOut, smem_u32(buf), col0, lr0);
             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
           }
           ++nstore;
@@ -482,13 +494,13 @@ dist_tc2_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant
           }
           const int trow = col0 + lane;
           if (trow < n) {
-            if (chunk_min_m) chunk_min_m[(long long)trow * nchunks + (r0 >> 5)] = tmn;
+            if (chunk_min_m) chunk_min_m[(long long)trow * cmm_pitch + (lr0 >> 5)] = tmn;
             if (rowmax_key_m) atomicMax(rowmax_key_m + trow, f2ordered_int(tmx));
           }
         }
       }
       if (chunk_min && row_ok)           // nchunks = 8 slots per tile column block: (n0 >> 5) + c_first is a multiple of 4
-        *reinterpret_cast<float4*>(chunk_min + (long long)row * nchunks + (n0 >> 5) + c_first) =
+        *reinterpret_cast<float4*>(chunk_min + (long long)(lr0 + lane) * nchunks + (n0 >> 5) + c_first) =
             make_float4(cm4[0], cm4[1], cm4[2], cm4[3]);
       if (rowmax_key && row_ok && mx > -INFINITY) atomicMax(rowmax_key + row, f2ordered_int(mx));
     }
@@ -612,7 +624,43 @@ int launch_dist_tc_block(const __half* Ahi, const __half* Alo, long long lda, co
   dist_tc2_kernel<<<2 * clusters, THREADS, SMEM_BYTES, s>>>(mAhi, mAlo, mBhi, mBlo, mOut, ra, rb, a_amax, b_amax, m, n,
                                                             dp / BK, metric, rowmax_key, chunk_min, pitch,
                                                             symmetric, (int)ntiles, out, ld_out, dbg, rowmax_key_m,
-                                                            chunk_min_m);
+                                                            chunk_min_m, pitch, nullptr, 1);
+  return check_launch("dist_tc2_kernel");
+}
+
+// Sharded symmetric contraction of a multi-rank job: this rank computes the upper-triangle tiles (mb <= nb) of the
+// tile rows it owns under the snake scheme (common.cuh) -- `tiles` is that list in global tile coordinates, built by
+// the host (engine.py, cached per (N, world, rank)).  A = B = all n rows.  Stored: out[nloc, ld_out] = the rank's own
+// rows in upper-only form (columns left of a row's 256-wide diagonal block are never written); chunk_min[nloc, cm_pitch]
+// their chunk minima (defined from the diagonal block on); rowmax_key[n] (global rows) receives atomicMax from direct
+// AND mirrored tiles -- the maximum over the part of each row this rank has seen; chunk_min_m[n, cmm_pitch] the chunk
+// minima of the mirrored tiles, row i holding 8 * (number of owned tile rows above i's) valid leading entries.
+int launch_dist_tc_sharded(const __half* hi, const __half* lo, long long ld, const float* sq, const uint32_t* amax,
+                           int n, int dp, const int* tiles, int ntiles, int world, float* out, long long ld_out,
+                           int nloc, int* rowmax_key, float* chunk_min, int cm_pitch, float* chunk_min_m,
+                           int cmm_pitch, cudaStream_t s) {
+  using namespace tc2;
+  if (n == 0 || ntiles == 0) return REID_OK;
+  REID_REQUIRE(dp % BK == 0 && ld % 8 == 0 && ld_out % 4 == 0, "dist_tc_sharded: bad pitches");
+  REID_REQUIRE(cm_pitch % 4 == 0 && cm_pitch >= chunk_pitch(n) && ((uintptr_t)chunk_min & 15) == 0 && cmm_pitch >= 8,
+               "dist_tc_sharded: chunk-minimum arrays must be 16-byte aligned with pitch >= %d", chunk_pitch(n));
+  CUtensorMap mAhi, mAlo, mBhi, mBlo, mOut;
+  int rc;
+  if ((rc = make_map(&mAhi, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, hi, dp, n, ld, BK, CM, "A_hi"))) return rc;
+  if ((rc = make_map(&mAlo, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, lo, dp, n, ld, BK, CM, "A_lo"))) return rc;
+  if ((rc = make_map(&mBhi, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, hi, dp, n, ld, BK, HB, "B_hi"))) return rc;
+  if ((rc = make_map(&mBlo, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, lo, dp, n, ld, BK, HB, "B_lo"))) return rc;
+  if ((rc = make_map(&mOut, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, out, n, nloc, ld_out, 32, 32, "out"))) return rc;
+  int dev = 0, sms = 0;
+  REID_CUDA(cudaGetDevice(&dev));
+  REID_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  REID_CUDA(cudaFuncSetAttribute(dist_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+  const int pairs = sms / 2;
+  const int clusters = ntiles < pairs ? ntiles : pairs;
+  dist_tc2_kernel<<<2 * clusters, THREADS, SMEM_BYTES, s>>>(mAhi, mAlo, mBhi, mBlo, mOut, sq, sq, amax, amax, n, n,
+                                                            dp / BK, 0, rowmax_key, chunk_min, cm_pitch, 2, ntiles, out,
+                                                            ld_out, 0, rowmax_key, chunk_min_m, cmm_pitch,
+                                                            reinterpret_cast<const int2*>(tiles), world);
   return check_launch("dist_tc2_kernel");
 }
 

@@ -171,7 +171,7 @@ js_dense_query(const int qi, const int* __restrict__ Qc, const __half* __restric
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   unsigned long long* wq = reinterpret_cast<unsigned long long*>(aux + JsLayout::queue) + w * 2 * JS_QSLOTS;
   // qi: local query index (D / rowmax / out rows)
-  const long long row = q0 + (long long)qi * q_stride;   // global probe index (V_qe row)
+  const long long row = own_row(q0, q_stride, qi);        // global probe index (V_qe row)
 #ifdef REID_JS_PROFILE
   long long _t0 = clock64();
 #endif

@@ -61,7 +61,7 @@ overlap_sparse_kernel(const int* __restrict__ Qc, const __half* __restrict__ Qv,
 
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   const int qi = blockIdx.x;
-  const long long row = q0 + (long long)qi * q_stride;
+  const long long row = own_row(q0, q_stride, qi);
   const long long o = qoff[row];
   const int nq = Qn[row];
   const int nw = R.nw;

@@ -49,7 +49,41 @@ int launch_reciprocal_sets(const int* nbr, int N, int K, int k1, int* rfull, int
                            int* nhalf, cudaStream_t s);
 int launch_expand_weights(const int* rfull, const int* nfull, const int* rhalf, const int* nhalf, int row0,
                           int row_stride, int rows, int k1, const float* D, long long ld, const int* rowmax_key, int* Vc,
-                          __half* Vv, int* Vn, int upper_only, cudaStream_t s);
+                          __half* Vv, int* Vn, int upper_only, const float* const* panels, int out_global,
+                          cudaStream_t s);
+int launch_dist_tc_sharded(const __half* hi, const __half* lo, long long ld, const float* sq, const uint32_t* amax,
+                           int n, int dp, const int* tiles, int ntiles, int world, float* out, long long ld_out,
+                           int nloc, int* rowmax_key, float* chunk_min, int cm_pitch, float* chunk_min_m,
+                           int cmm_pitch, cudaStream_t s);
+int launch_shard_tau(int n, int rank, int world, const float* cm_d, int pitch_d, const float* cm_m, int pitch_m, int K,
+                     unsigned* tau_key, cudaStream_t s);
+int launch_shard_dstar(int n, int rank, int world, const int* stats, long long slot, int* key_g, int* key_l,
+                       float* dstar, int* count, int* cthr_key, cudaStream_t s);
+int launch_shard_push(const float* D, int nloc, int rank, int world, int n, long long ld, const float* cm_d,
+                      int pitch_d, const float* dstar, const int* cthr_key, int* count, unsigned long long* pbuf,
+                      int cap, cudaStream_t s);
+int launch_shard_merge_local(const float* D, long long ld, int n, int rank, int world, const float* cm_d, int pitch_d,
+                             const float* cm_m, int pitch_m, const int* key_g, const float* dstar, const int* count,
+                             const unsigned long long* pbuf, int cap, int K, unsigned char* const* peers,
+                             long long inbox_off, int nloc_max, cudaStream_t s);
+int launch_shard_merge_final(int nloc, int rank, int world, int K, const unsigned long long* inbox, int nloc_max,
+                             unsigned char* const* peers, long long nbr_off, float* nbr_val, cudaStream_t s);
+// fabric.cu: peer-memory arena, flag barrier, copy kernels
+int fabric_alloc(long long bytes, void** out);
+int fabric_free(void* p);
+int fabric_export(void* p, void* handle64);
+int fabric_open(const void* handle64, void** out);
+int fabric_close(void* p);
+int launch_fabric_barrier(unsigned char* const* peers, long long flags_off, int rank, int world, unsigned epoch,
+                          cudaStream_t s);
+int launch_fabric_bcast(unsigned char* const* peers, int rank, int world, long long offset, long long bytes,
+                        cudaStream_t s);
+int launch_fabric_bcast_rows(unsigned char* const* peers, int rank, int world, long long offset, int row_bytes, int n,
+                             cudaStream_t s);
+int launch_fabric_bcast_ell(unsigned char* const* peers, int rank, int world, long long off_cnt, long long off_cols,
+                            long long off_vals, int cap1, int n, cudaStream_t s);
+int launch_fabric_bcast_pool(unsigned char* const* peers, int rank, int world, long long off_cnt, long long off_cols,
+                             long long off_vals, const long long* off, int n, cudaStream_t s);
 int launch_qe_bound(const int* nbr, int K, int k2, const int* Vn, int row0, int row_stride, int rows,
                     int* ub, cudaStream_t s);
 int launch_exclusive_scan(const int* in, int n, long long* out, cudaStream_t s);

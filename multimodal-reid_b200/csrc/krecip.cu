@@ -77,13 +77,15 @@ expand_weights_kernel(const int* __restrict__ rfull, const int* __restrict__ nfu
                       const int* __restrict__ rhalf, const int* __restrict__ nhalf, int row0,
                       int row_stride, int rows, int k1p, int h, const float* __restrict__ D, long long ld,
                       const int* __restrict__ rowmax_key, int cap1, int capP,
-                      int* __restrict__ Vc, __half* __restrict__ Vv, int* __restrict__ Vn, int upper_only) {
+                      int* __restrict__ Vc, __half* __restrict__ Vv, int* __restrict__ Vn, int upper_only,
+                      const float* const* __restrict__ panels, int out_global) {
   extern __shared__ int smem_i[];
   const int wpb = blockDim.x >> 5;
   const int w = threadIdx.x >> 5, lane = lane_id();
   const int lrow = blockIdx.x * wpb + w;          // local row: D / rowmax / V are indexed by it
   if (lrow >= rows) return;
-  const int row = row0 + lrow * row_stride;       // global probe index
+  const int row = (int)own_row(row0, row_stride, lrow);       // global probe index (common.cuh: cyclic or snake blocks)
+  const long long vrow = out_global ? row : lrow;              // where the V row is written
   const int per_warp = k1p + capP + cap1 + 3 * k1p;
   int* R = smem_i + (long long)w * per_warp;
   int* E = R + k1p;
@@ -160,17 +162,26 @@ expand_weights_kernel(const int* __restrict__ rfull, const int* __restrict__ nfu
   const float* drow = D + (long long)lrow * ld;
   for (int j = lane; j < nU; j += 32) {
     const int e = E[j];                       // upper_only: left of the row's diagonal block only the mirror image exists
-    const float dv = (upper_only && e < (lrow & ~255)) ? D[(long long)e * ld + lrow] : drow[e];
+    float dv;
+    if (upper_only && e < (row & ~255)) {
+      // D[e, row]: on one rank a row of the same matrix; in a sharded job it sits in the panel of the rank that owns e's
+      // tile row -- read over NVLink (a few dozen 4-byte loads per row; bit-identical: the element was computed once)
+      const float* src = panels ? panels[snake_owner(e >> 8, -row_stride)] + (long long)snake_local_row(e, -row_stride) * ld
+                                : D + (long long)e * ld;
+      dv = src[row];
+    } else {
+      dv = drow[e];
+    }
     float o = __fdiv_rn(dv, m);
     W[j] = np_expf(-o);
   }
   __syncwarp();
   const float s = np_sum_f32(W, nU);
   for (int j = lane; j < nU; j += 32) {
-    Vc[(long long)lrow * cap1 + j] = E[j];
-    Vv[(long long)lrow * cap1 + j] = __float2half_rn(__fdiv_rn(W[j], s));
+    Vc[vrow * cap1 + j] = E[j];
+    Vv[vrow * cap1 + j] = __float2half_rn(__fdiv_rn(W[j], s));
   }
-  if (lane == 0) Vn[lrow] = nU;
+  if (lane == 0) Vn[vrow] = nU;
 }
 
 int launch_reciprocal_sets(const int* nbr, int N, int K, int k1, int* rfull, int* nfull, int* rhalf,
@@ -187,9 +198,11 @@ int launch_reciprocal_sets(const int* nbr, int N, int K, int k1, int* rfull, int
 
 int launch_expand_weights(const int* rfull, const int* nfull, const int* rhalf, const int* nhalf,
                           int row0, int row_stride, int rows, int k1, const float* D, long long ld,
-                          const int* rowmax_key, int* Vc, __half* Vv, int* Vn, int upper_only, cudaStream_t s) {
+                          const int* rowmax_key, int* Vc, __half* Vv, int* Vn, int upper_only,
+                          const float* const* panels, int out_global, cudaStream_t s) {
   if (rows == 0) return REID_OK;
-  REID_REQUIRE(!upper_only || (row0 == 0 && row_stride == 1), "expand_weights: upper_only needs all rows on one rank");
+  REID_REQUIRE(!upper_only || (row0 == 0 && row_stride == 1) || (row_stride < 0 && panels),
+               "expand_weights: upper_only needs all rows on one rank, or the sharded form with the peers' panels");
   const int k1p = k1 + 1, h = half_k(k1);
   const int cap1 = v_row_capacity(k1);
   int capP = 32;
@@ -203,7 +216,8 @@ int launch_expand_weights(const int* rfull, const int* nfull, const int* rhalf, 
   REID_CUDA(cudaFuncSetAttribute(expand_weights_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   expand_weights_kernel<<<cdiv(rows, wpb), wpb * 32, smem, s>>>(rfull, nfull, rhalf, nhalf, row0,
                                                                row_stride, rows, k1p, h, D, ld,
-                                                               rowmax_key, cap1, capP, Vc, Vv, Vn, upper_only);
+                                                               rowmax_key, cap1, capP, Vc, Vv, Vn, upper_only, panels,
+                                                               out_global);
   return check_launch("expand_weights_kernel");
 }
 

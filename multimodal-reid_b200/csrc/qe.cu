@@ -13,7 +13,7 @@ __global__ void qe_bound_kernel(const int* __restrict__ nbr, int K, int k2, cons
                                 int row0, int row_stride, int rows, int* __restrict__ ub) {
   int l = blockIdx.x * blockDim.x + threadIdx.x;
   if (l >= rows) return;
-  const long long i = row0 + (long long)l * row_stride;
+  const long long i = own_row(row0, row_stride, l);
   int t = 0;
   for (int r = 0; r < k2; ++r) t += Vn[nbr[i * K + r]];
   ub[l] = t;
@@ -159,10 +159,11 @@ qe_expand_kernel(const int* __restrict__ nbr, int K, int k2, const int* __restri
   const int w = threadIdx.x >> 5, lane = lane_id();
   const int lrow = blockIdx.x * wpb + w;          // local row: qoff / Qn are indexed by it
   if (lrow >= rows) return;
-  const long long row = row0 + (long long)lrow * row_stride;
+  const long long row = own_row(row0, row_stride, lrow);
+  const long long orow = row_stride < 0 ? row : lrow;   // snake ownership (sharded path): qoff / Qn are GLOBAL tables
   unsigned long long* buf = smem_q + (long long)w * cap_sort * 2;
   const int* src = nbr + row * K;
-  const long long out0 = qoff[lrow];
+  const long long out0 = qoff[orow];
   const float kf = (float)k2;
 
   int total = 0;
@@ -238,7 +239,7 @@ qe_expand_kernel(const int* __restrict__ nbr, int K, int k2, const int* __restri
       }
       nout += __popc(bal);
     }
-    if (lane == 0) Qn[lrow] = nout;
+    if (lane == 0) Qn[orow] = nout;
     return;
   }
 
@@ -272,7 +273,7 @@ qe_expand_kernel(const int* __restrict__ nbr, int K, int k2, const int* __restri
     ++nout;
     if (hit) ++pos;
   }
-  if (lane == 0) Qn[lrow] = nout;
+  if (lane == 0) Qn[orow] = nout;
 }
 
 int launch_qe_bound(const int* nbr, int K, int k2, const int* Vn, int row0, int row_stride, int rows,

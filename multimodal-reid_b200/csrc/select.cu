@@ -259,21 +259,22 @@ __device__ __forceinline__ void warp_bitonic_u64_sel(unsigned long long* a, int 
   }
 }
 
-// Pass 1 + bound of the hinted selection for one row (one warp): the raw-D threshold D* such that the row's K nearest
-// (in O = D / m order) all have D <= D*; INFINITY when no monotone filter applies.
+// Pass 1 of the hinted selection, split into pieces so that the sharded selection (a rank sees only part of a row's
+// chunk minima, in two arrays) can reuse them:
+//   keep_chunks   folds chunk minima cm[c_begin .. c_end) into the lane's S smallest, ascending in keep[]
+//   keep_kth      K-th smallest of the warp's 32*S kept values as an ordered key (0xffffffff when fewer than K chunks
+//                 were offered: no bound)
+//   dstar_of_tau  the raw-D threshold D* >= tau such that the row's K nearest in O = D / m order all have D <= D*
+//                 (quotients of neighbouring floats can coincide); INFINITY when no monotone filter applies
 template <int S>
-__device__ __forceinline__ float row_dstar(const float* __restrict__ cm, int nch, int K, float m) {
+__device__ __forceinline__ void keep_chunks(const float* __restrict__ cm, int c_begin, int c_end, float (&keep)[S]) {
   const int lane = lane_id();
-  // pass 1: the S smallest chunk minima of this lane's share, ascending in keep[]
-  float keep[S];
-#pragma unroll
-  for (int s = 0; s < S; ++s) keep[s] = INFINITY;
   // lane l takes chunks l, l + 32, ...: neighbours cluster in adjacent chunks when the gallery is ordered by identity,
   // and a lane keeps only S values, so adjacent chunks must go to different lanes for the bound to stay tight
-  for (int c = lane; c < nch; c += 8 * 32) {
+  for (int c = c_begin + lane; c < c_end; c += 8 * 32) {
     float v[8];
 #pragma unroll
-    for (int u = 0; u < 8; ++u) v[u] = c + u * 32 < nch ? __ldg(cm + c + u * 32) : INFINITY;
+    for (int u = 0; u < 8; ++u) v[u] = c + u * 32 < c_end ? __ldg(cm + c + u * 32) : INFINITY;
 #pragma unroll
     for (int u = 0; u < 8; ++u) {
       float x = v[u];
@@ -281,6 +282,10 @@ __device__ __forceinline__ float row_dstar(const float* __restrict__ cm, int nch
       for (int s = 0; s < S; ++s) { const float lo = fminf(keep[s], x); x = fmaxf(keep[s], x); keep[s] = lo; }
     }
   }
+}
+
+template <int S>
+__device__ __forceinline__ uint32_t keep_kth(const float (&keep)[S], int nch, int K) {
   // K-th smallest of the 32*S kept values: largest prefix t with #{key < t} < K, built bit by bit
   uint32_t t = 0xffffffffu;                               // fewer chunks than K: every chunk is a candidate
   if (nch >= K) {
@@ -296,8 +301,12 @@ __device__ __forceinline__ float row_dstar(const float* __restrict__ cm, int nch
       if (cnt < K) t = trial;                             // fewer than K keys below trial: the K-th is >= trial
     }
   }
-  float dstar = key2f(t);
-  if (m > 0.0f && m < INFINITY && nch >= K && dstar == dstar) {
+  return t;
+}
+
+__device__ __forceinline__ float dstar_of_tau(uint32_t tau_key, float m) {
+  float dstar = key2f(tau_key);
+  if (tau_key != 0xffffffffu && m > 0.0f && m < INFINITY && dstar == dstar) {
     const float tau_o = __fdiv_rn(dstar, m);
     for (int it = 0; it < 64; ++it) {
       const float x = dstar;
@@ -310,8 +319,17 @@ __device__ __forceinline__ float row_dstar(const float* __restrict__ cm, int nch
   } else {
     dstar = INFINITY;                                   // degenerate maximum: no monotone filter, take everything
   }
-
   return dstar;
+}
+
+// Pass 1 + bound for one row whose chunk minima lie in one array (one warp)
+template <int S>
+__device__ __forceinline__ float row_dstar(const float* __restrict__ cm, int nch, int K, float m) {
+  float keep[S];
+#pragma unroll
+  for (int s = 0; s < S; ++s) keep[s] = INFINITY;
+  keep_chunks<S>(cm, 0, nch, keep);
+  return dstar_of_tau(keep_kth<S>(keep, nch, K), m);
 }
 
 template <int S>
@@ -471,19 +489,23 @@ select_thr_kernel(int rows, const int* __restrict__ rowmax_key, const float* __r
 }
 
 __global__ void __launch_bounds__(SELH_WPB * 32, 5)
-select_push_kernel(const float* __restrict__ D, int n, long long ld, const float* __restrict__ chunk_min, int nch,
-                   int cm_pitch, const float* __restrict__ dstar, const int* __restrict__ cthr_key,
-                   int* __restrict__ count, unsigned long long* __restrict__ pbuf, int cap, int pf) {
+select_push_kernel(const float* __restrict__ D, int lrows, int row0, int row_stride, int n, long long ld,
+                   const float* __restrict__ chunk_min, int nch, int cm_pitch, const float* __restrict__ dstar,
+                   const int* __restrict__ cthr_key, int* __restrict__ count, unsigned long long* __restrict__ pbuf,
+                   int cap, int pf) {
   __shared__ unsigned short list_s[SELH_WPB][SELP_LIST];
   __shared__ unsigned long long own_s[SELH_WPB][SELH_CAND];
   __shared__ int nlist_s[SELH_WPB];
   const int w = threadIdx.x >> 5, lane = lane_id();
-  const int row = blockIdx.x * SELH_WPB + w;
-  if (row >= n) return;
+  // D / chunk_min hold the `lrows` rows this rank stores (all n on one rank); thresholds, counters and candidate
+  // records are indexed by GLOBAL row, so a rank of a sharded job pushes into the lists of rows it does not own
+  const int lrow = blockIdx.x * SELH_WPB + w;
+  if (lrow >= lrows) return;
+  const int row = (int)own_row(row0, row_stride, lrow);
   unsigned short* list = list_s[w];
   unsigned long long* own = own_s[w];         // this row's own candidates: staged, appended with one atomic at the end
-  const float* p = D + (long long)row * ld;
-  const float* cm = chunk_min + (long long)row * cm_pitch;
+  const float* p = D + (long long)lrow * ld;
+  const float* cm = chunk_min + (long long)lrow * cm_pitch;
   const float ds = dstar[row];
   const int dsk = thr_key(ds);
   const int tri0 = row & ~255;                // first stored column of this row
@@ -680,7 +702,7 @@ int launch_select_topk_scatter(const float* D, int n, long long ld, const int* r
 #undef REID_SELT
   if (int rc = check_launch("select_thr_kernel")) return rc;
   const char* pfe = getenv("REID_SEL_PF");
-  select_push_kernel<<<grid, threads, 0, s>>>(D, n, ld, chunk_min, nch, pitch, dstar, cthr, count, pbuf, cap,
+  select_push_kernel<<<grid, threads, 0, s>>>(D, n, 0, 1, n, ld, chunk_min, nch, pitch, dstar, cthr, count, pbuf, cap,
                                               pfe ? atoi(pfe) : 1);
   if (int rc = check_launch("select_push_kernel")) return rc;
   select_merge_kernel<<<grid, threads, 0, s>>>(D, n, ld, rowmax_key, chunk_min, nch, pitch, dstar, count, pbuf, cap, K,
@@ -688,6 +710,220 @@ int launch_select_topk_scatter(const float* D, int n, long long ld, const int* r
   return check_launch("select_merge_kernel");
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Sharded scatter selection (multi-rank symmetric contraction, launch_dist_tc_sharded).  Rank r holds of row i
+//   * the direct part   D_r[local(i), j], j >= first column of i's diagonal block      -- only if r owns i's tile row
+//   * the mirrored part D_r[local(j), i] for the rows j of every tile row r owns ABOVE i's
+// and the matching chunk minima (cm_d suffix / cm_m compact prefix).  Every element of the symmetric matrix is computed by
+// exactly one rank and offered to both rows it belongs to, so the union over ranks of the per-rank parts is the whole row.
+//   shard_tau     per row: K-th smallest of the chunk minima this rank holds (an upper bound of the row's K-th element)
+//   -- exchange: row maxima (max over ranks) and tau (min over ranks), 8 bytes per row and rank --
+//   shard_dstar   D*[i] from the global tau and maximum (same rule as one rank), group thresholds, counters
+//   select_push   as on one rank, over the rank's stored rows; candidates of ALL rows accumulate locally
+//   merge_local   per row: sort this rank's candidates, its K best (O key, column) records go to the row owner's inbox
+//   -- barrier --
+//   merge_final   per owned row: the P x K records, sorted; first K = the row's neighbour list, written to every rank
+// The (O key, column) order is total, so the lists do not depend on P or on arrival order: bit-identical to one rank.
+// ---------------------------------------------------------------------------------------------
+template <int S>
+__global__ void __launch_bounds__(SELH_WPB * 32)
+shard_tau_kernel(int n, int rank, int P, const float* __restrict__ cm_d, int pitch_d, const float* __restrict__ cm_m,
+                 int pitch_m, int K, unsigned* __restrict__ tau_key) {
+  const int w = threadIdx.x >> 5, lane = lane_id();
+  const int i = blockIdx.x * SELH_WPB + w;
+  if (i >= n) return;
+  const int ti = i >> 8;
+  const int npre = 8 * snake_tiles_below(ti, rank, P);
+  float keep[S];
+#pragma unroll
+  for (int s = 0; s < S; ++s) keep[s] = INFINITY;
+  keep_chunks<S>(cm_m + (long long)i * pitch_m, 0, npre, keep);
+  int nch = npre;
+  if (snake_owner(ti, P) == rank) {
+    const int nchunks = (n + 31) >> 5;
+    keep_chunks<S>(cm_d + (long long)snake_local_row(i, P) * pitch_d, ti * 8, nchunks, keep);
+    nch += nchunks - ti * 8;
+  }
+  const uint32_t t = keep_kth<S>(keep, nch, K);
+  if (lane == 0) tau_key[i] = t;
+}
+
+// stats: P slots of `slot` ints -- slot p = {row-maximum keys (ordered int) [n], tau keys (unsigned) [n]} of rank p
+__global__ void __launch_bounds__(256)
+shard_dstar_kernel(int n, int rank, int P, const int* __restrict__ stats, long long slot, int* __restrict__ key_g,
+                   int* __restrict__ key_l, float* __restrict__ dstar, int* __restrict__ count,
+                   int* __restrict__ cthr_key) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int mk = REID_ROWMAX_INIT;
+  unsigned tk = 0xffffffffu;
+  for (int p = 0; p < P; ++p) {
+    mk = max(mk, stats[p * slot + i]);
+    tk = min(tk, (unsigned)stats[p * slot + n + i]);
+  }
+  const float ds = dstar_of_tau(tk, ordered_int2f(mk));
+  key_g[i] = mk;
+  if (snake_owner(i >> 8, P) == rank) key_l[snake_local_row(i, P)] = mk;
+  dstar[i] = ds;
+  count[i] = 0;
+  atomicMax(cthr_key + (i >> 5), thr_key(ds));
+}
+
+__global__ void __launch_bounds__(SELH_WPB * 32)
+shard_merge_local_kernel(const float* __restrict__ D, long long ld, int n, int rank, int P,
+                         const float* __restrict__ cm_d, int pitch_d, const float* __restrict__ cm_m, int pitch_m,
+                         const int* __restrict__ key_g, const float* __restrict__ dstar_in,
+                         const int* __restrict__ count, const unsigned long long* __restrict__ pbuf, int cap, int K,
+                         unsigned char* const* __restrict__ peers, long long inbox_off, int nloc_max) {
+  __shared__ unsigned long long cand_s[SELH_WPB][SELH_CAND];
+  const int w = threadIdx.x >> 5, lane = lane_id();
+  const int i = blockIdx.x * SELH_WPB + w;
+  if (i >= n) return;
+  unsigned long long* cand = cand_s[w];
+  const int ti = i >> 8;
+  const int owner = snake_owner(ti, P);
+  unsigned long long* dst = reinterpret_cast<unsigned long long*>(peers[owner] + inbox_off) +
+                            ((long long)rank * nloc_max + snake_local_row(i, P)) * K;
+  const float m = ordered_int2f(key_g[i]);
+  const int cnt = count[i];
+  if (cnt <= cap) {
+    const unsigned long long* src = pbuf + (long long)i * cap;
+    for (int x = lane; x < cnt; x += 32) {
+      const unsigned long long e = src[x];
+      cand[x] = make_ck(__uint_as_float((unsigned)(e >> 32)), m, (int)(unsigned)(e & 0xffffffffu));
+    }
+    int P2 = 32;
+    while (P2 < cnt) P2 <<= 1;
+    for (int x = cnt + lane; x < P2; x += 32) cand[x] = ~0ull;
+    __syncwarp();
+    warp_bitonic_u64_sel(cand, P2, lane);
+    for (int x = lane; x < K; x += 32) dst[x] = x < P2 ? cand[x] : ~0ull;
+    return;
+  }
+  // more candidates than slots (massive ties): K rounds of warp-wide arg-min over everything this rank holds of the row
+  const float ds = dstar_in[i];
+  const int nchunks = (n + 31) >> 5;
+  const bool mine = owner == rank;
+  const int li = snake_local_row(i, P);
+  const int npre = 8 * snake_tiles_below(ti, rank, P);
+  const float* cmd = cm_d + (long long)li * pitch_d;
+  const float* cmm = cm_m + (long long)i * pitch_m;
+  unsigned long long last = 0;
+  for (int r = 0; r < K; ++r) {
+    unsigned long long best = ~0ull;
+    if (mine) {
+      for (int cc = ti * 8; cc < nchunks; ++cc) {
+        if (!(__ldg(cmd + cc) <= ds || ds == INFINITY)) continue;
+        const int col = cc * 32 + lane;
+        if (col < n) {
+          const unsigned long long k0 = make_ck(__ldg(D + (long long)li * ld + col), m, col);
+          if ((r == 0 || k0 > last) && k0 < best) best = k0;
+        }
+      }
+    }
+    for (int c = 0; c < npre; ++c) {
+      if (!(__ldg(cmm + c) <= ds || ds == INFINITY)) continue;
+      const int lj = (c >> 3) * 256 + (c & 7) * 32 + lane;                       // local row of the mirrored element
+      const int j = snake_global_tile(c >> 3, rank, P) * 256 + (c & 7) * 32 + lane;
+      const unsigned long long k0 = make_ck(__ldg(D + (long long)lj * ld + i), m, j);
+      if ((r == 0 || k0 > last) && k0 < best) best = k0;
+    }
+    best = warp_min_u64(best);
+    if (best != ~0ull) last = best;
+    if (lane == 0) dst[r] = best;
+  }
+}
+
+constexpr int SHF_WPB = 4;
+__global__ void __launch_bounds__(SHF_WPB * 32)
+shard_merge_final_kernel(int nloc, int rank, int P, int K, const unsigned long long* __restrict__ inbox, int nloc_max,
+                         int P2, unsigned char* const* __restrict__ peers, long long nbr_off,
+                         float* __restrict__ nbr_val) {
+  extern __shared__ unsigned long long fin_s[];
+  const int w = threadIdx.x >> 5, lane = lane_id();
+  const int l = blockIdx.x * SHF_WPB + w;
+  if (l >= nloc) return;
+  unsigned long long* cand = fin_s + (long long)w * P2;
+  const int total = P * K;
+  for (int x = lane; x < P2; x += 32)
+    cand[x] = x < total ? inbox[((long long)(x / K) * nloc_max + l) * K + (x % K)] : ~0ull;
+  __syncwarp();
+  warp_bitonic_u64_sel(cand, P2, lane);
+  const long long row = own_row(rank, -P, l);
+  for (int x = lane; x < K; x += 32) {
+    const unsigned long long k0 = cand[x];
+    const int col = (int)(unsigned)(k0 & 0xffffffffu);
+    for (int p = 0; p < P; ++p) reinterpret_cast<int*>(peers[p] + nbr_off)[row * K + x] = col;
+    if (nbr_val) nbr_val[(long long)l * K + x] = key2f((uint32_t)(k0 >> 32));
+  }
+}
+
+int launch_shard_tau(int n, int rank, int world, const float* cm_d, int pitch_d, const float* cm_m, int pitch_m, int K,
+                     unsigned* tau_key, cudaStream_t s) {
+  if (n == 0) return REID_OK;
+  REID_REQUIRE(K >= 1 && K <= 256, "shard_tau: K=%d outside [1,256]", K);
+  REID_REQUIRE(rank >= 0 && rank < world, "shard_tau: rank %d of %d", rank, world);
+  const int grid = cdiv(n, SELH_WPB), threads = SELH_WPB * 32;
+#define REID_SHT(SS) shard_tau_kernel<SS><<<grid, threads, 0, s>>>(n, rank, world, cm_d, pitch_d, cm_m, pitch_m, K, tau_key)
+  if (K <= 32) REID_SHT(1);
+  else if (K <= 64) REID_SHT(2);
+  else if (K <= 128) REID_SHT(4);
+  else REID_SHT(8);
+#undef REID_SHT
+  return check_launch("shard_tau_kernel");
+}
+
+int launch_shard_dstar(int n, int rank, int world, const int* stats, long long slot, int* key_g, int* key_l,
+                       float* dstar, int* count, int* cthr_key, cudaStream_t s) {
+  if (n == 0) return REID_OK;
+  REID_REQUIRE(slot >= 2ll * n, "shard_dstar: slot of %lld ints < 2 n", slot);
+  REID_CUDA(cudaMemsetAsync(cthr_key, 0x80, (size_t)4 * chunk_pitch(n), s));      // below every ordered float key
+  shard_dstar_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, rank, world, stats, slot, key_g, key_l, dstar, count, cthr_key);
+  return check_launch("shard_dstar_kernel");
+}
+
+int launch_shard_push(const float* D, int nloc, int rank, int world, int n, long long ld, const float* cm_d,
+                      int pitch_d, const float* dstar, const int* cthr_key, int* count, unsigned long long* pbuf,
+                      int cap, cudaStream_t s) {
+  if (nloc == 0) return REID_OK;
+  REID_REQUIRE(cap >= 1 && cap <= SELH_CAND, "shard_push: cap=%d outside [1,%d]", cap, SELH_CAND);
+  REID_REQUIRE(cdiv(n, 32) <= 65535, "shard_push: %d rows exceed the 16-bit chunk list", n);
+  REID_REQUIRE(((uintptr_t)cm_d & 15) == 0 && pitch_d % 4 == 0 && ((uintptr_t)cthr_key & 15) == 0,
+               "shard_push: chunk minima / thresholds must be 16-byte aligned");
+  const char* pfe = getenv("REID_SEL_PF");
+  select_push_kernel<<<cdiv(nloc, SELH_WPB), SELH_WPB * 32, 0, s>>>(D, nloc, rank, -world, n, ld, cm_d, cdiv(n, 32),
+                                                                     pitch_d, dstar, cthr_key, count, pbuf, cap,
+                                                                     pfe ? atoi(pfe) : 1);
+  return check_launch("select_push_kernel");
+}
+
+int launch_shard_merge_local(const float* D, long long ld, int n, int rank, int world, const float* cm_d, int pitch_d,
+                             const float* cm_m, int pitch_m, const int* key_g, const float* dstar, const int* count,
+                             const unsigned long long* pbuf, int cap, int K, unsigned char* const* peers,
+                             long long inbox_off, int nloc_max, cudaStream_t s) {
+  if (n == 0) return REID_OK;
+  REID_REQUIRE(cap >= 1 && cap <= SELH_CAND && K >= 1 && K <= 256, "shard_merge_local: cap=%d K=%d", cap, K);
+  REID_REQUIRE(inbox_off % 8 == 0, "shard_merge_local: inbox offset must be 8-byte aligned");
+  shard_merge_local_kernel<<<cdiv(n, SELH_WPB), SELH_WPB * 32, 0, s>>>(D, ld, n, rank, world, cm_d, pitch_d, cm_m,
+                                                                        pitch_m, key_g, dstar, count, pbuf, cap, K,
+                                                                        peers, inbox_off, nloc_max);
+  return check_launch("shard_merge_local_kernel");
+}
+
+int launch_shard_merge_final(int nloc, int rank, int world, int K, const unsigned long long* inbox, int nloc_max,
+                             unsigned char* const* peers, long long nbr_off, float* nbr_val, cudaStream_t s) {
+  if (nloc == 0) return REID_OK;
+  int P2 = 32;
+  while (P2 < world * K) P2 <<= 1;
+  const size_t smem = (size_t)SHF_WPB * P2 * 8;
+  REID_REQUIRE(smem <= 200 * 1024, "shard_merge_final: %d ranks x K=%d do not fit shared memory", world, K);
+  REID_REQUIRE(nbr_off % 4 == 0, "shard_merge_final: table offset must be 4-byte aligned");
+  REID_CUDA(cudaFuncSetAttribute(shard_merge_final_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  shard_merge_final_kernel<<<cdiv(nloc, SHF_WPB), SHF_WPB * 32, smem, s>>>(nloc, rank, world, K, inbox, nloc_max, P2,
+                                                                            peers, nbr_off, nbr_val);
+  return check_launch("shard_merge_final_kernel");
+}
 
 int launch_select_topk(const float* D, int rows, int cols, long long ld, const int* rowmax_key, int K,
                        int* nbr, float* nbr_val, int cap_override, cudaStream_t s) {

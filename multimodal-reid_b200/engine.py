@@ -18,6 +18,7 @@ import numpy as np
 import torch
 
 from . import _lib
+from . import fabric as _fabric
 
 METRIC_SQEUCLIDEAN = 0
 METRIC_ARCCOS = 1
@@ -228,6 +229,15 @@ class Engine:
         self._ubmax_seen = 256
         self.qe_replicate_below = 300_000   # N * k2 up to which every rank runs the query expansion for all rows
         self._cw_hint = {}          # k1 -> width of the V rows exchanged between ranks (see rerank_from_panel)
+        # world > 1: symmetric contraction sharded by tile rows + exchanges through peer memory (fabric.py); the NCCL
+        # all-gather path of round 1 remains as the fallback when CUDA IPC / peer access is unavailable
+        self.use_fabric = True
+        self.fabric = None
+        self._fabric_failed = False
+        self.fabric_pool_bytes = 24 << 30   # largest query-expansion pool the arena may hold (structural bound)
+        self._layouts, self._tile_cache, self._own_cache = {}, {}, {}
+        self.last_tiles = 0
+        self.last_path = "single"           # which multi-rank path the last rerank_features call took: fabric | nccl | single
 
     # ------------------------------------------------------------------ timing helpers
     def enable_timers(self, on=True):
@@ -746,7 +756,7 @@ class Engine:
         return keys, start, lst, T
 
     def jaccard_score(self, Qc, Qv, qoff, Qn, csc, D, key, q: int, N: int, lam: float, nq_local: int, q0, q_stride,
-                      ids, max_rank: int, want_final: bool):
+                      ids, max_rank: int, want_final: bool, fabric=None):
         """Fused K9–K12 for this rank's queries.  ids = (q_pids_local, g_pids, q_cams_local, g_cams).
         Returns (final or None, (cmc, mAP, n_valid, ap_all, first_all))."""
         colptr, csc_ent = csc
@@ -766,7 +776,7 @@ class Engine:
                       _ptr(D), D.stride(0), _ptr(key), q0, q_stride, nq_local, q, N, c1, c2, _ptr(out),
                       ldf, _ptr(q_pids), _ptr(q_cams), _ptr(g_cams), _ptr(keys), _ptr(start), _ptr(lst), T, max_rank,
                       _ptr(ap), _ptr(first), _ptr(hist), _ptr(nvalid), _ptr(ws), ws_bytes, self.sparse_cap, _stream())
-        return out, self._score_common(launch, nq_local, max_rank, q, span="jaccard_score")
+        return out, self._score_common(launch, nq_local, max_rank, q, span="jaccard_score", fabric=fabric)
 
     # ------------------------------------------------------------------ K4–K10 from a distance panel
     def rerank_from_panel(self, D: torch.Tensor, key: torch.Tensor, q: int, N: int, k1: int, k2: int, lam: float,
@@ -850,11 +860,174 @@ class Engine:
             return final
         return res
 
+    # ------------------------------------------------------------------ sharded symmetric path over peer memory
+    def _fabric_for(self, N: int, q: int, K: int, k1: int, k2: int, max_rank: int):
+        """(Fabric, Layout) for this problem, or None when peer memory is unavailable (then the NCCL path runs).
+        Collective on first use / growth."""
+        cm = self.comm
+        if cm.world == 1 or not self.use_fabric or self._fabric_failed or self.engine == ENGINES["simt"]:
+            return None
+        cap1 = v_row_capacity(k1)
+        replicate = k2 == 1 or N * k2 <= self.qe_replicate_below
+        pool = 0 if replicate else N * k2 * cap1
+        if pool * 6 > self.fabric_pool_bytes:
+            return None                         # structural pool bound too large for the arena: NCCL path sizes it exactly
+        key = (N, q, K, cap1, cm.world, pool, max_rank)
+        if key not in self._layouts:
+            self._layouts[key] = _fabric.make_layout(N, q, K, cap1, cm.world, pool, max_rank)
+        L = self._layouts[key]
+        if self.fabric is None:
+            self.fabric = _fabric.Fabric(cm, self.device, _lib)
+        if not self.fabric.ensure(L.total):
+            self._fabric_failed = True
+            if cm.rank == 0:
+                import warnings
+                warnings.warn("reid_b200: peer-memory fabric unavailable (" + self.fabric.last_error
+                              + "); using the NCCL all-gather path")
+            return None
+        return self.fabric, L
+
+    def _tiles_for(self, N: int):
+        key = (N, self.comm.rank, self.comm.world)
+        if key not in self._tile_cache:
+            t = _fabric.tile_list(N, self.comm.rank, self.comm.world)
+            self._tile_cache[key] = (torch.from_numpy(t).to(self.device), int(t.shape[0]))
+        return self._tile_cache[key]
+
+    def _own_index(self, n: int, rank: int | None = None) -> torch.Tensor:
+        """Global index of every local row of `rank` (default: this rank) in an n-row table, on the device."""
+        r = self.comm.rank if rank is None else rank
+        key = (n, r, self.comm.world)
+        if key not in self._own_cache:
+            self._own_cache[key] = torch.from_numpy(_fabric.own_row_index(n, r, self.comm.world)).to(self.device)
+        return self._own_cache[key]
+
+    def rerank_features_fabric(self, fab, L, feats: torch.Tensor, q: int, k1: int, k2: int, lam: float, normalize: bool,
+                               score: tuple | None = None, want_final: bool = True):
+        """reranking.py:29-100 (+ evaluate.py:40-88 when `score`) on world > 1 ranks with the SYMMETRIC contraction
+        sharded by tile rows (snake ownership, fabric.py) and every exchange written into the peers' arenas by kernels:
+
+          prep (replicated) -> upper-triangle tiles of the own tile rows -> per-row bounds -> [stats] -> thresholds,
+          scatter selection over the stored tiles -> local top-K records to the row owners [inbox] -> final merge,
+          neighbour lists written to every rank [nbr] -> reciprocal sets (replicated) -> V rows of the own probes
+          (mirrored distances read from the owner's panel over NVLink) [V] -> query expansion (own rows [pool], or
+          replicated for small N) -> inverted index (replicated) -> Jaccard + lambda-mix (+ CMC/mAP) of the own queries
+          [scores].  [x] = one peer-memory exchange + one flag barrier; no host synchronisation, no NCCL call.
+        Returns what rerank_features returns; rows are this rank's queries in snake order (Engine._own_index(q))."""
+        cm = self.comm
+        r, P = cm.rank, cm.world
+        N, K = feats.shape[0], L.K
+        cap1 = L.cap1
+        nloc = _fabric.owned_rows(N, r, P)
+        st = _stream
+        peers = C.c_void_p(fab.peers.data_ptr())
+        with self.span("prep"):
+            allf = self.prepare(feats, normalize)
+        tiles, ntiles = self._tiles_for(N)
+        self.last_tiles = ntiles
+        panel = fab.view(L.panel, (L.nloc_max, L.ld), torch.float32)
+        stats_mine = fab.view(L.stats + r * L.stats_slot, (2, N), torch.int32)
+        cpitch = self.lib.reid_chunk_pitch(N)
+        ntl = _fabric.owned_tiles(N, r, P)
+        pitch_m = max(8, 8 * ntl)
+        with self.span("dist"):
+            cm_d = self._empty((max(nloc, 1), cpitch), torch.float32)
+            cm_m = self._empty((N, pitch_m), torch.float32)
+            _lib.call("reid_rowmax_init", _ptr(stats_mine[0]), N, st())
+            _lib.call("reid_dist_sharded", _ptr(allf.hi), _ptr(allf.lo), allf.hi.stride(0), _ptr(allf.sq), _ptr(allf.amax),
+                      N, allf.dp, _ptr(tiles), ntiles, P, _ptr(panel), L.ld, nloc, _ptr(stats_mine[0]), _ptr(cm_d),
+                      cpitch, _ptr(cm_m), pitch_m, st())
+        with self.span("select"):
+            _lib.call("reid_shard_tau", N, r, P, _ptr(cm_d), cpitch, _ptr(cm_m), pitch_m, K, _ptr(stats_mine[1]), st())
+        with self.span("x_stats"):
+            fab.bcast(L.stats + r * L.stats_slot, L.stats_slot)
+            fab.barrier()
+        with self.span("select"):
+            cap = 256
+            key_g = self._empty((N,), torch.int32)
+            key_l = self._empty((max(nloc, 1),), torch.int32)
+            dstar = self._empty((N,), torch.float32)
+            count = self._empty((N,), torch.int32)
+            cthr = self._empty((cpitch,), torch.int32)
+            pbuf = self._empty((N, cap), torch.int64)
+            stats_all = fab.view(L.stats, (P * L.stats_slot // 4,), torch.int32)
+            _lib.call("reid_shard_dstar", N, r, P, _ptr(stats_all), L.stats_slot // 4, _ptr(key_g), _ptr(key_l), _ptr(dstar), _ptr(count),
+                      _ptr(cthr), st())
+            _lib.call("reid_shard_push", _ptr(panel), nloc, r, P, N, L.ld, _ptr(cm_d), cpitch, _ptr(dstar), _ptr(cthr),
+                      _ptr(count), _ptr(pbuf), cap, st())
+            _lib.call("reid_shard_merge_local", _ptr(panel), L.ld, N, r, P, _ptr(cm_d), cpitch, _ptr(cm_m), pitch_m,
+                      _ptr(key_g), _ptr(dstar), _ptr(count), _ptr(pbuf), cap, K, peers, L.inbox, L.nloc_max, st())
+        with self.span("x_inbox"):
+            fab.barrier()
+        with self.span("select"):
+            inbox = fab.view(L.inbox, (P, L.nloc_max, K), torch.int64)
+            _lib.call("reid_shard_merge_final", nloc, r, P, K, _ptr(inbox), L.nloc_max, peers, L.nbr, None, st())
+        with self.span("x_nbr"):
+            fab.barrier()
+        nbr = fab.view(L.nbr, (N, K), torch.int32)
+        Vn = fab.view(L.vn, (N,), torch.int32)
+        Vc = fab.view(L.vc, (N, cap1), torch.int32)
+        Vv = fab.view(L.vv, (N, cap1), torch.float16)
+        with self.span("krecip"):
+            sets = self.krecip_sets(nbr, k1)
+            rfull, nfull, rhalf, nhalf = sets
+            panels = fab.peers_at(L.panel)
+            _lib.call("reid_krecip_V_sharded", _ptr(rfull), _ptr(nfull), _ptr(rhalf), _ptr(nhalf), r, P, nloc, k1,
+                      _ptr(panel), L.ld, _ptr(key_l), _ptr(panels), _ptr(Vc), _ptr(Vv), _ptr(Vn), st())
+        with self.span("x_V"):
+            fab.bcast_ell(L.vn, L.vc, L.vv, cap1, N)
+            fab.barrier()
+        if k2 == 1:
+            qoff = self._empty((N + 1,), torch.int64)
+            _lib.call("reid_ell_offsets", N, cap1, _ptr(qoff), st())
+            Qc, Qv, Qn = Vc.reshape(-1), Vv.reshape(-1), Vn
+            nnz_bound = N * cap1
+        elif L.pool_elems == 0:
+            with self.span("qe"):                 # small problem: every rank expands all rows itself, no exchange
+                Qc, Qv, qoff, Qn, nnz_bound = self.query_expansion(nbr, k2, Vc, Vv, Vn, N, 0, 1)
+        else:
+            with self.span("qe"):
+                ub = self._empty((N,), torch.int32)
+                _lib.call("reid_qe_bound", _ptr(nbr), K, k2, _ptr(Vn), 0, 1, N, _ptr(ub), st())
+                qoff = self._empty((N + 1,), torch.int64)
+                _lib.call("reid_exclusive_scan", _ptr(ub), N, _ptr(qoff), st())
+                Qn = fab.view(L.qn, (N,), torch.int32)
+                Qc = fab.view(L.qc, (L.pool_elems,), torch.int32)
+                Qv = fab.view(L.qv, (L.pool_elems,), torch.float16)
+                cap_sort = self._qe_cap_hint()
+                self._ubmax_pinned.copy_(ub.max().to(torch.int64).reshape(1), non_blocking=True)
+                self._ubmax_event.record()
+                self._ubmax_pending = True
+                _lib.call("reid_qe_k2_capped", _ptr(nbr), K, k2, _ptr(Vc), _ptr(Vv), _ptr(Vn), cap1, r, -P, nloc,
+                          _ptr(qoff), cap_sort, _ptr(Qc), _ptr(Qv), _ptr(Qn), st())
+            with self.span("x_qe"):
+                fab.bcast_pool(L.qn, L.qc, L.qv, qoff, N)
+                fab.barrier()
+            nnz_bound = L.pool_elems
+        with self.span("csc"):
+            csc = self.inverted_index(Qc, Qv, qoff, Qn, N, nnz_bound)
+        nq_local = _fabric.owned_rows(q, r, P)
+        if score is not None:
+            ids, max_rank = score
+            return self.jaccard_score(Qc, Qv, qoff, Qn, csc, panel, key_l, q, N, lam, nq_local, r, -P, ids, max_rank,
+                                      want_final, fabric=(fab, L))
+        with self.span("jaccard_mix"):
+            return self.jaccard_mix(Qc, Qv, qoff, Qn, csc, panel, key_l, q, N, lam, nq_local, r, -P)
+
     def rerank_features(self, feats: torch.Tensor, q: int, k1: int, k2: int, lam: float, normalize: bool,
                         detail: dict | None = None, score: tuple | None = None, want_final: bool = True):
         """feats: [N, d] float32 on the device, queries first (reranking.py:29-44 then the rest)."""
         cm = self.comm
         N = feats.shape[0]
+        if cm.world > 1 and detail is None:
+            fl = self._fabric_for(N, q, max(k1 + 1, k2), k1, k2, score[1] if score is not None else 50)
+            if fl is not None:
+                self.last_path = "fabric"
+                if N < max(k1 + 1, k2):
+                    raise NotImplementedError(f"re-ranking needs at least max(k1+1, k2) samples, got {N}")
+                return self.rerank_features_fabric(fl[0], fl[1], feats, q, k1, k2, lam, normalize, score=score,
+                                                   want_final=want_final)
+        self.last_path = "nccl" if cm.world > 1 else "single"
         with self.span("prep"):
             allf = self.prepare(feats, normalize)
             mine = allf if cm.world == 1 else allf.rows(slice(cm.rank, N, cm.world))
@@ -881,11 +1054,19 @@ class Engine:
                           lam: float, normalize: bool, max_rank: int = 50):
         """The evaluator's hot path end to end (evaluate.py:110-132 with reranking=True): features and ids of
         all N samples (queries first) -> (cmc, mAP, n_valid, ap, first_hit); the q x g matrix is never written."""
-        cm = self.comm
-        mine = slice(cm.rank, q, cm.world)
+        mine = self.own_queries(feats.shape[0], q, k1, k2, max_rank)
         ids = (pids[:q][mine].contiguous(), pids[q:].contiguous(), cams[:q][mine].contiguous(), cams[q:].contiguous())
         _, res = self.rerank_features(feats, q, k1, k2, lam, normalize, score=(ids, max_rank), want_final=False)
         return res
+
+    def own_queries(self, N: int, q: int, k1: int, k2: int, max_rank: int = 50) -> torch.Tensor:
+        """Global indices of the queries whose rows this rank produces in rerank_features / evaluate_reranked for this
+        problem, in the order of the returned rows: snake blocks on the peer-memory path, rank + l * world on the NCCL
+        path (collective on first use: the fabric is set up here)."""
+        cm = self.comm
+        if cm.world > 1 and self._fabric_for(N, q, max(k1 + 1, k2), k1, k2, max_rank) is not None:
+            return self._own_index(q)
+        return torch.arange(cm.rank, q, cm.world, device=self.device)
 
     # ------------------------------------------------------------------ K11 + K12
     def rank_rows(self, dist: torch.Tensor, g: int) -> torch.Tensor:
@@ -898,8 +1079,10 @@ class Engine:
                   _ptr(ranked), _stream())
         return ranked
 
-    def _score_common(self, launch, nq, max_rank, q_total, span="score"):
+    def _score_common(self, launch, nq, max_rank, q_total, span="score", fabric=None):
         cm = self.comm
+        if fabric is not None and cm.world > 1:
+            return self._score_fabric(launch, nq, max_rank, q_total, span, *fabric)
         ap = self._empty((nq,), torch.float64)
         first = self._empty((nq,), torch.int32)
         hist = self._zeros((max_rank,), torch.int32)
@@ -925,6 +1108,43 @@ class Engine:
         _lib.call("reid_score_finalize", _ptr(ap_all), q_all, _ptr(hist), max_rank, _ptr(nvalid), _ptr(cmc),
                   _ptr(mAP), _stream())
         return cmc, mAP, nvalid, ap_all, first_all
+
+    def _score_fabric(self, launch, nq, max_rank, q_total, span, fab, L):
+        """Scores of the own queries (snake order) written straight into this rank's slot of the arena, one copy to the
+        peers, one barrier; every rank then reads all slots in global query order."""
+        cm = self.comm
+        r, P = cm.rank, cm.world
+        assert max_rank <= L.max_rank and nq <= L.nq_max and q_total == L.q
+        base = L.scores + r * L.score_slot
+        ap = fab.view(base, (L.nq_max,), torch.float64)
+        first = fab.view(base + 8 * L.nq_max, (L.nq_max,), torch.int32)
+        tail = fab.view(base + 12 * L.nq_max, (L.max_rank + 1,), torch.int32)
+        tail.zero_()
+        hist, nvalid = tail[:max_rank], tail[L.max_rank:]
+        with self.span(span):
+            launch(ap, first, hist, nvalid)
+        with self.span("x_score"):
+            fab.bcast(base, L.score_slot)
+            fab.barrier()
+            key = ("score_gather", L.q, P, L.score_slot, L.nq_max)
+            if key not in self._own_cache:
+                pos64 = torch.empty((L.q,), dtype=torch.int64, device=self.device)
+                for p in range(P):
+                    idx = self._own_index(L.q, p)
+                    pos64[idx] = p * (L.score_slot // 8) + torch.arange(idx.numel(), device=self.device)
+                pos32 = (pos64 // (L.score_slot // 8)) * (L.score_slot // 4) + 2 * L.nq_max + pos64 % (L.score_slot // 8)
+                self._own_cache[key] = (pos64, pos32)
+            pos64, pos32 = self._own_cache[key]
+            ap_all = fab.view(L.scores, (P * L.score_slot // 8,), torch.float64)[pos64]
+            first_all = fab.view(L.scores, (P * L.score_slot // 4,), torch.int32)[pos32]
+            tails = fab.view(L.scores, (P, L.score_slot // 4), torch.int32)[:, 3 * L.nq_max: 3 * L.nq_max + L.max_rank + 1]
+            both = tails.sum(0, dtype=torch.int32)
+            hist_all, nvalid_all = both[:max_rank].contiguous(), both[L.max_rank:].contiguous()
+        cmc = self._empty((max_rank,), torch.float32)
+        mAP = self._empty((1,), torch.float64)
+        _lib.call("reid_score_finalize", _ptr(ap_all), L.q, _ptr(hist_all), max_rank, _ptr(nvalid_all), _ptr(cmc),
+                  _ptr(mAP), _stream())
+        return cmc, mAP, nvalid_all, ap_all, first_all
 
     def score(self, ranked: torch.Tensor, q_pids, g_pids, q_cams, g_cams, max_rank: int, q_total: int | None = None):
         """K12 on a materialised ranking.  ranked: this rank's [nq_local, g]; q_pids/q_cams: the

@@ -20,9 +20,21 @@ def _to_device_f32(x, device) -> torch.Tensor:
     return x.to(device, non_blocking=True).contiguous()
 
 
+_single = {}
+
+
+def _single_rank_engine(eng: _engine.Engine) -> _engine.Engine:
+    key = str(eng.device)
+    if key not in _single:
+        _single[key] = _engine.Engine(eng.device, comm=_engine.Comm(single=True))
+    return _single[key]
+
+
 def re_ranking_device(probFea, galFea, k1, k2, lambda_value, local_distmat=None, only_local=False,
                       eng: _engine.Engine | None = None) -> torch.Tensor:
-    """Same as :func:`re_ranking` but returns the device tensor [q_local, g] (float32)."""
+    """Same as :func:`re_ranking` but returns the device tensor [q_local, g] (float32).  On several ranks the rows are
+    this rank's queries: `Engine.own_queries(N, q, k1, k2)` names them (snake blocks on the peer-memory path, rank +
+    l * world on the NCCL path and for a caller-supplied local_distmat)."""
     eng = eng or _engine.default_engine()
     q = int(probFea.shape[0])
     g = int(galFea.shape[0])
@@ -30,11 +42,14 @@ def re_ranking_device(probFea, galFea, k1, k2, lambda_value, local_distmat=None,
     dev = eng.device
     cm = eng.comm
     if only_local or local_distmat is not None:
-        if cm.world != 1:
-            raise NotImplementedError("local_distmat is supported on a single rank only")
         L = _to_device_f32(local_distmat, dev)
         if L.shape != (N, N):
             raise ValueError(f"local_distmat must be {N}x{N}, got {tuple(L.shape)}")
+        if cm.world != 1:
+            # The caller's N x N matrix is replicated on every rank already, and nothing about it is sharded: every rank
+            # runs the one-rank path on it ("replicas") and keeps the rows of its own queries (rank, rank + world, ...),
+            # the same rows re_ranking returns on the NCCL path.
+            eng = _single_rank_engine(eng)
     if only_local:
         # the reference reads column i of the matrix for probe i (reranking.py:46)
         D = eng.transposed(L)
@@ -50,6 +65,8 @@ def re_ranking_device(probFea, galFea, k1, k2, lambda_value, local_distmat=None,
             eng.transposed(L, D, accumulate=True)
             key = eng.rowmax(D, N)
             final = eng.rerank_from_panel(D, key, q, N, k1, k2, lambda_value)
+    if (only_local or local_distmat is not None) and cm.world != 1:
+        final = final[cm.rank:: cm.world]
     return final[:, :g]
 
 

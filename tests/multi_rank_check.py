@@ -19,35 +19,85 @@ def main():
     rank = int(os.environ["RANK"])
     world = int(os.environ["WORLD_SIZE"])
     local = int(os.environ.get("LOCAL_RANK", rank))
+    # REID_MR_SAME_GPU=1: every rank on cuda:0, rendezvous over gloo -- the peer-memory path (CUDA IPC arenas, flag
+    # barriers, sharded symmetric contraction) is exercised functionally on a ONE-GPU box; the contexts time-slice, so a
+    # barrier costs a time slice, and the NCCL path (which refuses two ranks on one device) is skipped
+    same_gpu = os.environ.get("REID_MR_SAME_GPU", "0") == "1"
+    if same_gpu:
+        local = 0
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
-    dist.init_process_group("nccl", device_id=dev)
+    if same_gpu:
+        dist.init_process_group("gloo")
+    else:
+        dist.init_process_group("nccl", device_id=dev)
     engine = importlib.import_module("multimodal-reid_b200.engine")
     synth = importlib.import_module("multimodal-reid_b200.synth")
     multi = engine.Engine(dev)
     single = engine.Engine(dev, comm=engine.Comm(single=True))
-    single.symmetric = False        # compare against the full tile schedule: that is what every rank of a job runs
+    single.symmetric = False        # NCCL path: every rank runs the full tile schedule on its cyclic rows
+    single_sym = engine.Engine(dev, comm=engine.Comm(single=True))   # peer-memory path == the one-rank DEFAULT (symmetric
+    #                                                                  upper-only contraction): mirrored entries are copies
     assert multi.comm.world == world and single.comm.world == 1
-    for name, k1, k2, seed in (("small", 20, 6, 0), ("small", 50, 15, 1), ("mid", 20, 6, 2), ("tiny", 7, 1, 3)):
+    cases = [("small", 20, 6, 0), ("small", 50, 15, 1), ("mid", 20, 6, 2), ("tiny", 7, 1, 3)]
+    if os.environ.get("REID_MR_BIG", "0") == "1":
+        cases.append(("duke", 20, 6, 4))                 # 78 tile rows: every rank owns several, mirrored reads cross ranks
+    for name, k1, k2, seed in cases:
         sh = synth.SHAPES[name]
         qf, gf, qp, gp, qc, gc = synth.make(sh, seed)
         feats = torch.cat([qf, gf]).to(dev)
         q, g = sh.q, sh.g
+        N = q + g
         ids = [t.to(dev) for t in (qp, gp, qc, gc)]
-        ref = single.rerank_features(feats, q, k1, k2, 0.3, normalize=True)
-        mine = slice(rank, q, world)
-        for below in (300_000, 0):          # query expansion replicated on every rank / sharded + exchanged
-            multi.qe_replicate_below = below
-            got = multi.rerank_features(feats, q, k1, k2, 0.3, normalize=True)
-            assert torch.equal(got[:, :g], ref[mine, :g]), \
-                f"{name}: rank {rank} rows differ from the single-rank result (qe_replicate_below={below})"
-        r1 = single.evaluate_dist(ref, g, *ids, 50)
-        r2 = multi.evaluate_dist(got, g, ids[0][mine].contiguous(), ids[1], ids[2][mine].contiguous(), ids[3], 50,
-                                 q_total=q)
-        for a, b, what in zip(r1, r2, ("cmc", "mAP", "n_valid", "ap", "first_hit")):
-            assert torch.equal(a, b), f"{name}: {what} differs on rank {rank}"
-        if rank == 0:
-            print(f"{name} k1={k1} k2={k2}: {world}-rank result == 1-rank result, mAP {float(r2[1]):.6f}", flush=True)
+        pids, cams = torch.cat([qp, gp]).to(dev), torch.cat([qc, gc]).to(dev)
+        refs = {}
+        for nm, eng1 in (("fabric", single_sym), ("nccl", single)):
+            ref_ = eng1.rerank_features(feats, q, k1, k2, 0.3, normalize=True)
+            refs[nm] = (ref_, eng1.evaluate_dist(ref_, g, *ids, 50),
+                        eng1.evaluate_reranked(feats, q, pids, cams, k1, k2, 0.3, normalize=True))
+        # peer-memory path (symmetric contraction sharded by tile rows) and the NCCL all-gather path (cyclic rows)
+        for use_fabric in ((True,) if same_gpu else (True, False)):
+            multi.use_fabric = use_fabric
+            for below in (300_000, 0):          # query expansion replicated on every rank / sharded + exchanged
+                multi.qe_replicate_below = below
+                mine = multi.own_queries(N, q, k1, k2)
+                got = multi.rerank_features(feats, q, k1, k2, 0.3, normalize=True)
+                path = multi.last_path
+                assert path == ("fabric" if use_fabric and not multi._fabric_failed else "nccl"), path
+                ref, r1, e1 = refs[path]
+                assert got.shape[0] == mine.numel()
+                assert torch.equal(got[:, :g], ref[mine, :g]), \
+                    f"{name}: rank {rank} rows differ from the single-rank result ({path}, qe_replicate_below={below})"
+                e2 = multi.evaluate_reranked(feats, q, pids, cams, k1, k2, 0.3, normalize=True)
+                for a, b, what in zip(e1, e2, ("cmc", "mAP", "n_valid", "ap", "first_hit")):
+                    assert torch.equal(a, b), f"{name}: fused {what} differs on rank {rank} ({path}, below={below})"
+            if path == "nccl":
+                r2 = multi.evaluate_dist(got, g, ids[0][mine].contiguous(), ids[1], ids[2][mine].contiguous(), ids[3], 50,
+                                         q_total=q)
+                for a, b, what in zip(r1, r2, ("cmc", "mAP", "n_valid", "ap", "first_hit")):
+                    assert torch.equal(a, b), f"{name}: {what} differs on rank {rank}"
+            if rank == 0:
+                print(f"{name} k1={k1} k2={k2} [{path}]: {world}-rank result == 1-rank result, mAP {float(e2[1]):.6f}",
+                      flush=True)
+    multi.use_fabric = True
+    multi.qe_replicate_below = 300_000
+    # reranking.py:43-44 / :33-34 with a caller-supplied N x N matrix on several ranks: replicas, own rows returned
+    rr = importlib.import_module("multimodal-reid_b200.reranking")
+    sh = synth.SHAPES["tiny"]
+    qf, gf, *_ = synth.make(sh, 8)
+    fn = torch.nn.functional.normalize(torch.cat([qf, gf]), dim=1, p=2)
+    Lm = torch.rand((fn.shape[0], fn.shape[0]), generator=torch.Generator().manual_seed(3)) * 0.05
+    for only in (False, True):
+        a = rr.re_ranking_device(fn[: sh.q], fn[sh.q:], 20, 6, 0.3, local_distmat=Lm, only_local=only, eng=multi)
+        b = rr.re_ranking_device(fn[: sh.q], fn[sh.q:], 20, 6, 0.3, local_distmat=Lm, only_local=only, eng=single_sym)
+        assert torch.equal(a, b[rank::world]), f"local_distmat (only_local={only}) differs on rank {rank}"
+    if rank == 0:
+        print(f"local_distmat on {world} ranks == 1 rank (additive and only_local)", flush=True)
+    if same_gpu:
+        assert not multi._fabric_failed, multi.fabric.last_error
+        dist.barrier()
+        dist.destroy_process_group()
+        return
     # the drop-in evaluator on host batches: sharded upload + all-gather == replicated upload, bit for bit
     import contextlib
     import io
