@@ -79,6 +79,12 @@ REID_API int reid_prepare_features(const float* X, int n, int d, int64_t ld_x, i
  * max|x| over the WHOLE matrix and is used as is -- rows prepared in separate calls then share one scaling exponent */
 REID_API int reid_prepare_rows(const float* X, int n, int d, int64_t ld_x, int normalize, float* x32, reid_half* hi,
                       reid_half* lo, int dpad, float* sq, float* nrm, uint32_t* amax, int preset_amax, void* stream);
+/* the same with the flip-TTA average of the callers fused in front (prompt_learning.py:775-776,
+ * zero_shot_learning.py:121-125: `(embeddings + embeddings_augmented) / 2` before get_cmc_map): every row is
+ * (X[i] + X_aug[i]) / 2 in float32 -- one rounded add, an exact halving -- formed on the fly, then treated as above */
+REID_API int reid_prepare_rows_tta(const float* X, const float* X_aug, int n, int d, int64_t ld_x, int64_t ld_aug,
+                          int normalize, float* x32, reid_half* hi, reid_half* lo, int dpad, float* sq, float* nrm,
+                          uint32_t* amax, int preset_amax, void* stream);
 
 /* K1/K2/K3  evaluate.py:7-26, reranking.py:36-41.  out[i, j] for A rows i < m, B rows j < n.
  * metric 0: (ra[i] + rb[j]) - 2 a.b with ra/rb = squared norms; metric 1: arccos(clip(a.b *

@@ -148,8 +148,18 @@ int reid_prepare_rows(const float* X, int n, int d, int64_t ld_x, int normalize,
   ENTER();
   REID_REQUIRE(n >= 0 && d >= 1 && ld_x >= d, "prepare_rows: bad shape n=%d d=%d ld=%lld", n, d, (long long)ld_x);
   REID_REQUIRE(dpad >= d && dpad % 64 == 0, "prepare_rows: dpad=%d must be a multiple of 64 >= d=%d", dpad, d);
-  return launch_prep_rows(X, n, d, ld_x, normalize, x32, H(hi), H(lo), dpad, sq, nrm, amax, preset_amax ? 1 : 0,
-                          S(stream));
+  return launch_prep_rows(X, nullptr, 0, n, d, ld_x, normalize, x32, H(hi), H(lo), dpad, sq, nrm, amax,
+                          preset_amax ? 1 : 0, S(stream));
+}
+
+int reid_prepare_rows_tta(const float* X, const float* X_aug, int n, int d, int64_t ld_x, int64_t ld_aug, int normalize,
+                          float* x32, reid_half* hi, reid_half* lo, int dpad, float* sq, float* nrm, uint32_t* amax,
+                          int preset_amax, void* stream) {
+  ENTER();
+  REID_REQUIRE(n >= 0 && d >= 1 && ld_x >= d && ld_aug >= d && X_aug, "prepare_rows_tta: bad shape n=%d d=%d", n, d);
+  REID_REQUIRE(dpad >= d && dpad % 64 == 0, "prepare_rows_tta: dpad=%d must be a multiple of 64 >= d=%d", dpad, d);
+  return launch_prep_rows(X, X_aug, ld_aug, n, d, ld_x, normalize, x32, H(hi), H(lo), dpad, sq, nrm, amax,
+                          preset_amax ? 1 : 0, S(stream));
 }
 
 int reid_dist_clock_probe(int64_t* host_out4) {

@@ -18,8 +18,9 @@ static inline int padded_width(int d) { return (d + 63) / 64 * 64; }   // tensor
 // row pitch of the 32-column chunk minima: 8 slots per 256-column tile, so a tile's slots are 16-byte aligned groups
 static inline int chunk_pitch(int n) { return 8 * ((n + 255) / 256); }
 
-int launch_prep_rows(const float* X, int n, int d, long long ld_x, int normalize, float* x32, __half* hi,
-                     __half* lo, int dp, float* sq, float* nrm, uint32_t* amax, int preset_amax, cudaStream_t s);
+int launch_prep_rows(const float* X, const float* X2, long long ld_x2, int n, int d, long long ld_x, int normalize,
+                     float* x32, __half* hi, __half* lo, int dp, float* sq, float* nrm, uint32_t* amax, int preset_amax,
+                     cudaStream_t s);
 int launch_prep(const float* X, int n, int d, long long ld_x, int normalize, float* x32, __half* hi, __half* lo,
                 int dp, float* sq, float* nrm, uint32_t* amax, cudaStream_t s);
 int launch_dist_simt(const float* A, long long lda, const float* ra, int m, const float* B, long long ldb,

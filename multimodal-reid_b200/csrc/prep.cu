@@ -11,7 +11,11 @@
 namespace reid {
 
 // pass 1: one warp per row -> x32 (normalised, padded), sq, nrm, global max|x| (float bits)
-__global__ void __launch_bounds__(256) prep_rows_kernel(const float* __restrict__ X, int n, int d,
+// X2 != NULL: the row is the flip-TTA average (X + X2) / 2 of two embedding passes (prompt_learning.py:775-776,
+// zero_shot_learning.py:121-125: `(emb + emb_aug) / 2` in float32 -- one rounded add, an exact halving), formed on
+// the fly: the averaged matrix is never written or re-read.
+__global__ void __launch_bounds__(256) prep_rows_kernel(const float* __restrict__ X, const float* __restrict__ X2,
+                                                        long long ld_x2, int n, int d,
                                                         long long ld_x, int normalize,
                                                         float* __restrict__ x32, int dp,
                                                         float* __restrict__ sq, float* __restrict__ nrm,
@@ -20,9 +24,11 @@ __global__ void __launch_bounds__(256) prep_rows_kernel(const float* __restrict_
   if (row >= n) return;
   const int lane = lane_id();
   const float* x = X + (long long)row * ld_x;
+  const float* x2 = X2 ? X2 + (long long)row * ld_x2 : nullptr;
+  auto at = [&](int k) { return x2 ? __fmul_rn(__fadd_rn(x[k], x2[k]), 0.5f) : x[k]; };
   float ss = 0.0f;
   for (int k = lane; k < d; k += 32) {
-    float v = x[k];
+    float v = at(k);
     ss = __fmaf_rn(v, v, ss);
   }
 #pragma unroll
@@ -33,7 +39,7 @@ __global__ void __launch_bounds__(256) prep_rows_kernel(const float* __restrict_
   float* o32 = x32 + (long long)row * dp;
   for (int k = lane; k < dp; k += 32) {
     float y = 0.0f;
-    if (k < d) y = normalize ? __fdiv_rn(x[k], denom) : x[k];
+    if (k < d) y = normalize ? __fdiv_rn(at(k), denom) : at(k);
     o32[k] = y;
     ss2 = __fmaf_rn(y, y, ss2);
     mx = fmaxf(mx, fabsf(y));
@@ -84,17 +90,18 @@ __global__ void __launch_bounds__(256) split_f16_kernel(const float* __restrict_
 
 int launch_prep(const float* X, int n, int d, long long ld_x, int normalize, float* x32, __half* hi,
                 __half* lo, int dp, float* sq, float* nrm, uint32_t* amax, cudaStream_t s) {
-  return launch_prep_rows(X, n, d, ld_x, normalize, x32, hi, lo, dp, sq, nrm, amax, 0, s);
+  return launch_prep_rows(X, nullptr, 0, n, d, ld_x, normalize, x32, hi, lo, dp, sq, nrm, amax, 0, s);
 }
 
 // preset_amax: *amax already holds the bits of a bound on max|x| of the WHOLE matrix these rows belong to (the streamed
 // evaluator prepares the rows chunk by chunk, so the matrix-wide maximum is not known yet); it is used as is.
-int launch_prep_rows(const float* X, int n, int d, long long ld_x, int normalize, float* x32, __half* hi,
-                     __half* lo, int dp, float* sq, float* nrm, uint32_t* amax, int preset_amax, cudaStream_t s) {
+int launch_prep_rows(const float* X, const float* X2, long long ld_x2, int n, int d, long long ld_x, int normalize,
+                     float* x32, __half* hi, __half* lo, int dp, float* sq, float* nrm, uint32_t* amax, int preset_amax,
+                     cudaStream_t s) {
   if (!preset_amax) REID_CUDA(cudaMemsetAsync(amax, 0, sizeof(uint32_t), s));
   if (n == 0) return REID_OK;
   const int wpb = 8;
-  prep_rows_kernel<<<cdiv(n, wpb), wpb * 32, 0, s>>>(X, n, d, ld_x, normalize, x32, dp, sq, nrm,
+  prep_rows_kernel<<<cdiv(n, wpb), wpb * 32, 0, s>>>(X, X2, ld_x2, n, d, ld_x, normalize, x32, dp, sq, nrm,
                                                      preset_amax ? nullptr : amax);
   int rc = check_launch("prep_rows_kernel");
   if (rc) return rc;

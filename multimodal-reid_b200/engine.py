@@ -276,9 +276,22 @@ class Engine:
         return torch.zeros(shape, dtype=dtype, device=self.device)
 
     # ------------------------------------------------------------------ K13
-    def prepare(self, X: torch.Tensor, normalize: bool) -> Features:
-        """X: [n, d] float32 on the device (row-major)."""
+    def prepare(self, X: torch.Tensor, normalize: bool, X_aug: torch.Tensor | None = None) -> Features:
+        """X: [n, d] float32 on the device (row-major).  X_aug (same shape): the second embedding pass of the callers'
+        flip test-time augmentation; rows become (X + X_aug) / 2 inside the prologue kernel (reid_prepare_rows_tta)."""
         assert X.is_cuda and X.dtype == torch.float32 and X.dim() == 2 and X.stride(1) == 1
+        if X_aug is not None:
+            assert X_aug.is_cuda and X_aug.dtype == torch.float32 and X_aug.shape == X.shape and X_aug.stride(1) == 1
+            n, d = X.shape
+            dp = self.lib.reid_padded_width(d)
+            x32, hi, lo = (self._empty((n, dp), t) for t in (torch.float32, torch.float16, torch.float16))
+            sq, nrm = self._empty((n,), torch.float32), self._empty((n,), torch.float32)
+            amax = (torch.full((1,), _ONE_BITS, dtype=torch.int32, device=self.device) if normalize
+                    else self._empty((1,), torch.int32))
+            _lib.call("reid_prepare_rows_tta", _ptr(X), _ptr(X_aug), n, d, X.stride(0), X_aug.stride(0),
+                      1 if normalize else 0, _ptr(x32), _ptr(hi), _ptr(lo), dp, _ptr(sq), _ptr(nrm), _ptr(amax),
+                      1 if normalize else 0, _stream())
+            return Features(x32, hi, lo, sq, nrm, amax, d)
         n, d = X.shape
         dp = self.lib.reid_padded_width(d)
         x32 = self._empty((n, dp), torch.float32)
@@ -903,7 +916,7 @@ class Engine:
         return self._own_cache[key]
 
     def rerank_features_fabric(self, fab, L, feats: torch.Tensor, q: int, k1: int, k2: int, lam: float, normalize: bool,
-                               score: tuple | None = None, want_final: bool = True):
+                               score: tuple | None = None, want_final: bool = True, feats_aug=None):
         """reranking.py:29-100 (+ evaluate.py:40-88 when `score`) on world > 1 ranks with the SYMMETRIC contraction
         sharded by tile rows (snake ownership, fabric.py) and every exchange written into the peers' arenas by kernels:
 
@@ -922,7 +935,7 @@ class Engine:
         st = _stream
         peers = C.c_void_p(fab.peers.data_ptr())
         with self.span("prep"):
-            allf = self.prepare(feats, normalize)
+            allf = self.prepare(feats, normalize, feats_aug)
         tiles, ntiles = self._tiles_for(N)
         self.last_tiles = ntiles
         panel = fab.view(L.panel, (L.nloc_max, L.ld), torch.float32)
@@ -1015,8 +1028,10 @@ class Engine:
             return self.jaccard_mix(Qc, Qv, qoff, Qn, csc, panel, key_l, q, N, lam, nq_local, r, -P)
 
     def rerank_features(self, feats: torch.Tensor, q: int, k1: int, k2: int, lam: float, normalize: bool,
-                        detail: dict | None = None, score: tuple | None = None, want_final: bool = True):
-        """feats: [N, d] float32 on the device, queries first (reranking.py:29-44 then the rest)."""
+                        detail: dict | None = None, score: tuple | None = None, want_final: bool = True,
+                        feats_aug: torch.Tensor | None = None):
+        """feats: [N, d] float32 on the device, queries first (reranking.py:29-44 then the rest).  feats_aug: optional
+        second embedding pass; the rows used are (feats + feats_aug) / 2 (the callers' flip-TTA average, fused)."""
         cm = self.comm
         N = feats.shape[0]
         if cm.world > 1 and detail is None:
@@ -1026,10 +1041,10 @@ class Engine:
                 if N < max(k1 + 1, k2):
                     raise NotImplementedError(f"re-ranking needs at least max(k1+1, k2) samples, got {N}")
                 return self.rerank_features_fabric(fl[0], fl[1], feats, q, k1, k2, lam, normalize, score=score,
-                                                   want_final=want_final)
+                                                   want_final=want_final, feats_aug=feats_aug)
         self.last_path = "nccl" if cm.world > 1 else "single"
         with self.span("prep"):
-            allf = self.prepare(feats, normalize)
+            allf = self.prepare(feats, normalize, feats_aug)
             mine = allf if cm.world == 1 else allf.rows(slice(cm.rank, N, cm.world))
         with self.span("dist"):
             tri = False
@@ -1051,12 +1066,13 @@ class Engine:
                                       want_final=want_final, upper_only=tri)
 
     def evaluate_reranked(self, feats: torch.Tensor, q: int, pids: torch.Tensor, cams: torch.Tensor, k1: int, k2: int,
-                          lam: float, normalize: bool, max_rank: int = 50):
+                          lam: float, normalize: bool, max_rank: int = 50, feats_aug: torch.Tensor | None = None):
         """The evaluator's hot path end to end (evaluate.py:110-132 with reranking=True): features and ids of
         all N samples (queries first) -> (cmc, mAP, n_valid, ap, first_hit); the q x g matrix is never written."""
         mine = self.own_queries(feats.shape[0], q, k1, k2, max_rank)
         ids = (pids[:q][mine].contiguous(), pids[q:].contiguous(), cams[:q][mine].contiguous(), cams[q:].contiguous())
-        _, res = self.rerank_features(feats, q, k1, k2, lam, normalize, score=(ids, max_rank), want_final=False)
+        _, res = self.rerank_features(feats, q, k1, k2, lam, normalize, score=(ids, max_rank), want_final=False,
+                                      feats_aug=feats_aug)
         return res
 
     def own_queries(self, N: int, q: int, k1: int, k2: int, max_rank: int = 50) -> torch.Tensor:

@@ -135,6 +135,7 @@ class R1_mAP_eval():
 
     def reset(self):
         self.feats = []
+        self.feats_aug = []          # extension: second (flipped) embedding pass, see update()
         self.pids = []
         self.camids = []
 
@@ -156,9 +157,16 @@ class R1_mAP_eval():
     def camids(self, value):
         self._cam_store = _IdStore(value)
 
-    def update(self, output):  # called once for each batch
+    def update(self, output, feat_aug=None):  # called once for each batch
+        """evaluate.py:104-108.  Extension (keyword, default = the reference's behaviour): `feat_aug`, the embeddings
+        of the horizontally flipped batch.  The reference's scripts average the two passes themselves before calling
+        the evaluator (prompt_learning.py:775-776: `(embeddings + embeddings_augmented) / 2`); given both, compute()
+        forms the average inside the prologue kernel instead (same float32 arithmetic, one pass less over N x d)."""
         feat, pid, camid = output
         self.feats.append(feat.detach())
+        if feat_aug is not None:
+            assert tuple(feat_aug.shape) == tuple(feat.shape), "feat_aug must match feat"
+            self.feats_aug.append(feat_aug.detach())
         self._pid_store.extend(pid)
         self._cam_store.extend(camid)
 
@@ -167,7 +175,10 @@ class R1_mAP_eval():
         dev = eng.device
         # Features still in host memory + re-ranking on one rank: the copy is streamed under the contraction
         # (engine.prepare_dist_streamed) instead of being finished first.  Same bits either way.
-        streamed = (self.reranking and self.feat_norm and eng.stream_h2d and eng.comm.world == 1
+        tta = len(getattr(self, "feats_aug", [])) > 0
+        if tta:
+            assert len(self.feats_aug) == len(self.feats), "feat_aug must be given for every batch or for none"
+        streamed = (not tta and self.reranking and self.feat_norm and eng.stream_h2d and eng.comm.world == 1
                     and eng.engine != _engine.ENGINES["simt"] and eng.symmetric and eng.upper_only
                     and len(self.feats) > 0
                     and all(isinstance(f, torch.Tensor) and not f.is_cuda and f.dtype == torch.float32 and f.dim() == 2
@@ -178,13 +189,14 @@ class R1_mAP_eval():
         if streamed:
             feats = None
             N = sum(int(f.shape[0]) for f in self.feats)
-        elif host_f32 and eng.comm.world > 1 and eng.shard_h2d:
+        elif host_f32 and eng.comm.world > 1 and eng.shard_h2d and not tta:
             # several ranks, features in host memory: every rank uploads 1/world of the rows, NCCL all-gather does the rest
             feats = eng.comm.upload_sharded(self.feats, dev)
             N = feats.shape[0]
         else:
             feats = torch.cat([_to_device_f32(f, dev) for f in self.feats], dim=0)
             N = feats.shape[0]
+        feats_aug = torch.cat([_to_device_f32(f, dev) for f in self.feats_aug], dim=0) if tta else None
         if self.feat_norm:
             print("The test feature is normalized")
         q = self.num_query
@@ -203,14 +215,14 @@ class R1_mAP_eval():
                 cmc, mAP, nvalid, _, _ = eng.evaluate_reranked_host(self.feats, q, pids, camids, k1, k2, lam, max_rank)
             else:
                 cmc, mAP, nvalid, _, _ = eng.evaluate_reranked(feats, q, pids, camids, k1, k2, lam, self.feat_norm,
-                                                               max_rank)
+                                                               max_rank, feats_aug=feats_aug)
             assert int(nvalid.item()) > 0, "Error: all query identities do not appear in gallery"
             cmc, mAP = cmc.cpu().numpy(), np.float64(mAP.item())
             print("Rank@{:d}:{:.1%}, Rank@{:d}:{:.1%}, Rank@{:d}:{:.1%}, mAP:{:.1%}".format(1, cmc[0], 5, cmc[4], 10, cmc[9], mAP))
             return cmc, mAP
         else:
             print('=> Computing DistMat with euclidean_distance')
-            allf = eng.prepare(feats, self.feat_norm)
+            allf = eng.prepare(feats, self.feat_norm, feats_aug)
             dist, _ = eng.dist(allf.rows(slice(eng.comm.rank, q, eng.comm.world)), allf.rows(slice(q, N)),
                                _engine.METRIC_SQEUCLIDEAN)
         # evaluate.py:132 does not forward self.max_rank: always 50

@@ -152,3 +152,36 @@ def test_two_ranks_match_one_rank():
                         "--master-addr", "127.0.0.1", "--master-port", "29533",
                         os.path.join(root, "tests", "multi_rank_check.py")], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+def test_flip_tta_average_fused_into_the_prologue(api, eng, synth, oracle):
+    """the callers' `(embeddings + embeddings_augmented) / 2` (prompt_learning.py:775-776) formed inside
+    the prologue kernel: same bits as averaging first, and the evaluator fed both passes == the oracle on the average."""
+    evaluate, _ = api
+    sh = synth.SHAPES["small"]
+    qf, gf, qp, gp, qc, gc = synth.make(sh, 7)
+    a = torch.cat([qf, gf])
+    b = a + 0.3 * torch.randn(a.shape, generator=torch.Generator().manual_seed(1))
+    avg = (a + b) / 2
+    fa = eng.prepare(a.cuda(), True, b.cuda())
+    fb = eng.prepare(avg.cuda(), True)
+    for x, y in ((fa.x32, fb.x32), (fa.hi, fb.hi), (fa.lo, fb.lo), (fa.sq, fb.sq), (fa.nrm, fb.nrm)):
+        assert torch.equal(x, y)
+    pids, cams = torch.cat([qp, gp]), torch.cat([qc, gc])
+    for rerank in (False, True):
+        res = []
+        for fused in (True, False):
+            e = evaluate.R1_mAP_eval(sh.q, feat_norm=True, reranking=rerank, rerank_params=(20, 6, 0.3))
+            e.reset()
+            for s0 in range(0, a.shape[0], 500):          # batches, like the scripts' loaders
+                sl = slice(s0, s0 + 500)
+                if fused:
+                    e.update((a[sl], pids[sl], cams[sl]), feat_aug=b[sl])
+                else:
+                    e.update((avg[sl], pids[sl], cams[sl]))
+            with contextlib.redirect_stdout(io.StringIO()):
+                res.append(e.compute())
+        assert (res[0][0] == res[1][0]).all() and res[0][1] == res[1][1]
+        c_o, m_o = oracle.evaluate_features(avg.numpy(), pids.numpy(), cams.numpy(), sh.q, True, rerank,
+                                            k1=20, k2=6, lam=0.3)
+        assert np.abs(res[0][0] - c_o).max() <= METRIC_TOL and abs(res[0][1] - m_o) <= METRIC_TOL
