@@ -205,9 +205,9 @@ overlap_sparse_kernel(const int* __restrict__ Qc, const __half* __restrict__ Qv,
 // ---------------------------------------------------------------------------------------------
 constexpr int SS_T = 256;
 constexpr int SS_CAP = 512;     // identity-group entries staged / matches ranked per pass over the row
-constexpr int SS_STG = 256;     // floats of the query's row of D per ring stage (1 KB, one cp.async.bulk)
-constexpr int SS_NST = 4;       // ring stages per warp: SS_NST - 1 bulk copies in flight (8 warps: 24 KB per CTA)
-constexpr int SS_NEED = 8192;   // segment flags (bytes): rows of up to 2 M columns
+constexpr int SS_STG = 2048;    // floats of the query's row of D per ring stage (8 KB, one cp.async.bulk)
+constexpr int SS_NST = 4;       // ring stages: SS_NST - 1 bulk copies (24 KB) in flight per CTA
+constexpr int SS_NEED = 1024;   // stage flags (bytes): rows of up to 2 M columns
 constexpr int SS_NB = 2048;     // cells of the raw-D histogram of untouched entries below the worst match's threshold
 
 struct SsLayout {               // after bitmap + prefix
@@ -221,7 +221,7 @@ struct SsLayout {               // after bitmap + prefix
   static constexpr size_t queue = (thrB + SS_CAP * 4 + 15) & ~(size_t)15;
   static constexpr size_t hist = queue + (size_t)SS_NEED;                          // int[SS_NB]
   static constexpr size_t ring = (hist + (size_t)SS_NB * 4 + 127) & ~(size_t)127;  // float[SS_NST][SS_STG]
-  static constexpr size_t bytes = ring + (size_t)(SS_T / 32) * SS_NST * SS_STG * 4;
+  static constexpr size_t bytes = ring + (size_t)SS_NST * SS_STG * 4;
 };
 
 // overlap value of probe g from the packed record (0 when the query does not touch g)
@@ -302,7 +302,7 @@ score_sparse_kernel(const unsigned char* __restrict__ recs, const int* __restric
   float* thrB = reinterpret_cast<float*>(aux + SsLayout::thrB);
   int* hist = reinterpret_cast<int*>(aux + SsLayout::hist);
   __shared__ int s_lo, s_len, s_total, s_cnt, s_first, s_zfast;
-  __shared__ __align__(8) unsigned long long s_full[SS_T / 32][SS_NST];   // ring barriers: one phase per bulk copy
+  __shared__ __align__(8) unsigned long long s_full[SS_NST];      // ring barriers: one phase per bulk copy
 
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   const unsigned char* rec = recs + (size_t)qi * R.bytes;
@@ -314,11 +314,11 @@ score_sparse_kernel(const unsigned char* __restrict__ recs, const int* __restric
     for (int i = tid; i < used; i += T) dst[i] = __ldg(src + i);
   }
   if (tid == 0) {
-    for (int i = 0; i < (SS_T / 32) * SS_NST; ++i) ss_mbar_init(ss_smem_u32(&s_full[0][0] + i), 1);
+    for (int i = 0; i < SS_NST; ++i) ss_mbar_init(ss_smem_u32(&s_full[i]), 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  int ring_seq = 0;                                    // bulk copies this warp has consumed so far
-  int ring_pseq = 0;                                   // ... requested so far
+  int ring_seq = 0;                                    // bulk copies consumed so far (all threads count alike)
+  int ring_pseq = 0;                                   // ... issued so far (thread 0)
   const float m = ordered_int2f(rowmax_key[qi]);
   const float* drow = D + (long long)qi * ld;
   const float* cm_row = chunk_min ? chunk_min + (long long)qi * cm_pitch : nullptr;   // minima of the row's 32-column chunks
@@ -495,58 +495,59 @@ score_sparse_kernel(const unsigned char* __restrict__ recs, const int* __restric
       }
     } else {
       const float dthr = thrB[P - 1];                              // untouched and D > dthr: after every match
-      // The gallery part of the row goes through per-warp rings of SS_NST shared-memory stages of SS_STG floats (1 KB),
-      // filled by cp.async.bulk (lane 0 issues, one mbarrier per stage counts the bytes): warp w owns the segments w,
-      // w + 8, ... of the row, keeps SS_NST - 1 copies in flight whatever it is doing, and never waits for another warp
-      // (a CTA-wide barrier per stage made every stage pay the slowest warp's atomics).  Round 1 kept two register-
-      // staged loads per thread in flight: 42 % of HBM.  A segment is skipped altogether when the query touches none of
-      // its columns and every 32-column chunk minimum recorded by the contraction lies above dthr.
+      // The gallery part of the row goes through a ring of SS_NST shared-memory stages of SS_STG floats, filled by
+      // cp.async.bulk (thread 0 issues, an mbarrier per stage counts the bytes): SS_NST - 1 copies = 24 KB are in flight
+      // per CTA whatever the consumers are doing, which is what a latency-bound streaming kernel was missing (round 1:
+      // 42 % of HBM with two register-staged loads per thread in flight).  A stage is skipped altogether when the query
+      // touches none of its columns and every 32-column chunk minimum recorded by the contraction lies above dthr.
       const int gs0 = q & ~31;                                    // first staged column (128-byte aligned)
       const int ldN = min((N + 31) & ~31, (int)min(ld, (long long)0x7fffffe0));   // staged columns end here (inside the row pitch)
-      const int nseg = (ldN - gs0 + SS_STG - 1) / SS_STG;
-      unsigned char* need = aux + SsLayout::queue;                // [nseg] segment flags
-      float* ring = reinterpret_cast<float*>(aux + SsLayout::ring) + w * SS_NST * SS_STG;
+      const int nst = (ldN - gs0 + SS_STG - 1) / SS_STG;
+      unsigned char* need = aux + SsLayout::queue;                // [nst] stage flags
+      float* ring = reinterpret_cast<float*>(aux + SsLayout::ring);
       {
         const int nch = ldN >> 5;
-        constexpr int CPS = SS_STG / 32;                           // chunks (= bitmap words) per segment: 8
-        for (int k0 = 0; k0 < nseg; k0 += T / CPS) {
-          const int k = k0 + tid / CPS;
-          const int c = (gs0 >> 5) + k * CPS + (tid % CPS);
-          const bool on = k < nseg && c < nch && (bm[c] != 0u || cm_row == nullptr || __ldg(cm_row + c) <= dthr);
-          const unsigned b = __ballot_sync(FULL, on);
-          if ((tid % CPS) == 0 && k < nseg) need[k] = ((b >> (lane & ~(CPS - 1))) & ((1u << CPS) - 1u)) ? 1 : 0;
+        for (int k = w; k < nst; k += T / 32) {
+          bool on = false;
+#pragma unroll
+          for (int u = 0; u < SS_STG / 32 / 32; ++u) {
+            const int c = (gs0 >> 5) + k * (SS_STG / 32) + u * 32 + lane;       // chunk == bitmap word
+            if (c < nch) on |= bm[c] != 0u || cm_row == nullptr || __ldg(cm_row + c) <= dthr;
+          }
+          on = __any_sync(FULL, on);
+          if (lane == 0) need[k] = on ? 1 : 0;
         }
       }
       __syncthreads();
-      int pj = w;                                                 // producer cursor: next segment to request
+      int pk = 0;                                                 // producer cursor (thread 0)
       auto produce = [&]() {
-        while (pj < nseg && !need[pj]) pj += T / 32;
-        if (pj < nseg) {
-          if (lane == 0) {
-            const int start = gs0 + pj * SS_STG;
-            const uint32_t bytes = (uint32_t)min(SS_STG, ldN - start) * 4u;
-            const uint32_t bar = ss_smem_u32(&s_full[w][ring_pseq % SS_NST]);
-            ss_mbar_expect_tx(bar, bytes);
-            ss_bulk_g2s(ss_smem_u32(ring + (ring_pseq % SS_NST) * SS_STG), drow + start, bytes, bar);
-          }
+        while (pk < nst && !need[pk]) ++pk;
+        if (pk < nst) {
+          const int start = gs0 + pk * SS_STG;
+          const uint32_t bytes = (uint32_t)min(SS_STG, ldN - start) * 4u;
+          const int slot = ring_pseq % SS_NST;
+          const uint32_t bar = ss_smem_u32(&s_full[slot]);
+          ss_mbar_expect_tx(bar, bytes);
+          ss_bulk_g2s(ss_smem_u32(ring + slot * SS_STG), drow + start, bytes, bar);
           ++ring_pseq;
-          pj += T / 32;
+          ++pk;
         }
       };
-      for (int i = 0; i < SS_NST - 1; ++i) produce();
-      for (int k = w; k < nseg; k += T / 32) {
+      if (tid == 0)
+        for (int i = 0; i < SS_NST - 1; ++i) produce();
+      for (int k = 0; k < nst; ++k) {
         if (!need[k]) continue;
         const int slot = ring_seq % SS_NST;
-        ss_mbar_wait(ss_smem_u32(&s_full[w][slot]), (uint32_t)(ring_seq / SS_NST) & 1u);
+        ss_mbar_wait(ss_smem_u32(&s_full[slot]), (uint32_t)(ring_seq / SS_NST) & 1u);
         ++ring_seq;
         const float4* st4 = reinterpret_cast<const float4*>(ring + slot * SS_STG);
         const int start = gs0 + k * SS_STG;
-        // two groups of 4 consecutive entries per lane (float4 index lane and lane + 32: conflict-free)
+        // two groups of 4 consecutive entries per thread (float4 index tid and tid + 256: conflict-free)
 #pragma unroll
-        for (int h = 0; h < SS_STG / 4 / 32; ++h) {
-          const int g = start + (h * 32 + lane) * 4;
+        for (int h = 0; h < SS_STG / 4 / T; ++h) {
+          const int g = start + (h * T + tid) * 4;
           if (g >= N) continue;
-          const float4 x = st4[h * 32 + lane];
+          const float4 x = st4[h * T + tid];
           unsigned vm = 0xfu;                                     // gallery columns of this group
           if (g < q) vm = g + 4 <= q ? 0u : (0xfu << (q - g)) & 0xfu;
           if (g + 4 > N) vm &= 0xfu >> (g + 4 - N);
@@ -555,19 +556,16 @@ score_sparse_kernel(const unsigned char* __restrict__ recs, const int* __restric
           const unsigned um = vm & ~b4;                           // untouched: ranked by raw distance
           unsigned tb = vm & b4;                                  // touched by the query's Jaccard term
           const float dv[4] = {x.x, x.y, x.z, x.w};
-          unsigned mz = 0;
           if (um && fminf(fminf(x.x, x.y), fminf(x.z, x.w)) <= dthr) {
 #pragma unroll
-            for (int e = 0; e < 4; ++e) {                         // independent atomics: all in flight together
-              if (((um >> e) & 1u) && dv[e] <= dthr)
-                if (atomicAdd(hist + ss_cell(dv[e], hscale), 1) < 0) mz |= 1u << e;   // a cell that holds a threshold
+            for (int e = 0; e < 4; ++e) {
+              if (((um >> e) & 1u) && dv[e] <= dthr) {
+                if (atomicAdd(hist + ss_cell(dv[e], hscale), 1) < 0) {   // a cell that holds a threshold: ranked exactly
+                  const int bin = ss_zero_bin(dv[e], g + e - q, thrA, thrB, mk, P);
+                  if (bin < P) bin_add(hv, bin);
+                }
+              }
             }
-          }
-          while (mz) {                                            // rare: ranked exactly against the thresholds
-            const int e = __ffs(mz) - 1;
-            mz &= mz - 1;
-            const int bin = ss_zero_bin(dv[e], g + e - q, thrA, thrB, mk, P);
-            if (bin < P) bin_add(hv, bin);
           }
           if (tb) {                                               // ~4 % of the entries: evaluated in full, in place
             const int base = (int)pre[g >> 5];
@@ -581,8 +579,8 @@ score_sparse_kernel(const unsigned char* __restrict__ recs, const int* __restric
             }
           }
         }
-        __syncwarp();                                             // the slot consumed one stage ago is free again
-        produce();
+        __syncthreads();                                          // the slot consumed one stage ago is free again
+        if (tid == 0) produce();
       }
     }
     __syncthreads();
@@ -695,7 +693,7 @@ int launch_jaccard_sparse(const int* Qc, const __half* Qv, const long long* qoff
   if (rc) return rc;
   const size_t smem2 = R.bytes + SsLayout::bytes;
   REID_CUDA(cudaFuncSetAttribute(score_sparse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
-  REID_REQUIRE((N + SS_STG - 1) / SS_STG + 1 <= SS_NEED, "jaccard_sparse: %d columns exceed the segment flags", N);
+  REID_REQUIRE((N + SS_STG - 1) / SS_STG + 1 <= SS_NEED, "jaccard_sparse: %d columns exceed the stage flags", N);
   REID_REQUIRE(((uintptr_t)D & 15) == 0 && ld % 4 == 0, "jaccard_sparse: rows of D must be 16-byte aligned");
   score_sparse_kernel<<<nq_local, SS_T, smem2, s>>>(recs, rec_count, cap, D, ld, rowmax_key, q, N, c1, c2, out, ld_out,
                                                    sc, chunk_min, cm_pitch);
