@@ -205,9 +205,7 @@ overlap_sparse_kernel(const int* __restrict__ Qc, const __half* __restrict__ Qv,
 // ---------------------------------------------------------------------------------------------
 constexpr int SS_T = 256;
 constexpr int SS_CAP = 512;     // identity-group entries staged / matches ranked per pass over the row
-constexpr int SS_STG = 2048;    // floats of the query's row of D per ring stage (8 KB, one cp.async.bulk)
-constexpr int SS_NST = 4;       // ring stages: SS_NST - 1 bulk copies (24 KB) in flight per CTA
-constexpr int SS_NEED = 1024;   // stage flags (bytes): rows of up to 2 M columns
+constexpr int SS_CMASK = 8192;  // bytes of the chunk mask (one bit per 32-column chunk: rows of up to 2 M columns)
 constexpr int SS_NB = 2048;     // cells of the raw-D histogram of untouched entries below the worst match's threshold
 
 struct SsLayout {               // after bitmap + prefix
@@ -219,9 +217,8 @@ struct SsLayout {               // after bitmap + prefix
   static constexpr size_t thrA = hp + (SS_CAP + 1) * 4;                // float[SS_CAP]
   static constexpr size_t thrB = thrA + SS_CAP * 4;                    // float[SS_CAP]
   static constexpr size_t queue = (thrB + SS_CAP * 4 + 15) & ~(size_t)15;
-  static constexpr size_t hist = queue + (size_t)SS_NEED;                          // int[SS_NB]
-  static constexpr size_t ring = (hist + (size_t)SS_NB * 4 + 127) & ~(size_t)127;  // float[SS_NST][SS_STG]
-  static constexpr size_t bytes = ring + (size_t)SS_NST * SS_STG * 4;
+  static constexpr size_t hist = queue + (size_t)SS_CMASK;                         // int[SS_NB]
+  static constexpr size_t bytes = hist + (size_t)SS_NB * 4;
 };
 
 // overlap value of probe g from the packed record (0 when the query does not touch g)
@@ -253,34 +250,7 @@ __device__ __forceinline__ int ss_zero_bin(float d, int col, const float* thrA, 
   }
   return bin;
 }
-// mbarrier / bulk-copy primitives of the row ring (cp.async.bulk: the Blackwell/Hopper asynchronous copy engine moves
-// 8 KB global -> shared per instruction and signals an mbarrier; no registers, no per-thread address arithmetic)
-__device__ __forceinline__ uint32_t ss_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void ss_mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void ss_mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void ss_mbar_wait(uint32_t bar, uint32_t parity) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred P1;\n\t"
-      "SS_WAIT_LOOP:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
-      "@P1 bra SS_WAIT_DONE;\n\t"
-      "bra SS_WAIT_LOOP;\n\t"
-      "SS_WAIT_DONE:\n\t"
-      "}" ::"r"(bar), "r"(parity)
-      : "memory");
-}
-__device__ __forceinline__ void ss_bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-               ::"r"(dst), "l"(src), "r"(bytes), "r"(bar)
-               : "memory");
-}
-
-__global__ void __launch_bounds__(SS_T, 2)
+__global__ void __launch_bounds__(SS_T, 4)
 score_sparse_kernel(const unsigned char* __restrict__ recs, const int* __restrict__ rec_count, int cap,
                     const float* __restrict__ D, long long ld, const int* __restrict__ rowmax_key, int q, int N,
                     float c1, float c2, float* __restrict__ out, long long ld_out, ScoreArgs sc,
@@ -292,7 +262,7 @@ score_sparse_kernel(const unsigned char* __restrict__ recs, const int* __restric
   const SparseRec R = sparse_rec(N, cap);
   unsigned* bm = reinterpret_cast<unsigned*>(smem_s);
   unsigned short* pre = reinterpret_cast<unsigned short*>(smem_s + R.prefix);
-  unsigned char* aux = smem_s + R.bytes;              // the whole record (bitmap, prefixes, packed values) is staged
+  unsigned char* aux = smem_s + R.vals;
   unsigned long long* mk = reinterpret_cast<unsigned long long*>(aux + SsLayout::mk);
   int* gcol = reinterpret_cast<int*>(aux + SsLayout::gcol);
   float* gd = reinterpret_cast<float*>(aux + SsLayout::gd);
@@ -302,23 +272,15 @@ score_sparse_kernel(const unsigned char* __restrict__ recs, const int* __restric
   float* thrB = reinterpret_cast<float*>(aux + SsLayout::thrB);
   int* hist = reinterpret_cast<int*>(aux + SsLayout::hist);
   __shared__ int s_lo, s_len, s_total, s_cnt, s_first, s_zfast;
-  __shared__ __align__(8) unsigned long long s_full[SS_NST];      // ring barriers: one phase per bulk copy
 
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   const unsigned char* rec = recs + (size_t)qi * R.bytes;
-  const __half* vals = reinterpret_cast<const __half*>(smem_s + R.vals);
+  const __half* vals = reinterpret_cast<const __half*>(rec + R.vals);          // stays in global memory (L2)
   {
     const uint4* src = reinterpret_cast<const uint4*>(rec);
     uint4* dst = reinterpret_cast<uint4*>(smem_s);
-    const int used = (int)((R.vals + (size_t)rec_count[qi] * 2 + 15) >> 4);          // packed values: only the used part
-    for (int i = tid; i < used; i += T) dst[i] = __ldg(src + i);
+    for (int i = tid; i < (int)(R.vals >> 4); i += T) dst[i] = __ldg(src + i);
   }
-  if (tid == 0) {
-    for (int i = 0; i < SS_NST; ++i) ss_mbar_init(ss_smem_u32(&s_full[i]), 1);
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
-  int ring_seq = 0;                                    // bulk copies consumed so far (all threads count alike)
-  int ring_pseq = 0;                                   // ... issued so far (thread 0)
   const float m = ordered_int2f(rowmax_key[qi]);
   const float* drow = D + (long long)qi * ld;
   const float* cm_row = chunk_min ? chunk_min + (long long)qi * cm_pitch : nullptr;   // minima of the row's 32-column chunks
@@ -495,92 +457,73 @@ score_sparse_kernel(const unsigned char* __restrict__ recs, const int* __restric
       }
     } else {
       const float dthr = thrB[P - 1];                              // untouched and D > dthr: after every match
-      // The gallery part of the row goes through a ring of SS_NST shared-memory stages of SS_STG floats, filled by
-      // cp.async.bulk (thread 0 issues, an mbarrier per stage counts the bytes): SS_NST - 1 copies = 24 KB are in flight
-      // per CTA whatever the consumers are doing, which is what a latency-bound streaming kernel was missing (round 1:
-      // 42 % of HBM with two register-staged loads per thread in flight).  A stage is skipped altogether when the query
-      // touches none of its columns and every 32-column chunk minimum recorded by the contraction lies above dthr.
-      const int gs0 = q & ~31;                                    // first staged column (128-byte aligned)
-      const int ldN = min((N + 31) & ~31, (int)min(ld, (long long)0x7fffffe0));   // staged columns end here (inside the row pitch)
-      const int nst = (ldN - gs0 + SS_STG - 1) / SS_STG;
-      unsigned char* need = aux + SsLayout::queue;                // [nst] stage flags
-      float* ring = reinterpret_cast<float*>(aux + SsLayout::ring);
+      // (1) overlapping entries = the set bits of the query's bitmap over the gallery columns (2-5 k of N): walked from
+      //     the bitmap, their distances gathered (one 32-byte sector each), evaluated in full.  Keeping them out of the
+      //     streaming loop removes its per-iteration ballot / scan / queue work (70 % issue-active in round 1).
       {
-        const int nch = ldN >> 5;
-        for (int k = w; k < nst; k += T / 32) {
-          bool on = false;
-#pragma unroll
-          for (int u = 0; u < SS_STG / 32 / 32; ++u) {
-            const int c = (gs0 >> 5) + k * (SS_STG / 32) + u * 32 + lane;       // chunk == bitmap word
-            if (c < nch) on |= bm[c] != 0u || cm_row == nullptr || __ldg(cm_row + c) <= dthr;
+        const int w0 = q >> 5, nwords = (N + 31) >> 5;
+        for (int wd = w0 + tid; wd < nwords; wd += T) {
+          unsigned bits = bm[wd];
+          int idx = pre[wd];
+          if (wd == w0) {
+            const unsigned below = (1u << (q & 31)) - 1u;
+            idx += __popc(bits & below);
+            bits &= ~below;
           }
-          on = __any_sync(FULL, on);
-          if (lane == 0) need[k] = on ? 1 : 0;
+          while (bits) {
+            const int g = wd * 32 + __ffs(bits) - 1;
+            bits &= bits - 1;
+            const float f = final_value(vals[idx++], __ldg(drow + g), m, c1h, c2);
+            const unsigned long long key = final_key(f, g - q);
+            if (key <= maxkey) bin_add(hv, lower_bound_u64(mk, P, key));
+          }
+        }
+      }
+      // (2) which 32-column chunks can hold an untouched entry at or below the threshold: the contraction recorded every
+      //     chunk's minimum, so a chunk with minimum > dthr is never even read (its overlapping entries were handled
+      //     above).  One bit per chunk in shared memory.
+      unsigned* cmask = reinterpret_cast<unsigned*>(aux + SsLayout::queue);
+      {
+        const int nch = (N + 31) >> 5;
+        for (int c = tid; c < ((nch + 31) & ~31); c += T) {
+          const bool on = c < nch && c >= (q >> 5) && (cm_row == nullptr || __ldg(cm_row + c) <= dthr);
+          const unsigned b = __ballot_sync(FULL, on);
+          if (lane == 0) cmask[c >> 5] = b;
         }
       }
       __syncthreads();
-      int pk = 0;                                                 // producer cursor (thread 0)
-      auto produce = [&]() {
-        while (pk < nst && !need[pk]) ++pk;
-        if (pk < nst) {
-          const int start = gs0 + pk * SS_STG;
-          const uint32_t bytes = (uint32_t)min(SS_STG, ldN - start) * 4u;
-          const int slot = ring_pseq % SS_NST;
-          const uint32_t bar = ss_smem_u32(&s_full[slot]);
-          ss_mbar_expect_tx(bar, bytes);
-          ss_bulk_g2s(ss_smem_u32(ring + slot * SS_STG), drow + start, bytes, bar);
-          ++ring_pseq;
-          ++pk;
-        }
+      // (3) untouched entries: one pass over the marked chunks, 8 entries per thread and iteration, loads two iterations
+      //     ahead; an unread group is +inf and falls through the first compare
+      const float4* d4 = reinterpret_cast<const float4*>(drow);
+      auto ldg8 = [&](int g, float4& x0, float4& x1) {
+        if (g < N && ((cmask[g >> 10] >> ((g >> 5) & 31)) & 1u)) { x0 = __ldg(d4 + (g >> 2)); x1 = __ldg(d4 + (g >> 2) + 1); }
+        else { x0 = make_float4(INFINITY, INFINITY, INFINITY, INFINITY); x1 = x0; }
       };
-      if (tid == 0)
-        for (int i = 0; i < SS_NST - 1; ++i) produce();
-      for (int k = 0; k < nst; ++k) {
-        if (!need[k]) continue;
-        const int slot = ring_seq % SS_NST;
-        ss_mbar_wait(ss_smem_u32(&s_full[slot]), (uint32_t)(ring_seq / SS_NST) & 1u);
-        ++ring_seq;
-        const float4* st4 = reinterpret_cast<const float4*>(ring + slot * SS_STG);
-        const int start = gs0 + k * SS_STG;
-        // two groups of 4 consecutive entries per thread (float4 index tid and tid + 256: conflict-free)
+      constexpr int STRIDE = T * 8;
+      int gb = (q & ~7) + tid * 8;                                 // this thread's 8 aligned entries
+      float4 c0, c1v, n0, n1, f0, f1;                              // current, next, next-but-one
+      ldg8(gb, c0, c1v);
+      ldg8(gb + STRIDE, n0, n1);
+      for (; gb < N; gb += STRIDE) {
+        ldg8(gb + 2 * STRIDE, f0, f1);
+        const float dmin = fminf(fminf(fminf(c0.x, c0.y), fminf(c0.z, c0.w)), fminf(fminf(c1v.x, c1v.y), fminf(c1v.z, c1v.w)));
+        if (dmin <= dthr) {                                        // something here may rank before the worst match
+          unsigned um = 0xffu;                                     // gallery columns of this group that the query does not touch
+          if (gb < q) um &= 0xffu << (q - gb);                     // q - gb in [1, 7]: gb >= (q & ~7)
+          if (gb + 8 > N) um &= 0xffu >> (gb + 8 - N);
+          um &= ~(bm[gb >> 5] >> (gb & 31));
+          const float dv[8] = {c0.x, c0.y, c0.z, c0.w, c1v.x, c1v.y, c1v.z, c1v.w};
 #pragma unroll
-        for (int h = 0; h < SS_STG / 4 / T; ++h) {
-          const int g = start + (h * T + tid) * 4;
-          if (g >= N) continue;
-          const float4 x = st4[h * T + tid];
-          unsigned vm = 0xfu;                                     // gallery columns of this group
-          if (g < q) vm = g + 4 <= q ? 0u : (0xfu << (q - g)) & 0xfu;
-          if (g + 4 > N) vm &= 0xfu >> (g + 4 - N);
-          const unsigned wbits = bm[g >> 5];
-          const unsigned b4 = (wbits >> (g & 31)) & 0xfu;
-          const unsigned um = vm & ~b4;                           // untouched: ranked by raw distance
-          unsigned tb = vm & b4;                                  // touched by the query's Jaccard term
-          const float dv[4] = {x.x, x.y, x.z, x.w};
-          if (um && fminf(fminf(x.x, x.y), fminf(x.z, x.w)) <= dthr) {
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              if (((um >> e) & 1u) && dv[e] <= dthr) {
-                if (atomicAdd(hist + ss_cell(dv[e], hscale), 1) < 0) {   // a cell that holds a threshold: ranked exactly
-                  const int bin = ss_zero_bin(dv[e], g + e - q, thrA, thrB, mk, P);
-                  if (bin < P) bin_add(hv, bin);
-                }
+          for (int e = 0; e < 8; ++e) {
+            if (((um >> e) & 1u) && dv[e] <= dthr) {
+              if (atomicAdd(hist + ss_cell(dv[e], hscale), 1) < 0) {     // a cell that holds a threshold: ranked exactly
+                const int bin = ss_zero_bin(dv[e], gb + e - q, thrA, thrB, mk, P);
+                if (bin < P) bin_add(hv, bin);
               }
             }
           }
-          if (tb) {                                               // ~4 % of the entries: evaluated in full, in place
-            const int base = (int)pre[g >> 5];
-            while (tb) {
-              const int e = __ffs(tb) - 1;
-              tb &= tb - 1;
-              const int slot_v = base + __popc(wbits & ((1u << ((g & 31) + e)) - 1u));   // packed slot of probe g + e
-              const float f = final_value(vals[slot_v], dv[e], m, c1h, c2);
-              const unsigned long long key = final_key(f, g + e - q);
-              if (key <= maxkey) bin_add(hv, lower_bound_u64(mk, P, key));
-            }
-          }
         }
-        __syncthreads();                                          // the slot consumed one stage ago is free again
-        if (tid == 0) produce();
+        c0 = n0; c1v = n1; n0 = f0; n1 = f1;
       }
     }
     __syncthreads();
@@ -670,7 +613,7 @@ long long jaccard_sparse_ws_bytes(int nq, int N, int cap) {
 bool jaccard_sparse_fits(int N, int cap) {
   const SparseRec R = sparse_rec(N, cap);
   const size_t k1 = R.bytes + (size_t)OS_RING * OS_SLOT * 8 + OS_CHUNK * 16;
-  const size_t k2 = R.bytes + SsLayout::bytes;
+  const size_t k2 = R.vals + SsLayout::bytes;
   return cap >= 64 && cap <= 65535 && k1 <= 200 * 1024 && k2 <= 200 * 1024;
 }
 
@@ -691,10 +634,9 @@ int launch_jaccard_sparse(const int* Qc, const __half* Qv, const long long* qoff
                                                     rec_count, *over_list, *over_n);
   int rc = check_launch("overlap_sparse_kernel");
   if (rc) return rc;
-  const size_t smem2 = R.bytes + SsLayout::bytes;
+  const size_t smem2 = R.vals + SsLayout::bytes;
   REID_CUDA(cudaFuncSetAttribute(score_sparse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
-  REID_REQUIRE((N + SS_STG - 1) / SS_STG + 1 <= SS_NEED, "jaccard_sparse: %d columns exceed the stage flags", N);
-  REID_REQUIRE(((uintptr_t)D & 15) == 0 && ld % 4 == 0, "jaccard_sparse: rows of D must be 16-byte aligned");
+  REID_REQUIRE((N + 31) / 32 <= SS_CMASK * 8, "jaccard_sparse: %d columns exceed the chunk mask", N);
   score_sparse_kernel<<<nq_local, SS_T, smem2, s>>>(recs, rec_count, cap, D, ld, rowmax_key, q, N, c1, c2, out, ld_out,
                                                    sc, chunk_min, cm_pitch);
   return check_launch("score_sparse_kernel");
