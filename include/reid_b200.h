@@ -301,9 +301,7 @@ REID_API int reid_pid_index(const int64_t* g_pid, int g, int T, uint64_t* keys, 
  * is produced: the kept rank of every true match is the number of non-junk entries at or before it in stable
  * (distance, column) order.  `out` may be NULL: then the q x g re-ranked matrix is never written.
  * q_pid / q_cam: ids of this window's queries [nq]; g_cam [g]; keys/start/list/T from reid_pid_index.
- * Score outputs as in reid_score_rows.  chunk_min (optional, [nq, cm_pitch], reid_dist's 32-column chunk minima of the
- * same rows of D): entries the query's Jaccard term does not touch rank by raw distance alone, so a chunk whose minimum
- * lies above the threshold of the query's worst match is never read -- the row is streamed only where it can matter. */
+ * Score outputs as in reid_score_rows. */
 REID_API int reid_jaccard_score(const int32_t* Qc, const reid_half* Qv, const int64_t* qoff, const int32_t* Qn,
                        const int64_t* colptr, const uint64_t* csc_ent,
                        const float* D, int64_t ld, const int32_t* rowmax_key, int q0, int q_stride,
@@ -311,7 +309,7 @@ REID_API int reid_jaccard_score(const int32_t* Qc, const reid_half* Qv, const in
                        const int64_t* q_pid, const int64_t* q_cam, const int64_t* g_cam,
                        const uint64_t* pid_keys, const int64_t* pid_start, const int32_t* pid_list, int pid_T,
                        int max_rank, double* ap, int32_t* first_hit, int32_t* cmc_hist, int32_t* n_valid,
-                       void* ws, int64_t ws_bytes, int cap, const float* chunk_min, int cm_pitch, void* stream);
+                       void* ws, int64_t ws_bytes, int cap, void* stream);
 
 /* K11  evaluate.py:40.  Stable full ranking of every row (ascending distance, ties by column).
  * Workspace: keyA, keyB, idxA of rows*g 32-bit words each. */

@@ -464,11 +464,9 @@ int reid_jaccard_score(const int32_t* Qc, const reid_half* Qv, const int64_t* qo
                        float c2, float* out, int64_t ld_out, const int64_t* q_pid, const int64_t* q_cam,
                        const int64_t* g_cam, const uint64_t* pid_keys, const int64_t* pid_start,
                        const int32_t* pid_list, int pid_T, int max_rank, double* ap, int32_t* first_hit,
-                       int32_t* cmc_hist, int32_t* n_valid, void* ws, int64_t ws_bytes, int cap, const float* chunk_min,
-                       int cm_pitch, void* stream) {
+                       int32_t* cmc_hist, int32_t* n_valid, void* ws, int64_t ws_bytes, int cap, void* stream) {
   ENTER();
   REID_REQUIRE(q >= 0 && q <= N && q_stride != 0, "jaccard_score: bad shape q=%d N=%d", q, N);
-  REID_REQUIRE(chunk_min == nullptr || cm_pitch >= (N + 31) / 32, "jaccard_score: chunk-minimum pitch %d too small", cm_pitch);
   REID_REQUIRE(ap != nullptr, "jaccard_score: ap is NULL (use reid_jaccard_mix for the matrix alone)");
   return launch_jaccard_score(Qc, HC(Qv), reinterpret_cast<const long long*>(qoff), Qn,
                               reinterpret_cast<const long long*>(colptr),
@@ -478,7 +476,7 @@ int reid_jaccard_score(const int32_t* Qc, const reid_half* Qv, const int64_t* qo
                               reinterpret_cast<const long long*>(g_cam),
                               reinterpret_cast<const unsigned long long*>(pid_keys),
                               reinterpret_cast<const long long*>(pid_start), pid_list, pid_T, max_rank, ap,
-                              first_hit, cmc_hist, n_valid, ws, ws_bytes, cap, chunk_min, cm_pitch, S(stream));
+                              first_hit, cmc_hist, n_valid, ws, ws_bytes, cap, S(stream));
 }
 
 int reid_rank_rows(const float* dist, int rows, int g, int64_t ld, uint32_t* keyA, uint32_t* keyB,

@@ -625,7 +625,7 @@ int launch_jaccard_sparse(const int* Qc, const __half* Qv, const long long* qoff
                           const long long* colptr, const unsigned long long* csc_ent, const float* D, long long ld,
                           const int* rowmax_key, int q0, int q_stride, int nq_local, int q, int N, float c1, float c2,
                           float* out, long long ld_out, const ScoreArgs& sc, void* ws, int cap, int** over_list,
-                          int** over_n, const float* chunk_min, int cm_pitch, cudaStream_t s);
+                          int** over_n, cudaStream_t s);
 
 // ws != NULL (ws_bytes >= jaccard_sparse_ws_bytes) selects the sparse path: per-query packed overlap records, with
 // the dense kernel below run afterwards as a persistent grid over the queries that did not fit `cap`.
@@ -636,7 +636,7 @@ int launch_jaccard_score(const int* Qc, const __half* Qv, const long long* qoff,
                          const long long* q_pid, const long long* q_cam, const long long* g_cam,
                          const unsigned long long* pid_keys, const long long* pid_start, const int* pid_list,
                          int pid_T, int max_rank, double* ap, int* first_hit, int* cmc_hist, int* n_valid,
-                         void* ws, long long ws_bytes, int cap, const float* chunk_min, int cm_pitch, cudaStream_t s) {
+                         void* ws, long long ws_bytes, int cap, cudaStream_t s) {
   if (nq_local == 0) return REID_OK;
   const int Npad = (int)round_up(N, 8);
   const int threads = N <= 32768 ? 256 : 512;
@@ -662,7 +662,7 @@ int launch_jaccard_score(const int* Qc, const __half* Qv, const long long* qoff,
                  "jaccard: workspace of %lld B is smaller than reid_jaccard_ws_bytes() = %lld B", ws_bytes,
                  jaccard_sparse_ws_bytes(nq_local, N, cap));
     const int rc = launch_jaccard_sparse(Qc, Qv, qoff, Qn, colptr, csc_ent, D, ld, rowmax_key, q0, q_stride, nq_local, q,
-                                         N, c1, c2, out, ld_out, sc, ws, cap, &over_list, &over_n, chunk_min, cm_pitch, s);
+                                         N, c1, c2, out, ld_out, sc, ws, cap, &over_list, &over_n, s);
     if (rc) return rc;
     int dev = 0, sms = 0;
     REID_CUDA(cudaGetDevice(&dev));
@@ -704,7 +704,7 @@ int launch_jaccard_mix(const int* Qc, const __half* Qv, const long long* qoff, c
                        long long ld_j, void* ws, long long ws_bytes, int cap, cudaStream_t s) {
   return launch_jaccard_score(Qc, Qv, qoff, Qn, colptr, csc_ent, D, ld, rowmax_key, q0, q_stride, nq_local,
                               q, N, c1, c2, out, ld_out, jaccard_out, ld_j, nullptr, nullptr, nullptr, nullptr,
-                              nullptr, nullptr, 0, 0, nullptr, nullptr, nullptr, nullptr, ws, ws_bytes, cap, nullptr, 0, s);
+                              nullptr, nullptr, 0, 0, nullptr, nullptr, nullptr, nullptr, ws, ws_bytes, cap, s);
 }
 
 long long launch_jaccard_ws_bytes(int nq, int N, int cap) {

@@ -205,7 +205,8 @@ overlap_sparse_kernel(const int* __restrict__ Qc, const __half* __restrict__ Qv,
 // ---------------------------------------------------------------------------------------------
 constexpr int SS_T = 256;
 constexpr int SS_CAP = 512;     // identity-group entries staged / matches ranked per pass over the row
-constexpr int SS_CMASK = 8192;  // bytes of the chunk mask (one bit per 32-column chunk: rows of up to 2 M columns)
+constexpr int SS_QSLOTS = 64;   // per-warp queue capacity: untouched entries before the second-worst match (8 B)
+constexpr int SS_QA = 128;      // per-warp queue capacity: overlapping entries (4 B; shares SS_QSLOTS * 8 bytes)
 constexpr int SS_NB = 2048;     // cells of the raw-D histogram of untouched entries below the worst match's threshold
 
 struct SsLayout {               // after bitmap + prefix
@@ -217,7 +218,7 @@ struct SsLayout {               // after bitmap + prefix
   static constexpr size_t thrA = hp + (SS_CAP + 1) * 4;                // float[SS_CAP]
   static constexpr size_t thrB = thrA + SS_CAP * 4;                    // float[SS_CAP]
   static constexpr size_t queue = (thrB + SS_CAP * 4 + 15) & ~(size_t)15;
-  static constexpr size_t hist = queue + (size_t)SS_CMASK;                         // int[SS_NB]
+  static constexpr size_t hist = queue + (size_t)(SS_T / 32) * 2 * SS_QSLOTS * 8;   // int[SS_NB]
   static constexpr size_t bytes = hist + (size_t)SS_NB * 4;
 };
 
@@ -230,6 +231,23 @@ __device__ __forceinline__ __half sp_t(const unsigned* bm, const unsigned short*
   return vals[(int)pre[g >> 5] + __popc(wd & (bit - 1))];
 }
 
+// Overlap queue entries are probe indices; the raw distance is re-read (L1/L2: the line was streamed a moment ago)
+// alongside the packed overlap value, so the two dependent-load latencies overlap.
+static __device__ __noinline__ void sp_drain_overlap(const int* qa, int cnt, const unsigned* bm,
+                                                     const unsigned short* pre, const __half* vals,
+                                                     const float* __restrict__ drow, float m, float c1h, float c2, int q,
+                                                     const unsigned long long* mk, int P, unsigned long long maxkey,
+                                                     int* hv) {
+  const int lane = threadIdx.x & 31;
+  if (lane < cnt) {
+    const int g = qa[lane];
+    const float d = __ldg(drow + g);
+    const float f = final_value(sp_t(bm, pre, vals, g), d, m, c1h, c2);
+    const unsigned long long key = final_key(f, g - q);
+    if (key <= maxkey) bin_add(hv, lower_bound_u64(mk, P, key));
+  }
+  __syncwarp();
+}
 // Untouched entries (overlap 0) rank by raw D alone.  Those at or below the worst match's threshold are counted in a
 // histogram of SS_NB cells over [0, threshold]: cell(d) is monotone in d, so an entry in a cell that holds no match
 // threshold lies on the same side of every threshold as the whole cell.  Cells that do hold one are marked (sign bit);
@@ -250,11 +268,16 @@ __device__ __forceinline__ int ss_zero_bin(float d, int col, const float* thrA, 
   }
   return bin;
 }
+__device__ __forceinline__ float ss_pick8(const float4& a, const float4& b, int e) {
+  const float lo = (e & 2) ? ((e & 1) ? a.w : a.z) : ((e & 1) ? a.y : a.x);
+  const float hi = (e & 2) ? ((e & 1) ? b.w : b.z) : ((e & 1) ? b.y : b.x);
+  return (e & 4) ? hi : lo;
+}
+
 __global__ void __launch_bounds__(SS_T, 4)
 score_sparse_kernel(const unsigned char* __restrict__ recs, const int* __restrict__ rec_count, int cap,
                     const float* __restrict__ D, long long ld, const int* __restrict__ rowmax_key, int q, int N,
-                    float c1, float c2, float* __restrict__ out, long long ld_out, ScoreArgs sc,
-                    const float* __restrict__ chunk_min, int cm_pitch) {
+                    float c1, float c2, float* __restrict__ out, long long ld_out, ScoreArgs sc) {
   constexpr int T = SS_T;
   const int qi = blockIdx.x;
   if (rec_count[qi] < 0) return;                          // on the overflow list: the dense kernel scores it
@@ -274,6 +297,7 @@ score_sparse_kernel(const unsigned char* __restrict__ recs, const int* __restric
   __shared__ int s_lo, s_len, s_total, s_cnt, s_first, s_zfast;
 
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  unsigned long long* wq = reinterpret_cast<unsigned long long*>(aux + SsLayout::queue) + w * 2 * SS_QSLOTS;
   const unsigned char* rec = recs + (size_t)qi * R.bytes;
   const __half* vals = reinterpret_cast<const __half*>(rec + R.vals);          // stays in global memory (L2)
   {
@@ -283,7 +307,6 @@ score_sparse_kernel(const unsigned char* __restrict__ recs, const int* __restric
   }
   const float m = ordered_int2f(rowmax_key[qi]);
   const float* drow = D + (long long)qi * ld;
-  const float* cm_row = chunk_min ? chunk_min + (long long)qi * cm_pitch : nullptr;   // minima of the row's 32-column chunks
   const float c1h = __half2float(__float2half_rn(c1));
   const bool scoring = sc.ap != nullptr;
   long long qc = 0;
@@ -448,83 +471,90 @@ score_sparse_kernel(const unsigned char* __restrict__ recs, const int* __restric
       }
       for (; g < N; g += T) slow(g, __ldg(drow + g));
       wrote = true;
-    } else if (!zfast) {
-      // degenerate row maximum / lambda: no monotone shortcut, every gallery entry is evaluated in full
-      for (int g = q + tid; g < N; g += T) {
-        const float f = final_value(tval(g), __ldg(drow + g), m, c1h, c2);
-        const unsigned long long key = final_key(f, g - q);
-        if (key <= maxkey) bin_add(hv, lower_bound_u64(mk, P, key));
-      }
     } else {
-      const float dthr = thrB[P - 1];                              // untouched and D > dthr: after every match
-      // (1) overlapping entries = the set bits of the query's bitmap over the gallery columns (2-5 k of N): walked from
-      //     the bitmap, their distances gathered (one 32-byte sector each), evaluated in full.  Keeping them out of the
-      //     streaming loop removes its per-iteration ballot / scan / queue work (70 % issue-active in round 1).
-      {
-        const int w0 = q >> 5, nwords = (N + 31) >> 5;
-        for (int wd = w0 + tid; wd < nwords; wd += T) {
-          unsigned bits = bm[wd];
-          int idx = pre[wd];
-          if (wd == w0) {
-            const unsigned below = (1u << (q & 31)) - 1u;
-            idx += __popc(bits & below);
-            bits &= ~below;
-          }
-          while (bits) {
-            const int g = wd * 32 + __ffs(bits) - 1;
-            bits &= bits - 1;
-            const float f = final_value(vals[idx++], __ldg(drow + g), m, c1h, c2);
-            const unsigned long long key = final_key(f, g - q);
-            if (key <= maxkey) bin_add(hv, lower_bound_u64(mk, P, key));
-          }
-        }
-      }
-      // (2) which 32-column chunks can hold an untouched entry at or below the threshold: the contraction recorded every
-      //     chunk's minimum, so a chunk with minimum > dthr is never even read (its overlapping entries were handled
-      //     above).  One bit per chunk in shared memory.
-      unsigned* cmask = reinterpret_cast<unsigned*>(aux + SsLayout::queue);
-      {
-        const int nch = (N + 31) >> 5;
-        for (int c = tid; c < ((nch + 31) & ~31); c += T) {
-          const bool on = c < nch && c >= (q >> 5) && (cm_row == nullptr || __ldg(cm_row + c) <= dthr);
-          const unsigned b = __ballot_sync(FULL, on);
-          if (lane == 0) cmask[c >> 5] = b;
-        }
-      }
-      __syncthreads();
-      // (3) untouched entries: one pass over the marked chunks, 8 entries per thread and iteration, loads two iterations
-      //     ahead; an unread group is +inf and falls through the first compare
+      const float dthr = zfast ? thrB[P - 1] : -INFINITY;          // untouched and D > dthr: after every match
+      int* qa = reinterpret_cast<int*>(wq);                        // SS_QA slots of 4 bytes
+      int na = 0;
       const float4* d4 = reinterpret_cast<const float4*>(drow);
       auto ldg8 = [&](int g, float4& x0, float4& x1) {
-        if (g < N && ((cmask[g >> 10] >> ((g >> 5) & 31)) & 1u)) { x0 = __ldg(d4 + (g >> 2)); x1 = __ldg(d4 + (g >> 2) + 1); }
-        else { x0 = make_float4(INFINITY, INFINITY, INFINITY, INFINITY); x1 = x0; }
+        if (g < N) { x0 = __ldg(d4 + (g >> 2)); x1 = __ldg(d4 + (g >> 2) + 1); }
+        else { x0 = make_float4(0.f, 0.f, 0.f, 0.f); x1 = x0; }
       };
       constexpr int STRIDE = T * 8;
-      int gb = (q & ~7) + tid * 8;                                 // this thread's 8 aligned entries
-      float4 c0, c1v, n0, n1, f0, f1;                              // current, next, next-but-one
+      int gw = (q & ~7) + (tid & ~31) * 8;                        // warp-uniform base of this warp's group
+      int gb = gw + lane * 8;                                     // this lane's 8 aligned entries
+      float4 c0, c1v, n0, n1, f0, f1;                             // current, next, next-but-one
       ldg8(gb, c0, c1v);
       ldg8(gb + STRIDE, n0, n1);
-      for (; gb < N; gb += STRIDE) {
+      for (; gw < N; gw += STRIDE, gb += STRIDE) {
         ldg8(gb + 2 * STRIDE, f0, f1);
+        // which of this lane's 8 entries are gallery columns, and which of those overlap
+        unsigned vm = 0;
+        if (gb < N) {
+          vm = 0xffu;
+          if (gb < q) vm &= 0xffu << (q - gb);                    // q - gb in [1, 7]: gb >= (q & ~7)
+          if (gb + 8 > N) vm &= 0xffu >> (gb + 8 - N);
+        }
+        const unsigned tb = gb < N ? (bm[gb >> 5] >> (gb & 31)) & vm : 0u;
         const float dmin = fminf(fminf(fminf(c0.x, c0.y), fminf(c0.z, c0.w)), fminf(fminf(c1v.x, c1v.y), fminf(c1v.z, c1v.w)));
-        if (dmin <= dthr) {                                        // something here may rank before the worst match
-          unsigned um = 0xffu;                                     // gallery columns of this group that the query does not touch
-          if (gb < q) um &= 0xffu << (q - gb);                     // q - gb in [1, 7]: gb >= (q & ~7)
-          if (gb + 8 > N) um &= 0xffu >> (gb + 8 - N);
-          um &= ~(bm[gb >> 5] >> (gb & 31));
+        unsigned ma = zfast ? tb : vm;
+        unsigned mz = 0;
+        if (zfast && vm != 0 && dmin <= dthr) {                   // something untouched ranks before the worst match
           const float dv[8] = {c0.x, c0.y, c0.z, c0.w, c1v.x, c1v.y, c1v.z, c1v.w};
 #pragma unroll
           for (int e = 0; e < 8; ++e) {
-            if (((um >> e) & 1u) && dv[e] <= dthr) {
-              if (atomicAdd(hist + ss_cell(dv[e], hscale), 1) < 0) {     // a cell that holds a threshold: ranked exactly
-                const int bin = ss_zero_bin(dv[e], gb + e - q, thrA, thrB, mk, P);
-                if (bin < P) bin_add(hv, bin);
+            if ((((vm & ~tb) >> e) & 1u) && dv[e] <= dthr) {
+              if (atomicAdd(hist + ss_cell(dv[e], hscale), 1) < 0) mz |= 1u << e;     // a cell that holds a threshold
+            }
+          }
+        }
+        if (__any_sync(FULL, ma != 0)) {
+          const int mine = __popc(ma);
+          int incl = mine;
+#pragma unroll
+          for (int off = 1; off < 32; off <<= 1) {
+            const int y = __shfl_up_sync(FULL, incl, off);
+            if (lane >= off) incl += y;
+          }
+          const int totA = __shfl_sync(FULL, incl, 31);
+          if (na + totA > SS_QA && na > 0) {                      // make room: partial pass
+            sp_drain_overlap(qa, na, bm, pre, vals, drow, m, c1h, c2, q, mk, P, maxkey, hv);
+            na = 0;
+          }
+          if (totA <= SS_QA) {
+            int pos = na + incl - mine;
+            unsigned bits = ma;
+            while (bits) {
+              const int e = __ffs(bits) - 1;
+              bits &= bits - 1;
+              qa[pos++] = gb + e;
+            }
+            na += totA;
+            __syncwarp();
+            while (na >= 32) { na -= 32; sp_drain_overlap(qa + na, 32, bm, pre, vals, drow, m, c1h, c2, q, mk, P, maxkey, hv); }
+          } else {                                                // dense stretch: one entry per lane at a time
+#pragma unroll 1
+            for (int e = 0; e < 8; ++e) {
+              const bool on = (ma >> e) & 1u;
+              const unsigned act = __ballot_sync(FULL, on);
+              if (act) {
+                if (on) qa[__popc(act & ((1u << lane) - 1))] = gb + e;
+                __syncwarp();
+                sp_drain_overlap(qa, __popc(act), bm, pre, vals, drow, m, c1h, c2, q, mk, P, maxkey, hv);
               }
             }
           }
         }
+        while (mz) {                                              // divergent, rare: ranked against the thresholds
+          const int e = __ffs(mz) - 1;
+          mz &= mz - 1;
+          const int bin = ss_zero_bin(ss_pick8(c0, c1v, e), gb + e - q, thrA, thrB, mk, P);
+          if (bin < P) bin_add(hv, bin);
+        }
+        __syncwarp();
         c0 = n0; c1v = n1; n0 = f0; n1 = f1;
       }
+      if (na > 0) sp_drain_overlap(qa, na, bm, pre, vals, drow, m, c1h, c2, q, mk, P, maxkey, hv);
     }
     __syncthreads();
     if (use_hist) {
@@ -621,7 +651,7 @@ int launch_jaccard_sparse(const int* Qc, const __half* Qv, const long long* qoff
                           const long long* colptr, const unsigned long long* csc_ent, const float* D, long long ld,
                           const int* rowmax_key, int q0, int q_stride, int nq_local, int q, int N, float c1, float c2,
                           float* out, long long ld_out, const ScoreArgs& sc, void* ws, int cap, int** over_list,
-                          int** over_n, const float* chunk_min, int cm_pitch, cudaStream_t s) {
+                          int** over_n, cudaStream_t s) {
   const SparseRec R = sparse_rec(N, cap);
   unsigned char* recs = static_cast<unsigned char*>(ws);
   int* rec_count = reinterpret_cast<int*>(recs + (((size_t)R.bytes * nq_local + 15) & ~(size_t)15));
@@ -636,9 +666,8 @@ int launch_jaccard_sparse(const int* Qc, const __half* Qv, const long long* qoff
   if (rc) return rc;
   const size_t smem2 = R.vals + SsLayout::bytes;
   REID_CUDA(cudaFuncSetAttribute(score_sparse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
-  REID_REQUIRE((N + 31) / 32 <= SS_CMASK * 8, "jaccard_sparse: %d columns exceed the chunk mask", N);
   score_sparse_kernel<<<nq_local, SS_T, smem2, s>>>(recs, rec_count, cap, D, ld, rowmax_key, q, N, c1, c2, out, ld_out,
-                                                   sc, chunk_min, cm_pitch);
+                                                   sc);
   return check_launch("score_sparse_kernel");
 }
 

@@ -110,7 +110,7 @@ int launch_jaccard_score(const int* Qc, const __half* Qv, const long long* qoff,
                          const long long* q_pid, const long long* q_cam, const long long* g_cam,
                          const unsigned long long* pid_keys, const long long* pid_start, const int* pid_list,
                          int pid_T, int max_rank, double* ap, int* first_hit, int* cmc_hist, int* n_valid,
-                         void* ws, long long ws_bytes, int cap, const float* chunk_min, int cm_pitch, cudaStream_t s);
+                         void* ws, long long ws_bytes, int cap, cudaStream_t s);
 long long launch_jaccard_ws_bytes(int nq, int N, int cap);   // 0 if the sparse path cannot be used for this N / cap
 int launch_rank_rows(const float* dist, int rows, int g, long long ld_dist, uint32_t* keyA, uint32_t* keyB,
                      int* idxA, int* idx_out, cudaStream_t s);

@@ -222,7 +222,6 @@ class Engine:
         self.shard_h2d = True               # evaluator on several ranks: each uploads 1/world of the host rows, all-gather over NVLink
         self._copy_stream = None
         self.scatter_select = True          # upper-only selection in scatter form (reid_topk_rows_scatter)
-        self.score_chunk_skip = True        # scoring never reads chunks of D whose recorded minimum cannot matter
         self.qe_nosync_bytes = 4 << 30       # budget for sizing the query-expansion pools without a host read
         self._ubmax_pinned = torch.zeros(1, dtype=torch.int64).pin_memory()
         self._ubmax_event = torch.cuda.Event()
@@ -770,7 +769,7 @@ class Engine:
         return keys, start, lst, T
 
     def jaccard_score(self, Qc, Qv, qoff, Qn, csc, D, key, q: int, N: int, lam: float, nq_local: int, q0, q_stride,
-                      ids, max_rank: int, want_final: bool, fabric=None, chunk_min: torch.Tensor | None = None):
+                      ids, max_rank: int, want_final: bool, fabric=None):
         """Fused K9–K12 for this rank's queries.  ids = (q_pids_local, g_pids, q_cams_local, g_cams).
         Returns (final or None, (cmc, mAP, n_valid, ap_all, first_all))."""
         colptr, csc_ent = csc
@@ -784,15 +783,12 @@ class Engine:
         c1 = float(np.float16(1 - lam))
         c2 = float(np.float32(lam))
         ws, ws_bytes = self._jaccard_ws(nq_local, N)
-        cmin = chunk_min if (chunk_min is not None and self.score_chunk_skip) else None
-        cm_pitch = int(cmin.stride(0)) if cmin is not None else 0
 
         def launch(ap, first, hist, nvalid):
             _lib.call("reid_jaccard_score", _ptr(Qc), _ptr(Qv), _ptr(qoff), _ptr(Qn), _ptr(colptr), _ptr(csc_ent),
                       _ptr(D), D.stride(0), _ptr(key), q0, q_stride, nq_local, q, N, c1, c2, _ptr(out),
                       ldf, _ptr(q_pids), _ptr(q_cams), _ptr(g_cams), _ptr(keys), _ptr(start), _ptr(lst), T, max_rank,
-                      _ptr(ap), _ptr(first), _ptr(hist), _ptr(nvalid), _ptr(ws), ws_bytes, self.sparse_cap,
-                      _ptr(cmin), cm_pitch, _stream())
+                      _ptr(ap), _ptr(first), _ptr(hist), _ptr(nvalid), _ptr(ws), ws_bytes, self.sparse_cap, _stream())
         return out, self._score_common(launch, nq_local, max_rank, q, span="jaccard_score", fabric=fabric)
 
     # ------------------------------------------------------------------ K4–K10 from a distance panel
@@ -867,7 +863,7 @@ class Engine:
             assert detail is None
             ids, max_rank = score
             return self.jaccard_score(Qc, Qv, qoff, Qn, csc, D, key, q, N, lam, nq_local, r, P, ids, max_rank,
-                                      want_final, chunk_min=chunk_min)
+                                      want_final)
         with self.span("jaccard_mix"):
             res = self.jaccard_mix(Qc, Qv, qoff, Qn, csc, D, key, q, N, lam, nq_local, r, P,
                                    want_jaccard=detail is not None)
@@ -1027,7 +1023,7 @@ class Engine:
         if score is not None:
             ids, max_rank = score
             return self.jaccard_score(Qc, Qv, qoff, Qn, csc, panel, key_l, q, N, lam, nq_local, r, -P, ids, max_rank,
-                                      want_final, fabric=(fab, L), chunk_min=cm_d)
+                                      want_final, fabric=(fab, L))
         with self.span("jaccard_mix"):
             return self.jaccard_mix(Qc, Qv, qoff, Qn, csc, panel, key_l, q, N, lam, nq_local, r, -P)
 

@@ -392,25 +392,3 @@ def test_streamed_blocks_match_single_launch(eng, engine_mod, synth, name, batch
             assert torch.equal(u, v), f"{name}: {what} differs between the streamed and the resident evaluation"
     finally:
         eng.symmetric = saved
-
-
-@pytest.mark.parametrize("name,k1,k2", [("mid", 20, 6), ("small", 50, 15), ("tiny", 20, 6)])
-def test_score_chunk_skip_and_dense_paths_agree(eng, synth, name, k1, k2):
-    """The fused Jaccard + CMC/mAP kernel in its three forms -- sparse records with the chunk-minimum skip (chunks of D
-    whose recorded minimum lies above the worst match's threshold are never read), sparse records streaming the whole
-    row, and the dense shared-memory row -- must produce the same AP / first hits / CMC bit for bit."""
-    sh = synth.SHAPES[name]
-    qf, gf, qp, gp, qc, gc = synth.make(sh, 3)
-    X = torch.cat([qf, gf]).to(eng.device)
-    pids, cams = torch.cat([qp, gp]).to(eng.device), torch.cat([qc, gc]).to(eng.device)
-    saved = eng.score_chunk_skip, eng.sparse_cap
-    try:
-        res = []
-        for skip, cap in ((True, saved[1]), (False, saved[1]), (True, 0)):
-            eng.score_chunk_skip, eng.sparse_cap = skip, cap
-            res.append(eng.evaluate_reranked(X, sh.q, pids, cams, k1, k2, 0.3, normalize=True, max_rank=50))
-    finally:
-        eng.score_chunk_skip, eng.sparse_cap = saved
-    for other in res[1:]:
-        for a, b, what in zip(res[0], other, ("cmc", "mAP", "n_valid", "ap", "first_hit")):
-            assert torch.equal(a, b), what
