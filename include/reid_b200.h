@@ -178,6 +178,57 @@ REID_API int reid_krecip_V_tri(const int32_t* rfull, const int32_t* nfull, const
                       const int32_t* rowmax_key, int32_t* Vc, reid_half* Vv, int32_t* Vn, int upper_only,
                       void* stream);
 
+/* ---- Re-ranking without any dense matrix (100k queries x 1M gallery; reranking.py:46-100 and
+ * evaluate.py:40-88 with D, V and the final matrix never materialised).  The contraction produces panels
+ * (reid_dist on row / column blocks); these entry points work on lists.  Query windows use (q0, q_stride) as elsewhere.
+ *
+ * reid_lists_rekey: reranking.py:46,48 from per-row WIDE raw-distance lists (widx/wval [rows, Kw]: the Kw nearest columns
+ * by (D, column), e.g. from reid_topk_rows_hinted over the panels of an N x N sweep) and the rows' global maxima: the
+ * first K columns in (D / max, column) order -> nbr[rows, K].  *ambiguous counts rows whose K-th quotient equals the
+ * list's last one (an unseen column could tie): enlarge Kw.
+ * reid_krecip_V_lists: reid_krecip_V for all rows with every distance D[i, e] looked up in row i's wide list; a miss is
+ * recomputed from the float32 features x32 / squared norms sq and counted in *misses.
+ * reid_overlap_lists: reranking.py:86-92 for a window of queries with a shared-memory hash table instead of an N-bit row:
+ * per query the gallery columns (target - q) it overlaps, ascending, and the float16 overlap sums -> ocol / ot at
+ * [l * cap_o ...], ocnt[l] (-1 and *overflow += 1 when a query touches more than cap_o <= 8192 gallery columns).
+ * reid_rr_prepare: per query, from the distances of its same-identity gallery columns (group arrays as
+ * reid_stream_group_*) and its overlap list: true final keys of the group (gkey, gjunk), the sorted match keys mk, and
+ * for every match the raw-distance thresholds thrA / thrB (largest D whose untouched final value is < / <= the match's).
+ * reid_stream_count_panel_rr: second sweep over the q x g panels: bins[goff + b] += entries that come after exactly b
+ * matches when ranked as if the Jaccard term did not touch them.
+ * reid_stream_score_rr: corrects the bins by the special entries (same identity, overlap targets; od = their exact
+ * distances gathered from the panels) and turns them into AP / first hit / CMC histogram (evaluate.py:53-80).
+ * reid_rr_topk: exact top-K of every re-ranked row = merge(tidx/tval: its Kd nearest by raw distance, overlap list);
+ * *ambiguous counts rows whose K-th value reaches the untouched bound of the Kd-th distance (enlarge Kd). */
+REID_API int reid_lists_rekey(const int32_t* widx, const float* wval, int rows, int Kw, const int32_t* rowmax_key, int K,
+                     int32_t* nbr, int32_t* ambiguous, void* stream);
+REID_API int reid_krecip_V_lists(const int32_t* rfull, const int32_t* nfull, const int32_t* rhalf, const int32_t* nhalf,
+                        int rows, int k1, const int32_t* rowmax_key, const int32_t* wl_idx, const float* wl_val, int Kw,
+                        const float* x32, int64_t ldx, const float* sq, int32_t* Vc, reid_half* Vv, int32_t* Vn,
+                        int32_t* misses, void* stream);
+REID_API int reid_overlap_lists(const int32_t* Qc, const reid_half* Qv, const int64_t* qoff, const int32_t* Qn,
+                       const int64_t* colptr, const uint64_t* csc_ent, int q0, int q_stride, int nq, int q, int cap_o,
+                       int32_t* ocol, reid_half* ot, int32_t* ocnt, int32_t* overflow, void* stream);
+REID_API int reid_rr_prepare(int nq, int q0, int q_stride, const int32_t* glo, const int32_t* glen, const int64_t* goff,
+                    const int32_t* list, const float* gd, const int64_t* q_cam, const int64_t* g_cam,
+                    const int32_t* rowmax_key, float c1, float c2, int cap_o, const int32_t* ocol, const reid_half* ot,
+                    const int32_t* ocnt, uint64_t* gkey, uint8_t* gjunk, uint64_t* mk, float* thrA, float* thrB,
+                    int32_t* nmatch, int32_t* overflow, void* stream);
+REID_API int reid_stream_count_panel_rr(const float* panel, int64_t ld, int rows, int c0, int c1, const int64_t* goff,
+                               const uint64_t* mk, const float* thrA, const float* thrB, const int32_t* nmatch,
+                               int32_t* bins, void* stream);
+REID_API int reid_stream_score_rr(int nq, int q0, int q_stride, const int32_t* glo, const int32_t* glen,
+                         const int64_t* goff, const int32_t* list, const float* gd, const uint64_t* gkey,
+                         const uint8_t* gjunk, const uint64_t* mk, const float* thrA, const float* thrB,
+                         const int32_t* nmatch, const int32_t* bins, int cap_o, const int32_t* ocol, const reid_half* ot,
+                         const float* od, const int32_t* ocnt, const int64_t* q_pid, const int64_t* g_pid,
+                         const int32_t* rowmax_key, float c1, float c2, int max_rank, double* ap, int32_t* first_hit,
+                         int32_t* cmc_hist, int32_t* n_valid, void* stream);
+REID_API int reid_rr_topk(int nq, int q0, int q_stride, const int32_t* tidx, const float* tval, int Kd, int g, int cap_o,
+                 const int32_t* ocol, const reid_half* ot, const float* od, const int32_t* ocnt,
+                 const int32_t* rowmax_key, float c1, float c2, int K, int32_t* out_idx, float* out_val,
+                 int32_t* ambiguous, void* stream);
+
 /* ---- Sharded symmetric path (no reference function: the reference is single-process) ----------------
  * One process per GPU.  Wherever an entry point takes (row0, row_stride) / (q0, q_stride), a NEGATIVE stride selects
  * "snake block" ownership: world = -stride ranks own the 256-row tile rows of the symmetric N x N matrix in

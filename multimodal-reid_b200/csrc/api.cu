@@ -352,6 +352,75 @@ int reid_krecip_V_sharded(const int32_t* rfull, const int32_t* nfull, const int3
                                reinterpret_cast<const float* const*>(panels), 1, S(stream));
 }
 
+/* ---- re-ranking without any dense matrix --------------------------------------------------------- */
+#define LL(p) reinterpret_cast<const long long*>(p)
+#define ULL(p) reinterpret_cast<const unsigned long long*>(p)
+
+int reid_lists_rekey(const int32_t* widx, const float* wval, int rows, int Kw, const int32_t* rowmax_key, int K,
+                     int32_t* nbr, int32_t* ambiguous, void* stream) {
+  ENTER();
+  return launch_lists_rekey(widx, wval, rows, Kw, rowmax_key, K, nbr, ambiguous, S(stream));
+}
+
+int reid_krecip_V_lists(const int32_t* rfull, const int32_t* nfull, const int32_t* rhalf, const int32_t* nhalf, int rows,
+                        int k1, const int32_t* rowmax_key, const int32_t* wl_idx, const float* wl_val, int Kw,
+                        const float* x32, int64_t ldx, const float* sq, int32_t* Vc, reid_half* Vv, int32_t* Vn,
+                        int32_t* misses, void* stream) {
+  ENTER();
+  REID_REQUIRE(k1 >= 1 && Kw >= 1 && wl_idx && wl_val && x32 && sq && misses, "krecip_V_lists: bad arguments");
+  return launch_expand_weights_wl(rfull, nfull, rhalf, nhalf, 0, 1, rows, k1, nullptr, 0, rowmax_key, Vc, H(Vv), Vn, 0,
+                                  nullptr, 0, wl_idx, wl_val, Kw, x32, ldx, sq, misses, S(stream));
+}
+
+int reid_overlap_lists(const int32_t* Qc, const reid_half* Qv, const int64_t* qoff, const int32_t* Qn,
+                       const int64_t* colptr, const uint64_t* csc_ent, int q0, int q_stride, int nq, int q, int cap_o,
+                       int32_t* ocol, reid_half* ot, int32_t* ocnt, int32_t* overflow, void* stream) {
+  ENTER();
+  REID_REQUIRE(q_stride != 0 && nq >= 0 && q >= 0, "overlap_lists: bad window");
+  return launch_overlap_hash(Qc, HC(Qv), LL(qoff), Qn, LL(colptr), ULL(csc_ent), q0, q_stride, nq, q, cap_o, ocol, H(ot),
+                             ocnt, overflow, S(stream));
+}
+
+int reid_rr_prepare(int nq, int q0, int q_stride, const int32_t* glo, const int32_t* glen, const int64_t* goff,
+                    const int32_t* list, const float* gd, const int64_t* q_cam, const int64_t* g_cam,
+                    const int32_t* rowmax_key, float c1, float c2, int cap_o, const int32_t* ocol, const reid_half* ot,
+                    const int32_t* ocnt, uint64_t* gkey, uint8_t* gjunk, uint64_t* mk, float* thrA, float* thrB,
+                    int32_t* nmatch, int32_t* overflow, void* stream) {
+  ENTER();
+  return launch_rr_prepare(nq, q0, q_stride, glo, glen, LL(goff), list, gd, LL(q_cam), LL(g_cam), rowmax_key, c1, c2,
+                           cap_o, ocol, HC(ot), ocnt, reinterpret_cast<unsigned long long*>(gkey), gjunk,
+                           reinterpret_cast<unsigned long long*>(mk), thrA, thrB, nmatch, overflow, S(stream));
+}
+
+int reid_stream_count_panel_rr(const float* panel, int64_t ld, int rows, int c0, int c1, const int64_t* goff,
+                               const uint64_t* mk, const float* thrA, const float* thrB, const int32_t* nmatch,
+                               int32_t* bins, void* stream) {
+  ENTER();
+  return launch_count_panel_rr(panel, ld, rows, c0, c1, LL(goff), ULL(mk), thrA, thrB, nmatch, bins, S(stream));
+}
+
+int reid_stream_score_rr(int nq, int q0, int q_stride, const int32_t* glo, const int32_t* glen, const int64_t* goff,
+                         const int32_t* list, const float* gd, const uint64_t* gkey, const uint8_t* gjunk,
+                         const uint64_t* mk, const float* thrA, const float* thrB, const int32_t* nmatch,
+                         const int32_t* bins, int cap_o, const int32_t* ocol, const reid_half* ot, const float* od,
+                         const int32_t* ocnt, const int64_t* q_pid, const int64_t* g_pid, const int32_t* rowmax_key,
+                         float c1, float c2, int max_rank, double* ap, int32_t* first_hit, int32_t* cmc_hist,
+                         int32_t* n_valid, void* stream) {
+  ENTER();
+  return launch_score_counts_rr(nq, q0, q_stride, glo, glen, LL(goff), list, gd, ULL(gkey), gjunk, ULL(mk), thrA, thrB,
+                                nmatch, bins, cap_o, ocol, HC(ot), od, ocnt, LL(q_pid), LL(g_pid), rowmax_key, c1, c2,
+                                max_rank, ap, first_hit, cmc_hist, n_valid, S(stream));
+}
+
+int reid_rr_topk(int nq, int q0, int q_stride, const int32_t* tidx, const float* tval, int Kd, int g, int cap_o,
+                 const int32_t* ocol, const reid_half* ot, const float* od, const int32_t* ocnt,
+                 const int32_t* rowmax_key, float c1, float c2, int K, int32_t* out_idx, float* out_val,
+                 int32_t* ambiguous, void* stream) {
+  ENTER();
+  return launch_rr_topk(nq, q0, q_stride, tidx, tval, Kd, g, cap_o, ocol, HC(ot), od, ocnt, rowmax_key, c1, c2, K,
+                        out_idx, out_val, ambiguous, S(stream));
+}
+
 int reid_fabric_alloc(int64_t bytes, void** out) { ENTER(); return fabric_alloc(bytes, out); }
 int reid_fabric_free(void* p) { return fabric_free(p); }
 int reid_fabric_export(void* p, void* handle64) { ENTER(); return fabric_export(p, handle64); }

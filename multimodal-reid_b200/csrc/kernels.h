@@ -52,6 +52,35 @@ int launch_expand_weights(const int* rfull, const int* nfull, const int* rhalf, 
                           int row_stride, int rows, int k1, const float* D, long long ld, const int* rowmax_key, int* Vc,
                           __half* Vv, int* Vn, int upper_only, const float* const* panels, int out_global,
                           cudaStream_t s);
+int launch_expand_weights_wl(const int* rfull, const int* nfull, const int* rhalf, const int* nhalf, int row0,
+                             int row_stride, int rows, int k1, const float* D, long long ld, const int* rowmax_key,
+                             int* Vc, __half* Vv, int* Vn, int upper_only, const float* const* panels, int out_global,
+                             const int* wl_idx, const float* wl_val, int Kw, const float* x32, long long ldx,
+                             const float* sq, int* wl_miss, cudaStream_t s);
+// stream_rerank.cu (re-ranking without any dense matrix)
+int launch_lists_rekey(const int* widx, const float* wval, int rows, int Kw, const int* rowmax_key, int K, int* nbr,
+                       int* ambiguous, cudaStream_t s);
+int launch_overlap_hash(const int* Qc, const __half* Qv, const long long* qoff, const int* Qn, const long long* colptr,
+                        const unsigned long long* csc_ent, int q0, int q_stride, int nq, int q, int cap_o, int* ocol,
+                        __half* ot, int* ocnt, int* overflow, cudaStream_t s);
+int launch_rr_prepare(int nq, int q0, int q_stride, const int* glo, const int* glen, const long long* goff,
+                      const int* list, const float* gd, const long long* q_cam, const long long* g_cam,
+                      const int* rowmax_key, float c1, float c2, int cap_o, const int* ocol, const __half* ot,
+                      const int* ocnt, unsigned long long* gkey, unsigned char* gjunk, unsigned long long* mk,
+                      float* thrA, float* thrB, int* nmatch, int* overflow, cudaStream_t s);
+int launch_count_panel_rr(const float* panel, long long ld, int rows, int c0, int c1, const long long* goff,
+                          const unsigned long long* mk, const float* thrA, const float* thrB, const int* nmatch,
+                          int* bins, cudaStream_t s);
+int launch_score_counts_rr(int nq, int q0, int q_stride, const int* glo, const int* glen, const long long* goff,
+                           const int* list, const float* gd, const unsigned long long* gkey, const unsigned char* gjunk,
+                           const unsigned long long* mk, const float* thrA, const float* thrB, const int* nmatch,
+                           const int* bins, int cap_o, const int* ocol, const __half* ot, const float* od,
+                           const int* ocnt, const long long* q_pid, const long long* g_pid, const int* rowmax_key,
+                           float c1, float c2, int max_rank, double* ap, int* first_hit, int* cmc_hist, int* n_valid,
+                           cudaStream_t s);
+int launch_rr_topk(int nq, int q0, int q_stride, const int* tidx, const float* tval, int Kd, int g, int cap_o,
+                   const int* ocol, const __half* ot, const float* od, const int* ocnt, const int* rowmax_key, float c1,
+                   float c2, int K, int* out_idx, float* out_val, int* ambiguous, cudaStream_t s);
 int launch_dist_tc_sharded(const __half* hi, const __half* lo, long long ld, const float* sq, const uint32_t* amax,
                            int n, int dp, const int* tiles, int ntiles, int world, float* out, long long ld_out,
                            int nloc, int* rowmax_key, float* chunk_min, int cm_pitch, float* chunk_min_m,

@@ -78,7 +78,9 @@ expand_weights_kernel(const int* __restrict__ rfull, const int* __restrict__ nfu
                       int row_stride, int rows, int k1p, int h, const float* __restrict__ D, long long ld,
                       const int* __restrict__ rowmax_key, int cap1, int capP,
                       int* __restrict__ Vc, __half* __restrict__ Vv, int* __restrict__ Vn, int upper_only,
-                      const float* const* __restrict__ panels, int out_global) {
+                      const float* const* __restrict__ panels, int out_global, const int* __restrict__ wl_idx,
+                      const float* __restrict__ wl_val, int Kw, const float* __restrict__ x32, long long ldx,
+                      const float* __restrict__ sq, int* __restrict__ wl_miss) {
   extern __shared__ int smem_i[];
   const int wpb = blockDim.x >> 5;
   const int w = threadIdx.x >> 5, lane = lane_id();
@@ -159,11 +161,29 @@ expand_weights_kernel(const int* __restrict__ rfull, const int* __restrict__ nfu
   }
   // Gaussian weights on the normalised distance, numpy-exact exp and pairwise sum
   const float m = ordered_int2f(rowmax_key[lrow]);
-  const float* drow = D + (long long)lrow * ld;
+  const float* drow = D ? D + (long long)lrow * ld : nullptr;
   for (int j = lane; j < nU; j += 32) {
     const int e = E[j];                       // upper_only: left of the row's diagonal block only the mirror image exists
     float dv;
-    if (upper_only && e < (row & ~255)) {
+    if (wl_idx) {
+      // streamed form (no matrix anywhere): D[row, e] is looked up in the row's wide raw-distance neighbour list -- the
+      // exact value the contraction produced.  E_i consists of reciprocal neighbours of reciprocal neighbours, so a miss
+      // is rare; it is recomputed from the float32 features (agrees with the tensor-core value to ~1e-6) and counted.
+      const int* li = wl_idx + (long long)row * Kw;
+      int hit = -1;
+      for (int t = 0; t < Kw; ++t)
+        if (li[t] == e) { hit = t; break; }
+      if (hit >= 0) {
+        dv = wl_val[(long long)row * Kw + hit];
+      } else {
+        const float* a = x32 + (long long)row * ldx;
+        const float* b = x32 + (long long)e * ldx;
+        float acc = 0.0f;
+        for (int k = 0; k < (int)ldx; ++k) acc = __fmaf_rn(a[k], b[k], acc);
+        dv = __fmaf_rn(-2.0f, acc, __fadd_rn(sq[row], sq[e]));
+        atomicAdd(wl_miss, 1);
+      }
+    } else if (upper_only && e < (row & ~255)) {
       // D[e, row]: on one rank a row of the same matrix; in a sharded job it sits in the panel of the rank that owns e's
       // tile row -- read over NVLink (a few dozen 4-byte loads per row; bit-identical: the element was computed once)
       const float* src = panels ? panels[snake_owner(e >> 8, -row_stride)] + (long long)snake_local_row(e, -row_stride) * ld
@@ -200,7 +220,17 @@ int launch_expand_weights(const int* rfull, const int* nfull, const int* rhalf, 
                           int row0, int row_stride, int rows, int k1, const float* D, long long ld,
                           const int* rowmax_key, int* Vc, __half* Vv, int* Vn, int upper_only,
                           const float* const* panels, int out_global, cudaStream_t s) {
+  return launch_expand_weights_wl(rfull, nfull, rhalf, nhalf, row0, row_stride, rows, k1, D, ld, rowmax_key, Vc, Vv, Vn,
+                                  upper_only, panels, out_global, nullptr, nullptr, 0, nullptr, 0, nullptr, nullptr, s);
+}
+
+int launch_expand_weights_wl(const int* rfull, const int* nfull, const int* rhalf, const int* nhalf,
+                             int row0, int row_stride, int rows, int k1, const float* D, long long ld,
+                             const int* rowmax_key, int* Vc, __half* Vv, int* Vn, int upper_only,
+                             const float* const* panels, int out_global, const int* wl_idx, const float* wl_val, int Kw,
+                             const float* x32, long long ldx, const float* sq, int* wl_miss, cudaStream_t s) {
   if (rows == 0) return REID_OK;
+  REID_REQUIRE(D != nullptr || wl_idx != nullptr, "expand_weights: neither a distance matrix nor wide lists");
   REID_REQUIRE(!upper_only || (row0 == 0 && row_stride == 1) || (row_stride < 0 && panels),
                "expand_weights: upper_only needs all rows on one rank, or the sharded form with the peers' panels");
   const int k1p = k1 + 1, h = half_k(k1);
@@ -217,7 +247,7 @@ int launch_expand_weights(const int* rfull, const int* nfull, const int* rhalf, 
   expand_weights_kernel<<<cdiv(rows, wpb), wpb * 32, smem, s>>>(rfull, nfull, rhalf, nhalf, row0,
                                                                row_stride, rows, k1p, h, D, ld,
                                                                rowmax_key, cap1, capP, Vc, Vv, Vn, upper_only, panels,
-                                                               out_global);
+                                                               out_global, wl_idx, wl_val, Kw, x32, ldx, sq, wl_miss);
   return check_launch("expand_weights_kernel");
 }
 

@@ -409,15 +409,16 @@ class Engine:
         return (n + 31) // 32 * 32
 
     def dist(self, A: Features, B: Features, metric: int = METRIC_SQEUCLIDEAN, want_rowmax: bool = False,
-             engine: int | None = None, want_chunk_min: bool = False, upper_only: bool = False):
+             engine: int | None = None, want_chunk_min: bool = False, upper_only: bool = False,
+             key_in: torch.Tensor | None = None):
         """Returns (D [m, pitch] float32 — use D[:, :n] —, rowmax_key [m] int32 or None)
         [, chunk_min [m, ceil(n/32)] float32 when want_chunk_min (tensor-core engine only)]."""
         assert A.dp == B.dp
         m, n = A.n, B.n
         ld = self.pitch(n)
         D = self._empty((m, ld), torch.float32)
-        key = None
-        if want_rowmax:
+        key = key_in                 # row maxima accumulate into a caller's array (panels of one row block): no init here
+        if want_rowmax and key is None:
             key = self._empty((m,), torch.int32)
             _lib.call("reid_rowmax_init", _ptr(key), m, _stream())
         ra, rb = (A.sq, B.sq) if metric == METRIC_SQEUCLIDEAN else (A.nrm, B.nrm)
@@ -491,13 +492,15 @@ class Engine:
         return [(c0, starts[i + 1] if i + 1 < len(starts) else g) for i, c0 in enumerate(starts)]
 
     def retrieve_topk(self, Q: Features, G: Features, K: int, metric: int = METRIC_SQEUCLIDEAN,
-                      rows_per_pass: int = 16384, cols_per_pass: int = 65536, on_panel=None):
+                      rows_per_pass: int = 16384, cols_per_pass: int = 65536, on_panel=None,
+                      rowmax: torch.Tensor | None = None):
         """Exact K nearest gallery rows of every query row, ascending in stable (distance, column) order, WITHOUT the
         q x g matrix ever existing (100k x 1M x 4 B = 400 GB): the contraction writes one [rows_per_pass, cols_per_pass]
         panel at a time together with its 32-column chunk minima, the hinted selection reads ~K chunks per row of it,
         and the per-block winners [rows, blocks * K] are selected once more.  Candidate position order equals global
         column order among equal distances, so the result is bit for bit what selection over the full matrix gives.
-        Returns (idx int32 [q, K], dist float32 [q, K]); raw distances (the selection's divisor is 1)."""
+        Returns (idx int32 [q, K], dist float32 [q, K]); raw distances (the selection's divisor is 1).
+        rowmax: optional int32 [q] (reid_rowmax_init'ed): receives every row's maximum over ALL gallery columns."""
         q, g = Q.n, G.n
         if not 1 <= K <= min(g, 256):
             raise ValueError(f"K={K} outside [1, min(g, 256)]")
@@ -520,7 +523,8 @@ class Engine:
                     ci = self._empty((m, nb * K), torch.int32)
                 for b, (c0, c1) in enumerate(blocks):
                     with self.span("dist"):
-                        D, _, cmin = self.dist(A, G.rows(slice(c0, c1)), metric, want_rowmax=False, want_chunk_min=True)
+                        D, _, cmin = self.dist(A, G.rows(slice(c0, c1)), metric, want_rowmax=False, want_chunk_min=True,
+                                               key_in=None if rowmax is None else rowmax[r0:r1])
                     with self.span("select"):
                         idx, val = self.topk_rows(D, c1 - c0, unit[:m], K, want_values=True, chunk_min=cmin)
                         if nb == 1:
@@ -607,6 +611,152 @@ class Engine:
                     del D
         finally:
             self.symmetric = sym
+
+    # ------------------------------------------------------------------ re-ranking with no dense matrix
+    def evaluate_streamed_reranked(self, allf: Features, q: int, pids: torch.Tensor, cams: torch.Tensor, k1: int,
+                                   k2: int, lam: float, topk: int = 100, max_rank: int = 50, Kw: int = 64,
+                                   Kd: int | None = None, cap_o: int = 8192, rows_per_pass: int = 16384,
+                                   cols_per_pass: int = 65536, detail: dict | None = None):
+        """reranking.py:29-100 + evaluate.py:40-88 for a problem whose N x N (and q x g) matrix cannot exist (BASELINE
+        config 5: 100k queries x 1M gallery): k-reciprocal re-ranked CMC / mAP and the exact top-`topk` of every
+        re-ranked row.  allf: the prepared N = q + g rows (queries first), pids / cams [N] int64 on the device.
+
+          A  N x N panel sweep (this rank's rows, cyclic): per row the Kw nearest by raw distance and the row maximum
+             -> all-gather -> lists re-keyed by D / max: initial_rank[:, :K]                          (reranking.py:46-48)
+          B  reciprocal sets, V weights (distances looked up in the wide lists), k2 expansion, inverted index -- the
+             sparse kernels of the materialised path, replicated on every rank                      (reranking.py:51-82)
+          C  own queries: ordered float16 Jaccard chain into per-query overlap lists                (reranking.py:84-93)
+          D  q x g sweep 1: top-Kd by raw distance; exact distances of the same-identity and of the overlap columns
+          E  final keys of the special entries, raw-distance thresholds of every match                  (reranking.py:95)
+          F  q x g sweep 2: every entry binned as if untouched; G  corrections, AP / CMC; exact top-k merge
+        Same arithmetic as the materialised path with the full (non-symmetric) tile schedule: identical results whenever
+        `diag["v_misses"]` is 0 (tests/test_gpu_retrieval.py).  Returns ((cmc, mAP, n_valid, ap, first_hit),
+        (idx int32 [nq_local, topk], final float32 [nq_local, topk]), diag)."""
+        cm = self.comm
+        r, P = cm.rank, cm.world
+        N = allf.n
+        g = N - q
+        K = max(k1 + 1, k2)
+        Kw = min(max(Kw, K), N, 256)
+        Kd = min(g, 256, topk + 28) if Kd is None else min(Kd, g, 256)
+        if not (1 <= topk <= Kd and N >= K):
+            raise ValueError(f"topk={topk} / K={K} do not fit q={q}, g={g}")
+        st = _stream
+        # ---- A
+        with self.span("nn_sweep"):
+            A = allf.rows(slice(r, N, P))
+            key_l = self._empty((A.n,), torch.int32)
+            _lib.call("reid_rowmax_init", _ptr(key_l), A.n, st())
+            widx_l, wval_l = self.retrieve_topk(A, allf, Kw, METRIC_SQEUCLIDEAN, rows_per_pass, cols_per_pass,
+                                                rowmax=key_l)
+        with self.span("x_lists"):
+            widx, wval, key = cm.gather_rows(widx_l, N), cm.gather_rows(wval_l, N), cm.gather_rows(key_l, N)
+        # ---- B (replicated)
+        flags = self._zeros((5,), torch.int32)      # rekey ambiguous | V misses | overlap overflow | group overflow | topk ambiguous
+        with self.span("krecip"):
+            nbr = self._empty((N, K), torch.int32)
+            _lib.call("reid_lists_rekey", _ptr(widx), _ptr(wval), N, Kw, _ptr(key), K, _ptr(nbr), _ptr(flags[0:]), st())
+            rfull, nfull, rhalf, nhalf = self.krecip_sets(nbr, k1)
+            cap1 = v_row_capacity(k1)
+            Vc = self._empty((N, cap1), torch.int32)
+            Vv = self._empty((N, cap1), torch.float16)
+            Vn = self._empty((N,), torch.int32)
+            _lib.call("reid_krecip_V_lists", _ptr(rfull), _ptr(nfull), _ptr(rhalf), _ptr(nhalf), N, k1, _ptr(key),
+                      _ptr(widx), _ptr(wval), Kw, _ptr(allf.x32), allf.x32.stride(0), _ptr(allf.sq), _ptr(Vc), _ptr(Vv),
+                      _ptr(Vn), _ptr(flags[1:]), st())
+        if k2 != 1:
+            with self.span("qe"):
+                Qc, Qv, qoff, Qn, nnz_bound = self.query_expansion(nbr, k2, Vc, Vv, Vn, N, 0, 1)
+        else:
+            qoff = self._empty((N + 1,), torch.int64)
+            _lib.call("reid_ell_offsets", N, cap1, _ptr(qoff), st())
+            Qc, Qv, Qn = Vc.reshape(-1), Vv.reshape(-1), Vn
+            nnz_bound = N * cap1
+        with self.span("csc"):
+            colptr, csc_ent = self.inverted_index(Qc, Qv, qoff, Qn, N, nnz_bound)
+        # ---- C
+        nq = cm.local_count(q)
+        qsel = slice(r, q, P)
+        q_pids, g_pids = pids[:q][qsel].contiguous(), pids[q:].contiguous()
+        q_cams, g_cams = cams[:q][qsel].contiguous(), cams[q:].contiguous()
+        with self.span("overlap"):
+            ocol = self._empty((max(nq, 1) * cap_o,), torch.int32)
+            ot = self._empty((max(nq, 1) * cap_o,), torch.float16)
+            od = self._zeros((max(nq, 1) * cap_o,), torch.float32)
+            ocnt = self._empty((max(nq, 1),), torch.int32)
+            _lib.call("reid_overlap_lists", _ptr(Qc), _ptr(Qv), _ptr(qoff), _ptr(Qn), _ptr(colptr), _ptr(csc_ent), r, P,
+                      nq, q, cap_o, _ptr(ocol), _ptr(ot), _ptr(ocnt), _ptr(flags[2:]), st())
+        # ---- D
+        Qf, Gf = allf.rows(qsel), allf.rows(slice(q, N))
+        keys, start, lst, T = self.pid_index(g_pids)
+        glo = self._empty((max(nq, 1),), torch.int32)
+        glen = self._empty((max(nq, 1),), torch.int32)
+        _lib.call("reid_stream_group_lookup", _ptr(q_pids), nq, _ptr(keys), _ptr(start), T, _ptr(glo), _ptr(glen), st())
+        goff = self._zeros((nq + 1,), torch.int64)
+        goff[1:] = torch.cumsum(glen[:nq], 0, dtype=torch.int64)
+        sizes = torch.stack([goff[-1], glen[:nq].max().to(torch.int64) if nq else goff[-1]]).tolist()   # one host read
+        total, longest = int(sizes[0]), int(sizes[1])
+        if longest > 1024:
+            raise _lib.ReidError(f"an identity has {longest} gallery samples; the streamed scorer holds at most 1024 per query")
+        gd = self._empty((max(total, 1),), torch.float32)
+        oglo = torch.arange(max(nq, 1), device=self.device, dtype=torch.int32) * cap_o
+        ooff = oglo.to(torch.int64)
+
+        def gather(D, r0, m, c0, c1):
+            _lib.call("reid_stream_group_gather", _ptr(D), D.stride(0), m, c0, c1, _ptr(glo[r0:]), _ptr(glen[r0:]),
+                      _ptr(goff[r0:]), _ptr(lst), _ptr(gd), st())
+            _lib.call("reid_stream_group_gather", _ptr(D), D.stride(0), m, c0, c1, _ptr(oglo[r0:]), _ptr(ocnt[r0:]),
+                      _ptr(ooff[r0:]), _ptr(ocol), _ptr(od), st())
+
+        with self.span("sweep1"):
+            tidx, tval = self.retrieve_topk(Qf, Gf, Kd, METRIC_SQEUCLIDEAN, rows_per_pass, cols_per_pass, on_panel=gather)
+        # ---- E
+        c1 = float(np.float16(1 - lam))
+        c2 = float(np.float32(lam))
+        gkey = self._empty((max(total, 1),), torch.int64)
+        gjunk = self._empty((max(total, 1),), torch.uint8)
+        mk = self._empty((max(total, 1),), torch.int64)
+        thrA = self._empty((max(total, 1),), torch.float32)
+        thrB = self._empty((max(total, 1),), torch.float32)
+        nmatch = self._empty((max(nq, 1),), torch.int32)
+        bins = self._zeros((max(total, 1),), torch.int32)
+        with self.span("rr_prepare"):
+            _lib.call("reid_rr_prepare", nq, r, P, _ptr(glo), _ptr(glen), _ptr(goff), _ptr(lst), _ptr(gd), _ptr(q_cams),
+                      _ptr(g_cams), _ptr(key), c1, c2, cap_o, _ptr(ocol), _ptr(ot), _ptr(ocnt), _ptr(gkey), _ptr(gjunk),
+                      _ptr(mk), _ptr(thrA), _ptr(thrB), _ptr(nmatch), _ptr(flags[3:]), st())
+
+        # ---- F
+        def count(D, r0, m, c0, c1):
+            _lib.call("reid_stream_count_panel_rr", _ptr(D), D.stride(0), m, c0, c1, _ptr(goff[r0:]), _ptr(mk), _ptr(thrA),
+                      _ptr(thrB), _ptr(nmatch[r0:]), _ptr(bins), st())
+
+        with self.span("sweep2"):
+            self._sweep(Qf, Gf, METRIC_SQEUCLIDEAN, rows_per_pass, cols_per_pass, count)
+
+        # ---- G
+        def launch(ap, first, hist, nvalid):
+            _lib.call("reid_stream_score_rr", nq, r, P, _ptr(glo), _ptr(glen), _ptr(goff), _ptr(lst), _ptr(gd), _ptr(gkey),
+                      _ptr(gjunk), _ptr(mk), _ptr(thrA), _ptr(thrB), _ptr(nmatch), _ptr(bins), cap_o, _ptr(ocol), _ptr(ot),
+                      _ptr(od), _ptr(ocnt), _ptr(q_pids), _ptr(g_pids), _ptr(key), c1, c2, max_rank, _ptr(ap), _ptr(first),
+                      _ptr(hist), _ptr(nvalid), st())
+        res = self._score_common(launch, nq, max_rank, q, span="score")
+        with self.span("rr_topk"):
+            out_i = self._empty((max(nq, 1), topk), torch.int32)
+            out_v = self._empty((max(nq, 1), topk), torch.float32)
+            _lib.call("reid_rr_topk", nq, r, P, _ptr(tidx), _ptr(tval), Kd, g, cap_o, _ptr(ocol), _ptr(ot), _ptr(od),
+                      _ptr(ocnt), _ptr(key), c1, c2, topk, _ptr(out_i), _ptr(out_v), _ptr(flags[4:]), st())
+        f = [int(v) for v in flags.tolist()]
+        diag = {"rekey_ambiguous": f[0], "v_misses": f[1], "overlap_overflow": f[2], "group_overflow": f[3],
+                "topk_ambiguous": f[4], "Kw": Kw, "Kd": Kd}
+        if f[2] or f[3]:
+            raise _lib.ReidError(f"streamed re-ranking: {f[2]} queries touch more than cap_o={cap_o} gallery columns, "
+                                 f"largest identity group {f[3]} (limit 1024)")
+        if f[0] or f[4]:
+            raise _lib.ReidError(f"streamed re-ranking: candidate lists too short for exactness ({f[0]} rows at Kw={Kw}, "
+                                 f"{f[4]} queries at Kd={Kd}); raise Kw / Kd")
+        if detail is not None:
+            detail.update(nbr=nbr, Vc=Vc, Vv=Vv, Vn=Vn, key=key, ocol=ocol, ot=ot, od=od, ocnt=ocnt, tidx=tidx, tval=tval)
+        return res, (out_i[:nq], out_v[:nq]), diag
 
     # ------------------------------------------------------------------ K6
     def krecip_sets(self, nbr: torch.Tensor, k1: int):

@@ -66,3 +66,30 @@ def streamed_eval(qf, gf, q_pids, g_pids, q_camids, g_camids, max_rank: int = 50
     if cm.world > 1:
         idx, val = cm.gather_rows(idx, q), cm.gather_rows(val, q)
     return out + (idx.cpu().numpy(), val.cpu().numpy())
+
+
+def streamed_rerank_eval(qf, gf, q_pids, g_pids, q_camids, g_camids, k1: int = 20, k2: int = 6, lambda_value: float = 0.3,
+                         topk: int = 100, max_rank: int = 50, feat_norm: bool = True, rows_per_pass: int = 16384,
+                         cols_per_pass: int = 65536, wide: int = 64, cap_o: int = 8192, return_diag: bool = False):
+    """``R1_mAP_eval(reranking=True)`` semantics (evaluate.py:110-135 with re_ranking's k1 / k2 / lambda_value,
+    reranking.py:29-100) for a query / gallery pair whose N x N matrix cannot exist (BASELINE config 5: 100k x 1M):
+    returns ``(cmc float32[max_rank], mAP float64, indices int32 [q, topk], final float32 [q, topk])`` -- CMC / mAP of the
+    k-reciprocal re-ranked distances and the exact top-k of every re-ranked row.  With several ranks the rows of the
+    N x N sweep and the queries are sharded cyclically; neighbour lists and results are all-gathered."""
+    eng = _engine.default_engine()
+    cm = eng.comm
+    q, g = int(qf.shape[0]), int(gf.shape[0])
+    if g < max_rank:
+        max_rank = g
+        print("Note: number of gallery samples is quite small, got {}".format(g))
+    allf = eng.prepare(torch.cat([_to_device_f32(qf, eng.device), _to_device_f32(gf, eng.device)]), feat_norm)
+    pids = torch.cat([_ids(q_pids, eng.device), _ids(g_pids, eng.device)])
+    cams = torch.cat([_ids(q_camids, eng.device), _ids(g_camids, eng.device)])
+    (cmc, mAP, nvalid, _, _), (idx, val), diag = eng.evaluate_streamed_reranked(
+        allf, q, pids, cams, k1, k2, lambda_value, topk=topk, max_rank=max_rank, Kw=wide, cap_o=cap_o,
+        rows_per_pass=rows_per_pass, cols_per_pass=cols_per_pass)
+    assert int(nvalid.item()) > 0, "Error: all query identities do not appear in gallery"
+    if cm.world > 1:
+        idx, val = cm.gather_rows(idx.contiguous(), q), cm.gather_rows(val.contiguous(), q)
+    out = (cmc.cpu().numpy(), np.float64(mAP.item()), idx.cpu().numpy(), val.cpu().numpy())
+    return out + (diag,) if return_diag else out
