@@ -186,8 +186,11 @@ REID_API int reid_krecip_V_tri(const int32_t* rfull, const int32_t* nfull, const
  * by (D, column), e.g. from reid_topk_rows_hinted over the panels of an N x N sweep) and the rows' global maxima: the
  * first K columns in (D / max, column) order -> nbr[rows, K].  *ambiguous counts rows whose K-th quotient equals the
  * list's last one (an unseen column could tie): enlarge Kw.
- * reid_krecip_V_lists: reid_krecip_V for all rows with every distance D[i, e] looked up in row i's wide list; a miss is
- * recomputed from the float32 features x32 / squared norms sq and counted in *misses.
+ * reid_krecip_V_lists: reid_krecip_V for all rows with every distance D[i, e] looked up in row i's wide list, then in
+ * the caller's table of extra pairs (mt_keys = row << 32 | column ascending, mt_vals; may be NULL).  A pair in neither is
+ * counted in *misses, written to miss_out (up to miss_cap) and, for this call only, recomputed from the float32 features
+ * x32 / squared norms sq: call once to collect the misses, contract those pairs (reid_dist on the gathered rows -- the
+ * same arithmetic as the panels), call again with the table.
  * reid_overlap_lists: reranking.py:86-92 for a window of queries with a shared-memory hash table instead of an N-bit row:
  * per query the gallery columns (target - q) it overlaps, ascending, and the float16 overlap sums -> ocol / ot at
  * [l * cap_o ...], ocnt[l] (-1 and *overflow += 1 when a query touches more than cap_o <= 8192 gallery columns).
@@ -205,7 +208,8 @@ REID_API int reid_lists_rekey(const int32_t* widx, const float* wval, int rows, 
 REID_API int reid_krecip_V_lists(const int32_t* rfull, const int32_t* nfull, const int32_t* rhalf, const int32_t* nhalf,
                         int rows, int k1, const int32_t* rowmax_key, const int32_t* wl_idx, const float* wl_val, int Kw,
                         const float* x32, int64_t ldx, const float* sq, int32_t* Vc, reid_half* Vv, int32_t* Vn,
-                        int32_t* misses, void* stream);
+                        int32_t* misses, const uint64_t* mt_keys, const float* mt_vals, int mt_n, uint64_t* miss_out,
+                        int miss_cap, void* stream);
 REID_API int reid_overlap_lists(const int32_t* Qc, const reid_half* Qv, const int64_t* qoff, const int32_t* Qn,
                        const int64_t* colptr, const uint64_t* csc_ent, int q0, int q_stride, int nq, int q, int cap_o,
                        int32_t* ocol, reid_half* ot, int32_t* ocnt, int32_t* overflow, void* stream);

@@ -365,11 +365,13 @@ int reid_lists_rekey(const int32_t* widx, const float* wval, int rows, int Kw, c
 int reid_krecip_V_lists(const int32_t* rfull, const int32_t* nfull, const int32_t* rhalf, const int32_t* nhalf, int rows,
                         int k1, const int32_t* rowmax_key, const int32_t* wl_idx, const float* wl_val, int Kw,
                         const float* x32, int64_t ldx, const float* sq, int32_t* Vc, reid_half* Vv, int32_t* Vn,
-                        int32_t* misses, void* stream) {
+                        int32_t* misses, const uint64_t* mt_keys, const float* mt_vals, int mt_n, uint64_t* miss_out,
+                        int miss_cap, void* stream) {
   ENTER();
   REID_REQUIRE(k1 >= 1 && Kw >= 1 && wl_idx && wl_val && x32 && sq && misses, "krecip_V_lists: bad arguments");
   return launch_expand_weights_wl(rfull, nfull, rhalf, nhalf, 0, 1, rows, k1, nullptr, 0, rowmax_key, Vc, H(Vv), Vn, 0,
-                                  nullptr, 0, wl_idx, wl_val, Kw, x32, ldx, sq, misses, S(stream));
+                                  nullptr, 0, wl_idx, wl_val, Kw, x32, ldx, sq, misses, ULL(mt_keys), mt_vals, mt_n,
+                                  reinterpret_cast<unsigned long long*>(miss_out), miss_cap, S(stream));
 }
 
 int reid_overlap_lists(const int32_t* Qc, const reid_half* Qv, const int64_t* qoff, const int32_t* Qn,

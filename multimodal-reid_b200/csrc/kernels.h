@@ -56,7 +56,8 @@ int launch_expand_weights_wl(const int* rfull, const int* nfull, const int* rhal
                              int row_stride, int rows, int k1, const float* D, long long ld, const int* rowmax_key,
                              int* Vc, __half* Vv, int* Vn, int upper_only, const float* const* panels, int out_global,
                              const int* wl_idx, const float* wl_val, int Kw, const float* x32, long long ldx,
-                             const float* sq, int* wl_miss, cudaStream_t s);
+                             const float* sq, int* wl_miss, const unsigned long long* mt_keys, const float* mt_vals,
+                             int mt_n, unsigned long long* miss_out, int miss_cap, cudaStream_t s);
 // stream_rerank.cu (re-ranking without any dense matrix)
 int launch_lists_rekey(const int* widx, const float* wval, int rows, int Kw, const int* rowmax_key, int K, int* nbr,
                        int* ambiguous, cudaStream_t s);

@@ -80,7 +80,9 @@ expand_weights_kernel(const int* __restrict__ rfull, const int* __restrict__ nfu
                       int* __restrict__ Vc, __half* __restrict__ Vv, int* __restrict__ Vn, int upper_only,
                       const float* const* __restrict__ panels, int out_global, const int* __restrict__ wl_idx,
                       const float* __restrict__ wl_val, int Kw, const float* __restrict__ x32, long long ldx,
-                      const float* __restrict__ sq, int* __restrict__ wl_miss) {
+                      const float* __restrict__ sq, int* __restrict__ wl_miss,
+                      const unsigned long long* __restrict__ mt_keys, const float* __restrict__ mt_vals, int mt_n,
+                      unsigned long long* __restrict__ miss_out, int miss_cap) {
   extern __shared__ int smem_i[];
   const int wpb = blockDim.x >> 5;
   const int w = threadIdx.x >> 5, lane = lane_id();
@@ -168,20 +170,35 @@ expand_weights_kernel(const int* __restrict__ rfull, const int* __restrict__ nfu
     if (wl_idx) {
       // streamed form (no matrix anywhere): D[row, e] is looked up in the row's wide raw-distance neighbour list -- the
       // exact value the contraction produced.  E_i consists of reciprocal neighbours of reciprocal neighbours, so a miss
-      // is rare; it is recomputed from the float32 features (agrees with the tensor-core value to ~1e-6) and counted.
+      // is rare.  Misses are looked up in a second table (mt_keys = row << 32 | column, sorted): the caller runs this
+      // kernel once to collect them (miss_out), contracts exactly those pairs on the tensor cores, and runs it again.
+      // A pair in neither place is recomputed from the float32 features (~1e-6 off the tensor-core value) and counted.
       const int* li = wl_idx + (long long)row * Kw;
       int hit = -1;
       for (int t = 0; t < Kw; ++t)
         if (li[t] == e) { hit = t; break; }
+      int mhit = -1;
+      const unsigned long long pk = ((unsigned long long)(unsigned)row << 32) | (unsigned)e;
+      if (hit < 0 && mt_keys) {
+        int lo = 0, hi = mt_n;
+        while (lo < hi) {
+          const int mid = (lo + hi) >> 1;
+          if (mt_keys[mid] < pk) lo = mid + 1; else hi = mid;
+        }
+        if (lo < mt_n && mt_keys[lo] == pk) mhit = lo;
+      }
       if (hit >= 0) {
         dv = wl_val[(long long)row * Kw + hit];
+      } else if (mhit >= 0) {
+        dv = mt_vals[mhit];
       } else {
         const float* a = x32 + (long long)row * ldx;
         const float* b = x32 + (long long)e * ldx;
         float acc = 0.0f;
         for (int k = 0; k < (int)ldx; ++k) acc = __fmaf_rn(a[k], b[k], acc);
         dv = __fmaf_rn(-2.0f, acc, __fadd_rn(sq[row], sq[e]));
-        atomicAdd(wl_miss, 1);
+        const int pos = atomicAdd(wl_miss, 1);
+        if (miss_out && pos < miss_cap) miss_out[pos] = pk;
       }
     } else if (upper_only && e < (row & ~255)) {
       // D[e, row]: on one rank a row of the same matrix; in a sharded job it sits in the panel of the rank that owns e's
@@ -221,14 +238,17 @@ int launch_expand_weights(const int* rfull, const int* nfull, const int* rhalf, 
                           const int* rowmax_key, int* Vc, __half* Vv, int* Vn, int upper_only,
                           const float* const* panels, int out_global, cudaStream_t s) {
   return launch_expand_weights_wl(rfull, nfull, rhalf, nhalf, row0, row_stride, rows, k1, D, ld, rowmax_key, Vc, Vv, Vn,
-                                  upper_only, panels, out_global, nullptr, nullptr, 0, nullptr, 0, nullptr, nullptr, s);
+                                  upper_only, panels, out_global, nullptr, nullptr, 0, nullptr, 0, nullptr, nullptr,
+                                  nullptr, nullptr, 0, nullptr, 0, s);
 }
 
 int launch_expand_weights_wl(const int* rfull, const int* nfull, const int* rhalf, const int* nhalf,
                              int row0, int row_stride, int rows, int k1, const float* D, long long ld,
                              const int* rowmax_key, int* Vc, __half* Vv, int* Vn, int upper_only,
                              const float* const* panels, int out_global, const int* wl_idx, const float* wl_val, int Kw,
-                             const float* x32, long long ldx, const float* sq, int* wl_miss, cudaStream_t s) {
+                             const float* x32, long long ldx, const float* sq, int* wl_miss,
+                             const unsigned long long* mt_keys, const float* mt_vals, int mt_n,
+                             unsigned long long* miss_out, int miss_cap, cudaStream_t s) {
   if (rows == 0) return REID_OK;
   REID_REQUIRE(D != nullptr || wl_idx != nullptr, "expand_weights: neither a distance matrix nor wide lists");
   REID_REQUIRE(!upper_only || (row0 == 0 && row_stride == 1) || (row_stride < 0 && panels),
@@ -247,7 +267,8 @@ int launch_expand_weights_wl(const int* rfull, const int* nfull, const int* rhal
   expand_weights_kernel<<<cdiv(rows, wpb), wpb * 32, smem, s>>>(rfull, nfull, rhalf, nhalf, row0,
                                                                row_stride, rows, k1p, h, D, ld,
                                                                rowmax_key, cap1, capP, Vc, Vv, Vn, upper_only, panels,
-                                                               out_global, wl_idx, wl_val, Kw, x32, ldx, sq, wl_miss);
+                                                               out_global, wl_idx, wl_val, Kw, x32, ldx, sq, wl_miss,
+                                                               mt_keys, mt_vals, mt_n, miss_out, miss_cap);
   return check_launch("expand_weights_kernel");
 }
 

@@ -661,9 +661,39 @@ class Engine:
             Vc = self._empty((N, cap1), torch.int32)
             Vv = self._empty((N, cap1), torch.float16)
             Vn = self._empty((N,), torch.int32)
-            _lib.call("reid_krecip_V_lists", _ptr(rfull), _ptr(nfull), _ptr(rhalf), _ptr(nhalf), N, k1, _ptr(key),
-                      _ptr(widx), _ptr(wval), Kw, _ptr(allf.x32), allf.x32.stride(0), _ptr(allf.sq), _ptr(Vc), _ptr(Vv),
-                      _ptr(Vn), _ptr(flags[1:]), st())
+            miss_cap = max(1 << 16, N * 2)
+            miss_out = self._empty((miss_cap,), torch.int64)
+
+            def v_pass(mt_keys, mt_vals, mt_n, out, cap):
+                flags[1:2].zero_()
+                _lib.call("reid_krecip_V_lists", _ptr(rfull), _ptr(nfull), _ptr(rhalf), _ptr(nhalf), N, k1, _ptr(key),
+                          _ptr(widx), _ptr(wval), Kw, _ptr(allf.x32), allf.x32.stride(0), _ptr(allf.sq), _ptr(Vc),
+                          _ptr(Vv), _ptr(Vn), _ptr(flags[1:]), _ptr(mt_keys), _ptr(mt_vals), mt_n, _ptr(out), cap, st())
+
+            v_pass(None, None, 0, miss_out, miss_cap)
+            n_miss = int(flags[1].item())                  # pairs of E_i outside row i's wide list (host read)
+            pairs_recomputed = n_miss
+            if n_miss > miss_cap:
+                raise _lib.ReidError(f"streamed re-ranking: {n_miss} V pairs fell outside the wide lists (Kw={Kw}); raise Kw")
+            if n_miss:
+                # exactly those pairs on the tensor cores: gathered operand rows, 2048 pairs per contraction, diagonals
+                mt_keys = torch.sort(miss_out[:n_miss]).values
+                mt_vals = self._empty((n_miss,), torch.float32)
+                ri, ci = (mt_keys >> 32), (mt_keys & 0xFFFFFFFF)
+                sym = self.symmetric
+                self.symmetric = False
+                try:
+                    for a in range(0, n_miss, 2048):
+                        b = min(n_miss, a + 2048)
+                        fa = Features(allf.x32[ri[a:b]], allf.hi[ri[a:b]], allf.lo[ri[a:b]], allf.sq[ri[a:b]],
+                                      allf.nrm[ri[a:b]], allf.amax, allf.d)
+                        fb = Features(allf.x32[ci[a:b]], allf.hi[ci[a:b]], allf.lo[ci[a:b]], allf.sq[ci[a:b]],
+                                      allf.nrm[ci[a:b]], allf.amax, allf.d)
+                        Dm, _ = self.dist(fa, fb, METRIC_SQEUCLIDEAN)
+                        mt_vals[a:b] = torch.diagonal(Dm[:, : b - a])
+                finally:
+                    self.symmetric = sym
+                v_pass(mt_keys, mt_vals, n_miss, None, 0)
         if k2 != 1:
             with self.span("qe"):
                 Qc, Qv, qoff, Qn, nnz_bound = self.query_expansion(nbr, k2, Vc, Vv, Vn, N, 0, 1)
@@ -746,8 +776,8 @@ class Engine:
             _lib.call("reid_rr_topk", nq, r, P, _ptr(tidx), _ptr(tval), Kd, g, cap_o, _ptr(ocol), _ptr(ot), _ptr(od),
                       _ptr(ocnt), _ptr(key), c1, c2, topk, _ptr(out_i), _ptr(out_v), _ptr(flags[4:]), st())
         f = [int(v) for v in flags.tolist()]
-        diag = {"rekey_ambiguous": f[0], "v_misses": f[1], "overlap_overflow": f[2], "group_overflow": f[3],
-                "topk_ambiguous": f[4], "Kw": Kw, "Kd": Kd}
+        diag = {"rekey_ambiguous": f[0], "v_misses": f[1], "v_pairs_recontracted": pairs_recomputed,
+                "overlap_overflow": f[2], "group_overflow": f[3], "topk_ambiguous": f[4], "Kw": Kw, "Kd": Kd}
         if f[2] or f[3]:
             raise _lib.ReidError(f"streamed re-ranking: {f[2]} queries touch more than cap_o={cap_o} gallery columns, "
                                  f"largest identity group {f[3]} (limit 1024)")

@@ -199,7 +199,7 @@ def test_streamed_rerank_equals_materialised(eng, engine_mod, synth, oracle, nam
         eng.symmetric = saved
     allf = eng.prepare(X, True)
     sdet = {}
-    res, (idx, val), diag = eng.evaluate_streamed_reranked(allf, q, pids, cams, k1, k2, 0.3, topk=topk, Kw=128,
+    res, (idx, val), diag = eng.evaluate_streamed_reranked(allf, q, pids, cams, k1, k2, 0.3, topk=topk, Kw=64,
                                                            cap_o=4096, rows_per_pass=rows_pp, cols_per_pass=cols_pp,
                                                            detail=sdet)
     print(f"[a13] {name} k1={k1} k2={k2}: {diag}")
