@@ -31,6 +31,12 @@ def main():
     ap.add_argument("--rows-per-pass", type=int, default=16384)
     ap.add_argument("--cols-per-pass", type=int, default=65536)
     ap.add_argument("--score", action="store_true", help="also CMC / mAP over the streamed problem (two sweeps)")
+    ap.add_argument("--rerank", action="store_true",
+                    help="k-reciprocal re-ranked CMC / mAP + exact top-k of the re-ranked rows (N x N sweep + two q x g sweeps)")
+    ap.add_argument("--k1", type=int, default=20)
+    ap.add_argument("--k2", type=int, default=6)
+    ap.add_argument("--lam", type=float, default=0.3)
+    ap.add_argument("--wide", type=int, default=64, help="neighbours kept per row by the N x N sweep")
     ap.add_argument("--ids", type=int, default=50_000, help="identities (gallery draws from 1.2x as many), 32 cameras")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -68,8 +74,17 @@ def main():
     qp_l, qc_l = qp[mine].contiguous(), qc[mine].contiguous()
     score_out = {}
 
+    pids_all, cams_all = torch.cat([qp, gp]), torch.cat([qc, gc])
+    diag_out = {}
+
     def step():
-        if args.score:
+        if args.rerank:
+            (cmc, mAP, nv, _, _), (idx, val), diag = eng.evaluate_streamed_reranked(
+                allf, q, pids_all, cams_all, args.k1, args.k2, args.lam, topk=K, Kw=args.wide,
+                rows_per_pass=args.rows_per_pass, cols_per_pass=args.cols_per_pass)
+            score_out.update(cmc=cmc, mAP=mAP, nv=nv)
+            diag_out.update(diag)
+        elif args.score:
             (cmc, mAP, nv, _, _), (idx, val) = eng.evaluate_streamed(Q, G, qp_l, gp, qc_l, gc, 50, K,
                                                                      rows_per_pass=args.rows_per_pass,
                                                                      cols_per_pass=args.cols_per_pass, q_total=q)
@@ -110,15 +125,20 @@ def main():
         rows_local = cm.local_count(q)
         flops = 2.0 * rows_local * g * d
         dist_ms = stages.get("dist", float("nan"))
-        sweeps = 2 if args.score else 1
+        sweeps = 2 if (args.score or args.rerank) else 1
         flops *= sweeps
-        line = {"metric": ("top-k retrieval + CMC/mAP" if args.score else "top-k retrieval")
+        if args.rerank:                          # + this rank's rows of the N x N sweep
+            flops += 2.0 * cm.local_count(q + g) * (q + g) * d
+        line = {"metric": ("k-reciprocal re-ranked top-k + CMC/mAP" if args.rerank else
+                           "top-k retrieval + CMC/mAP" if args.score else "top-k retrieval")
                           + " q x g pairs/sec (matrix never materialised)",
                 "value": q * g / (ms * 1e-3), "unit": "pairs/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
                 "dtype": "f32 (fp16-split tensor-core contraction)", "data": "synthetic",
                 "config": {"workload": "scaled retrieval", "q": q, "g": g, "d": d, "topk": K,
                            "rows_per_pass": args.rows_per_pass, "cols_per_pass": args.cols_per_pass,
+                           "rerank": ({"k1": args.k1, "k2": args.k2, "lambda": args.lam, "wide": args.wide, **diag_out}
+                                      if args.rerank else None),
                            "inputs": "larger than L2 (no flush needed)"},
                 "gpu_launches": launches, "stages_ms": stages,
                 "roofline": {"kernel": "dist_tc2_kernel (rectangular panels)", "bound": "tensor",
@@ -129,7 +149,8 @@ def main():
                               "GB/s_over_dist": 4.0 * rows_local * g * (1 + 1 / 32) / (dist_ms * 1e-3) / 1e9,
                               "peak": hbm},
                 "score": ({"mAP": float(score_out["mAP"].item()), "rank1": float(score_out["cmc"][0].item()),
-                           "n_valid": int(score_out["nv"].item()), "sweeps": 2} if args.score else None),
+                           "n_valid": int(score_out["nv"].item()), "sweeps": 3 if args.rerank else 2}
+                          if (args.score or args.rerank) else None),
                 "first_row": {"idx": idx[0, :5].tolist(), "dist": [round(float(x), 6) for x in val[0, :5]]}}
         print(json.dumps(line))
     if world > 1:

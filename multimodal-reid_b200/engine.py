@@ -678,21 +678,26 @@ class Engine:
             if n_miss:
                 # exactly those pairs on the tensor cores: gathered operand rows, 2048 pairs per contraction, diagonals
                 mt_keys = torch.sort(miss_out[:n_miss]).values
-                mt_vals = self._empty((n_miss,), torch.float32)
+                mt_vals = self._zeros((n_miss,), torch.float32)
                 ri, ci = (mt_keys >> 32), (mt_keys & 0xFFFFFFFF)
                 sym = self.symmetric
                 self.symmetric = False
                 try:
-                    for a in range(0, n_miss, 2048):
-                        b = min(n_miss, a + 2048)
-                        fa = Features(allf.x32[ri[a:b]], allf.hi[ri[a:b]], allf.lo[ri[a:b]], allf.sq[ri[a:b]],
-                                      allf.nrm[ri[a:b]], allf.amax, allf.d)
-                        fb = Features(allf.x32[ci[a:b]], allf.hi[ci[a:b]], allf.lo[ci[a:b]], allf.sq[ci[a:b]],
-                                      allf.nrm[ci[a:b]], allf.amax, allf.d)
+                    chunk = 8192                 # pairs per contraction: [8192 x 8192] = 1 024 tiles, 8 192 values kept
+                    starts = list(range(0, n_miss, chunk))
+                    for a in starts[r::P]:       # ranks take the chunks in turn; the values are summed across ranks below
+                        b = min(n_miss, a + chunk)
+                        none = allf.x32[:0]      # the float32 rows are not operands of the tensor-core contraction
+                        fa = Features(none, allf.hi[ri[a:b]], allf.lo[ri[a:b]], allf.sq[ri[a:b]], allf.nrm[ri[a:b]],
+                                      allf.amax, allf.d)
+                        fb = Features(none, allf.hi[ci[a:b]], allf.lo[ci[a:b]], allf.sq[ci[a:b]], allf.nrm[ci[a:b]],
+                                      allf.amax, allf.d)
                         Dm, _ = self.dist(fa, fb, METRIC_SQEUCLIDEAN)
                         mt_vals[a:b] = torch.diagonal(Dm[:, : b - a])
+                        del Dm, fa, fb
                 finally:
                     self.symmetric = sym
+                cm.all_reduce_sum(mt_vals)       # every value was written by one rank, the others hold exact zeros
                 v_pass(mt_keys, mt_vals, n_miss, None, 0)
         if k2 != 1:
             with self.span("qe"):
