@@ -193,7 +193,8 @@ REID_API int reid_krecip_V_tri(const int32_t* rfull, const int32_t* nfull, const
  * same arithmetic as the panels), call again with the table.
  * reid_overlap_lists: reranking.py:86-92 for a window of queries with a shared-memory hash table instead of an N-bit row:
  * per query the gallery columns (target - q) it overlaps, ascending, and the float16 overlap sums -> ocol / ot at
- * [l * cap_o ...], ocnt[l] (-1 and *overflow += 1 when a query touches more than cap_o <= 8192 gallery columns).
+ * [l * cap_o ...], ocnt[l] (-1 and *overflow += 1 when a query touches more than cap_o gallery columns, or more than
+ * 8192 inside one of the ceil(cap_o / 4096) column ranges the gallery is processed in).
  * reid_rr_prepare: per query, from the distances of its same-identity gallery columns (group arrays as
  * reid_stream_group_*) and its overlap list: true final keys of the group (gkey, gjunk), the sorted match keys mk, and
  * for every match the raw-distance thresholds thrA / thrB (largest D whose untouched final value is < / <= the match's).
@@ -211,8 +212,11 @@ REID_API int reid_krecip_V_lists(const int32_t* rfull, const int32_t* nfull, con
                         int32_t* misses, const uint64_t* mt_keys, const float* mt_vals, int mt_n, uint64_t* miss_out,
                         int miss_cap, void* stream);
 REID_API int reid_overlap_lists(const int32_t* Qc, const reid_half* Qv, const int64_t* qoff, const int32_t* Qn,
-                       const int64_t* colptr, const uint64_t* csc_ent, int q0, int q_stride, int nq, int q, int cap_o,
-                       int32_t* ocol, reid_half* ot, int32_t* ocnt, int32_t* overflow, void* stream);
+                       const int64_t* colptr, const uint64_t* csc_ent, int q0, int q_stride, int nq, int q, int N,
+                       int cap_o, int32_t* ocol, reid_half* ot, int32_t* ocnt, int32_t* overflow, void* stream);
+/* od[l * cap_o + e] = panel[l, ocol[l * cap_o + e] - c0] for the listed columns inside the panel's block [c0, c1) */
+REID_API int reid_stream_list_gather(const float* panel, int64_t ld, int rows, int c0, int c1, int cap_o,
+                            const int32_t* ocol, const int32_t* ocnt, float* od, void* stream);
 REID_API int reid_rr_prepare(int nq, int q0, int q_stride, const int32_t* glo, const int32_t* glen, const int64_t* goff,
                     const int32_t* list, const float* gd, const int64_t* q_cam, const int64_t* g_cam,
                     const int32_t* rowmax_key, float c1, float c2, int cap_o, const int32_t* ocol, const reid_half* ot,

@@ -62,8 +62,10 @@ int launch_expand_weights_wl(const int* rfull, const int* nfull, const int* rhal
 int launch_lists_rekey(const int* widx, const float* wval, int rows, int Kw, const int* rowmax_key, int K, int* nbr,
                        int* ambiguous, cudaStream_t s);
 int launch_overlap_hash(const int* Qc, const __half* Qv, const long long* qoff, const int* Qn, const long long* colptr,
-                        const unsigned long long* csc_ent, int q0, int q_stride, int nq, int q, int cap_o, int* ocol,
-                        __half* ot, int* ocnt, int* overflow, cudaStream_t s);
+                        const unsigned long long* csc_ent, int q0, int q_stride, int nq, int q, int N, int cap_o,
+                        int* ocol, __half* ot, int* ocnt, int* overflow, cudaStream_t s);
+int launch_list_gather_sorted(const float* panel, long long ld, int rows, int c0, int c1, int cap_o, const int* ocol,
+                              const int* ocnt, float* od, cudaStream_t s);
 int launch_rr_prepare(int nq, int q0, int q_stride, const int* glo, const int* glen, const long long* goff,
                       const int* list, const float* gd, const long long* q_cam, const long long* g_cam,
                       const int* rowmax_key, float c1, float c2, int cap_o, const int* ocol, const __half* ot,

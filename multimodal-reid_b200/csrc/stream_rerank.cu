@@ -96,8 +96,9 @@ constexpr int OH_CAP = 8192;             // distinct gallery targets per query (
 __global__ void __launch_bounds__(OH_T)
 overlap_hash_kernel(const int* __restrict__ Qc, const __half* __restrict__ Qv, const long long* __restrict__ qoff,
                     const int* __restrict__ Qn, const long long* __restrict__ colptr,
-                    const unsigned long long* __restrict__ csc_ent, int q0, int q_stride, int q, int cap_o,
-                    int* __restrict__ ocol, __half* __restrict__ ot, int* __restrict__ ocnt, int* __restrict__ overflow) {
+                    const unsigned long long* __restrict__ csc_ent, int q0, int q_stride, int q, int N, int cap_o,
+                    int nrange, int* __restrict__ ocol, __half* __restrict__ ot, int* __restrict__ ocnt,
+                    int* __restrict__ overflow) {
   extern __shared__ __align__(16) unsigned char oh_smem[];
   int* keys = reinterpret_cast<int*>(oh_smem);                                   // [OH_SLOTS] target or -1
   __half* tv = reinterpret_cast<__half*>(oh_smem + (size_t)OH_SLOTS * 4);         // [OH_SLOTS] running overlap
@@ -105,68 +106,109 @@ overlap_hash_kernel(const int* __restrict__ Qc, const __half* __restrict__ Qv, c
   __shared__ int s_new, s_n, s_bad;
   const int qi = blockIdx.x, tid = threadIdx.x;
   const long long row = own_row(q0, q_stride, qi);
-  for (int i = tid; i < OH_SLOTS; i += OH_T) { keys[i] = -1; tv[i] = __ushort_as_half(0); }
-  if (tid == 0) { s_new = 0; s_n = 0; s_bad = 0; }
-  __syncthreads();
   const long long off = qoff[row];
   const int nq_cols = Qn[row];
-  for (int ci = 0; ci < nq_cols; ++ci) {                     // ascending columns: the reference's order of additions
-    const int c = Qc[off + ci];
-    const float vq = __half2float(Qv[off + ci]);
-    const long long p0 = colptr[c];
-    const int len = (int)(colptr[c + 1] - p0);
-    for (int p = tid; p < len; p += OH_T) {                 // entries of one column hit distinct targets
-      const unsigned long long ent = csc_ent[p0 + p];
-      const int g = (int)(unsigned)(ent & 0xffffffffu);
-      if (g < q) continue;                                   // only gallery columns reach final[:q, q:]
-      const float v = __half2float(__ushort_as_half((unsigned short)(ent >> 32)));
-      unsigned slot = ((unsigned)g * 2654435761u) >> (32 - 14);
-      bool placed = false;
-      for (int probe = 0; probe < OH_SLOTS; ++probe) {
-        const int cur = atomicCAS(&keys[slot], -1, g);
-        if (cur == -1) { atomicAdd(&s_new, 1); placed = true; break; }
-        if (cur == g) { placed = true; break; }
-        slot = (slot + 1) & (OH_SLOTS - 1);
+  const int g = N - q;
+  const int span = (g + nrange - 1) / nrange;               // gallery columns per pass
+  int written = 0;                                           // entries already in the output (uniform)
+  // A query at the 1M-gallery scale overlaps tens of thousands of gallery rows -- more than a shared-memory table
+  // holds -- so the gallery is cut into `nrange` column ranges and the chain is run once per range: every pass walks
+  // all of the query's column lists but keeps only the targets of its range (each target's additions still come in
+  // ascending column order), then emits them sorted; ranges ascend, so the concatenation is sorted too.
+  for (int rg = 0; rg < nrange; ++rg) {
+    const int glo = q + rg * span, ghi = min(N, glo + span);
+    for (int i = tid; i < OH_SLOTS; i += OH_T) { keys[i] = -1; tv[i] = __ushort_as_half(0); }
+    if (tid == 0) { s_new = 0; s_n = 0; s_bad = 0; }
+    __syncthreads();
+    for (int ci = 0; ci < nq_cols; ++ci) {                   // ascending columns: the reference's order of additions
+      const int c = Qc[off + ci];
+      const float vq = __half2float(Qv[off + ci]);
+      const long long p0 = colptr[c];
+      const int len = (int)(colptr[c + 1] - p0);
+      for (int p = tid; p < len; p += OH_T) {               // entries of one column hit distinct targets
+        const unsigned long long ent = csc_ent[p0 + p];
+        const int gt = (int)(unsigned)(ent & 0xffffffffu);
+        if (gt < glo || gt >= ghi) continue;                 // only gallery columns (of this range) reach final[:q, q:]
+        const float v = __half2float(__ushort_as_half((unsigned short)(ent >> 32)));
+        unsigned slot = ((unsigned)gt * 2654435761u) >> (32 - 14);
+        bool placed = false;
+        for (int probe = 0; probe < OH_SLOTS; ++probe) {
+          const int cur = atomicCAS(&keys[slot], -1, gt);
+          if (cur == -1) { atomicAdd(&s_new, 1); placed = true; break; }
+          if (cur == gt) { placed = true; break; }
+          slot = (slot + 1) & (OH_SLOTS - 1);
+        }
+        if (!placed) { s_bad = 1; continue; }                // table full: reported below, the query is refused
+        tv[slot] = __float2half_rn(__fadd_rn(__half2float(tv[slot]), fminf(vq, v)));   // fp16 add: fp32 add, RN to fp16
       }
-      if (!placed) { s_bad = 1; continue; }                  // table full: reported below, the query is refused
-      tv[slot] = __float2half_rn(__fadd_rn(__half2float(tv[slot]), fminf(vq, v)));   // fp16 add: fp32 add, RN to fp16
+      __syncthreads();                                       // the next column's additions come after this one's
     }
-    __syncthreads();                                         // the next column's additions come after this one's
+    const int nnew = s_new, bad = s_bad;                     // (the last column's barrier ordered these)
+    if (bad || nnew > OH_CAP || written + nnew > cap_o) {
+      if (tid == 0) { ocnt[qi] = -1; atomicAdd(overflow, 1); }
+      return;
+    }
+    for (int i = tid; i < OH_SLOTS; i += OH_T) {
+      const int gt = keys[i];
+      if (gt >= 0) comp[atomicAdd(&s_n, 1)] = ((unsigned long long)(unsigned)(gt - q) << 16) | __half_as_ushort(tv[i]);
+    }
+    __syncthreads();
+    const int n = s_n;
+    int P2 = 32;
+    while (P2 < n) P2 <<= 1;
+    for (int i = n + tid; i < P2; i += OH_T) comp[i] = ~0ull;
+    __syncthreads();
+    sr_block_bitonic<OH_T>(comp, P2);
+    for (int i = tid; i < n; i += OH_T) {
+      const unsigned long long e = comp[i];
+      ocol[(long long)qi * cap_o + written + i] = (int)(e >> 16);
+      ot[(long long)qi * cap_o + written + i] = __ushort_as_half((unsigned short)(e & 0xffffu));
+    }
+    written += n;
+    __syncthreads();                                         // comp / the table are reused by the next range
   }
   static_assert(OH_SLOTS == 1 << 14, "hash shift");
-  if (s_bad || s_new > OH_CAP || s_new > cap_o) {
-    if (tid == 0) { ocnt[qi] = -1; atomicAdd(overflow, 1); }
-    return;
-  }
-  for (int i = tid; i < OH_SLOTS; i += OH_T) {
-    const int g = keys[i];
-    if (g >= 0) comp[atomicAdd(&s_n, 1)] = ((unsigned long long)(unsigned)(g - q) << 16) | __half_as_ushort(tv[i]);
-  }
-  __syncthreads();
-  const int n = s_n;
-  int P2 = 32;
-  while (P2 < n) P2 <<= 1;
-  for (int i = n + tid; i < P2; i += OH_T) comp[i] = ~0ull;
-  __syncthreads();
-  sr_block_bitonic<OH_T>(comp, P2);
-  for (int i = tid; i < n; i += OH_T) {
-    const unsigned long long e = comp[i];
-    ocol[(long long)qi * cap_o + i] = (int)(e >> 16);
-    ot[(long long)qi * cap_o + i] = __ushort_as_half((unsigned short)(e & 0xffffu));
-  }
-  if (tid == 0) ocnt[qi] = n;
+  if (tid == 0) ocnt[qi] = written;
 }
 
 int launch_overlap_hash(const int* Qc, const __half* Qv, const long long* qoff, const int* Qn, const long long* colptr,
-                        const unsigned long long* csc_ent, int q0, int q_stride, int nq, int q, int cap_o, int* ocol,
-                        __half* ot, int* ocnt, int* overflow, cudaStream_t s) {
+                        const unsigned long long* csc_ent, int q0, int q_stride, int nq, int q, int N, int cap_o,
+                        int* ocol, __half* ot, int* ocnt, int* overflow, cudaStream_t s) {
   if (nq == 0) return REID_OK;
-  REID_REQUIRE(cap_o >= 1 && cap_o <= OH_CAP, "overlap_hash: cap_o=%d outside [1, %d]", cap_o, OH_CAP);
+  REID_REQUIRE(cap_o >= 1 && q >= 0 && N > q, "overlap_hash: cap_o=%d q=%d N=%d", cap_o, q, N);
+  // ranges sized so that a query filling its whole budget still puts only ~half of OH_CAP into one table
+  int nrange = (cap_o + OH_CAP / 2 - 1) / (OH_CAP / 2);
+  if (nrange > N - q) nrange = N - q;
   const size_t smem = (size_t)OH_SLOTS * 6 + (size_t)OH_CAP * 8;
   REID_CUDA(cudaFuncSetAttribute(overlap_hash_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  overlap_hash_kernel<<<nq, OH_T, smem, s>>>(Qc, Qv, qoff, Qn, colptr, csc_ent, q0, q_stride, q, cap_o, ocol, ot, ocnt,
-                                              overflow);
+  overlap_hash_kernel<<<nq, OH_T, smem, s>>>(Qc, Qv, qoff, Qn, colptr, csc_ent, q0, q_stride, q, N, cap_o, nrange, ocol,
+                                              ot, ocnt, overflow);
   return check_launch("overlap_hash_kernel");
+}
+
+// distances of a query's listed columns from one panel; the lists are ascending, so only the slice that falls into the
+// panel's column block [c0, c1) is visited.  One warp per panel row.
+__global__ void __launch_bounds__(256)
+list_gather_sorted_kernel(const float* __restrict__ panel, long long ld, int rows, int c0, int c1, int cap_o,
+                          const int* __restrict__ ocol, const int* __restrict__ ocnt, float* __restrict__ od) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int n = ocnt[row];
+  const int* oc = ocol + (long long)row * cap_o;
+  int lo = 0, hi = n;
+  while (lo < hi) { const int mid = (lo + hi) >> 1; if (oc[mid] < c0) lo = mid + 1; else hi = mid; }
+  const int a = lo;
+  hi = n;
+  while (lo < hi) { const int mid = (lo + hi) >> 1; if (oc[mid] < c1) lo = mid + 1; else hi = mid; }
+  for (int e = a + lane_id(); e < lo; e += 32)
+    od[(long long)row * cap_o + e] = panel[(long long)row * ld + (oc[e] - c0)];
+}
+
+int launch_list_gather_sorted(const float* panel, long long ld, int rows, int c0, int c1, int cap_o, const int* ocol,
+                              const int* ocnt, float* od, cudaStream_t s) {
+  if (rows == 0) return REID_OK;
+  list_gather_sorted_kernel<<<cdiv(rows, 8), 256, 0, s>>>(panel, ld, rows, c0, c1, cap_o, ocol, ocnt, od);
+  return check_launch("list_gather_sorted_kernel");
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -409,6 +451,7 @@ score_counts_rr_kernel(int nq, int q0, int q_stride, const int* __restrict__ glo
 // ---------------------------------------------------------------------------------------------
 // exact top-K of the re-ranked row
 // ---------------------------------------------------------------------------------------------
+constexpr int RT_CAND = 8192;      // candidate keys per query in shared memory (64 KB)
 __global__ void __launch_bounds__(256)
 rr_topk_kernel(int nq, int q0, int q_stride, const int* __restrict__ tidx, const float* __restrict__ tval, int Kd, int g,
                int cap_o, const int* __restrict__ ocol, const __half* __restrict__ ot, const float* __restrict__ od,
@@ -424,15 +467,23 @@ rr_topk_kernel(int nq, int q0, int q_stride, const int* __restrict__ tidx, const
   const long long ob = (long long)qi * cap_o;
   const float m = ordered_int2f(rowmax_key[own_row(q0, q_stride, qi)]);
   const float c1h = __half2float(__float2half_rn(c1));
+  // J <= 1 only lowers a final value, so the K nearest by raw distance all end at or below final0(D_K): nothing above
+  // that bound can be among the K best of the re-ranked row -- the tens of thousands of overlap targets are filtered by it
+  const float cut = final_value(__ushort_as_half(0), tval[(long long)qi * Kd + K - 1], m, c1h, c2);
   for (int x = tid; x < Kd; x += 256) {                   // nearest by raw distance: untouched ones rank by final0(D)
     const int col = tidx[(long long)qi * Kd + x];
     if (rr_find(ocol + ob, no, col) >= 0) continue;       // touched: enters below with its true value
     keys[atomicAdd(&s_n, 1)] = final_key(final_value(__ushort_as_half(0), tval[(long long)qi * Kd + x], m, c1h, c2), col);
   }
-  for (int x = tid; x < no; x += 256)
-    keys[atomicAdd(&s_n, 1)] = final_key(final_value(ot[ob + x], od[ob + x], m, c1h, c2), ocol[ob + x]);
+  for (int x = tid; x < no; x += 256) {
+    const float f = final_value(ot[ob + x], od[ob + x], m, c1h, c2);
+    if (!(f > cut)) {
+      const int at = atomicAdd(&s_n, 1);
+      if (at < RT_CAND) keys[at] = final_key(f, ocol[ob + x]);
+    }
+  }
   __syncthreads();
-  const int n = s_n;
+  const int n = min(s_n, RT_CAND);
   int P2 = 32;
   while (P2 < n) P2 <<= 1;
   for (int i = n + tid; i < P2; i += 256) keys[i] = ~0ull;
@@ -443,10 +494,14 @@ rr_topk_kernel(int nq, int q0, int q_stride, const int* __restrict__ tidx, const
     out_val[(long long)qi * K + i] = key2f((uint32_t)(keys[i] >> 32));
   }
   // an untouched entry beyond the raw-distance list has final0 >= final0(last listed D): the first K are exact unless
-  // the K-th value reaches that bound
-  if (tid == 0 && Kd < g) {
-    const float bound = final_value(__ushort_as_half(0), tval[(long long)qi * Kd + Kd - 1], m, c1h, c2);
-    if (!(key2f((uint32_t)(keys[K - 1] >> 32)) < bound)) atomicAdd(ambiguous, 1);
+  // the K-th value reaches that bound (or the candidate buffer overflowed)
+  if (tid == 0) {
+    bool amb = s_n > RT_CAND;
+    if (Kd < g) {
+      const float bound = final_value(__ushort_as_half(0), tval[(long long)qi * Kd + Kd - 1], m, c1h, c2);
+      amb |= !(key2f((uint32_t)(keys[K - 1] >> 32)) < bound);
+    }
+    if (amb) atomicAdd(ambiguous, 1);
   }
 }
 
@@ -490,10 +545,8 @@ int launch_rr_topk(int nq, int q0, int q_stride, const int* tidx, const float* t
                    float c2, int K, int* out_idx, float* out_val, int* ambiguous, cudaStream_t s) {
   if (nq == 0) return REID_OK;
   REID_REQUIRE(K >= 1 && K <= Kd && Kd <= g, "rr_topk: K=%d Kd=%d g=%d", K, Kd, g);
-  int P2 = 32;
-  while (P2 < Kd + cap_o) P2 <<= 1;
-  const size_t smem = (size_t)P2 * 8;
-  REID_REQUIRE(smem <= 200 * 1024, "rr_topk: %d + %d candidates do not fit shared memory", Kd, cap_o);
+  REID_REQUIRE(Kd <= RT_CAND / 2, "rr_topk: Kd=%d too large", Kd);
+  const size_t smem = (size_t)RT_CAND * 8;
   REID_CUDA(cudaFuncSetAttribute(rr_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   rr_topk_kernel<<<nq, 256, smem, s>>>(nq, q0, q_stride, tidx, tval, Kd, g, cap_o, ocol, ot, od, ocnt, rowmax_key, c1, c2,
                                       K, out_idx, out_val, ambiguous);

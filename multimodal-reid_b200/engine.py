@@ -615,7 +615,7 @@ class Engine:
     # ------------------------------------------------------------------ re-ranking with no dense matrix
     def evaluate_streamed_reranked(self, allf: Features, q: int, pids: torch.Tensor, cams: torch.Tensor, k1: int,
                                    k2: int, lam: float, topk: int = 100, max_rank: int = 50, Kw: int = 64,
-                                   Kd: int | None = None, cap_o: int = 8192, rows_per_pass: int = 16384,
+                                   Kd: int | None = None, cap_o: int = 32768, rows_per_pass: int = 16384,
                                    cols_per_pass: int = 65536, detail: dict | None = None):
         """reranking.py:29-100 + evaluate.py:40-88 for a problem whose N x N (and q x g) matrix cannot exist (BASELINE
         config 5: 100k queries x 1M gallery): k-reciprocal re-ranked CMC / mAP and the exact top-`topk` of every
@@ -720,7 +720,7 @@ class Engine:
             od = self._zeros((max(nq, 1) * cap_o,), torch.float32)
             ocnt = self._empty((max(nq, 1),), torch.int32)
             _lib.call("reid_overlap_lists", _ptr(Qc), _ptr(Qv), _ptr(qoff), _ptr(Qn), _ptr(colptr), _ptr(csc_ent), r, P,
-                      nq, q, cap_o, _ptr(ocol), _ptr(ot), _ptr(ocnt), _ptr(flags[2:]), st())
+                      nq, q, N, cap_o, _ptr(ocol), _ptr(ot), _ptr(ocnt), _ptr(flags[2:]), st())
         # ---- D
         Qf, Gf = allf.rows(qsel), allf.rows(slice(q, N))
         keys, start, lst, T = self.pid_index(g_pids)
@@ -734,14 +734,12 @@ class Engine:
         if longest > 1024:
             raise _lib.ReidError(f"an identity has {longest} gallery samples; the streamed scorer holds at most 1024 per query")
         gd = self._empty((max(total, 1),), torch.float32)
-        oglo = torch.arange(max(nq, 1), device=self.device, dtype=torch.int32) * cap_o
-        ooff = oglo.to(torch.int64)
 
         def gather(D, r0, m, c0, c1):
             _lib.call("reid_stream_group_gather", _ptr(D), D.stride(0), m, c0, c1, _ptr(glo[r0:]), _ptr(glen[r0:]),
                       _ptr(goff[r0:]), _ptr(lst), _ptr(gd), st())
-            _lib.call("reid_stream_group_gather", _ptr(D), D.stride(0), m, c0, c1, _ptr(oglo[r0:]), _ptr(ocnt[r0:]),
-                      _ptr(ooff[r0:]), _ptr(ocol), _ptr(od), st())
+            _lib.call("reid_stream_list_gather", _ptr(D), D.stride(0), m, c0, c1, cap_o, _ptr(ocol[r0 * cap_o:]),
+                      _ptr(ocnt[r0:]), _ptr(od[r0 * cap_o:]), st())
 
         with self.span("sweep1"):
             tidx, tval = self.retrieve_topk(Qf, Gf, Kd, METRIC_SQEUCLIDEAN, rows_per_pass, cols_per_pass, on_panel=gather)

@@ -70,7 +70,7 @@ def streamed_eval(qf, gf, q_pids, g_pids, q_camids, g_camids, max_rank: int = 50
 
 def streamed_rerank_eval(qf, gf, q_pids, g_pids, q_camids, g_camids, k1: int = 20, k2: int = 6, lambda_value: float = 0.3,
                          topk: int = 100, max_rank: int = 50, feat_norm: bool = True, rows_per_pass: int = 16384,
-                         cols_per_pass: int = 65536, wide: int = 64, cap_o: int = 8192, return_diag: bool = False):
+                         cols_per_pass: int = 65536, wide: int = 64, cap_o: int = 32768, return_diag: bool = False):
     """``R1_mAP_eval(reranking=True)`` semantics (evaluate.py:110-135 with re_ranking's k1 / k2 / lambda_value,
     reranking.py:29-100) for a query / gallery pair whose N x N matrix cannot exist (BASELINE config 5: 100k x 1M):
     returns ``(cmc float32[max_rank], mAP float64, indices int32 [q, topk], final float32 [q, topk])`` -- CMC / mAP of the

@@ -200,7 +200,8 @@ def test_streamed_rerank_equals_materialised(eng, engine_mod, synth, oracle, nam
     allf = eng.prepare(X, True)
     sdet = {}
     res, (idx, val), diag = eng.evaluate_streamed_reranked(allf, q, pids, cams, k1, k2, 0.3, topk=topk, Kw=64,
-                                                           cap_o=4096, rows_per_pass=rows_pp, cols_per_pass=cols_pp,
+                                                           cap_o=12288 if name == "mid" else 4096, rows_per_pass=rows_pp,
+                                                           cols_per_pass=cols_pp,
                                                            detail=sdet)
     print(f"[a13] {name} k1={k1} k2={k2}: {diag}")
     assert diag["v_misses"] == 0, "a V weight fell back to the float32 recomputation on this instance"
