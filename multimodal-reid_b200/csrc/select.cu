@@ -441,10 +441,14 @@ int launch_select_topk_hinted(const float* D, int rows, int cols, long long ld, 
 #define REID_SELH(SS)                                                                                          \
   select_topk_hinted_kernel<SS><<<grid, threads, 0, s>>>(D, rows, cols, ld, rowmax_key, chunk_min, nch, chunk_pitch(cols), K, nbr, \
                                                          nbr_val, cap, list_cap, upper_only)
-  if (K <= 32) REID_SELH(1);
-  else if (K <= 64) REID_SELH(2);
-  else if (K <= 128) REID_SELH(4);
-  else REID_SELH(8);
+  // the warp keeps 32 * S chunk minima; their K-th smallest is the bound, so 32 * S must exceed K comfortably: at
+  // K == 32 * S the "K-th smallest kept" is the LARGEST kept value -- a useless bound (measured: K = 64 with S = 2
+  // sent most rows to the exact arg-min fallback, 41 s instead of 0.6 s over a 1.1 M x 1.1 M panel sweep)
+  if (K <= 16) REID_SELH(1);
+  else if (K <= 40) REID_SELH(2);
+  else if (K <= 80) REID_SELH(4);
+  else if (K <= 160) REID_SELH(8);
+  else REID_SELH(16);
 #undef REID_SELH
   return check_launch("select_topk_hinted_kernel");
 }
@@ -695,10 +699,14 @@ int launch_select_topk_scatter(const float* D, int n, long long ld, const int* r
   const int grid = cdiv(n, SELH_WPB), threads = SELH_WPB * 32;
 #define REID_SELT(SS) \
   select_thr_kernel<SS><<<grid, threads, 0, s>>>(n, rowmax_key, chunk_min, nch, pitch, K, dstar, cthr, count)
-  if (K <= 32) REID_SELT(1);
-  else if (K <= 64) REID_SELT(2);
-  else if (K <= 128) REID_SELT(4);
-  else REID_SELT(8);
+  // the warp keeps 32 * S chunk minima; their K-th smallest is the bound, so 32 * S must exceed K comfortably: at
+  // K == 32 * S the "K-th smallest kept" is the LARGEST kept value -- a useless bound (measured: K = 64 with S = 2
+  // sent most rows to the exact arg-min fallback, 41 s instead of 0.6 s over a 1.1 M x 1.1 M panel sweep)
+  if (K <= 16) REID_SELT(1);
+  else if (K <= 40) REID_SELT(2);
+  else if (K <= 80) REID_SELT(4);
+  else if (K <= 160) REID_SELT(8);
+  else REID_SELT(16);
 #undef REID_SELT
   if (int rc = check_launch("select_thr_kernel")) return rc;
   const char* pfe = getenv("REID_SEL_PF");
@@ -866,10 +874,14 @@ int launch_shard_tau(int n, int rank, int world, const float* cm_d, int pitch_d,
   REID_REQUIRE(rank >= 0 && rank < world, "shard_tau: rank %d of %d", rank, world);
   const int grid = cdiv(n, SELH_WPB), threads = SELH_WPB * 32;
 #define REID_SHT(SS) shard_tau_kernel<SS><<<grid, threads, 0, s>>>(n, rank, world, cm_d, pitch_d, cm_m, pitch_m, K, tau_key)
-  if (K <= 32) REID_SHT(1);
-  else if (K <= 64) REID_SHT(2);
-  else if (K <= 128) REID_SHT(4);
-  else REID_SHT(8);
+  // the warp keeps 32 * S chunk minima; their K-th smallest is the bound, so 32 * S must exceed K comfortably: at
+  // K == 32 * S the "K-th smallest kept" is the LARGEST kept value -- a useless bound (measured: K = 64 with S = 2
+  // sent most rows to the exact arg-min fallback, 41 s instead of 0.6 s over a 1.1 M x 1.1 M panel sweep)
+  if (K <= 16) REID_SHT(1);
+  else if (K <= 40) REID_SHT(2);
+  else if (K <= 80) REID_SHT(4);
+  else if (K <= 160) REID_SHT(8);
+  else REID_SHT(16);
 #undef REID_SHT
   return check_launch("shard_tau_kernel");
 }
