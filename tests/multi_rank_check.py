@@ -139,6 +139,17 @@ def main():
     assert (idx_m == idx_s.cpu().numpy()).all() and (val_m == val_s.cpu().numpy()).all(), "streamed top-k differs"
     if rank == 0:
         print(f"streamed retrieval + CMC/mAP: {world}-rank result == 1-rank result, mAP {map_m:.6f}", flush=True)
+    # k-reciprocal re-ranking with no dense matrix: sharded sweeps + all-gathered lists == one rank
+    cm_m, map_m, ridx_m, rval_m = retrieval.streamed_rerank_eval(qf2, gf2, qp2, gp2, qc2, gc2, k1=12, k2=4, lambda_value=0.3,
+                                                                 topk=25, rows_per_pass=256, cols_per_pass=768,
+                                                                 cap_o=8192)
+    pids2, cams2 = torch.cat([ids2[0], ids2[1]]), torch.cat([ids2[2], ids2[3]])
+    (cmc_s, map_s, _, _, _), (ridx_s, rval_s), _ = single.evaluate_streamed_reranked(
+        allf, qn, pids2, cams2, 12, 4, 0.3, topk=25, rows_per_pass=256, cols_per_pass=768, cap_o=8192)
+    assert (cm_m == cmc_s.cpu().numpy()).all() and map_m == float(map_s.item()), "streamed re-ranked CMC/mAP differs"
+    assert (ridx_m == ridx_s.cpu().numpy()).all() and (rval_m == rval_s.cpu().numpy()).all(), "re-ranked top-k differs"
+    if rank == 0:
+        print(f"streamed re-ranking (no dense matrix): {world}-rank result == 1-rank result, mAP {map_m:.6f}", flush=True)
     dist.barrier()
     dist.destroy_process_group()
 
