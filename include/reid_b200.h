@@ -178,6 +178,23 @@ REID_API int reid_krecip_V_tri(const int32_t* rfull, const int32_t* nfull, const
                       const int32_t* rowmax_key, int32_t* Vc, reid_half* Vv, int32_t* Vn, int upper_only,
                       void* stream);
 
+/* ---- The whole evaluation as ONE call (reid_eval_e2e / reid_workspace_bytes) ------------------------------
+ * evaluate.py:110-134 with reranking=True on one GPU: feats [N, d] float32 (row pitch ld, queries first), pids / cams
+ * [N] int64 -> cmc[max_rank] float32, mAP float64, n_valid (all device memory; evaluate.py:82 asserts n_valid > 0, the
+ * caller checks it after reading the result back).  normalize != 0 applies F.normalize first (evaluate.py:112-114).
+ * k1 / k2 / lambda_value as re_ranking (reranking.py:29; R1_mAP_eval.compute passes 50, 15, 0.3).  max_rank <= g: the
+ * caller clips it and prints the note of evaluate.py:37-39.  Optional per-query outputs ap[q] (float64, -1 for queries
+ * whose identity is absent from the gallery) and first_hit[q].  Every intermediate buffer lives in `workspace`
+ * (256-byte aligned, reid_eval_workspace_bytes(...) bytes: sized by structural bounds, dominated by the 4 N^2-byte
+ * distance matrix): the call allocates nothing, never synchronises and never reads the device back -- a fixed
+ * sequence of ~30 launches on `stream` that can be captured in a CUDA graph.  Same kernels, same bits as the host
+ * layer's one-rank path (tests/test_gpu_api.py). */
+REID_API int64_t reid_eval_workspace_bytes(int N, int q, int d, int k1, int k2, int max_rank);
+REID_API int reid_eval_reranked(const float* feats, int64_t ld, int N, int q, int d, const int64_t* pids,
+                       const int64_t* cams, int k1, int k2, double lambda_value, int normalize, int max_rank,
+                       void* workspace, int64_t workspace_bytes, float* cmc, double* mAP, int32_t* n_valid, double* ap,
+                       int32_t* first_hit, void* stream);
+
 /* ---- Re-ranking without any dense matrix (100k queries x 1M gallery; reranking.py:46-100 and
  * evaluate.py:40-88 with D, V and the final matrix never materialised).  The contraction produces panels
  * (reid_dist on row / column blocks); these entry points work on lists.  Query windows use (q0, q_stride) as elsewhere.

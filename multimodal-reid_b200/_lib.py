@@ -37,6 +37,8 @@ def _parse_header():
                 argtypes.append(_i)
             elif re.match(r"(const\s+)?float\b", a):
                 argtypes.append(_f)
+            elif re.match(r"(const\s+)?double\b", a):
+                argtypes.append(C.c_double)
             else:
                 raise ReidError(f"unhandled parameter type in header: {a!r}")
         restype = C.c_char_p if "char" in ret else (_l if "int64_t" in ret else C.c_int)

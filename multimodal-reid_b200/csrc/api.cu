@@ -429,6 +429,20 @@ int reid_rr_topk(int nq, int q0, int q_stride, const int32_t* tidx, const float*
                         out_idx, out_val, ambiguous, S(stream));
 }
 
+int64_t reid_eval_workspace_bytes(int N, int q, int d, int k1, int k2, int max_rank) {
+  return eval_workspace_bytes(N, q, d, k1, k2, max_rank);
+}
+
+int reid_eval_reranked(const float* feats, int64_t ld, int N, int q, int d, const int64_t* pids, const int64_t* cams,
+                       int k1, int k2, double lambda_value, int normalize, int max_rank, void* workspace,
+                       int64_t workspace_bytes, float* cmc, double* mAP, int32_t* n_valid, double* ap, int32_t* first_hit,
+                       void* stream) {
+  ENTER();
+  REID_REQUIRE(feats && pids && cams && cmc && mAP && n_valid && ld >= d, "eval_reranked: NULL argument or bad pitch");
+  return eval_reranked(feats, ld, N, q, d, LL(pids), LL(cams), k1, k2, lambda_value, normalize, max_rank, workspace,
+                       workspace_bytes, cmc, mAP, n_valid, ap, first_hit, S(stream));
+}
+
 int reid_fabric_alloc(int64_t bytes, void** out) { ENTER(); return fabric_alloc(bytes, out); }
 int reid_fabric_free(void* p) { return fabric_free(p); }
 int reid_fabric_export(void* p, void* handle64) { ENTER(); return fabric_export(p, handle64); }

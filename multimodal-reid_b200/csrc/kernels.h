@@ -101,6 +101,11 @@ int launch_shard_merge_local(const float* D, long long ld, int n, int rank, int 
                              long long inbox_off, int nloc_max, cudaStream_t s);
 int launch_shard_merge_final(int nloc, int rank, int world, int K, const unsigned long long* inbox, int nloc_max,
                              unsigned char* const* peers, long long nbr_off, float* nbr_val, cudaStream_t s);
+// eval_e2e.cu: the whole one-GPU evaluation as one call over a caller-provided workspace
+long long eval_workspace_bytes(int N, int q, int d, int k1, int k2, int max_rank);
+int eval_reranked(const float* feats, long long ld_x, int N, int q, int d, const long long* pids, const long long* cams,
+                  int k1, int k2, double lambda_value, int normalize, int max_rank, void* workspace, long long ws_bytes,
+                  float* cmc, double* mAP, int* n_valid, double* ap_out, int* first_out, cudaStream_t s);
 // fabric.cu: peer-memory arena, flag barrier, copy kernels
 int fabric_alloc(long long bytes, void** out);
 int fabric_free(void* p);

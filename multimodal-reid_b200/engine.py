@@ -222,6 +222,8 @@ class Engine:
         self.shard_h2d = True               # evaluator on several ranks: each uploads 1/world of the host rows, all-gather over NVLink
         self._copy_stream = None
         self.scatter_select = True          # upper-only selection in scatter form (reid_topk_rows_scatter)
+        self.c_entry = True                 # one rank: evaluate_reranked goes through the single C entry (reid_eval_reranked)
+        self._c_ws = None
         self.qe_nosync_bytes = 4 << 30       # budget for sizing the query-expansion pools without a host read
         self._ubmax_pinned = torch.zeros(1, dtype=torch.int64).pin_memory()
         self._ubmax_event = torch.cuda.Event()
@@ -1252,11 +1254,41 @@ class Engine:
                           lam: float, normalize: bool, max_rank: int = 50, feats_aug: torch.Tensor | None = None):
         """The evaluator's hot path end to end (evaluate.py:110-132 with reranking=True): features and ids of
         all N samples (queries first) -> (cmc, mAP, n_valid, ap, first_hit); the q x g matrix is never written."""
+        if (self.c_entry and self.comm.world == 1 and self.timers is None and feats_aug is None
+                and self.engine != ENGINES["simt"] and self.symmetric and self.upper_only and self.scatter_select
+                and self.sparse_cap == 8192 and feats.shape[0] >= max(k1 + 1, k2)):
+            return self.evaluate_reranked_single_call(feats, q, pids, cams, k1, k2, lam, normalize, max_rank)
         mine = self.own_queries(feats.shape[0], q, k1, k2, max_rank)
         ids = (pids[:q][mine].contiguous(), pids[q:].contiguous(), cams[:q][mine].contiguous(), cams[q:].contiguous())
         _, res = self.rerank_features(feats, q, k1, k2, lam, normalize, score=(ids, max_rank), want_final=False,
                                       feats_aug=feats_aug)
         return res
+
+    def evaluate_reranked_single_call(self, feats: torch.Tensor, q: int, pids: torch.Tensor, cams: torch.Tensor, k1: int,
+                                      k2: int, lam: float, normalize: bool, max_rank: int = 50):
+        """The same evaluation through the single C-ABI entry reid_eval_reranked (csrc/eval_e2e.cu): one call, one
+        cached workspace, no host read inside, ~30 launches issued from C++ instead of ~25 ctypes round trips.  Same
+        kernels, same bits as the staged path (tests/test_gpu_api.py).  One rank, tensor-core engine."""
+        assert feats.is_cuda and feats.dtype == torch.float32 and feats.stride(1) == 1
+        N, d = feats.shape
+        need = int(self.lib.reid_eval_workspace_bytes(N, q, d, k1, k2, max_rank))
+        if need < 0:
+            raise _lib.ReidError(self.lib.reid_last_error().decode())
+        if self._c_ws is None or self._c_ws.numel() < need:
+            self._c_ws = None
+            self._c_ws = self._empty((need,), torch.uint8)
+        pids = pids.contiguous()
+        cams = cams.contiguous()
+        cmc = self._empty((max_rank,), torch.float32)
+        mAP = self._empty((1,), torch.float64)
+        nvalid = self._empty((1,), torch.int32)
+        ap = self._empty((max(q, 1),), torch.float64)
+        first = self._empty((max(q, 1),), torch.int32)
+        _lib.call("reid_eval_reranked", _ptr(feats), feats.stride(0), N, q, d, _ptr(pids), _ptr(cams), k1, k2, float(lam),
+                  1 if normalize else 0, max_rank, _ptr(self._c_ws), self._c_ws.numel(), _ptr(cmc), _ptr(mAP), _ptr(nvalid),
+                  _ptr(ap), _ptr(first), _stream())
+        self.last_path = "single-call"
+        return cmc, mAP, nvalid, ap[:q], first[:q]
 
     def own_queries(self, N: int, q: int, k1: int, k2: int, max_rank: int = 50) -> torch.Tensor:
         """Global indices of the queries whose rows this rank produces in rerank_features / evaluate_reranked for this

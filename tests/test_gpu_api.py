@@ -185,3 +185,48 @@ def test_flip_tta_average_fused_into_the_prologue(api, eng, synth, oracle):
         c_o, m_o = oracle.evaluate_features(avg.numpy(), pids.numpy(), cams.numpy(), sh.q, True, rerank,
                                             k1=20, k2=6, lam=0.3)
         assert np.abs(res[0][0] - c_o).max() <= METRIC_TOL and abs(res[0][1] - m_o) <= METRIC_TOL
+
+
+@pytest.mark.parametrize("name,k1,k2", [("small", 20, 6), ("mid", 20, 6), ("small", 50, 15), ("tiny", 7, 1), ("duke", 20, 6)])
+def test_single_call_c_entry(eng, synth, name, k1, k2):
+    """the whole re-ranked evaluation through ONE C-ABI call (reid_eval_reranked) on a caller-provided
+    workspace -- bound here with raw ctypes, no host layer in between -- against the staged host-layer path: CMC, mAP,
+    n_valid, every AP and every first-hit rank bit for bit."""
+    import ctypes as C
+    import importlib
+    lib = importlib.import_module("multimodal-reid_b200._lib").load()
+    sh = synth.SHAPES[name]
+    qf, gf, qp, gp, qc, gc = synth.make(sh, 2)
+    dev = eng.device
+    X = torch.cat([qf, gf]).to(dev)                                  # host buffers -> device: the caller's business
+    pids, cams = torch.cat([qp, gp]).to(dev), torch.cat([qc, gc]).to(dev)
+    N, d, q = X.shape[0], X.shape[1], sh.q
+    saved = eng.c_entry
+    eng.c_entry = False
+    try:
+        want = eng.evaluate_reranked(X, q, pids, cams, k1, k2, 0.3, normalize=True, max_rank=50)
+    finally:
+        eng.c_entry = saved
+    need = lib.reid_eval_workspace_bytes(N, q, d, k1, k2, 50)
+    assert need > 4 * N * N
+    ws = torch.empty((need,), dtype=torch.uint8, device=dev)
+    cmc = torch.empty((50,), dtype=torch.float32, device=dev)
+    mAP = torch.empty((1,), dtype=torch.float64, device=dev)
+    nv = torch.empty((1,), dtype=torch.int32, device=dev)
+    ap = torch.empty((q,), dtype=torch.float64, device=dev)
+    first = torch.empty((q,), dtype=torch.int32, device=dev)
+    P = lambda t: C.c_void_p(t.data_ptr())
+    rc = lib.reid_eval_reranked(P(X), X.stride(0), N, q, d, P(pids), P(cams), k1, k2, 0.3, 1, 50, P(ws), need, P(cmc),
+                                P(mAP), P(nv), P(ap), P(first), C.c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc == 0, lib.reid_last_error().decode()
+    for a, b, what in zip(want, (cmc, mAP, nv, ap, first), ("cmc", "mAP", "n_valid", "ap", "first_hit")):
+        assert torch.equal(a, b), what
+    # and the host layer's own fast path takes the same entry
+    got = eng.evaluate_reranked(X, q, pids, cams, k1, k2, 0.3, normalize=True, max_rank=50)
+    assert eng.last_path == "single-call"
+    for a, b in zip(want, got):
+        assert torch.equal(a, b)
+    # too small a workspace is refused, not overrun
+    rc = lib.reid_eval_reranked(P(X), X.stride(0), N, q, d, P(pids), P(cams), k1, k2, 0.3, 1, 50, P(ws), need - 4096, P(cmc),
+                                P(mAP), P(nv), P(ap), P(first), C.c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc != 0 and b"workspace" in lib.reid_last_error()
