@@ -642,8 +642,9 @@ int launch_jaccard_score(const int* Qc, const __half* Qv, const long long* qoff,
   const int threads = N <= 32768 ? 256 : 512;
   const size_t smem = (((size_t)Npad * 2 + 15) & ~(size_t)15) + JsLayout::bytes(threads / 32);
   REID_REQUIRE(smem <= 227 * 1024,
-               "jaccard: N=%d needs %zu B of shared memory for the per-query overlap row "
-               "(limit 227 KB => N <= ~95k); larger galleries need the streaming variant",
+               "jaccard: N=%d needs %zu B of shared memory for the per-query overlap row (limit 227 KB => N <= ~110k); "
+               "larger problems go through the list-based path (reid_overlap_lists / Engine.evaluate_streamed_reranked / "
+               "retrieval.streamed_rerank_eval), which never holds a row of N entries",
                N, smem);
   REID_REQUIRE(ld % 4 == 0 && ld >= Npad, "jaccard: D pitch %lld must be a multiple of 4 and >= N rounded up to 8",
                ld);

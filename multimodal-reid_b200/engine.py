@@ -562,7 +562,12 @@ class Engine:
         _lib.call("reid_stream_group_lookup", _ptr(q_pids), nq, _ptr(keys), _ptr(start), T, _ptr(glo), _ptr(glen), _stream())
         goff = self._zeros((nq + 1,), torch.int64)
         goff[1:] = torch.cumsum(glen, 0, dtype=torch.int64)
-        total = int(goff[-1].item())                       # the evaluation's one host read before the sweeps
+        # the evaluation's one host read before the sweeps: buffer size, and the largest identity group -- refused here,
+        # not after two full contraction sweeps
+        sizes = torch.stack([goff[-1], glen.max().to(torch.int64) if nq else goff[-1]]).tolist()
+        total, longest = int(sizes[0]), int(sizes[1])
+        if longest > 1024:
+            raise _lib.ReidError(f"an identity has {longest} gallery samples; the streamed scorer holds at most 1024 per query")
         gd = self._empty((max(total, 1),), torch.float32)
         mkeys = self._empty((max(total, 1),), torch.int64)
         bins = self._zeros((max(total, 1),), torch.int32)
