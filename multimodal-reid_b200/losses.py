@@ -178,14 +178,37 @@ class WeightedRegularizedTriplet(object):
 class WeightedRegularizedTripletXBM(WeightedRegularizedTriplet):
     """losses.py:111-152 with the masks the code sets up (:126-128): positives = same label in the memory
     bank minus the anchor's own slot (the first N bank entries are the batch), negatives = different label.
-    NOTE the reference then indexes ``dist_mat[is_pos]`` with a *long* 0/1 tensor (:132, :137), which selects
-    rows 0 and 1 of the matrix instead of masking; that indexing slip is not reproduced."""
+
+    The reference then indexes ``dist_mat[is_pos]`` with a *long* 0/1 tensor (:132, :137).  That is integer (advanced)
+    indexing, not masking: it gathers rows 0 and 1 of the matrix for every element of the mask, so after ``view(N, -1)``
+    every anchor gets dist_ap = max(dist_mat[0:2]) and dist_an = min(dist_mat[0:2]) (each mask row holds both values).
+    Default: the intended masks.  ``reference_compat=True`` reproduces what the reference returns, value and gradient
+    (tests/test_gpu_losses.py compares it with the unmodified reference on the GPU box), so that a run can be
+    continued bit-compatibly; INTEGRATION.md 2b states the difference."""
+
+    def __init__(self, margin=None, reference_compat: bool = False):
+        super().__init__(margin)
+        self.reference_compat = reference_compat
 
     def __call__(self, global_feat, labels, global_feat_xbm, labels_xbm, normalize_feature=False):
         if normalize_feature:
             global_feat = F.normalize(global_feat, dim=-1)
             global_feat_xbm = F.normalize(global_feat_xbm, dim=-1)
         dev = global_feat.device
+        if self.reference_compat:
+            n = global_feat.shape[0]
+            lab, lab_x = _labels(labels, dev), _labels(labels_xbm, dev)
+            is_pos = lab[:, None].eq(lab_x[None, :]).long()
+            is_pos[:, :n] -= torch.eye(n, dtype=torch.long, device=dev)
+            rows = euclidean_dist(global_feat[:2], global_feat_xbm)            # the only rows the indexing ever reads
+            # a mask row that is all 0 (all 1) gathers row 0 (row 1) only; with both values present it gathers both
+            def pick(mask):
+                has1, has0 = mask.bool().any(1), (~mask.bool()).any(1)
+                r0 = rows[0].max() if mask is is_pos else rows[0].min()
+                r1 = rows[1].max() if mask is is_pos else rows[1].min()
+                both = torch.maximum(r0, r1) if mask is is_pos else torch.minimum(r0, r1)
+                return torch.where(has1 & has0, both, torch.where(has1, r1, r0))
+            return self._rank(pick(is_pos), pick(1 - is_pos))
         dist_ap, dist_an = _MinedPairs.apply(global_feat, global_feat_xbm, _labels(labels, dev),
                                              _labels(labels_xbm, dev), True)
         return self._rank(dist_ap, dist_an)

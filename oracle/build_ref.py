@@ -1,8 +1,8 @@
 """Recipe for `oracle/_ref/`: the UNMODIFIED reference files of the hot path, taken from where they lie.
 
 TEST / BASELINE INFRASTRUCTURE ONLY.  The reference is pure Python (no compiled sources), so "building" it means
-placing byte-identical copies of the two modules the path consists of -- `/root/reference/evaluate.py` and
-`/root/reference/reranking.py` -- under `oracle/_ref/`.  That directory is git-ignored (reference sources never enter
+placing byte-identical copies of the modules the path consists of -- `/root/reference/evaluate.py`,
+`/root/reference/reranking.py` and (for the training-side row f4) `/root/reference/losses.py` -- under `oracle/_ref/`.  That directory is git-ignored (reference sources never enter
 this repository's history) but NOT gpurun-ignored, so the files travel to the GPU box with the built `.so`, where
 `bench.py --impl reference` / `cpu_baseline` time them on the host cores (`kind: "reference"`) and the `-m gpu` parity
 tests use them as a second checker beside the oracle port.  `__graft_entry__.build()` runs this when `/root/reference`
@@ -23,7 +23,7 @@ import warnings
 HERE = os.path.dirname(os.path.abspath(__file__))
 REF_ROOT = os.environ.get("REID_REFERENCE_ROOT", "/root/reference")
 OUT = os.path.join(HERE, "_ref")
-FILES = ("evaluate.py", "reranking.py")
+FILES = ("evaluate.py", "reranking.py", "losses.py")      # losses.py: SURVEY 8(f4), live comparison on the GPU box
 
 
 def build(verbose: bool = False) -> bool:
@@ -79,6 +79,18 @@ def load():
             sys.modules["reranking"] = saved
     _cache["mods"] = (ev, rr)
     return ev, rr
+
+
+def load_losses():
+    """The unmodified reference losses.py (pure torch; its XBM variant calls .cuda(), so it only runs on the GPU box)."""
+    if "losses" not in _cache:
+        if not os.path.isfile(os.path.join(OUT, "losses.py")):
+            raise FileNotFoundError("oracle/_ref/losses.py is missing: run `python oracle/build_ref.py`")
+        spec = importlib.util.spec_from_file_location("_ref_losses_shipped", os.path.join(OUT, "losses.py"))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        _cache["losses"] = mod
+    return _cache["losses"]
 
 
 if __name__ == "__main__":
