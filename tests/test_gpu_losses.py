@@ -192,3 +192,39 @@ def test_fused_node_equals_composition(L):
     assert abs(loss_a.item() - loss_b.item()) < 1e-6
     np.testing.assert_allclose(a.grad.cpu().numpy(), b.grad.cpu().numpy(), rtol=1e-4,
                                atol=1e-5 * b.grad.abs().max().item())
+
+
+def test_against_the_unmodified_reference_live(L):
+    """The reference's own losses.py (oracle/_ref, shipped by oracle/build_ref.py) run on the GPU box next to the
+    drop-in: WeightedRegularizedTriplet value + gradient, and WeightedRegularizedTripletXBM in reference_compat mode
+    (losses.py:132,137 index the matrix with a long 0/1 tensor -- rows 0 and 1 -- and the compat mode returns exactly
+    that; the default mode implements the masks of :126-128 and is checked against the oracle elsewhere)."""
+    import importlib
+    build_ref = importlib.import_module("oracle.build_ref")
+    try:
+        ref = build_ref.load_losses()
+    except FileNotFoundError:
+        pytest.skip("oracle/_ref/losses.py did not travel")
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(32, 128, generator=g).cuda().requires_grad_()
+    bank = torch.cat([x.detach(), torch.randn(96, 128, generator=g).cuda()])
+    lab = (torch.arange(32) // 4).cuda()
+    lab_bank = torch.cat([lab, torch.randint(0, 8, (96,), generator=g).cuda()])
+
+    def run(fn):
+        x.grad = None
+        loss = fn()
+        loss.backward()
+        return float(loss), x.grad.clone()
+
+    for margin in (0.3, None):
+        lw, gw = run(lambda: ref.WeightedRegularizedTriplet(margin)(x, lab))
+        lg, gg = run(lambda: L.WeightedRegularizedTriplet(margin)(x, lab))
+        assert abs(lw - lg) <= 1e-5 and float((gw - gg).abs().max()) <= 1e-4 * max(1e-6, float(gw.abs().max()))
+        lw, gw = run(lambda: ref.WeightedRegularizedTripletXBM(margin)(x, lab, bank, lab_bank))
+        lg, gg = run(lambda: L.WeightedRegularizedTripletXBM(margin, reference_compat=True)(x, lab, bank, lab_bank))
+        assert abs(lw - lg) <= 1e-5, (margin, lw, lg)
+        assert float((gw - gg).abs().max()) <= 1e-4 * max(1e-6, float(gw.abs().max()))
+        # the default mode is a different (the intended) loss
+        ld, _ = run(lambda: L.WeightedRegularizedTripletXBM(margin)(x, lab, bank, lab_bank))
+        assert abs(ld - lw) > 1e-3
