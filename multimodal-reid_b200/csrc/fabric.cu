@@ -88,24 +88,35 @@ fabric_bcast_ell_kernel(unsigned char* const* __restrict__ peers, int rank, int 
   if (lane == 0) reinterpret_cast<int*>(peers[dstr] + off_cnt)[row] = cnt;
 }
 
-// CSR pool rows (off[n+1] int64 element offsets, identical on every rank; cnt[n]; cols int32; vals fp16)
+// CSR pool rows (off[n+1] int64 element offsets, identical on every rank; cnt[n]; cols int32; vals fp16).  The pool is
+// laid out in global row order, so the rows of one owned tile row are ONE contiguous region [off[r0], off[r1]): a block per
+// (owned tile row, destination) copies it with 16-byte stores (the slack between a row's count and its slot travels too --
+// cheaper than a warp per row issuing 4- and 2-byte stores: 0.37 ms -> see DESIGN 5 at 8 ranks).
+__device__ __forceinline__ void fabric_copy_bytes(unsigned char* __restrict__ dst, const unsigned char* __restrict__ src,
+                                                  long long bytes) {
+  // dst and src have the same alignment (same offset in identically laid out arenas)
+  long long head = (16 - ((uintptr_t)src & 15)) & 15;
+  if (head > bytes) head = bytes;
+  for (long long i = threadIdx.x; i < head; i += blockDim.x) dst[i] = src[i];
+  const long long body = (bytes - head) >> 4;
+  const uint4* s4 = reinterpret_cast<const uint4*>(src + head);
+  uint4* d4 = reinterpret_cast<uint4*>(dst + head);
+  for (long long i = threadIdx.x; i < body; i += blockDim.x) d4[i] = s4[i];
+  for (long long i = head + (body << 4) + threadIdx.x; i < bytes; i += blockDim.x) dst[i] = src[i];
+}
+
 __global__ void __launch_bounds__(256)
 fabric_bcast_pool_kernel(unsigned char* const* __restrict__ peers, int rank, int P, long long off_cnt,
-                         long long off_cols, long long off_vals, const long long* __restrict__ off, int n, int nloc) {
-  const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  const int l = gw % nloc, which = gw / nloc;
-  if (which >= P - 1) return;
+                         long long off_cols, long long off_vals, const long long* __restrict__ off, int n, int ntl) {
+  const int lt = blockIdx.x % ntl, which = blockIdx.x / ntl;
   const int dstr = which < rank ? which : which + 1;
-  const long long row = own_row(rank, -P, l);
-  if (row >= n) return;
-  const int cnt = reinterpret_cast<const int*>(peers[rank] + off_cnt)[row];
-  const long long a = off[row];
-  const int* sc = reinterpret_cast<const int*>(peers[rank] + off_cols) + a;
-  const __half* sv = reinterpret_cast<const __half*>(peers[rank] + off_vals) + a;
-  int* dc = reinterpret_cast<int*>(peers[dstr] + off_cols) + a;
-  __half* dv = reinterpret_cast<__half*>(peers[dstr] + off_vals) + a;
-  for (int j = lane; j < cnt; j += 32) { dc[j] = sc[j]; dv[j] = sv[j]; }
-  if (lane == 0) reinterpret_cast<int*>(peers[dstr] + off_cnt)[row] = cnt;
+  const long long r0 = (long long)snake_global_tile(lt, rank, P) * 256;
+  if (r0 >= n) return;
+  const long long r1 = r0 + 256 < n ? r0 + 256 : n;
+  const long long a = off[r0], b = off[r1];
+  fabric_copy_bytes(peers[dstr] + off_cols + a * 4, peers[rank] + off_cols + a * 4, (b - a) * 4);
+  fabric_copy_bytes(peers[dstr] + off_vals + a * 2, peers[rank] + off_vals + a * 2, (b - a) * 2);
+  fabric_copy_bytes(peers[dstr] + off_cnt + r0 * 4, peers[rank] + off_cnt + r0 * 4, (r1 - r0) * 4);
 }
 
 int fabric_alloc(long long bytes, void** out) {
@@ -187,11 +198,9 @@ int launch_fabric_bcast_ell(unsigned char* const* peers, int rank, int world, lo
 int launch_fabric_bcast_pool(unsigned char* const* peers, int rank, int world, long long off_cnt, long long off_cols,
                              long long off_vals, const long long* off, int n, cudaStream_t s) {
   if (world <= 1 || n == 0) return REID_OK;
-  const int nloc = owned_rows(n, rank, world);
-  if (nloc == 0) return REID_OK;
-  const long long warps = (long long)nloc * (world - 1);
-  fabric_bcast_pool_kernel<<<cdiv(warps * 32, 256), 256, 0, s>>>(peers, rank, world, off_cnt, off_cols, off_vals, off, n,
-                                                                nloc);
+  const int ntl = snake_tiles_below(cdiv(n, 256), rank, world);
+  if (ntl == 0) return REID_OK;
+  fabric_bcast_pool_kernel<<<ntl * (world - 1), 256, 0, s>>>(peers, rank, world, off_cnt, off_cols, off_vals, off, n, ntl);
   return check_launch("fabric_bcast_pool_kernel");
 }
 
