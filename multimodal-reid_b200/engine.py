@@ -210,6 +210,7 @@ class Engine:
         self.engine = ENGINES[engine]
         self.comm = comm or Comm()
         self.timers = None          # dict stage -> list[(start_event, end_event)] when profiling
+        self.nvtx = bool(int(__import__("os").environ.get("REID_NVTX", "0")))   # stage spans as NVTX ranges (nsys / ncu --nvtx)
         # Jaccard stage: packed per-query overlap records (jaccard_sparse.cu) with up to `sparse_cap` touched probes;
         # denser queries fall back to the dense shared-memory row (jaccard_score.cu).  sparse_cap = 0: dense only.
         self.sparse_cap = 8192
@@ -252,6 +253,8 @@ class Engine:
             self.eng, self.name = eng, name
 
         def __enter__(self):
+            if self.eng.nvtx:
+                torch.cuda.nvtx.range_push("reid:" + self.name)
             if self.eng.timers is not None:
                 self.a = torch.cuda.Event(enable_timing=True)
                 self.b = torch.cuda.Event(enable_timing=True)
@@ -259,6 +262,8 @@ class Engine:
             return self
 
         def __exit__(self, *exc):
+            if self.eng.nvtx:
+                torch.cuda.nvtx.range_pop()
             if self.eng.timers is not None:
                 self.b.record()
                 self.eng.timers.setdefault(self.name, []).append((self.a, self.b))
