@@ -360,6 +360,34 @@ def main():
                "mAP": float(map_e),
                "api": "evaluate.R1_mAP_eval(reranking=True).update(host tensors).compute()"}
 
+    # ---- BASELINE configs[1] names both distance functions at the Duke shape: the q x g matrices of evaluate.py:7-13 and
+    #      :16-26 and eval_func on them (device-resident, CUDA events, one rank), reported beside the headline
+    distmat = None
+    if world == 1 and N <= 40_000:
+        allf = eng.prepare(feats_d, True)
+        Qf, Gf = allf.rows(slice(0, q)), allf.rows(slice(q, N))
+        idq = (pids_d[:q].contiguous(), pids_d[q:].contiguous(), cams_d[:q].contiguous(), cams_d[q:].contiguous())
+
+        def timed_op(fn, reps=10):
+            for _ in range(3):
+                fn()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            flush.fill_(1)
+            a.record()
+            for _ in range(reps):
+                fn()
+            b.record()
+            torch.cuda.synchronize(dev)
+            return a.elapsed_time(b) / reps
+
+        De, _ = eng.dist(Qf, Gf, engine.METRIC_SQEUCLIDEAN)
+        distmat = {"euclidean_distance_ms": timed_op(lambda: eng.dist(Qf, Gf, engine.METRIC_SQEUCLIDEAN)),
+                   "cosine_similarity_ms": timed_op(lambda: eng.dist(Qf, Gf, engine.METRIC_ARCCOS)),
+                   "eval_func_ms": timed_op(lambda: eng.evaluate_dist(De, g, *idq, 50)),
+                   "note": "q x g matrix on the device (evaluate.py:7-13 / :16-26) and CMC/mAP of it (evaluate.py:29-88); "
+                           "no re-ranking, no host copies"}
+        del De, allf
+
     clocks = sampler.stop() if rank == 0 else None
 
     # ---- roofline of the dominant kernel (N x N distance contraction)
@@ -417,6 +445,12 @@ def main():
             gbs = b / (stages[k] * 1e-3) / 1e9
             hbm[k] = {"GB/s": gbs, "frac": gbs / peaks["hbm"]}
 
+    # ncu-measured DRAM bytes of the HBM-bound kernels (profiles/traffic.json, one launch each) with their ncu durations are
+    # in profiles/r02k_kernels_msmt17_key_metrics.txt; here: the stage-level algorithmic figures above plus those bytes
+    for kname in ("score_sparse_kernel", "select_push_kernel", "overlap_sparse_kernel"):
+        if world == 1 and kname in traffic_all:
+            hbm.setdefault("ncu_dram_bytes_per_launch", {})[kname] = traffic_all[kname]
+
     # ---- CPU baseline (rank 0, N == 1 only): oracle port on a bounded sample
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -439,7 +473,8 @@ def main():
                                     f"probe rows cyclic over {world} ranks, NCCL all-gathers"),
                        "l2_flush_between_steps": True, "engine": args.engine},
             "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
-            "stages_ms": stages, "hbm_stages": hbm, "mAP": float(mAP.item()), "rank1": float(cmc[0].item()),
+            "stages_ms": stages, "hbm_stages": hbm, "distmat_only": distmat, "mAP": float(mAP.item()),
+            "rank1": float(cmc[0].item()),
             "wall_s_timed_region": wall,
         }
         print(json.dumps(line), flush=True)
