@@ -291,8 +291,11 @@ def main():
             dist.barrier()
         torch.cuda.synchronize(dev)
 
+    host_enqueue = []       # host time spent issuing one step (no synchronisation inside): launch-bound when close to the step time
+
     def timed(fn, steps, timers=False):
         evs = []
+        host_enqueue.clear()
         barrier()
         t_wall = time.perf_counter()
         for _ in range(steps):
@@ -301,7 +304,9 @@ def main():
             if timers:
                 eng.enable_timers(True)
             a.record()
+            t_h = time.perf_counter()
             out = fn()
+            host_enqueue.append(time.perf_counter() - t_h)
             b.record()
             evs.append((a, b))
         barrier()
@@ -326,6 +331,7 @@ def main():
     l0 = lib.reid_launch_count()
     total_ms, per_step, out, wall = timed(step_resident, args.steps)
     launches = int(lib.reid_launch_count() - l0)
+    enqueue_ms = 1e3 * statistics.median(host_enqueue) if host_enqueue else None
     cmc, mAP = out
     ms_per_step = total_ms / args.steps
     value = q * g * args.steps / (total_ms * 1e-3)
@@ -472,7 +478,7 @@ def main():
                                     "peer memory (CUDA IPC over NVLink), flag barriers" if fabric_path else
                                     f"probe rows cyclic over {world} ranks, NCCL all-gathers"),
                        "l2_flush_between_steps": True, "engine": args.engine},
-            "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+            "e2e": e2e, "gpu_launches": launches, "host_enqueue_ms_per_step": enqueue_ms, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
             "stages_ms": stages, "hbm_stages": hbm, "distmat_only": distmat, "mAP": float(mAP.item()),
             "rank1": float(cmc[0].item()),
             "wall_s_timed_region": wall,
