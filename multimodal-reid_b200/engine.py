@@ -1161,12 +1161,15 @@ class Engine:
             cthr = self._empty((cpitch,), torch.int32)
             pbuf = self._empty((N, cap), torch.int64)
             stats_all = fab.view(L.stats, (P * L.stats_slot // 4,), torch.int32)
-            _lib.call("reid_shard_dstar", N, r, P, _ptr(stats_all), L.stats_slot // 4, _ptr(key_g), _ptr(key_l), _ptr(dstar), _ptr(count),
-                      _ptr(cthr), st())
-            _lib.call("reid_shard_push", _ptr(panel), nloc, r, P, N, L.ld, _ptr(cm_d), cpitch, _ptr(dstar), _ptr(cthr),
-                      _ptr(count), _ptr(pbuf), cap, st())
-            _lib.call("reid_shard_merge_local", _ptr(panel), L.ld, N, r, P, _ptr(cm_d), cpitch, _ptr(cm_m), pitch_m,
-                      _ptr(key_g), _ptr(dstar), _ptr(count), _ptr(pbuf), cap, K, peers, L.inbox, L.nloc_max, st())
+            with self.span(".sel_dstar"):
+                _lib.call("reid_shard_dstar", N, r, P, _ptr(stats_all), L.stats_slot // 4, _ptr(key_g), _ptr(key_l),
+                          _ptr(dstar), _ptr(count), _ptr(cthr), st())
+            with self.span(".sel_push"):
+                _lib.call("reid_shard_push", _ptr(panel), nloc, r, P, N, L.ld, _ptr(cm_d), cpitch, _ptr(dstar), _ptr(cthr),
+                          _ptr(count), _ptr(pbuf), cap, st())
+            with self.span(".sel_merge_local"):
+                _lib.call("reid_shard_merge_local", _ptr(panel), L.ld, N, r, P, _ptr(cm_d), cpitch, _ptr(cm_m), pitch_m,
+                          _ptr(key_g), _ptr(dstar), _ptr(count), _ptr(pbuf), cap, K, peers, L.inbox, L.nloc_max, st())
         with self.span("x_inbox"):
             fab.barrier()
         with self.span("select"):
@@ -1179,7 +1182,8 @@ class Engine:
         Vc = fab.view(L.vc, (N, cap1), torch.int32)
         Vv = fab.view(L.vv, (N, cap1), torch.float16)
         with self.span("krecip"):
-            sets = self.krecip_sets(nbr, k1)
+            with self.span(".krecip_sets"):
+                sets = self.krecip_sets(nbr, k1)
             rfull, nfull, rhalf, nhalf = sets
             panels = fab.peers_at(L.panel)
             _lib.call("reid_krecip_V_sharded", _ptr(rfull), _ptr(nfull), _ptr(rhalf), _ptr(nhalf), r, P, nloc, k1,
