@@ -10,7 +10,17 @@
 
 namespace reid {
 
+__device__ __forceinline__ int split_scale_exponent(uint32_t amax_bits) {   // == tc::scale_exponent
+  if ((amax_bits & 0x7fffffffu) == 0) return 0;
+  int E = (int)((amax_bits >> 23) & 0xff) - 127;
+  int e = 14 - E;
+  return max(-100, min(100, e));
+}
+
 // pass 1: one warp per row -> x32 (normalised, padded), sq, nrm, global max|x| (float bits)
+// With a PRESET scale (amax == NULL, preset != NULL: the caller already knows a bound on max|x|, e.g. 1 for normalised
+// rows) the float16 hi / lo operands are written here as well and the second pass is skipped: one read of X instead of a
+// write + re-read of x32 (the prologue is replicated on every rank of a multi-GPU job, so its cost does not shrink with P).
 // X2 != NULL: the row is the flip-TTA average (X + X2) / 2 of two embedding passes (prompt_learning.py:775-776,
 // zero_shot_learning.py:121-125: `(emb + emb_aug) / 2` in float32 -- one rounded add, an exact halving), formed on
 // the fly: the averaged matrix is never written or re-read.
@@ -19,7 +29,8 @@ __global__ void __launch_bounds__(256) prep_rows_kernel(const float* __restrict_
                                                         long long ld_x, int normalize,
                                                         float* __restrict__ x32, int dp,
                                                         float* __restrict__ sq, float* __restrict__ nrm,
-                                                        uint32_t* __restrict__ amax) {
+                                                        uint32_t* __restrict__ amax, const uint32_t* __restrict__ preset,
+                                                        __half* __restrict__ hi, __half* __restrict__ lo) {
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= n) return;
   const int lane = lane_id();
@@ -37,10 +48,17 @@ __global__ void __launch_bounds__(256) prep_rows_kernel(const float* __restrict_
   if (normalize) denom = fmaxf(sqrtf(ss), 1e-12f);     // F.normalize: x / max(||x||, eps)
   float ss2 = 0.0f, mx = 0.0f;
   float* o32 = x32 + (long long)row * dp;
+  const float sc = preset ? exp2f((float)split_scale_exponent(*preset)) : 0.0f;      // exact power of two
   for (int k = lane; k < dp; k += 32) {
     float y = 0.0f;
     if (k < d) y = normalize ? __fdiv_rn(at(k), denom) : at(k);
     o32[k] = y;
+    if (preset) {                                       // same arithmetic as split_f16_kernel
+      const float a = y * sc;
+      const __half h = __float2half_rn(a);
+      hi[(long long)row * dp + k] = h;
+      lo[(long long)row * dp + k] = __float2half_rn(__fsub_rn(a, __half2float(h)));
+    }
     ss2 = __fmaf_rn(y, y, ss2);
     mx = fmaxf(mx, fabsf(y));
   }
@@ -54,13 +72,6 @@ __global__ void __launch_bounds__(256) prep_rows_kernel(const float* __restrict_
     nrm[row] = sqrtf(ss2);
     if (amax && mx == mx && mx < INFINITY) atomicMax(amax, __float_as_uint(mx));   // non-negative floats order as uints
   }
-}
-
-__device__ __forceinline__ int split_scale_exponent(uint32_t amax_bits) {   // == tc::scale_exponent
-  if ((amax_bits & 0x7fffffffu) == 0) return 0;
-  int E = (int)((amax_bits >> 23) & 0xff) - 127;
-  int e = 14 - E;
-  return max(-100, min(100, e));
 }
 
 // pass 2: hi/lo float16 split with the matrix-wide exponent; 4 elements per thread
@@ -102,9 +113,10 @@ int launch_prep_rows(const float* X, const float* X2, long long ld_x2, int n, in
   if (n == 0) return REID_OK;
   const int wpb = 8;
   prep_rows_kernel<<<cdiv(n, wpb), wpb * 32, 0, s>>>(X, X2, ld_x2, n, d, ld_x, normalize, x32, dp, sq, nrm,
-                                                     preset_amax ? nullptr : amax);
+                                                     preset_amax ? nullptr : amax, preset_amax ? amax : nullptr, hi, lo);
   int rc = check_launch("prep_rows_kernel");
   if (rc) return rc;
+  if (preset_amax) return REID_OK;                      // operands written by the first pass
   const long long total4 = (long long)n * dp / 4;
   const int blocks = (int)((total4 + 255) / 256 < 148 * 8 ? (total4 + 255) / 256 : 148 * 8);
   split_f16_kernel<<<blocks, 256, 0, s>>>(x32, total4, amax, hi, lo);
