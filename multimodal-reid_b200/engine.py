@@ -793,7 +793,9 @@ class Engine:
             _lib.call("reid_rr_topk", nq, r, P, _ptr(tidx), _ptr(tval), Kd, g, cap_o, _ptr(ocol), _ptr(ot), _ptr(od),
                       _ptr(ocnt), _ptr(key), c1, c2, topk, _ptr(out_i), _ptr(out_v), _ptr(flags[4:]), st())
         f = [int(v) for v in flags.tolist()]
-        diag = {"rekey_ambiguous": f[0], "v_misses": f[1], "v_pairs_recontracted": pairs_recomputed,
+        osz = (torch.stack([ocnt[:nq].max(), ocnt[:nq].sum()]).tolist() if nq else [0, 0])
+        diag = {"overlap_targets_max": int(osz[0]), "overlap_targets_mean": (osz[1] / nq if nq else 0.0),
+                "rekey_ambiguous": f[0], "v_misses": f[1], "v_pairs_recontracted": pairs_recomputed,
                 "overlap_overflow": f[2], "group_overflow": f[3], "topk_ambiguous": f[4], "Kw": Kw, "Kd": Kd}
         if f[2] or f[3]:
             raise _lib.ReidError(f"streamed re-ranking: {f[2]} queries touch more than cap_o={cap_o} gallery columns, "
