@@ -302,8 +302,9 @@ REID_API int reid_krecip_V_sharded(const int32_t* rfull, const int32_t* nfull, c
 /* Peer-memory fabric: an arena per rank (cudaMalloc; export -> 64-byte CUDA IPC handle; open maps a peer's arena into
  * this process with peer access enabled), identical layout on every rank.  `peers` is a DEVICE array of world arena base
  * pointers (own arena at index rank).  barrier: a kernel on the stream -- stores `epoch` into flags[rank] of every peer
- * (release.sys) and waits until all of its own flags reached it; flags = world uint32 at flags_off of every arena,
- * zero-initialised; epochs grow by one per barrier.  bcast*: copy this rank's part of a replicated table into every
+ * (release.sys) and waits until all of its own flags reached it; flags = 64 uint32 at flags_off of every arena,
+ * zero-initialised; epochs grow by one per barrier.  epoch == 0: the kernel keeps the count itself (word 32 of the rank's
+ * own flag block) -- no per-call argument, so a step with barriers can be captured in a CUDA graph.  bcast*: copy this rank's part of a replicated table into every
  * peer's arena at the same offset: a byte range; the owned snake blocks of an [n, row_bytes] table; owned V rows in ELL
  * form (count + used prefix); owned rows of a CSR pool (cnt[n], int32 columns / float16 values at element offsets off[]). */
 REID_API int reid_fabric_alloc(int64_t bytes, void** out);

@@ -24,9 +24,22 @@ __device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
   return v;
 }
 
+// epoch == 0: the epoch is this rank's own count of barriers, kept in device memory beside its flags (word 32) and
+// advanced by the kernel itself -- every rank runs the same sequence of barriers, so the counts agree everywhere, and the
+// launch has no per-call argument: a step containing barriers can be captured in a CUDA graph and replayed.
 __global__ void fabric_barrier_kernel(unsigned char* const* __restrict__ peers, long long flags_off, int rank, int P,
                                       unsigned epoch) {
   const int s = threadIdx.x;
+  __shared__ unsigned e_s;
+  if (epoch == 0) {
+    if (s == 0) {
+      unsigned* cnt = reinterpret_cast<unsigned*>(peers[rank] + flags_off) + 32;
+      e_s = *cnt + 1;
+      *cnt = e_s;
+    }
+    __syncthreads();
+    epoch = e_s;
+  }
   if (s < P) {
     __threadfence_system();          // everything this GPU wrote before the barrier is visible before the flag is
     st_release_sys(reinterpret_cast<unsigned*>(peers[s] + flags_off) + rank, epoch);

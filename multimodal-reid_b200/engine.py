@@ -227,6 +227,8 @@ class Engine:
         self._c_ws = None
         self.graph_below = 50_000           # ... replayed as ONE CUDA-graph launch for problems of fewer rows (0: never)
         self._graphs = {}
+        self._graph_seen = {}
+        self._capturing = False
         self.qe_nosync_bytes = 4 << 30       # budget for sizing the query-expansion pools without a host read
         self._ubmax_pinned = torch.zeros(1, dtype=torch.int64).pin_memory()
         self._ubmax_event = torch.cuda.Event()
@@ -837,7 +839,7 @@ class Engine:
 
     def _qe_cap_hint(self) -> int:
         """Power-of-two merge-buffer size covering the longest union seen by the previous no-sync call (256 at first)."""
-        if self._ubmax_pending and self._ubmax_event.query():
+        if not self._capturing and self._ubmax_pending and self._ubmax_event.query():
             self._ubmax_seen = int(self._ubmax_pinned[0])
             self._ubmax_pending = False
         cap = 32
@@ -863,9 +865,10 @@ class Engine:
             # arrives through a pinned buffer; rows longer than that take the kernel's exact k2-way merge fallback.
             total = bound
             cap_sort = self._qe_cap_hint()
-            self._ubmax_pinned.copy_(ub.max().to(torch.int64).reshape(1), non_blocking=True)
-            self._ubmax_event.record()
-            self._ubmax_pending = True
+            if not self._capturing:               # (the hint's host round trip stays outside a captured step)
+                self._ubmax_pinned.copy_(ub.max().to(torch.int64).reshape(1), non_blocking=True)
+                self._ubmax_event.record()
+                self._ubmax_pending = True
         else:
             stats = [qoff[rows].reshape(1), ub.max().to(torch.int64).reshape(1)] if rows else []
             if extra is not None:
@@ -1211,9 +1214,10 @@ class Engine:
                 Qc = fab.view(L.qc, (L.pool_elems,), torch.int32)
                 Qv = fab.view(L.qv, (L.pool_elems,), torch.float16)
                 cap_sort = self._qe_cap_hint()
-                self._ubmax_pinned.copy_(ub.max().to(torch.int64).reshape(1), non_blocking=True)
-                self._ubmax_event.record()
-                self._ubmax_pending = True
+                if not self._capturing:
+                    self._ubmax_pinned.copy_(ub.max().to(torch.int64).reshape(1), non_blocking=True)
+                    self._ubmax_event.record()
+                    self._ubmax_pending = True
                 _lib.call("reid_qe_k2_capped", _ptr(nbr), K, k2, _ptr(Vc), _ptr(Vv), _ptr(Vn), cap1, r, -P, nloc,
                           _ptr(qoff), cap_sort, _ptr(Qc), _ptr(Qv), _ptr(Qn), st())
             with self.span("x_qe"):
@@ -1276,11 +1280,61 @@ class Engine:
                 and self.engine != ENGINES["simt"] and self.symmetric and self.upper_only and self.scatter_select
                 and self.sparse_cap == 8192 and feats.shape[0] >= max(k1 + 1, k2)):
             return self.evaluate_reranked_single_call(feats, q, pids, cams, k1, k2, lam, normalize, max_rank)
+        N = feats.shape[0]
+        if (self.comm.world > 1 and self.graph_below and N < self.graph_below and self.timers is None
+                and feats_aug is None and N * k2 * v_row_capacity(k1) * 14 <= self.qe_nosync_bytes):
+            res = self._evaluate_reranked_graph(feats, q, pids, cams, k1, k2, lam, normalize, max_rank)
+            if res is not None:
+                return res
+        return self._evaluate_reranked_staged(feats, q, pids, cams, k1, k2, lam, normalize, max_rank, feats_aug)
+
+    def _evaluate_reranked_staged(self, feats, q, pids, cams, k1, k2, lam, normalize, max_rank, feats_aug=None):
         mine = self.own_queries(feats.shape[0], q, k1, k2, max_rank)
         ids = (pids[:q][mine].contiguous(), pids[q:].contiguous(), cams[:q][mine].contiguous(), cams[q:].contiguous())
         _, res = self.rerank_features(feats, q, k1, k2, lam, normalize, score=(ids, max_rank), want_final=False,
                                       feats_aug=feats_aug)
         return res
+
+    def _evaluate_reranked_graph(self, feats, q, pids, cams, k1, k2, lam, normalize, max_rank):
+        """Several ranks, small problem: a step of the peer-memory path is ~60 launches of 5-80 us and the host needs
+        ~0.8 ms to issue them -- more than the GPUs need to run them (Duke on 8 B200s).  The step has no host read, no
+        library collective and argument-free barriers, so after three eager calls with the same buffers and parameters
+        it is captured in a CUDA graph per rank and replayed as one launch.  Every rank decides alike (same call
+        sequence), and eager and replayed steps issue the same barriers, so ranks may even mix the two.  Returns None
+        when the peer-memory path is not the one in use."""
+        N = feats.shape[0]
+        if self._fabric_for(N, q, max(k1 + 1, k2), k1, k2, max_rank) is None:
+            return None
+        key = (feats.data_ptr(), feats.stride(0), N, q, feats.shape[1], pids.data_ptr(), cams.data_ptr(), k1, k2,
+               float(lam), bool(normalize), max_rank, self.fabric.base)
+        ent = self._graphs.get(key)
+        if ent is None:
+            seen = self._graph_seen.get(key, 0) + 1
+            self._graph_seen[key] = seen
+            if seen < 4:
+                return self._evaluate_reranked_staged(feats, q, pids, cams, k1, k2, lam, normalize, max_rank)
+            try:
+                torch.cuda.current_stream(self.device).synchronize()
+                graph = torch.cuda.CUDAGraph()
+                self._capturing = True
+                try:
+                    with torch.cuda.graph(graph):
+                        out = self._evaluate_reranked_staged(feats, q, pids, cams, k1, k2, lam, normalize, max_rank)
+                finally:
+                    self._capturing = False
+                if len(self._graphs) >= 8:
+                    self._graphs.clear()
+                # (the graph addresses the inputs by pointer and the key holds those pointers: no reference is kept, so a
+                #  caller that frees and re-allocates its inputs every step gets the same addresses -- and this graph -- back)
+                ent = self._graphs[key] = (graph, out)
+            except Exception as e:                              # noqa: BLE001 -- eager from now on (same barriers)
+                import warnings
+                warnings.warn(f"reid_b200: CUDA-graph capture of the multi-rank step failed ({e}); launching eagerly")
+                self.graph_below = 0
+                return self._evaluate_reranked_staged(feats, q, pids, cams, k1, k2, lam, normalize, max_rank)
+        ent[0].replay()
+        self.last_path = "fabric-graph"
+        return tuple(t.clone() for t in ent[1])
 
     def evaluate_reranked_single_call(self, feats: torch.Tensor, q: int, pids: torch.Tensor, cams: torch.Tensor, k1: int,
                                       k2: int, lam: float, normalize: bool, max_rank: int = 50):
@@ -1336,7 +1390,7 @@ class Engine:
                         call(out)
                     if len(self._graphs) >= 8:
                         self._graphs.clear()
-                    ent = self._graphs[key] = (graph, base, (feats, pids, cams))     # keeps the captured buffers alive
+                    ent = self._graphs[key] = (graph, base)     # inputs are addressed by the pointers in the key
                 except Exception as e:                          # noqa: BLE001 -- capture unsupported here: eager from now on
                     import warnings
                     warnings.warn(f"reid_b200: CUDA-graph capture of the evaluation failed ({e}); launching eagerly")

@@ -266,8 +266,8 @@ class Fabric:
         return C.c_void_p(self.torch.cuda.current_stream().cuda_stream)
 
     def barrier(self, flags_off: int = 0):
-        self.epoch += 1
-        self._lib.call("reid_fabric_barrier", self._ptr(), flags_off, self.rank, self.world, self.epoch, self._stream())
+        # epoch 0: the kernel counts its own barriers in device memory (no per-call argument: graph-capturable)
+        self._lib.call("reid_fabric_barrier", self._ptr(), flags_off, self.rank, self.world, 0, self._stream())
 
     def bcast(self, offset: int, nbytes: int):
         self._lib.call("reid_fabric_bcast", self._ptr(), self.rank, self.world, offset, _align(nbytes, 16), self._stream())

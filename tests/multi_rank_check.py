@@ -81,6 +81,24 @@ def main():
                       flush=True)
     multi.use_fabric = True
     multi.qe_replicate_below = 300_000
+    # small problems on several ranks: after three eager calls with the same buffers the step is captured in a CUDA graph
+    # per rank and replayed as one launch (argument-free barriers) -- same bits, call after call
+    if not multi._fabric_failed:
+        for name, k1, k2, seed in (("small", 20, 6, 0), ("mid", 20, 6, 2)):
+            sh = synth.SHAPES[name]
+            qf, gf, qp, gp, qc, gc = synth.make(sh, seed)
+            feats = torch.cat([qf, gf]).to(dev)
+            pids, cams = torch.cat([qp, gp]).to(dev), torch.cat([qc, gc]).to(dev)
+            want = single_sym.evaluate_reranked(feats, sh.q, pids, cams, k1, k2, 0.3, normalize=True)
+            paths = []
+            for it in range(7):
+                got = multi.evaluate_reranked(feats, sh.q, pids, cams, k1, k2, 0.3, normalize=True)
+                paths.append(multi.last_path)
+                for a, b, what in zip(want, got, ("cmc", "mAP", "n_valid", "ap", "first_hit")):
+                    assert torch.equal(a, b), f"{name}: {what} differs on rank {rank} at call {it} ({multi.last_path})"
+            assert paths[-1] == "fabric-graph", paths
+            if rank == 0:
+                print(f"{name}: {world}-rank graph-replayed step == 1-rank result ({paths})", flush=True)
     # reranking.py:43-44 / :33-34 with a caller-supplied N x N matrix on several ranks: replicas, own rows returned
     rr = importlib.import_module("multimodal-reid_b200.reranking")
     sh = synth.SHAPES["tiny"]
