@@ -104,6 +104,9 @@ REID_API int reid_prepare_rows_tta(const float* X, const float* X_aug, int n, in
  * mirrored tiles are NOT stored (their row maxima and chunk minima still are) -- half the output stream; entries left of
  * a row's 256-wide diagonal block are then undefined and consumers must read D[col, row] instead (the _tri entry points
  * do).  Modes 1 and 2 apply when both operands are the same rows; a rectangle of different row sets always runs in full. */
+/* reid_launch_count() counts the kernels this library enqueued (host side).  A caller that captured a sequence of
+ * entry points in a CUDA graph reports the launches of every replay here, so that the count stays what ran on the GPU. */
+REID_API int reid_note_replayed_launches(int n);
 /* Diagnostics: with the environment variable REID_TC_DBG & 64 set, block 0 of reid_dist's kernel records
  * {clock64, globaltimer ns} at entry and exit; this copies the four values to HOST memory (synchronises). */
 REID_API int reid_dist_clock_probe(int64_t* host_out4);

@@ -227,7 +227,7 @@ class Engine:
         self._c_ws = None
         self.graph_below = 50_000           # ... replayed as ONE CUDA-graph launch for problems of fewer rows (0: never)
         self._graphs = {}
-        self._graph_seen = {}
+        self._graph_last_key, self._graph_run = None, 0
         self._capturing = False
         self.qe_nosync_bytes = 4 << 30       # budget for sizing the query-expansion pools without a host read
         self._ubmax_pinned = torch.zeros(1, dtype=torch.int64).pin_memory()
@@ -1309,32 +1309,40 @@ class Engine:
                float(lam), bool(normalize), max_rank, self.fabric.base)
         ent = self._graphs.get(key)
         if ent is None:
-            seen = self._graph_seen.get(key, 0) + 1
-            self._graph_seen[key] = seen
-            if seen < 4:
+            if not self._graph_due(key):
                 return self._evaluate_reranked_staged(feats, q, pids, cams, k1, k2, lam, normalize, max_rank)
             try:
                 torch.cuda.current_stream(self.device).synchronize()
                 graph = torch.cuda.CUDAGraph()
                 self._capturing = True
+                n0 = int(self.lib.reid_launch_count())
                 try:
                     with torch.cuda.graph(graph):
                         out = self._evaluate_reranked_staged(feats, q, pids, cams, k1, k2, lam, normalize, max_rank)
                 finally:
                     self._capturing = False
-                if len(self._graphs) >= 8:
-                    self._graphs.clear()
+                n_launch = int(self.lib.reid_launch_count()) - n0
                 # (the graph addresses the inputs by pointer and the key holds those pointers: no reference is kept, so a
                 #  caller that frees and re-allocates its inputs every step gets the same addresses -- and this graph -- back)
-                ent = self._graphs[key] = (graph, out)
+                ent = self._graphs[key] = (graph, out, n_launch)
             except Exception as e:                              # noqa: BLE001 -- eager from now on (same barriers)
                 import warnings
                 warnings.warn(f"reid_b200: CUDA-graph capture of the multi-rank step failed ({e}); launching eagerly")
                 self.graph_below = 0
                 return self._evaluate_reranked_staged(feats, q, pids, cams, k1, k2, lam, normalize, max_rank)
         ent[0].replay()
+        self.lib.reid_note_replayed_launches(ent[2])
         self.last_path = "fabric-graph"
         return tuple(t.clone() for t in ent[1])
+
+    def _graph_due(self, key) -> bool:
+        """Capture only for a caller that presents the SAME buffers and parameters four times in a row (a benchmark or
+        serving loop with resident inputs); inputs re-allocated every call never qualify, and at most 8 graphs exist."""
+        if key == self._graph_last_key:
+            self._graph_run += 1
+        else:
+            self._graph_last_key, self._graph_run = key, 1
+        return self._graph_run >= 4 and len(self._graphs) < 8
 
     def evaluate_reranked_single_call(self, feats: torch.Tensor, q: int, pids: torch.Tensor, cams: torch.Tensor, k1: int,
                                       k2: int, lam: float, normalize: bool, max_rank: int = 50):
@@ -1380,17 +1388,17 @@ class Engine:
             key = (feats.data_ptr(), feats.stride(0), N, q, d, pids.data_ptr(), cams.data_ptr(), k1, k2, float(lam),
                    bool(normalize), max_rank, self._c_ws.data_ptr())
             ent = self._graphs.get(key)
-            if ent is None:
+            if ent is None and self._graph_due(key):
                 try:
                     base, out = outputs()
                     call(out)                                   # eager once: function attributes, tensor maps, errors
                     torch.cuda.current_stream(self.device).synchronize()
                     graph = torch.cuda.CUDAGraph()
+                    n0 = int(self.lib.reid_launch_count())
                     with torch.cuda.graph(graph):
                         call(out)
-                    if len(self._graphs) >= 8:
-                        self._graphs.clear()
-                    ent = self._graphs[key] = (graph, base)     # inputs are addressed by the pointers in the key
+                    n_launch = int(self.lib.reid_launch_count()) - n0
+                    ent = self._graphs[key] = (graph, base, n_launch)     # inputs are addressed by the pointers in the key
                 except Exception as e:                          # noqa: BLE001 -- capture unsupported here: eager from now on
                     import warnings
                     warnings.warn(f"reid_b200: CUDA-graph capture of the evaluation failed ({e}); launching eagerly")
@@ -1398,6 +1406,7 @@ class Engine:
                     ent = None
             if ent is not None:
                 ent[0].replay()
+                self.lib.reid_note_replayed_launches(ent[2])
                 self.last_path = "single-call-graph"
                 cmc, mAP, nvalid, ap, first = views(ent[1].clone())     # one copy: results survive the next replay
                 return cmc, mAP, nvalid, ap[:q], first[:q]
