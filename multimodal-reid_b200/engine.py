@@ -225,7 +225,8 @@ class Engine:
         self.scatter_select = True          # upper-only selection in scatter form (reid_topk_rows_scatter)
         self.c_entry = True                 # one rank: evaluate_reranked goes through the single C entry (reid_eval_reranked)
         self._c_ws = None
-        self.graph_below = 50_000           # ... replayed as ONE CUDA-graph launch for problems of fewer rows (0: never)
+        # ... replayed as ONE CUDA-graph launch for problems of fewer rows (0: never; REID_GRAPH_BELOW overrides)
+        self.graph_below = int(__import__("os").environ.get("REID_GRAPH_BELOW", "50000"))
         self._graphs = {}
         self._graph_last_key, self._graph_run = None, 0
         self._capturing = False
