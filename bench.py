@@ -275,7 +275,7 @@ def main():
 
     def step_resident():
         cmc, mAP, nvalid, _, _ = eng.evaluate_reranked(feats_d, q, pids_d, cams_d, shape.k1, shape.k2, shape.lam,
-                                                       normalize=True, max_rank=50)
+                                                       normalize=True, max_rank=50, resident=True)
         return cmc, mAP
 
     def step_e2e():

@@ -1274,15 +1274,21 @@ class Engine:
                                       want_final=want_final, upper_only=tri)
 
     def evaluate_reranked(self, feats: torch.Tensor, q: int, pids: torch.Tensor, cams: torch.Tensor, k1: int, k2: int,
-                          lam: float, normalize: bool, max_rank: int = 50, feats_aug: torch.Tensor | None = None):
+                          lam: float, normalize: bool, max_rank: int = 50, feats_aug: torch.Tensor | None = None,
+                          resident: bool = False):
         """The evaluator's hot path end to end (evaluate.py:110-132 with reranking=True): features and ids of
-        all N samples (queries first) -> (cmc, mAP, n_valid, ap, first_hit); the q x g matrix is never written."""
+        all N samples (queries first) -> (cmc, mAP, n_valid, ap, first_hit); the q x g matrix is never written.
+        resident=True: the caller keeps feats / pids / cams in the same device buffers from call to call (a serving or
+        benchmark loop) -- small problems are then captured in a CUDA graph after four identical calls and replayed as
+        one launch.  Never inferred: a caller whose allocator merely happens to return the same addresses must not
+        trigger captures (measured: 3 ms per evaluation lost to repeated captures in the evaluator's e2e path)."""
         if (self.c_entry and self.comm.world == 1 and self.timers is None and feats_aug is None
                 and self.engine != ENGINES["simt"] and self.symmetric and self.upper_only and self.scatter_select
                 and self.sparse_cap == 8192 and feats.shape[0] >= max(k1 + 1, k2)):
-            return self.evaluate_reranked_single_call(feats, q, pids, cams, k1, k2, lam, normalize, max_rank)
+            return self.evaluate_reranked_single_call(feats, q, pids, cams, k1, k2, lam, normalize, max_rank,
+                                                      resident=resident)
         N = feats.shape[0]
-        if (self.comm.world > 1 and self.graph_below and N < self.graph_below and self.timers is None
+        if (resident and self.comm.world > 1 and self.graph_below and N < self.graph_below and self.timers is None
                 and feats_aug is None and N * k2 * v_row_capacity(k1) * 14 <= self.qe_nosync_bytes):
             res = self._evaluate_reranked_graph(feats, q, pids, cams, k1, k2, lam, normalize, max_rank)
             if res is not None:
@@ -1346,7 +1352,7 @@ class Engine:
         return self._graph_run >= 4 and len(self._graphs) < 8
 
     def evaluate_reranked_single_call(self, feats: torch.Tensor, q: int, pids: torch.Tensor, cams: torch.Tensor, k1: int,
-                                      k2: int, lam: float, normalize: bool, max_rank: int = 50):
+                                      k2: int, lam: float, normalize: bool, max_rank: int = 50, resident: bool = False):
         """The same evaluation through the single C-ABI entry reid_eval_reranked (csrc/eval_e2e.cu): one call, one
         cached workspace, no host read inside, ~30 launches issued from C++ instead of ~25 ctypes round trips.  Same
         kernels, same bits as the staged path (tests/test_gpu_api.py).  One rank, tensor-core engine."""
@@ -1382,7 +1388,7 @@ class Engine:
                       _ptr(mAP), _ptr(nvalid), _ptr(ap), _ptr(first), _stream())
 
         self.last_path = "single-call"
-        if self.graph_below and N < self.graph_below:
+        if resident and self.graph_below and N < self.graph_below:
             # Small problems are launch-bound (Duke: ~30 launches of 5-400 us): the call is a fixed launch sequence with
             # no allocation and no host read, so it is captured ONCE per (buffers, shape, parameters) and replayed as one
             # graph launch.  The outputs of a replay live in the graph's static tensors until the next replay.

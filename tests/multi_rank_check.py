@@ -92,7 +92,7 @@ def main():
             want = single_sym.evaluate_reranked(feats, sh.q, pids, cams, k1, k2, 0.3, normalize=True)
             paths = []
             for it in range(7):
-                got = multi.evaluate_reranked(feats, sh.q, pids, cams, k1, k2, 0.3, normalize=True)
+                got = multi.evaluate_reranked(feats, sh.q, pids, cams, k1, k2, 0.3, normalize=True, resident=True)
                 paths.append(multi.last_path)
                 for a, b, what in zip(want, got, ("cmc", "mAP", "n_valid", "ap", "first_hit")):
                     assert torch.equal(a, b), f"{name}: {what} differs on rank {rank} at call {it} ({multi.last_path})"
