@@ -322,7 +322,7 @@ def main():
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    n_warm = max(args.warmup, 3) + args.settle       # same count on every rank (the steps contain collectives)
+    n_warm = max(args.warmup, 5) + args.settle       # same count on every rank; >= 5 so that a graph capture (4th call) is done
     for _ in range(n_warm):
         out = step_resident()
     barrier()
