@@ -214,7 +214,8 @@ REID_API int reid_eval_reranked(const float* feats, int64_t ld, int N, int q, in
  * reid_overlap_lists: reranking.py:86-92 for a window of queries with a shared-memory hash table instead of an N-bit row:
  * per query the gallery columns (target - q) it overlaps, ascending, and the float16 overlap sums -> ocol / ot at
  * [l * cap_o ...], ocnt[l] (-1 and *overflow += 1 when a query touches more than cap_o gallery columns, or more than
- * 8192 inside one of the ceil(cap_o / 4096) column ranges the gallery is processed in).
+ * 8192 inside one of the column ranges the gallery is processed in: nrange of them, 0 = ceil(cap_o / 4096); every range
+ * costs one walk of the query's inverted lists, so a caller that knows the real list sizes passes fewer).
  * reid_rr_prepare: per query, from the distances of its same-identity gallery columns (group arrays as
  * reid_stream_group_*) and its overlap list: true final keys of the group (gkey, gjunk), the sorted match keys mk, and
  * for every match the raw-distance thresholds thrA / thrB (largest D whose untouched final value is < / <= the match's).
@@ -233,7 +234,8 @@ REID_API int reid_krecip_V_lists(const int32_t* rfull, const int32_t* nfull, con
                         int miss_cap, void* stream);
 REID_API int reid_overlap_lists(const int32_t* Qc, const reid_half* Qv, const int64_t* qoff, const int32_t* Qn,
                        const int64_t* colptr, const uint64_t* csc_ent, int q0, int q_stride, int nq, int q, int N,
-                       int cap_o, int32_t* ocol, reid_half* ot, int32_t* ocnt, int32_t* overflow, void* stream);
+                       int cap_o, int nrange, int32_t* ocol, reid_half* ot, int32_t* ocnt, int32_t* overflow,
+                       void* stream);
 /* od[l * cap_o + e] = panel[l, ocol[l * cap_o + e] - c0] for the listed columns inside the panel's block [c0, c1) */
 REID_API int reid_stream_list_gather(const float* panel, int64_t ld, int rows, int c0, int c1, int cap_o,
                             const int32_t* ocol, const int32_t* ocnt, float* od, void* stream);

@@ -381,11 +381,12 @@ int reid_krecip_V_lists(const int32_t* rfull, const int32_t* nfull, const int32_
 
 int reid_overlap_lists(const int32_t* Qc, const reid_half* Qv, const int64_t* qoff, const int32_t* Qn,
                        const int64_t* colptr, const uint64_t* csc_ent, int q0, int q_stride, int nq, int q, int N,
-                       int cap_o, int32_t* ocol, reid_half* ot, int32_t* ocnt, int32_t* overflow, void* stream) {
+                       int cap_o, int nrange, int32_t* ocol, reid_half* ot, int32_t* ocnt, int32_t* overflow,
+                       void* stream) {
   ENTER();
   REID_REQUIRE(q_stride != 0 && nq >= 0 && q >= 0, "overlap_lists: bad window");
-  return launch_overlap_hash(Qc, HC(Qv), LL(qoff), Qn, LL(colptr), ULL(csc_ent), q0, q_stride, nq, q, N, cap_o, ocol,
-                             H(ot), ocnt, overflow, S(stream));
+  return launch_overlap_hash(Qc, HC(Qv), LL(qoff), Qn, LL(colptr), ULL(csc_ent), q0, q_stride, nq, q, N, cap_o, nrange,
+                             ocol, H(ot), ocnt, overflow, S(stream));
 }
 
 int reid_stream_list_gather(const float* panel, int64_t ld, int rows, int c0, int c1, int cap_o, const int32_t* ocol,

@@ -63,7 +63,7 @@ int launch_lists_rekey(const int* widx, const float* wval, int rows, int Kw, con
                        int* ambiguous, cudaStream_t s);
 int launch_overlap_hash(const int* Qc, const __half* Qv, const long long* qoff, const int* Qn, const long long* colptr,
                         const unsigned long long* csc_ent, int q0, int q_stride, int nq, int q, int N, int cap_o,
-                        int* ocol, __half* ot, int* ocnt, int* overflow, cudaStream_t s);
+                        int nrange, int* ocol, __half* ot, int* ocnt, int* overflow, cudaStream_t s);
 int launch_list_gather_sorted(const float* panel, long long ld, int rows, int c0, int c1, int cap_o, const int* ocol,
                               const int* ocnt, float* od, cudaStream_t s);
 int launch_rr_prepare(int nq, int q0, int q_stride, const int* glo, const int* glen, const long long* goff,

@@ -173,11 +173,12 @@ overlap_hash_kernel(const int* __restrict__ Qc, const __half* __restrict__ Qv, c
 
 int launch_overlap_hash(const int* Qc, const __half* Qv, const long long* qoff, const int* Qn, const long long* colptr,
                         const unsigned long long* csc_ent, int q0, int q_stride, int nq, int q, int N, int cap_o,
-                        int* ocol, __half* ot, int* ocnt, int* overflow, cudaStream_t s) {
+                        int nrange, int* ocol, __half* ot, int* ocnt, int* overflow, cudaStream_t s) {
   if (nq == 0) return REID_OK;
-  REID_REQUIRE(cap_o >= 1 && q >= 0 && N > q, "overlap_hash: cap_o=%d q=%d N=%d", cap_o, q, N);
-  // ranges sized so that a query filling its whole budget still puts only ~half of OH_CAP into one table
-  int nrange = (cap_o + OH_CAP / 2 - 1) / (OH_CAP / 2);
+  REID_REQUIRE(cap_o >= 1 && q >= 0 && N > q && nrange >= 0, "overlap_hash: cap_o=%d q=%d N=%d", cap_o, q, N);
+  // default: ranges sized so that a query filling its whole budget still puts only ~half of OH_CAP into one table; a
+  // caller that knows how many targets its queries really touch passes fewer (every range costs one walk of the lists)
+  if (nrange == 0) nrange = (cap_o + OH_CAP / 2 - 1) / (OH_CAP / 2);
   if (nrange > N - q) nrange = N - q;
   const size_t smem = (size_t)OH_SLOTS * 6 + (size_t)OH_CAP * 8;
   REID_CUDA(cudaFuncSetAttribute(overlap_hash_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -229,6 +229,7 @@ class Engine:
         self.graph_below = int(__import__("os").environ.get("REID_GRAPH_BELOW", "50000"))
         self._graphs = {}
         self._graph_last_key, self._graph_run = None, 0
+        self._overlap_hint = {}             # (N, q, k1, k2) -> largest overlap list of the previous streamed re-ranking
         self._capturing = False
         self.qe_nosync_bytes = 4 << 30       # budget for sizing the query-expansion pools without a host read
         self._ubmax_pinned = torch.zeros(1, dtype=torch.int64).pin_memory()
@@ -736,8 +737,16 @@ class Engine:
             ot = self._empty((max(nq, 1) * cap_o,), torch.float16)
             od = self._zeros((max(nq, 1) * cap_o,), torch.float32)
             ocnt = self._empty((max(nq, 1),), torch.int32)
-            _lib.call("reid_overlap_lists", _ptr(Qc), _ptr(Qv), _ptr(qoff), _ptr(Qn), _ptr(colptr), _ptr(csc_ent), r, P,
-                      nq, q, N, cap_o, _ptr(ocol), _ptr(ot), _ptr(ocnt), _ptr(flags[2:]), st())
+            # column ranges: sized by the largest overlap list the previous call saw (x2 head room inside a range's 8 192
+            # slots); an overflow with hinted ranges is retried once with the default before it is reported
+            hint = self._overlap_hint.get((N, q, k1, k2), 0)
+            nrange = max(1, -(-2 * hint // 8192)) if hint else 0
+            for attempt in (nrange, 0):
+                flags[2:3].zero_()
+                _lib.call("reid_overlap_lists", _ptr(Qc), _ptr(Qv), _ptr(qoff), _ptr(Qn), _ptr(colptr), _ptr(csc_ent),
+                          r, P, nq, q, N, cap_o, attempt, _ptr(ocol), _ptr(ot), _ptr(ocnt), _ptr(flags[2:]), st())
+                if attempt == 0 or int(flags[2].item()) == 0:
+                    break
         # ---- D
         Qf, Gf = allf.rows(qsel), allf.rows(slice(q, N))
         keys, start, lst, T = self.pid_index(g_pids)
@@ -797,6 +806,7 @@ class Engine:
                       _ptr(ocnt), _ptr(key), c1, c2, topk, _ptr(out_i), _ptr(out_v), _ptr(flags[4:]), st())
         f = [int(v) for v in flags.tolist()]
         osz = (torch.stack([ocnt[:nq].max(), ocnt[:nq].sum()]).tolist() if nq else [0, 0])
+        self._overlap_hint[(N, q, k1, k2)] = cm.max_int(int(osz[0]), self.device)     # same ranges on every rank next time
         diag = {"overlap_targets_max": int(osz[0]), "overlap_targets_mean": (osz[1] / nq if nq else 0.0),
                 "rekey_ambiguous": f[0], "v_misses": f[1], "v_pairs_recontracted": pairs_recomputed,
                 "overlap_overflow": f[2], "group_overflow": f[3], "topk_ambiguous": f[4], "Kw": Kw, "Kd": Kd}

@@ -205,6 +205,11 @@ def test_streamed_rerank_equals_materialised(eng, engine_mod, synth, oracle, nam
                                                            detail=sdet)
     print(f"[a13] {name} k1={k1} k2={k2}: {diag}")
     assert diag["v_misses"] == 0, "a V weight fell back to the float32 recomputation on this instance"
+    # a second call sizes the Jaccard column ranges by the overlap lists the first one saw: same lists, same results
+    res2, (idx2, val2), _ = eng.evaluate_streamed_reranked(allf, q, pids, cams, k1, k2, 0.3, topk=topk, Kw=64,
+                                                          cap_o=12288 if name == "mid" else 4096, rows_per_pass=rows_pp,
+                                                          cols_per_pass=cols_pp)
+    assert torch.equal(idx, idx2) and torch.equal(val, val2) and all(torch.equal(a, b) for a, b in zip(res, res2))
     K = max(k1 + 1, k2)
     assert torch.equal(sdet["nbr"], det["nbr"][:, :K])
     assert torch.equal(sdet["Vn"], det["Vn"])
