@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define REID_ABI_VERSION 2
+#define REID_ABI_VERSION 3
 
 #define REID_OK 0
 #define REID_ERR_CUDA (-1)
@@ -219,6 +219,7 @@ REID_API int reid_eval_reranked(const float* feats, int64_t ld, int N, int q, in
  * reid_rr_prepare: per query, from the distances of its same-identity gallery columns (group arrays as
  * reid_stream_group_*) and its overlap list: true final keys of the group (gkey, gjunk), the sorted match keys mk, and
  * for every match the raw-distance thresholds thrA / thrB (largest D whose untouched final value is < / <= the match's).
+ * group_max (here and in the two calls below): the longest identity group, as for reid_stream_group_sort.
  * reid_stream_count_panel_rr: second sweep over the q x g panels: bins[goff + b] += entries that come after exactly b
  * matches when ranked as if the Jaccard term did not touch them.
  * reid_stream_score_rr: corrects the bins by the special entries (same identity, overlap targets; od = their exact
@@ -243,17 +244,17 @@ REID_API int reid_rr_prepare(int nq, int q0, int q_stride, const int32_t* glo, c
                     const int32_t* list, const float* gd, const int64_t* q_cam, const int64_t* g_cam,
                     const int32_t* rowmax_key, float c1, float c2, int cap_o, const int32_t* ocol, const reid_half* ot,
                     const int32_t* ocnt, uint64_t* gkey, uint8_t* gjunk, uint64_t* mk, float* thrA, float* thrB,
-                    int32_t* nmatch, int32_t* overflow, void* stream);
+                    int32_t* nmatch, int32_t* overflow, int group_max, void* stream);
 REID_API int reid_stream_count_panel_rr(const float* panel, int64_t ld, int rows, int c0, int c1, const int64_t* goff,
                                const uint64_t* mk, const float* thrA, const float* thrB, const int32_t* nmatch,
-                               int32_t* bins, void* stream);
+                               int32_t* bins, int group_max, void* stream);
 REID_API int reid_stream_score_rr(int nq, int q0, int q_stride, const int32_t* glo, const int32_t* glen,
                          const int64_t* goff, const int32_t* list, const float* gd, const uint64_t* gkey,
                          const uint8_t* gjunk, const uint64_t* mk, const float* thrA, const float* thrB,
                          const int32_t* nmatch, const int32_t* bins, int cap_o, const int32_t* ocol, const reid_half* ot,
                          const float* od, const int32_t* ocnt, const int64_t* q_pid, const int64_t* g_pid,
                          const int32_t* rowmax_key, float c1, float c2, int max_rank, double* ap, int32_t* first_hit,
-                         int32_t* cmc_hist, int32_t* n_valid, void* stream);
+                         int32_t* cmc_hist, int32_t* n_valid, int group_max, void* stream);
 REID_API int reid_rr_topk(int nq, int q0, int q_stride, const int32_t* tidx, const float* tval, int Kd, int g, int cap_o,
                  const int32_t* ocol, const reid_half* ot, const float* od, const int32_t* ocnt,
                  const int32_t* rowmax_key, float c1, float c2, int K, int32_t* out_idx, float* out_val,
@@ -419,6 +420,14 @@ REID_API int reid_score_finalize(const double* ap, int q, const int32_t* cmc_his
  * accumulated in the same pass (no prepared operands, any d, any pitch >= d). */
 REID_API int reid_pair_dist(const float* x, int64_t ldx, int m, const float* y, int64_t ldy, int n, int d, float* out,
                    int64_t ld_out, void* stream);
+/* The same op for large batches (B >= ~1024, cross-batch memories) on the tensor cores: rows split into the fp16 hi/lo
+ * operands of the evaluation path, contracted by the tcgen05 kernel of reid_dist (x.y to ~2^-22 |x||y|; upper triangle +
+ * mirrored stores when x and y are the same rows: pass the same pointer, pitch and count), clamped square root in place.
+ * workspace: reid_pair_dist_tc_workspace_bytes(m, n, d, same) bytes, 256-byte aligned; out 16-byte aligned with a pitch
+ * that is a multiple of 4.  No host synchronisation: capturable. */
+REID_API int64_t reid_pair_dist_tc_workspace_bytes(int m, int n, int d, int same);
+REID_API int reid_pair_dist_tc(const float* x, int64_t ldx, int m, const float* y, int64_t ldy, int n, int d, void* workspace,
+                      int64_t workspace_bytes, float* out, int64_t ld_out, void* stream);
 /* losses.py:31-83 `hard_example_mining` (and the masks of losses.py:126-139).  Per anchor row i of dist[m, n]:
  * dist_ap / p_ind = the largest entry among columns with lab_c == lab_r[i] (the anchor's own column i is left out when
  * skip_diag), dist_an / n_ind = the smallest among the others; ties keep the lowest column.  A row without a positive
@@ -444,14 +453,18 @@ REID_API int reid_triplet_grad(const float* x, int64_t ldx, int m, const float* 
                       int accumulate_gy, void* stream);
 
 /* ---- CMC / mAP when the q x g matrix is never materialised (evaluate.py:40-88 semantics) ----
- * The caller produces the matrix panel by panel (reid_dist on row chunks x column blocks), twice.
+ * The caller produces the matrix panel by panel (reid_dist on row chunks x column blocks).
  * Setup: reid_pid_index over the gallery ids; reid_stream_group_lookup -> for every query the slice [glo, glo+glen) of
  * pid_list holding the gallery columns of its identity; goff = exclusive prefix sum of glen (caller).
- * Sweep 1: reid_stream_group_gather on every panel fills gd[goff[i] + e] = D[i, pid_list[glo[i] + e]];
+ * Match distances gd[goff[i] + e] = D[i, pid_list[glo[i] + e]]: either reid_stream_group_gather on every panel of a
+ *          first sweep, or (what the host layer does) reid_dist on the gathered operand rows of those pairs, diagonal
+ *          kept -- the same bits, and the counting below can then share the ONE sweep with the top-k selection;
  *          reid_stream_group_sort: per query the matches' (distance, column) keys ascending in mkeys[goff .. goff+nmatch),
- *          the junk keys (same camera, evaluate.py:55) behind them; identities with more than 1024 gallery columns are
- *          reported through *overflow (largest group seen; 0 = none) and their queries skipped.
- * Sweep 2: reid_stream_count_panel on every panel adds to bins[goff[i] + b] the number of entries of the panel row with
+ *          the junk keys (same camera, evaluate.py:55) behind them.  group_max = the longest identity group (max of
+ *          glen; 0 = "at most 1024") sizes the per-query shared-memory arrays: 2^k entries, 1024 <= 2^k <= 8192; a larger
+ *          group_max is refused, and a query whose group exceeds what was announced is reported through *overflow
+ *          (largest group seen; 0 = none) and skipped.  The same group_max goes to every call of one evaluation.
+ * Sweep: reid_stream_count_panel on every panel adds to bins[goff[i] + b] the number of entries of the panel row with
  *          exactly b match keys below them (entries beyond the farthest match are skipped with one compare);
  *          bins zeroed by the caller.  rows/glo/glen/goff/nmatch pointers are those of the panel's first row.
  * Finally reid_stream_score: kept rank of every match = prefix sum of its bins minus the junk in front of it -> AP
@@ -462,9 +475,9 @@ REID_API int reid_stream_group_gather(const float* panel, int64_t ld, int rows, 
                              const int32_t* glen, const int64_t* goff, const int32_t* pid_list, float* gd, void* stream);
 REID_API int reid_stream_group_sort(int nq, const int32_t* glo, const int32_t* glen, const int64_t* goff,
                            const int32_t* pid_list, const float* gd, const int64_t* q_cam, const int64_t* g_cam,
-                           uint64_t* mkeys, int32_t* nmatch, int32_t* overflow, void* stream);
+                           uint64_t* mkeys, int32_t* nmatch, int32_t* overflow, int group_max, void* stream);
 REID_API int reid_stream_count_panel(const float* panel, int64_t ld, int rows, int c0, int c1, const int64_t* goff,
-                            const uint64_t* mkeys, const int32_t* nmatch, int32_t* bins, void* stream);
+                            const uint64_t* mkeys, const int32_t* nmatch, int32_t* bins, int group_max, void* stream);
 REID_API int reid_stream_score(int nq, const int32_t* glen, const int64_t* goff, const uint64_t* mkeys,
                       const int32_t* nmatch, const int32_t* bins, int max_rank, double* ap, int32_t* first_hit,
                       int32_t* cmc_hist, int32_t* n_valid, void* stream);

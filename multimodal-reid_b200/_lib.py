@@ -12,7 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libreid_b200.so")
 HEADER_PATH = os.path.join(_HERE, "..", "include", "reid_b200.h")
 
-ABI_VERSION = 2          # bumped whenever a signature in include/reid_b200.h changes
+ABI_VERSION = 3          # bumped whenever a signature in include/reid_b200.h changes
 _p = C.c_void_p
 _i = C.c_int
 _l = C.c_int64

@@ -399,18 +399,19 @@ int reid_rr_prepare(int nq, int q0, int q_stride, const int32_t* glo, const int3
                     const int32_t* list, const float* gd, const int64_t* q_cam, const int64_t* g_cam,
                     const int32_t* rowmax_key, float c1, float c2, int cap_o, const int32_t* ocol, const reid_half* ot,
                     const int32_t* ocnt, uint64_t* gkey, uint8_t* gjunk, uint64_t* mk, float* thrA, float* thrB,
-                    int32_t* nmatch, int32_t* overflow, void* stream) {
+                    int32_t* nmatch, int32_t* overflow, int group_max, void* stream) {
   ENTER();
   return launch_rr_prepare(nq, q0, q_stride, glo, glen, LL(goff), list, gd, LL(q_cam), LL(g_cam), rowmax_key, c1, c2,
                            cap_o, ocol, HC(ot), ocnt, reinterpret_cast<unsigned long long*>(gkey), gjunk,
-                           reinterpret_cast<unsigned long long*>(mk), thrA, thrB, nmatch, overflow, S(stream));
+                           reinterpret_cast<unsigned long long*>(mk), thrA, thrB, nmatch, overflow, group_max,
+                           S(stream));
 }
 
 int reid_stream_count_panel_rr(const float* panel, int64_t ld, int rows, int c0, int c1, const int64_t* goff,
                                const uint64_t* mk, const float* thrA, const float* thrB, const int32_t* nmatch,
-                               int32_t* bins, void* stream) {
+                               int32_t* bins, int group_max, void* stream) {
   ENTER();
-  return launch_count_panel_rr(panel, ld, rows, c0, c1, LL(goff), ULL(mk), thrA, thrB, nmatch, bins, S(stream));
+  return launch_count_panel_rr(panel, ld, rows, c0, c1, LL(goff), ULL(mk), thrA, thrB, nmatch, bins, group_max, S(stream));
 }
 
 int reid_stream_score_rr(int nq, int q0, int q_stride, const int32_t* glo, const int32_t* glen, const int64_t* goff,
@@ -419,11 +420,11 @@ int reid_stream_score_rr(int nq, int q0, int q_stride, const int32_t* glo, const
                          const int32_t* bins, int cap_o, const int32_t* ocol, const reid_half* ot, const float* od,
                          const int32_t* ocnt, const int64_t* q_pid, const int64_t* g_pid, const int32_t* rowmax_key,
                          float c1, float c2, int max_rank, double* ap, int32_t* first_hit, int32_t* cmc_hist,
-                         int32_t* n_valid, void* stream) {
+                         int32_t* n_valid, int group_max, void* stream) {
   ENTER();
   return launch_score_counts_rr(nq, q0, q_stride, glo, glen, LL(goff), list, gd, ULL(gkey), gjunk, ULL(mk), thrA, thrB,
                                 nmatch, bins, cap_o, ocol, HC(ot), od, ocnt, LL(q_pid), LL(g_pid), rowmax_key, c1, c2,
-                                max_rank, ap, first_hit, cmc_hist, n_valid, S(stream));
+                                max_rank, ap, first_hit, cmc_hist, n_valid, group_max, S(stream));
 }
 
 int reid_rr_topk(int nq, int q0, int q_stride, const int32_t* tidx, const float* tval, int Kd, int g, int cap_o,
@@ -621,6 +622,18 @@ int reid_pair_dist(const float* x, int64_t ldx, int m, const float* y, int64_t l
   return launch_pair_dist(x, ldx, m, y, ldy, n, d, out, ld_out, S(stream));
 }
 
+int64_t reid_pair_dist_tc_workspace_bytes(int m, int n, int d, int same) {
+  return pair_dist_tc_workspace_bytes(m, n, d, same);
+}
+
+int reid_pair_dist_tc(const float* x, int64_t ldx, int m, const float* y, int64_t ldy, int n, int d, void* workspace,
+                      int64_t workspace_bytes, float* out, int64_t ld_out, void* stream) {
+  ENTER();
+  REID_REQUIRE(m >= 0 && n >= 0 && d >= 1 && ldx >= d && ldy >= d && ld_out >= n, "pair_dist_tc: bad shape m=%d n=%d d=%d",
+               m, n, d);
+  return launch_pair_dist_tc(x, ldx, m, y, ldy, n, d, workspace, workspace_bytes, out, ld_out, S(stream));
+}
+
 int reid_hard_mine(const float* dist, int64_t ld, int m, int n, const int64_t* lab_r, const int64_t* lab_c,
                    int skip_diag, float* dist_ap, float* dist_an, int64_t* p_ind, int64_t* n_ind, void* stream) {
   ENTER();
@@ -677,20 +690,21 @@ int reid_stream_group_gather(const float* panel, int64_t ld, int rows, int c0, i
 
 int reid_stream_group_sort(int nq, const int32_t* glo, const int32_t* glen, const int64_t* goff, const int32_t* pid_list,
                            const float* gd, const int64_t* q_cam, const int64_t* g_cam, uint64_t* mkeys, int32_t* nmatch,
-                           int32_t* overflow, void* stream) {
+                           int32_t* overflow, int group_max, void* stream) {
   ENTER();
   REID_REQUIRE(nq >= 0, "stream_group_sort: bad shape");
   return launch_stream_group_sort(nq, glo, glen, LL(goff), pid_list, gd, LL(q_cam), LL(g_cam),
-                                  reinterpret_cast<unsigned long long*>(mkeys), nmatch, overflow, S(stream));
+                                  reinterpret_cast<unsigned long long*>(mkeys), nmatch, overflow, group_max,
+                                  S(stream));
 }
 
 int reid_stream_count_panel(const float* panel, int64_t ld, int rows, int c0, int c1, const int64_t* goff,
-                            const uint64_t* mkeys, const int32_t* nmatch, int32_t* bins, void* stream) {
+                            const uint64_t* mkeys, const int32_t* nmatch, int32_t* bins, int group_max, void* stream) {
   ENTER();
   REID_REQUIRE(rows >= 0 && c0 >= 0 && c1 >= c0 && ld >= c1 - c0 && ld % 4 == 0, "stream_count_panel: bad panel");
   REID_REQUIRE(((uintptr_t)panel & 15) == 0, "stream_count_panel: panel must be 16-byte aligned");
   return launch_stream_count_panel(panel, ld, rows, c0, c1, LL(goff), reinterpret_cast<const unsigned long long*>(mkeys),
-                                   nmatch, bins, S(stream));
+                                   nmatch, bins, group_max, S(stream));
 }
 
 int reid_stream_score(int nq, const int32_t* glen, const int64_t* goff, const uint64_t* mkeys, const int32_t* nmatch,

@@ -70,17 +70,17 @@ int launch_rr_prepare(int nq, int q0, int q_stride, const int* glo, const int* g
                       const int* list, const float* gd, const long long* q_cam, const long long* g_cam,
                       const int* rowmax_key, float c1, float c2, int cap_o, const int* ocol, const __half* ot,
                       const int* ocnt, unsigned long long* gkey, unsigned char* gjunk, unsigned long long* mk,
-                      float* thrA, float* thrB, int* nmatch, int* overflow, cudaStream_t s);
+                      float* thrA, float* thrB, int* nmatch, int* overflow, int group_max, cudaStream_t s);
 int launch_count_panel_rr(const float* panel, long long ld, int rows, int c0, int c1, const long long* goff,
                           const unsigned long long* mk, const float* thrA, const float* thrB, const int* nmatch,
-                          int* bins, cudaStream_t s);
+                          int* bins, int group_max, cudaStream_t s);
 int launch_score_counts_rr(int nq, int q0, int q_stride, const int* glo, const int* glen, const long long* goff,
                            const int* list, const float* gd, const unsigned long long* gkey, const unsigned char* gjunk,
                            const unsigned long long* mk, const float* thrA, const float* thrB, const int* nmatch,
                            const int* bins, int cap_o, const int* ocol, const __half* ot, const float* od,
                            const int* ocnt, const long long* q_pid, const long long* g_pid, const int* rowmax_key,
                            float c1, float c2, int max_rank, double* ap, int* first_hit, int* cmc_hist, int* n_valid,
-                           cudaStream_t s);
+                           int group_max, cudaStream_t s);
 int launch_rr_topk(int nq, int q0, int q_stride, const int* tidx, const float* tval, int Kd, int g, int cap_o,
                    const int* ocol, const __half* ot, const float* od, const int* ocnt, const int* rowmax_key, float c1,
                    float c2, int K, int* out_idx, float* out_val, int* ambiguous, cudaStream_t s);
@@ -163,6 +163,9 @@ int launch_transpose_add(const float* src, int n, long long ld_src, float* dst, 
                          cudaStream_t s);
 
 // train.cu
+long long pair_dist_tc_workspace_bytes(int m, int n, int d, int same);
+int launch_pair_dist_tc(const float* X, long long ldx, int m, const float* Y, long long ldy, int n, int d,
+                        void* workspace, long long ws_bytes, float* out, long long ldo, cudaStream_t s);
 int launch_pair_dist(const float* X, long long ldx, int m, const float* Y, long long ldy, int n, int d, float* out,
                      long long ldo, cudaStream_t s);
 int launch_hard_mine(const float* D, long long ld, int m, int n, const int64_t* lab_r, const int64_t* lab_c,
@@ -185,9 +188,11 @@ int launch_stream_group_gather(const float* panel, long long ld, int rows, int c
                                const int* glen, const long long* goff, const int* list, float* gd, cudaStream_t s);
 int launch_stream_group_sort(int nq, const int* glo, const int* glen, const long long* goff, const int* list,
                              const float* gd, const long long* q_cam, const long long* g_cam,
-                             unsigned long long* mkeys, int* nmatch, int* overflow, cudaStream_t s);
+                             unsigned long long* mkeys, int* nmatch, int* overflow, int group_max, cudaStream_t s);
 int launch_stream_count_panel(const float* panel, long long ld, int rows, int c0, int c1, const long long* goff,
-                              const unsigned long long* mkeys, const int* nmatch, int* bins, cudaStream_t s);
+                              const unsigned long long* mkeys, const int* nmatch, int* bins, int group_max,
+                              cudaStream_t s);
+int stream_group_cap(int group_max);   // shared-memory entries per query for a longest identity group: 2^k in [1024, 8192]
 int launch_stream_score(int nq, const int* glen, const long long* goff, const unsigned long long* mkeys,
                         const int* nmatch, const int* bins, int max_rank, double* ap, int* first_hit, int* cmc_hist,
                         int* n_valid, cudaStream_t s);

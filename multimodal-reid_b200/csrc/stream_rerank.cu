@@ -215,7 +215,9 @@ int launch_list_gather_sorted(const float* panel, long long ld, int rows, int c0
 // ---------------------------------------------------------------------------------------------
 // per-query preparation of the counting sweep
 // ---------------------------------------------------------------------------------------------
-constexpr int RR_CAP = 1024;       // same-identity gallery columns per query (as stream_score.cu)
+// same-identity gallery columns per query: shared-memory arrays of stream_group_cap(longest group) entries, 1 024 ... 8 192
+// (as stream_score.cu)
+constexpr int RR_CAP_MAX = 8192;
 
 // overlap value of gallery column `col` from the query's sorted target list (0 when the query does not touch it)
 __device__ __forceinline__ __half rr_overlap(const int* __restrict__ oc, const __half* __restrict__ ot, int n, int col) {
@@ -252,15 +254,16 @@ rr_prepare_kernel(int nq, int q0, int q_stride, const int* __restrict__ glo, con
                   const int* __restrict__ rowmax_key, float c1, float c2, int cap_o, const int* __restrict__ ocol,
                   const __half* __restrict__ ot, const int* __restrict__ ocnt, unsigned long long* __restrict__ gkey,
                   unsigned char* __restrict__ gjunk, unsigned long long* __restrict__ mk, float* __restrict__ thrA,
-                  float* __restrict__ thrB, int* __restrict__ nmatch, int* __restrict__ overflow) {
-  __shared__ unsigned long long sk[RR_CAP];
+                  float* __restrict__ thrB, int* __restrict__ nmatch, int* __restrict__ overflow, int cap) {
+  extern __shared__ __align__(16) unsigned char rr_smem[];
+  unsigned long long* sk = reinterpret_cast<unsigned long long*>(rr_smem);            // [cap]
   __shared__ int s_p;
   const int qi = blockIdx.x, tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
   const int lo = glo[qi], len = glen[qi];
   const long long off = goff[qi];
   const int no = ocnt[qi];
-  if (len > RR_CAP || no < 0) {
-    if (tid == 0) { if (len > RR_CAP) atomicMax(overflow, len); nmatch[qi] = 0; }
+  if (len > cap || no < 0) {
+    if (tid == 0) { if (len > cap) atomicMax(overflow, len); nmatch[qi] = 0; }
     return;
   }
   if (tid == 0) s_p = 0;
@@ -311,10 +314,12 @@ __global__ void __launch_bounds__(256)
 count_panel_rr_kernel(const float* __restrict__ panel, long long ld, int rows, int c0, int c1,
                       const long long* __restrict__ goff, const unsigned long long* __restrict__ mk,
                       const float* __restrict__ thrA, const float* __restrict__ thrB, const int* __restrict__ nmatch,
-                      int* __restrict__ bins) {
-  __shared__ unsigned long long sk[RR_CAP];
-  __shared__ float sA[RR_CAP], sB[RR_CAP];
-  __shared__ int hist[RR_CAP];
+                      int* __restrict__ bins, int cap) {
+  extern __shared__ __align__(16) unsigned char rr_smem[];
+  unsigned long long* sk = reinterpret_cast<unsigned long long*>(rr_smem);            // [cap] each
+  float* sA = reinterpret_cast<float*>(rr_smem + (size_t)cap * 8);
+  float* sB = sA + cap;
+  int* hist = reinterpret_cast<int*>(sB + cap);
   __shared__ int cells[RC_NB];
   const int row = blockIdx.x, tid = threadIdx.x;
   const int P = nmatch[row];
@@ -393,10 +398,12 @@ score_counts_rr_kernel(int nq, int q0, int q_stride, const int* __restrict__ glo
                        const float* __restrict__ od, const int* __restrict__ ocnt, const long long* __restrict__ q_pid,
                        const long long* __restrict__ g_pid, const int* __restrict__ rowmax_key, float c1, float c2,
                        int max_rank, double* __restrict__ ap, int* __restrict__ first_hit, int* __restrict__ cmc_hist,
-                       int* __restrict__ n_valid) {
-  __shared__ unsigned long long sk[RR_CAP];
-  __shared__ float sA[RR_CAP], sB[RR_CAP];
-  __shared__ int corr[RR_CAP];
+                       int* __restrict__ n_valid, int cap) {
+  extern __shared__ __align__(16) unsigned char rr_smem[];
+  unsigned long long* sk = reinterpret_cast<unsigned long long*>(rr_smem);            // [cap] each
+  float* sA = reinterpret_cast<float*>(rr_smem + (size_t)cap * 8);
+  float* sB = sA + cap;
+  int* corr = reinterpret_cast<int*>(sB + cap);
   const int qi = blockIdx.x, tid = threadIdx.x;
   const int P = nmatch[qi];
   if (P == 0) {                                          // identity absent from the gallery: skipped (evaluate.py:61-63)
@@ -511,19 +518,28 @@ int launch_rr_prepare(int nq, int q0, int q_stride, const int* glo, const int* g
                       const int* list, const float* gd, const long long* q_cam, const long long* g_cam,
                       const int* rowmax_key, float c1, float c2, int cap_o, const int* ocol, const __half* ot,
                       const int* ocnt, unsigned long long* gkey, unsigned char* gjunk, unsigned long long* mk,
-                      float* thrA, float* thrB, int* nmatch, int* overflow, cudaStream_t s) {
+                      float* thrA, float* thrB, int* nmatch, int* overflow, int group_max, cudaStream_t s) {
   if (nq == 0) return REID_OK;
-  rr_prepare_kernel<<<nq, 256, 0, s>>>(nq, q0, q_stride, glo, glen, goff, list, gd, q_cam, g_cam, rowmax_key, c1, c2, cap_o,
-                                      ocol, ot, ocnt, gkey, gjunk, mk, thrA, thrB, nmatch, overflow);
+  REID_REQUIRE(group_max <= RR_CAP_MAX, "rr_prepare: an identity has %d gallery samples; at most %d per query", group_max,
+               RR_CAP_MAX);
+  const int cap = stream_group_cap(group_max);
+  const size_t smem = (size_t)cap * 8;
+  REID_CUDA(cudaFuncSetAttribute(rr_prepare_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  rr_prepare_kernel<<<nq, 256, smem, s>>>(nq, q0, q_stride, glo, glen, goff, list, gd, q_cam, g_cam, rowmax_key, c1, c2,
+                                         cap_o, ocol, ot, ocnt, gkey, gjunk, mk, thrA, thrB, nmatch, overflow, cap);
   return check_launch("rr_prepare_kernel");
 }
 
 int launch_count_panel_rr(const float* panel, long long ld, int rows, int c0, int c1, const long long* goff,
                           const unsigned long long* mk, const float* thrA, const float* thrB, const int* nmatch,
-                          int* bins, cudaStream_t s) {
+                          int* bins, int group_max, cudaStream_t s) {
   if (rows == 0 || c1 <= c0) return REID_OK;
   REID_REQUIRE(ld % 4 == 0 && ((uintptr_t)panel & 15) == 0, "count_panel_rr: panel rows must be 16-byte aligned");
-  count_panel_rr_kernel<<<rows, 256, 0, s>>>(panel, ld, rows, c0, c1, goff, mk, thrA, thrB, nmatch, bins);
+  REID_REQUIRE(group_max <= RR_CAP_MAX, "count_panel_rr: group_max=%d exceeds %d", group_max, RR_CAP_MAX);
+  const int cap = stream_group_cap(group_max);
+  const size_t smem = (size_t)cap * 20;
+  REID_CUDA(cudaFuncSetAttribute(count_panel_rr_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  count_panel_rr_kernel<<<rows, 256, smem, s>>>(panel, ld, rows, c0, c1, goff, mk, thrA, thrB, nmatch, bins, cap);
   return check_launch("count_panel_rr_kernel");
 }
 
@@ -533,11 +549,15 @@ int launch_score_counts_rr(int nq, int q0, int q_stride, const int* glo, const i
                            const int* bins, int cap_o, const int* ocol, const __half* ot, const float* od,
                            const int* ocnt, const long long* q_pid, const long long* g_pid, const int* rowmax_key,
                            float c1, float c2, int max_rank, double* ap, int* first_hit, int* cmc_hist, int* n_valid,
-                           cudaStream_t s) {
+                           int group_max, cudaStream_t s) {
   if (nq == 0) return REID_OK;
-  score_counts_rr_kernel<<<nq, 128, 0, s>>>(nq, q0, q_stride, glo, glen, goff, list, gd, gkey, gjunk, mk, thrA, thrB,
-                                           nmatch, bins, cap_o, ocol, ot, od, ocnt, q_pid, g_pid, rowmax_key, c1, c2,
-                                           max_rank, ap, first_hit, cmc_hist, n_valid);
+  REID_REQUIRE(group_max <= RR_CAP_MAX, "score_counts_rr: group_max=%d exceeds %d", group_max, RR_CAP_MAX);
+  const int cap = stream_group_cap(group_max);
+  const size_t smem = (size_t)cap * 20;
+  REID_CUDA(cudaFuncSetAttribute(score_counts_rr_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  score_counts_rr_kernel<<<nq, 128, smem, s>>>(nq, q0, q_stride, glo, glen, goff, list, gd, gkey, gjunk, mk, thrA, thrB,
+                                              nmatch, bins, cap_o, ocol, ot, od, ocnt, q_pid, g_pid, rowmax_key, c1, c2,
+                                              max_rank, ap, first_hit, cmc_hist, n_valid, cap);
   return check_launch("score_counts_rr_kernel");
 }
 

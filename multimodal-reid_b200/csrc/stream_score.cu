@@ -1,9 +1,10 @@
 // CMC / mAP for a q x g problem whose distance matrix is never materialised (evaluate.py:40-88 semantics).
-// The matrix is produced panel by panel ([row chunk] x [column block]) by the contraction, twice:
-//   sweep 1  group_gather_kernel   picks out the distances of every query's same-identity gallery columns (its matches
-//                                  and its junk = same identity AND same camera, evaluate.py:53-55)
+// The matrix is produced panel by panel ([row chunk] x [column block]) by the contraction:
+//   before   (host layer)          the distances of every query's same-identity gallery columns (its matches and its junk
+//                                  = same identity AND same camera, evaluate.py:53-55) contracted as gathered pairs;
+//            group_gather_kernel   the alternative: picked out of the panels of a first sweep (the re-ranked path does)
 //            group_sort_kernel     per query: match keys (distance, column) sorted ascending, junk keys behind them
-//   sweep 2  count_panel_kernel    streams each panel row once: an entry closer than the query's farthest match is binned
+//   sweep    count_panel_kernel    streams each panel row once: an entry closer than the query's farthest match is binned
 //                                  by the number of match keys below it (binary search over a handful of keys in shared
 //                                  memory); bins are summed over the column blocks in global memory
 //   finally  score_counts_kernel   prefix sums give every match's position among ALL entries; the junk in front of it is
@@ -16,7 +17,14 @@
 
 namespace reid {
 
-constexpr int SG_CAP = 1024;      // same-identity gallery columns per query held in shared memory
+// Same-identity gallery columns of one query are held in shared memory: the arrays are sized by the caller's longest
+// identity group, rounded up to a power of two between 1 024 (the usual case: same footprint as a static array) and 8 192.
+constexpr int SG_CAP_MIN = 1024, SG_CAP_MAX = 8192;
+int stream_group_cap(int group_max) {
+  int cap = SG_CAP_MIN;
+  while (cap < group_max && cap < SG_CAP_MAX) cap <<= 1;
+  return cap;
+}
 
 __global__ void __launch_bounds__(256)
 group_lookup_kernel(const long long* __restrict__ q_pid, int nq, const unsigned long long* __restrict__ keys,
@@ -54,13 +62,14 @@ __global__ void __launch_bounds__(256)
 group_sort_kernel(int nq, const int* __restrict__ glo, const int* __restrict__ glen,
                   const long long* __restrict__ goff, const int* __restrict__ list, const float* __restrict__ gd,
                   const long long* __restrict__ q_cam, const long long* __restrict__ g_cam,
-                  unsigned long long* __restrict__ mkeys, int* __restrict__ nmatch, int* __restrict__ overflow) {
-  __shared__ unsigned long long sk[SG_CAP];
+                  unsigned long long* __restrict__ mkeys, int* __restrict__ nmatch, int* __restrict__ overflow, int cap) {
+  extern __shared__ __align__(16) unsigned char sg_smem[];
+  unsigned long long* sk = reinterpret_cast<unsigned long long*>(sg_smem);            // [cap]
   __shared__ int s_p, s_j;
   const int qi = blockIdx.x, tid = threadIdx.x;
   const int lo = glo[qi], len = glen[qi];
   const long long off = goff[qi];
-  if (len > SG_CAP) {
+  if (len > cap) {
     if (tid == 0) { atomicMax(overflow, len); nmatch[qi] = 0; }
     return;
   }
@@ -106,9 +115,10 @@ __device__ __forceinline__ int sg_cell(float d, float scale) {
 __global__ void __launch_bounds__(256)
 count_panel_kernel(const float* __restrict__ panel, long long ld, int rows, int c0, int c1,
                    const long long* __restrict__ goff, const unsigned long long* __restrict__ mkeys,
-                   const int* __restrict__ nmatch, int* __restrict__ bins) {
-  __shared__ unsigned long long sk[SG_CAP];
-  __shared__ int hist[SG_CAP];
+                   const int* __restrict__ nmatch, int* __restrict__ bins, int cap) {
+  extern __shared__ __align__(16) unsigned char sg_smem[];
+  unsigned long long* sk = reinterpret_cast<unsigned long long*>(sg_smem);            // [cap]
+  int* hist = reinterpret_cast<int*>(sg_smem + (size_t)cap * 8);                      // [cap]
   __shared__ int cells[SG_NB];
   const int row = blockIdx.x, tid = threadIdx.x;
   const int P = nmatch[row];
@@ -225,16 +235,26 @@ int launch_stream_group_gather(const float* panel, long long ld, int rows, int c
 
 int launch_stream_group_sort(int nq, const int* glo, const int* glen, const long long* goff, const int* list,
                              const float* gd, const long long* q_cam, const long long* g_cam,
-                             unsigned long long* mkeys, int* nmatch, int* overflow, cudaStream_t s) {
+                             unsigned long long* mkeys, int* nmatch, int* overflow, int group_max, cudaStream_t s) {
   if (nq == 0) return REID_OK;
-  group_sort_kernel<<<nq, 256, 0, s>>>(nq, glo, glen, goff, list, gd, q_cam, g_cam, mkeys, nmatch, overflow);
+  REID_REQUIRE(group_max <= SG_CAP_MAX, "stream_group_sort: an identity has %d gallery samples; at most %d per query",
+               group_max, SG_CAP_MAX);
+  const int cap = stream_group_cap(group_max);
+  const size_t smem = (size_t)cap * 8;
+  REID_CUDA(cudaFuncSetAttribute(group_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  group_sort_kernel<<<nq, 256, smem, s>>>(nq, glo, glen, goff, list, gd, q_cam, g_cam, mkeys, nmatch, overflow, cap);
   return check_launch("group_sort_kernel");
 }
 
 int launch_stream_count_panel(const float* panel, long long ld, int rows, int c0, int c1, const long long* goff,
-                              const unsigned long long* mkeys, const int* nmatch, int* bins, cudaStream_t s) {
+                              const unsigned long long* mkeys, const int* nmatch, int* bins, int group_max,
+                              cudaStream_t s) {
   if (rows == 0 || c1 <= c0) return REID_OK;
-  count_panel_kernel<<<rows, 256, 0, s>>>(panel, ld, rows, c0, c1, goff, mkeys, nmatch, bins);
+  REID_REQUIRE(group_max <= SG_CAP_MAX, "stream_count_panel: group_max=%d exceeds %d", group_max, SG_CAP_MAX);
+  const int cap = stream_group_cap(group_max);
+  const size_t smem = (size_t)cap * 12;
+  REID_CUDA(cudaFuncSetAttribute(count_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  count_panel_kernel<<<rows, 256, smem, s>>>(panel, ld, rows, c0, c1, goff, mkeys, nmatch, bins, cap);
   return check_launch("count_panel_kernel");
 }
 

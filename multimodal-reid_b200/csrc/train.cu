@@ -266,6 +266,100 @@ triplet_gy_kernel(const float* __restrict__ X, long long ldx, int m, const float
   if (nhit > 0 || !wrote) flush();
 }
 
+// ---------------------------------------------------------------------------------------------
+// Large batches (B >= ~1 024, cross-batch memories): the forward is a real GEMM (6.4 GFLOP at 1 024 x 1 024 x 3 072), so
+// it goes through the evaluation path's tensor-core contraction -- rows split into fp16 hi/lo operands (prep.cu; one
+// power-of-two scale per operand from its measured maximum), dist_tc2_kernel (x.y to ~2^-22 |x||y|, float32
+// accumulation; upper triangle + mirrored stores when x and y are the same rows), then the clamped square root in place.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+sqrt_clamp_kernel(float* __restrict__ D, long long ld, int m, int n4, int n, float floor_v) {
+  const long long total = (long long)m * n4;
+  for (long long i = blockIdx.x * 256ll + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
+    const int r = (int)(i / n4), c = (int)(i % n4) * 4;
+    float4* p = reinterpret_cast<float4*>(D + (long long)r * ld + c);        // pitch % 4 == 0: the pad columns exist
+    float4 v = *p;
+    v.x = __fsqrt_rn(fmaxf(v.x, floor_v));
+    v.y = __fsqrt_rn(fmaxf(v.y, floor_v));
+    v.z = __fsqrt_rn(fmaxf(v.z, floor_v));
+    v.w = __fsqrt_rn(fmaxf(v.w, floor_v));
+    if (c + 3 < n) {
+      *p = v;
+    } else {                                                                 // ragged last group: pad columns untouched
+      float* q = reinterpret_cast<float*>(p);
+      q[0] = v.x;
+      if (c + 1 < n) q[1] = v.y;
+      if (c + 2 < n) q[2] = v.z;
+    }
+  }
+}
+
+namespace {
+struct PairTcPlan {
+  int dp;
+  bool same;
+  float *x32a, *sqa, *nrma, *x32b, *sqb, *nrmb;
+  __half *hia, *loa, *hib, *lob;
+  uint32_t *amaxa, *amaxb;
+};
+size_t pair_tc_carve(PairTcPlan& p, unsigned char* base, int m, int n, int d, bool same) {
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    unsigned char* at = base ? base + off : nullptr;
+    off = (off + bytes + 255) & ~(size_t)255;
+    return at;
+  };
+  p.dp = padded_width(d);
+  p.same = same;
+  p.x32a = reinterpret_cast<float*>(take((size_t)m * p.dp * 4));
+  p.hia = reinterpret_cast<__half*>(take((size_t)m * p.dp * 2));
+  p.loa = reinterpret_cast<__half*>(take((size_t)m * p.dp * 2));
+  p.sqa = reinterpret_cast<float*>(take((size_t)m * 4));
+  p.nrma = reinterpret_cast<float*>(take((size_t)m * 4));
+  p.amaxa = reinterpret_cast<uint32_t*>(take(16));
+  if (same) {
+    p.x32b = p.x32a; p.hib = p.hia; p.lob = p.loa; p.sqb = p.sqa; p.nrmb = p.nrma; p.amaxb = p.amaxa;
+  } else {
+    p.x32b = reinterpret_cast<float*>(take((size_t)n * p.dp * 4));
+    p.hib = reinterpret_cast<__half*>(take((size_t)n * p.dp * 2));
+    p.lob = reinterpret_cast<__half*>(take((size_t)n * p.dp * 2));
+    p.sqb = reinterpret_cast<float*>(take((size_t)n * 4));
+    p.nrmb = reinterpret_cast<float*>(take((size_t)n * 4));
+    p.amaxb = reinterpret_cast<uint32_t*>(take(16));
+  }
+  return off;
+}
+}  // namespace
+
+long long pair_dist_tc_workspace_bytes(int m, int n, int d, int same) {
+  if (m < 0 || n < 0 || d < 1) return -1;
+  PairTcPlan p{};
+  return (long long)pair_tc_carve(p, nullptr, m, n, d, same != 0);
+}
+
+int launch_pair_dist_tc(const float* X, long long ldx, int m, const float* Y, long long ldy, int n, int d,
+                        void* workspace, long long ws_bytes, float* out, long long ldo, cudaStream_t s) {
+  if (m == 0 || n == 0) return REID_OK;
+  const bool same = X == Y && ldx == ldy && m == n;
+  PairTcPlan p{};
+  const size_t need = pair_tc_carve(p, static_cast<unsigned char*>(workspace), m, n, d, same);
+  REID_REQUIRE(workspace && ((uintptr_t)workspace & 255) == 0 && (size_t)ws_bytes >= need,
+               "pair_dist_tc: workspace of %lld B (256-byte aligned) needed, got %lld", (long long)need, ws_bytes);
+  REID_REQUIRE(ldo % 4 == 0 && ((uintptr_t)out & 15) == 0, "pair_dist_tc: output rows must be 16-byte aligned (pitch %lld)",
+               ldo);
+  int rc;
+  if ((rc = launch_prep(X, m, d, ldx, 0, p.x32a, p.hia, p.loa, p.dp, p.sqa, p.nrma, p.amaxa, s))) return rc;
+  if (!same && (rc = launch_prep(Y, n, d, ldy, 0, p.x32b, p.hib, p.lob, p.dp, p.sqb, p.nrmb, p.amaxb, s))) return rc;
+  if ((rc = launch_dist_tc(p.hia, p.loa, p.dp, p.sqa, p.amaxa, m, p.hib, p.lob, p.dp, p.sqb, p.amaxb, n, p.dp, 0, out, ldo,
+                           nullptr, nullptr, same ? 1 : 0, s))) return rc;
+  const int n4 = (n + 3) / 4;
+  const long long total = (long long)m * n4;
+  const long long want = (total + 255) / 256;
+  const int blocks = (int)(want < 148 * 8 ? want : 148 * 8);
+  sqrt_clamp_kernel<<<blocks, 256, 0, s>>>(out, ldo, m, n4, n, 1e-12f);
+  return check_launch("sqrt_clamp_kernel");
+}
+
 int launch_pair_dist(const float* X, long long ldx, int m, const float* Y, long long ldy, int n, int d, float* out,
                      long long ldo, cudaStream_t s) {
   if (m == 0 || n == 0) return REID_OK;

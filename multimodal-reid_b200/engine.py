@@ -23,6 +23,7 @@ from . import fabric as _fabric
 METRIC_SQEUCLIDEAN = 0
 METRIC_ARCCOS = 1
 ENGINES = {"auto": 0, "simt": 1, "tcgen05": 2}
+GROUP_MAX = 8192             # same-identity gallery samples per query the streamed scorers hold (csrc/stream_score.cu)
 
 
 def _ptr(t):
@@ -558,14 +559,40 @@ class Engine:
             self.symmetric = sym
         return out_i, out_v
 
+    def pair_distances(self, A: Features, B: Features, ri: torch.Tensor, ci: torch.Tensor,
+                       metric: int = METRIC_SQEUCLIDEAN, chunk: int = 8192) -> torch.Tensor:
+        """D[ri[p], ci[p]] for a list of (row of A, row of B) pairs with exactly the panels' arithmetic: the operand rows
+        are gathered and contracted `chunk` x `chunk` on the tensor cores, the diagonal kept (an entry's value does not
+        depend on the tile it is computed in).  ~1/chunk of each contraction is used, which is still cheap next to a
+        panel sweep: 2 M pairs at d = 512 are 244 contractions of 0.15 ms."""
+        npairs = int(ri.shape[0])
+        out = self._empty((max(npairs, 1),), torch.float32)
+        none = A.x32[:0]                 # the float32 rows are not operands of the tensor-core contraction
+        simt = self.engine == ENGINES["simt"]
+        sym = self.symmetric
+        self.symmetric = False
+        try:
+            for a in range(0, npairs, chunk):
+                b = min(npairs, a + chunk)
+                ra, cb = ri[a:b], ci[a:b]
+                fa = Features(A.x32[ra] if simt else none, A.hi[ra], A.lo[ra], A.sq[ra], A.nrm[ra], A.amax, A.d)
+                fb = Features(B.x32[cb] if simt else none, B.hi[cb], B.lo[cb], B.sq[cb], B.nrm[cb], B.amax, B.d)
+                Dm, _ = self.dist(fa, fb, metric)
+                out[a:b] = torch.diagonal(Dm[:, : b - a])
+                del Dm, fa, fb
+        finally:
+            self.symmetric = sym
+        return out[:npairs]
+
     def evaluate_streamed(self, Q: Features, G: Features, q_pids, g_pids, q_cams, g_cams, max_rank: int = 50,
                           K: int = 0, metric: int = METRIC_SQEUCLIDEAN, rows_per_pass: int = 16384,
                           cols_per_pass: int = 65536, q_total: int | None = None):
         """evaluate.py:40-88 (CMC / mAP with same-id same-camera junk removed) for a q x g problem too large to hold:
-        the contraction is swept twice over [rows_per_pass x cols_per_pass] panels (stream_score.cu) — sweep 1 collects the
-        distances of every query's same-identity columns (and, with K > 0, the exact top-K lists of retrieve_topk on
-        the same panels), sweep 2 counts the entries in front of every match.  Q / q_pids / q_cams are this rank's
-        queries.  Returns ((cmc, mAP, n_valid, ap, first_hit), (idx, dist) or None)."""
+        the distances of every query's same-identity columns are contracted as gathered pairs first (pair_distances) and
+        sorted into match keys; then the contraction is swept ONCE over [rows_per_pass x cols_per_pass] panels
+        (stream_score.cu), each panel feeding the exact top-K selection of retrieve_topk (K > 0) and the count of the
+        entries in front of every match.  Q / q_pids / q_cams are this rank's queries.
+        Returns ((cmc, mAP, n_valid, ap, first_hit), (idx, dist) or None)."""
         nq, g = Q.n, G.n
         keys, start, lst, T = self.pid_index(g_pids)
         glo = self._empty((nq,), torch.int32)
@@ -573,36 +600,40 @@ class Engine:
         _lib.call("reid_stream_group_lookup", _ptr(q_pids), nq, _ptr(keys), _ptr(start), T, _ptr(glo), _ptr(glen), _stream())
         goff = self._zeros((nq + 1,), torch.int64)
         goff[1:] = torch.cumsum(glen, 0, dtype=torch.int64)
-        # the evaluation's one host read before the sweeps: buffer size, and the largest identity group -- refused here,
-        # not after two full contraction sweeps
+        # the evaluation's one host read before the sweep: buffer size, and the largest identity group -- refused here,
+        # not after a full contraction sweep
         sizes = torch.stack([goff[-1], glen.max().to(torch.int64) if nq else goff[-1]]).tolist()
         total, longest = int(sizes[0]), int(sizes[1])
-        if longest > 1024:
-            raise _lib.ReidError(f"an identity has {longest} gallery samples; the streamed scorer holds at most 1024 per query")
-        gd = self._empty((max(total, 1),), torch.float32)
+        if longest > GROUP_MAX:
+            raise _lib.ReidError(f"an identity has {longest} gallery samples; the streamed scorer holds at most "
+                                 f"{GROUP_MAX} per query")
         mkeys = self._empty((max(total, 1),), torch.int64)
         bins = self._zeros((max(total, 1),), torch.int32)
         nmatch = self._empty((nq,), torch.int32)
         overflow = self._zeros((1,), torch.int32)
-
-        def gather(D, r0, m, c0, c1):
-            _lib.call("reid_stream_group_gather", _ptr(D), D.stride(0), m, c0, c1, _ptr(glo[r0:]), _ptr(glen[r0:]),
-                      _ptr(goff[r0:]), _ptr(lst), _ptr(gd), _stream())
+        # The distances of every query's same-identity columns are contracted directly (gathered operand rows, the
+        # panels' arithmetic), so the sorted match keys exist BEFORE the sweep and ONE sweep over the panels does the
+        # top-K selection and the counting (the first version swept twice: gather, then count).
+        with self.span("pairs"):
+            if total:
+                qi = torch.repeat_interleave(torch.arange(nq, device=self.device), glen.long(), output_size=total)
+                pos = torch.arange(total, device=self.device) - goff[:-1][qi]
+                gd = self.pair_distances(Q, G, qi, lst[glo.long()[qi] + pos].long(), metric)
+            else:
+                gd = self._empty((1,), torch.float32)
+            _lib.call("reid_stream_group_sort", nq, _ptr(glo), _ptr(glen), _ptr(goff), _ptr(lst), _ptr(gd), _ptr(q_cams),
+                      _ptr(g_cams), _ptr(mkeys), _ptr(nmatch), _ptr(overflow), longest, _stream())
 
         def count(D, r0, m, c0, c1):
             _lib.call("reid_stream_count_panel", _ptr(D), D.stride(0), m, c0, c1, _ptr(goff[r0:]), _ptr(mkeys),
-                      _ptr(nmatch[r0:]), _ptr(bins), _stream())
+                      _ptr(nmatch[r0:]), _ptr(bins), longest, _stream())
 
         top = None
-        with self.span("sweep1"):
+        with self.span("sweep"):
             if K > 0:
-                top = self.retrieve_topk(Q, G, K, metric, rows_per_pass, cols_per_pass, on_panel=gather)
+                top = self.retrieve_topk(Q, G, K, metric, rows_per_pass, cols_per_pass, on_panel=count)
             else:
-                self._sweep(Q, G, metric, rows_per_pass, cols_per_pass, gather)
-            _lib.call("reid_stream_group_sort", nq, _ptr(glo), _ptr(glen), _ptr(goff), _ptr(lst), _ptr(gd), _ptr(q_cams),
-                      _ptr(g_cams), _ptr(mkeys), _ptr(nmatch), _ptr(overflow), _stream())
-        with self.span("sweep2"):
-            self._sweep(Q, G, metric, rows_per_pass, cols_per_pass, count)
+                self._sweep(Q, G, metric, rows_per_pass, cols_per_pass, count)
 
         def launch(ap, first, hist, nvalid):
             _lib.call("reid_stream_score", nq, _ptr(glen), _ptr(goff), _ptr(mkeys), _ptr(nmatch), _ptr(bins), max_rank,
@@ -610,7 +641,8 @@ class Engine:
         res = self._score_common(launch, nq, max_rank, q_total, span="score")
         big = int(overflow.item())
         if big:
-            raise _lib.ReidError(f"an identity has {big} gallery samples; the streamed scorer holds at most 1024 per query")
+            raise _lib.ReidError(f"an identity has {big} gallery samples; the streamed scorer holds at most "
+                                 f"{GROUP_MAX} per query")
         return res, top
 
     def _sweep(self, Q: Features, G: Features, metric: int, rows_per_pass: int, cols_per_pass: int, on_panel):
@@ -644,9 +676,10 @@ class Engine:
           B  reciprocal sets, V weights (distances looked up in the wide lists), k2 expansion, inverted index -- the
              sparse kernels of the materialised path, replicated on every rank                      (reranking.py:51-82)
           C  own queries: ordered float16 Jaccard chain into per-query overlap lists                (reranking.py:84-93)
-          D  q x g sweep 1: top-Kd by raw distance; exact distances of the same-identity and of the overlap columns
-          E  final keys of the special entries, raw-distance thresholds of every match                  (reranking.py:95)
-          F  q x g sweep 2: every entry binned as if untouched; G  corrections, AP / CMC; exact top-k merge
+          D  distances of every query's same-identity columns, contracted as gathered pairs (pair_distances)
+          E  final keys of those entries, raw-distance thresholds of every match                        (reranking.py:95)
+          F  ONE q x g sweep: top-Kd by raw distance, exact distances of the overlap columns, every entry binned as if
+             untouched;  G  corrections by the special entries, AP / CMC; exact top-k merge
         Same arithmetic as the materialised path with the full (non-symmetric) tile schedule: identical results whenever
         `diag["v_misses"]` is 0 (tests/test_gpu_retrieval.py).  Returns ((cmc, mAP, n_valid, ap, first_hit),
         (idx int32 [nq_local, topk], final float32 [nq_local, topk]), diag)."""
@@ -757,18 +790,18 @@ class Engine:
         goff[1:] = torch.cumsum(glen[:nq], 0, dtype=torch.int64)
         sizes = torch.stack([goff[-1], glen[:nq].max().to(torch.int64) if nq else goff[-1]]).tolist()   # one host read
         total, longest = int(sizes[0]), int(sizes[1])
-        if longest > 1024:
-            raise _lib.ReidError(f"an identity has {longest} gallery samples; the streamed scorer holds at most 1024 per query")
-        gd = self._empty((max(total, 1),), torch.float32)
-
-        def gather(D, r0, m, c0, c1):
-            _lib.call("reid_stream_group_gather", _ptr(D), D.stride(0), m, c0, c1, _ptr(glo[r0:]), _ptr(glen[r0:]),
-                      _ptr(goff[r0:]), _ptr(lst), _ptr(gd), st())
-            _lib.call("reid_stream_list_gather", _ptr(D), D.stride(0), m, c0, c1, cap_o, _ptr(ocol[r0 * cap_o:]),
-                      _ptr(ocnt[r0:]), _ptr(od[r0 * cap_o:]), st())
-
-        with self.span("sweep1"):
-            tidx, tval = self.retrieve_topk(Qf, Gf, Kd, METRIC_SQEUCLIDEAN, rows_per_pass, cols_per_pass, on_panel=gather)
+        if longest > GROUP_MAX:
+            raise _lib.ReidError(f"an identity has {longest} gallery samples; the streamed scorer holds at most "
+                                 f"{GROUP_MAX} per query")
+        # the distances of the same-identity columns are contracted as gathered pairs (the panels' bits), so that the match
+        # thresholds exist before the q x g sweep and ONE sweep serves selection, the overlap columns and the counting
+        with self.span("pairs"):
+            if total:
+                qi = torch.repeat_interleave(torch.arange(nq, device=self.device), glen[:nq].long(), output_size=total)
+                pos = torch.arange(total, device=self.device) - goff[:-1][qi]
+                gd = self.pair_distances(Qf, Gf, qi, lst[glo[:nq].long()[qi] + pos].long())
+            else:
+                gd = self._empty((1,), torch.float32)
         # ---- E
         c1 = float(np.float16(1 - lam))
         c2 = float(np.float32(lam))
@@ -782,22 +815,24 @@ class Engine:
         with self.span("rr_prepare"):
             _lib.call("reid_rr_prepare", nq, r, P, _ptr(glo), _ptr(glen), _ptr(goff), _ptr(lst), _ptr(gd), _ptr(q_cams),
                       _ptr(g_cams), _ptr(key), c1, c2, cap_o, _ptr(ocol), _ptr(ot), _ptr(ocnt), _ptr(gkey), _ptr(gjunk),
-                      _ptr(mk), _ptr(thrA), _ptr(thrB), _ptr(nmatch), _ptr(flags[3:]), st())
+                      _ptr(mk), _ptr(thrA), _ptr(thrB), _ptr(nmatch), _ptr(flags[3:]), longest, st())
 
-        # ---- F
-        def count(D, r0, m, c0, c1):
+        # ---- F: the q x g sweep
+        def on_panel(D, r0, m, c0, c1):
+            _lib.call("reid_stream_list_gather", _ptr(D), D.stride(0), m, c0, c1, cap_o, _ptr(ocol[r0 * cap_o:]),
+                      _ptr(ocnt[r0:]), _ptr(od[r0 * cap_o:]), st())
             _lib.call("reid_stream_count_panel_rr", _ptr(D), D.stride(0), m, c0, c1, _ptr(goff[r0:]), _ptr(mk), _ptr(thrA),
-                      _ptr(thrB), _ptr(nmatch[r0:]), _ptr(bins), st())
+                      _ptr(thrB), _ptr(nmatch[r0:]), _ptr(bins), longest, st())
 
-        with self.span("sweep2"):
-            self._sweep(Qf, Gf, METRIC_SQEUCLIDEAN, rows_per_pass, cols_per_pass, count)
+        with self.span("sweep"):
+            tidx, tval = self.retrieve_topk(Qf, Gf, Kd, METRIC_SQEUCLIDEAN, rows_per_pass, cols_per_pass, on_panel=on_panel)
 
         # ---- G
         def launch(ap, first, hist, nvalid):
             _lib.call("reid_stream_score_rr", nq, r, P, _ptr(glo), _ptr(glen), _ptr(goff), _ptr(lst), _ptr(gd), _ptr(gkey),
                       _ptr(gjunk), _ptr(mk), _ptr(thrA), _ptr(thrB), _ptr(nmatch), _ptr(bins), cap_o, _ptr(ocol), _ptr(ot),
                       _ptr(od), _ptr(ocnt), _ptr(q_pids), _ptr(g_pids), _ptr(key), c1, c2, max_rank, _ptr(ap), _ptr(first),
-                      _ptr(hist), _ptr(nvalid), st())
+                      _ptr(hist), _ptr(nvalid), longest, st())
         res = self._score_common(launch, nq, max_rank, q, span="score")
         with self.span("rr_topk"):
             out_i = self._empty((max(nq, 1), topk), torch.int32)
@@ -812,7 +847,7 @@ class Engine:
                 "overlap_overflow": f[2], "group_overflow": f[3], "topk_ambiguous": f[4], "Kw": Kw, "Kd": Kd}
         if f[2] or f[3]:
             raise _lib.ReidError(f"streamed re-ranking: {f[2]} queries touch more than cap_o={cap_o} gallery columns, "
-                                 f"largest identity group {f[3]} (limit 1024)")
+                                 f"largest identity group {f[3]} (limit {GROUP_MAX})")
         if f[0] or f[4]:
             raise _lib.ReidError(f"streamed re-ranking: candidate lists too short for exactness ({f[0]} rows at Kw={Kw}, "
                                  f"{f[4]} queries at Kd={Kd}); raise Kw / Kd")

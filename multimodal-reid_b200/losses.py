@@ -27,6 +27,29 @@ def _labels(t: torch.Tensor, device) -> torch.Tensor:
     return t.to(device=device, dtype=torch.int64).contiguous()
 
 
+TC_MIN_ROWS = 1024          # from this batch size on the forward is a real GEMM: tensor cores (reid_pair_dist_tc)
+
+
+def _pair_dist_forward(xs: torch.Tensor, ys: torch.Tensor, same: bool, s) -> torch.Tensor:
+    """losses.py:14-28 into a fresh [m, n] tensor (a view of a pitched buffer only when n % 4 != 0 on the tensor path).  Batches below TC_MIN_ROWS run the
+    float32 CUDA-core kernel (latency-bound, one launch); larger ones the tcgen05 contraction of the evaluation path.
+    `same`: x and y are the same tensor object (upper triangle + mirrored stores)."""
+    m, d = xs.shape
+    n = ys.shape[0]
+    tc = min(m, n) >= TC_MIN_ROWS
+    ld = (n + 3) // 4 * 4 if tc else n          # the tensor-core store needs 16-byte aligned rows; contiguous otherwise
+    out = torch.empty((m, ld), dtype=torch.float32, device=xs.device)
+    if tc:
+        y_arg = xs if same else ys
+        nbytes = int(_lib.load().reid_pair_dist_tc_workspace_bytes(m, n, d, 1 if same else 0))
+        ws = torch.empty((nbytes,), dtype=torch.uint8, device=xs.device)
+        _lib.call("reid_pair_dist_tc", _ptr(xs), xs.stride(0), m, _ptr(y_arg), y_arg.stride(0), n, d, _ptr(ws), nbytes,
+                  _ptr(out), ld, s)
+    else:
+        _lib.call("reid_pair_dist", _ptr(xs), xs.stride(0), m, _ptr(ys), ys.stride(0), n, d, _ptr(out), ld, s)
+    return out[:, :n]
+
+
 class _PairDist(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, y):
@@ -35,10 +58,8 @@ class _PairDist(torch.autograd.Function):
         n = ys.shape[0]
         if ys.shape[1] != d:
             raise ValueError(f"feature widths differ: {d} vs {ys.shape[1]}")
-        out = torch.empty((m, n), dtype=torch.float32, device=xs.device)
         with torch.cuda.device(xs.device):
-            _lib.call("reid_pair_dist", _ptr(xs), xs.stride(0), m, _ptr(ys), ys.stride(0), n, d, _ptr(out), n,
-                      _stream())
+            out = _pair_dist_forward(xs, ys, x is y, _stream())
         ctx.save_for_backward(xs, ys, out)
         ctx.dtypes = (x.dtype, y.dtype)
         return out
@@ -53,8 +74,8 @@ class _PairDist(torch.autograd.Function):
         gx = torch.empty_like(xs, memory_format=torch.contiguous_format) if need_x else None
         gy = torch.empty_like(ys, memory_format=torch.contiguous_format) if need_y else None
         with torch.cuda.device(xs.device):
-            _lib.call("reid_pair_dist_grad", _ptr(xs), xs.stride(0), m, _ptr(ys), ys.stride(0), n, d, _ptr(dist), n,
-                      _ptr(G), n, _ptr(gx), d, _ptr(gy), d, 0, _stream())
+            _lib.call("reid_pair_dist_grad", _ptr(xs), xs.stride(0), m, _ptr(ys), ys.stride(0), n, d, _ptr(dist),
+                      dist.stride(0), _ptr(G), n, _ptr(gx), d, _ptr(gy), d, 0, _stream())
         gx = gx.to(ctx.dtypes[0]) if gx is not None else None
         gy = gy.to(ctx.dtypes[1]) if gy is not None else None
         return gx, gy
@@ -119,15 +140,14 @@ class _MinedPairs(torch.autograd.Function):
         m, d = xs.shape
         n = ys.shape[0]
         dev = xs.device
-        dist = torch.empty((m, n), dtype=torch.float32, device=dev)
         ap = torch.empty(m, dtype=torch.float32, device=dev)
         an = torch.empty(m, dtype=torch.float32, device=dev)
         pi = torch.empty(m, dtype=torch.int64, device=dev)
         ni = torch.empty(m, dtype=torch.int64, device=dev)
         with torch.cuda.device(dev):
             s = _stream()
-            _lib.call("reid_pair_dist", _ptr(xs), xs.stride(0), m, _ptr(ys), ys.stride(0), n, d, _ptr(dist), n, s)
-            _lib.call("reid_hard_mine", _ptr(dist), n, m, n, _ptr(lab_r), _ptr(lab_c), int(skip_diag), _ptr(ap),
+            dist = _pair_dist_forward(xs, ys, x is y, s)
+            _lib.call("reid_hard_mine", _ptr(dist), dist.stride(0), m, n, _ptr(lab_r), _ptr(lab_c), int(skip_diag), _ptr(ap),
                       _ptr(an), _ptr(pi), _ptr(ni), s)
         ctx.save_for_backward(xs, ys, ap, an, pi, ni)
         ctx.dtypes = (x.dtype, y.dtype)

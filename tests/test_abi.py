@@ -31,7 +31,7 @@ def test_every_declared_symbol_is_exported(lib):
 
 
 def test_host_constants(lib):
-    assert lib.reid_abi_version() == 2
+    assert lib.reid_abi_version() == 3
     assert [lib.reid_half_k(k) for k in (20, 50, 25, 5, 1)] == [11, 26, 13, 3, 1]     # reranking.py:60
     assert lib.reid_v_row_capacity(20) == 21 * 12
     assert [lib.reid_padded_width(d) for d in (512, 768, 1280, 1519, 64)] == [512, 768, 1280, 1536, 64]

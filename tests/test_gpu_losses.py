@@ -85,7 +85,8 @@ def test_dense_gradient_golden(L, path):
         np.testing.assert_allclose(got.cpu().numpy(), ref, rtol=1e-4, atol=1e-4 * np.abs(ref).max())
 
 
-@pytest.mark.parametrize("m,n,d", [(1, 1, 1), (33, 65, 31), (64, 64, 2048), (257, 1000, 100), (512, 512, 1280)])
+@pytest.mark.parametrize("m,n,d", [(1, 1, 1), (33, 65, 31), (64, 64, 2048), (257, 1000, 100), (512, 512, 1280),
+                                   (1024, 1024, 256), (1030, 1101, 130)])     # the last two: tensor-core forward
 def test_shapes_vs_oracle(L, m, n, d):
     g = torch.Generator().manual_seed(m * 131 + n)
     x = torch.randn(m, d, generator=g)
@@ -106,6 +107,40 @@ def test_shapes_vs_oracle(L, m, n, d):
     gx, gy = lo.euclidean_dist_grad(x.numpy(), y.numpy(), dist.detach().cpu().numpy(), R.numpy())
     np.testing.assert_allclose(xd.grad.cpu().numpy(), gx, rtol=1e-4, atol=1e-4 * max(np.abs(gx).max(), 1e-30))
     np.testing.assert_allclose(yd.grad.cpu().numpy(), gy, rtol=1e-4, atol=1e-4 * max(np.abs(gy).max(), 1e-30))
+
+
+def test_tensor_core_forward_same_rows(L):
+    """B >= 1 024 with x and y the same tensor: reid_pair_dist_tc (fp16 hi/lo operands, tcgen05 contraction, upper triangle
+    + mirrored stores) -- symmetric (bit for bit off the diagonal tiles), within the float32 path's tolerance of the oracle off the diagonal, and the
+    triplet loss + gradient built on it agree with the float32 CUDA-core forward (TC_MIN_ROWS raised)."""
+    mod = __import__("importlib").import_module("multimodal-reid_b200.losses")
+    g = torch.Generator().manual_seed(77)
+    m, d = 1100, 200
+    x = (torch.randn(m, d, generator=g) * (0.25 + torch.rand(m, 1, generator=g)) * 2).cuda()    # rows of mixed scale
+    dist = L.euclidean_dist(x, x)
+    assert dist.shape == (m, m)
+    # mirrored stores outside the 256 x 256 diagonal tiles; inside them D_ij and D_ji are accumulated in different orders
+    assert float(((dist - dist.t()).abs() / dist.clamp_min(1e-3)).max()) < 2e-6
+    blk = dist[300:500, 600:900]
+    assert torch.equal(blk, dist[600:900, 300:500].t())
+    want = lo.euclidean_dist(x.cpu().numpy(), x.cpu().numpy())
+    msk = _offdiag(want)
+    np.testing.assert_allclose(dist.cpu().numpy()[msk], want[msk], rtol=3e-5, atol=1e-5)
+    lab = (torch.arange(m) % 275).cuda()
+    a = x.clone().requires_grad_(True)
+    la = L.WeightedRegularizedTriplet(None)(a, lab)
+    la.backward()
+    saved = mod.TC_MIN_ROWS
+    mod.TC_MIN_ROWS = 1 << 30
+    try:
+        b = x.clone().requires_grad_(True)
+        lb = L.WeightedRegularizedTriplet(None)(b, lab)
+        lb.backward()
+    finally:
+        mod.TC_MIN_ROWS = saved
+    assert abs(la.item() - lb.item()) < 1e-5
+    np.testing.assert_allclose(a.grad.cpu().numpy(), b.grad.cpu().numpy(), rtol=1e-4,
+                               atol=1e-4 * b.grad.abs().max().item())
 
 
 def test_strided_and_half_inputs(L):

@@ -99,6 +99,7 @@ def _ids_case(q, g, n_id, n_cam, seed, absent=0):
     (300, 5000, 128, 60, 6, 128, 1024, 0),         # ~80 same-identity columns per query, a few junk
     (257, 4100, 64, 400, 2, 4096, 999, 20),        # two cameras: half of every group is junk; top-k on the same panels
     (90, 2500, 96, 3, 3, 50, 700, 0),              # groups of ~830 columns: most of the row ranks before the farthest match
+    (48, 6200, 64, 2, 3, 32, 2048, 0),             # groups of ~3 100 columns: shared-memory arrays of 4 096 entries
 ])
 def test_streamed_cmc_map_equals_materialised(eng, oracle, q, g, d, n_id, n_cam, rows, cols, K):
     qf, gf = _make(q, g, d, q * 7 + g, dup=25)
@@ -229,3 +230,40 @@ def test_streamed_rerank_equals_materialised(eng, engine_mod, synth, oracle, nam
     f = torch.nn.functional.normalize(torch.cat([qf, gf]), dim=1, p=2).numpy()
     c_o, m_o = oracle.cmc_map(oracle.re_ranking(f[:q], f[q:], k1, k2, 0.3), qp.numpy(), gp.numpy(), qc.numpy(), gc.numpy())
     assert np.abs(res[0].cpu().numpy() - c_o).max() <= 1e-5 and abs(float(res[1]) - m_o) <= 1e-5
+
+
+def test_streamed_rerank_large_identity_groups(eng):
+    """Identity groups beyond 1 024 gallery samples (the shared-memory arrays of the streamed scorers grow to the longest
+    group, 2^k <= 8 192): re-ranked CMC / mAP and top-k of the streamed path against the materialised one, bit for bit;
+    a group beyond the limit is refused before any sweep."""
+    q, g, d, k1, k2, topk = 40, 4700, 64, 10, 4, 30
+    qf, gf = _make(q, g, d, 4242, dup=10)
+    qp, gp, qc, gc = _ids_case(q, g, 2, 3, 99)          # two identities: ~2 350 same-identity columns per query
+    dev = eng.device
+    X = torch.cat([qf, gf]).to(dev)
+    pids, cams = torch.cat([qp, gp]).to(dev), torch.cat([qc, gc]).to(dev)
+    ids = (pids[:q].contiguous(), pids[q:].contiguous(), cams[:q].contiguous(), cams[q:].contiguous())
+    saved = eng.symmetric
+    eng.symmetric = False
+    try:
+        final = eng.rerank_features(X, q, k1, k2, 0.3, normalize=True, detail={})
+        want = eng.evaluate_dist(final, g, *ids, 50)
+    finally:
+        eng.symmetric = saved
+    allf = eng.prepare(X, True)
+    res, (idx, val), diag = eng.evaluate_streamed_reranked(allf, q, pids, cams, k1, k2, 0.3, topk=topk, Kw=64, cap_o=8192,
+                                                           rows_per_pass=512, cols_per_pass=1024)
+    assert diag["v_misses"] == 0 and diag["group_overflow"] == 0
+    order = torch.sort(final[:, :g] + 0.0, dim=1, stable=True)
+    assert torch.equal(idx.long(), order.indices[:, :topk]) and torch.equal(val, order.values[:, :topk])
+    for a, b, what in zip(want, res, ("cmc", "mAP", "n_valid", "ap", "first_hit")):
+        if what in ("ap", "mAP"):
+            assert float((a - b).abs().max()) <= 1e-13, what
+        else:
+            assert torch.equal(a, b), what
+    # beyond the limit: refused up front
+    one = torch.zeros(9000 + q, dtype=torch.int64, device=dev)
+    Xb = torch.randn(9000 + q, 32, generator=torch.Generator().manual_seed(1)).to(dev)
+    fb = eng.prepare(Xb, True)
+    with pytest.raises(Exception, match="at most 8192"):
+        eng.evaluate_streamed(fb.rows(slice(0, q)), fb.rows(slice(q, 9000 + q)), one[:q], one[q:], one[:q], one[q:] + 1)
