@@ -127,8 +127,9 @@ def main():
         dist_ms = stages.get("dist", float("nan"))
         # one q x g sweep in every mode (the match distances of the scoring modes are contracted as gathered pairs, stage
         # "pairs", not counted here)
-        if args.rerank:                          # + this rank's rows of the N x N sweep
-            flops += 2.0 * cm.local_count(q + g) * (q + g) * d
+        if args.rerank:                          # + this rank's share of the N x N sweep (half of it from the upper triangle)
+            half = diag_out.get("nn_sweep") == "upper half"
+            flops += 2.0 * (q + g) * (q + g) * d / world * (0.5 if half else 1.0)
         line = {"metric": ("k-reciprocal re-ranked top-k + CMC/mAP" if args.rerank else
                            "top-k retrieval + CMC/mAP" if args.score else "top-k retrieval")
                           + " q x g pairs/sec (matrix never materialised)",

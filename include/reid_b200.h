@@ -240,6 +240,23 @@ REID_API int reid_overlap_lists(const int32_t* Qc, const reid_half* Qv, const in
 /* od[l * cap_o + e] = panel[l, ocol[l * cap_o + e] - c0] for the listed columns inside the panel's block [c0, c1) */
 REID_API int reid_stream_list_gather(const float* panel, int64_t ld, int rows, int c0, int c1, int cap_o,
                             const int32_t* ocol, const int32_t* ocnt, float* od, void* stream);
+/* ---- neighbour lists of the symmetric N x N matrix from its upper half (step A of the streamed re-ranking) ----
+ * The caller contracts only the diagonal blocks (reid_dist_block mode 2 + reid_topk_rows_scatter: the initial lists and
+ * thresholds tau[row] = Kw-th distance) and the rectangles right of them (mode 3: the mirrored row maxima come with it).
+ * Rows of a rectangle [rows x cols] at (row0, c0) select from it as from any panel (reid_topk_rows_hinted); its COLUMNS --
+ * rows c0 .. c0+cols of the matrix -- receive every element <= tau[column]:
+ * reid_sym_push: chunk_min = the rectangle's 32-column chunk minima (pitch cm_pitch); candidates (D, global row) go to
+ *   pbuf[col * cap ...], count[col] (block-local column; zero before the first call); cthr_key: scratch, ceil(cols/32).
+ * reid_sym_fold: per column with candidates: running list (list_val / list_idx [N, Kw], ascending by (D, column); unused
+ *   slots +inf) + candidates -> the Kw nearest; tau[c0 + col] lowered; count reset; *overflow = largest count > cap seen
+ *   (the caller then falls back to the full sweep).
+ * reid_sym_merge: nlists partial lists per row ([nlists, rows, Kw]; one per rank) -> the Kw nearest. */
+REID_API int reid_sym_push(const float* panel, int64_t ld, int rows, int row0, int cols, int c0, const float* chunk_min,
+                  int cm_pitch, const float* tau, int32_t* cthr_key, int32_t* count, uint64_t* pbuf, int cap, void* stream);
+REID_API int reid_sym_fold(int cols, int c0, int Kw, float* list_val, int32_t* list_idx, float* tau, int32_t* count,
+                  const uint64_t* pbuf, int cap, int32_t* overflow, void* stream);
+REID_API int reid_sym_merge(int rows, int nlists, int Kw, const float* lists_val, const int32_t* lists_idx, float* out_val,
+                   int32_t* out_idx, void* stream);
 REID_API int reid_rr_prepare(int nq, int q0, int q_stride, const int32_t* glo, const int32_t* glen, const int64_t* goff,
                     const int32_t* list, const float* gd, const int64_t* q_cam, const int64_t* g_cam,
                     const int32_t* rowmax_key, float c1, float c2, int cap_o, const int32_t* ocol, const reid_half* ot,

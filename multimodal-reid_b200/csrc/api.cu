@@ -395,6 +395,28 @@ int reid_stream_list_gather(const float* panel, int64_t ld, int rows, int c0, in
   return launch_list_gather_sorted(panel, ld, rows, c0, c1, cap_o, ocol, ocnt, od, S(stream));
 }
 
+int reid_sym_push(const float* panel, int64_t ld, int rows, int row0, int cols, int c0, const float* chunk_min,
+                  int cm_pitch, const float* tau, int32_t* cthr_key, int32_t* count, uint64_t* pbuf, int cap, void* stream) {
+  ENTER();
+  REID_REQUIRE(rows >= 0 && cols >= 0 && ld >= cols && row0 >= 0 && c0 >= 0, "sym_push: bad panel");
+  return launch_sym_push(panel, ld, rows, row0, cols, c0, chunk_min, cm_pitch, tau, cthr_key, count,
+                         reinterpret_cast<unsigned long long*>(pbuf), cap, S(stream));
+}
+
+int reid_sym_fold(int cols, int c0, int Kw, float* list_val, int32_t* list_idx, float* tau, int32_t* count,
+                  const uint64_t* pbuf, int cap, int32_t* overflow, void* stream) {
+  ENTER();
+  REID_REQUIRE(cols >= 0 && c0 >= 0, "sym_fold: bad block");
+  return launch_sym_fold(cols, c0, Kw, list_val, list_idx, tau, count, ULL(pbuf), cap, overflow, S(stream));
+}
+
+int reid_sym_merge(int rows, int nlists, int Kw, const float* lists_val, const int32_t* lists_idx, float* out_val,
+                   int32_t* out_idx, void* stream) {
+  ENTER();
+  REID_REQUIRE(rows >= 0, "sym_merge: bad shape");
+  return launch_sym_merge(rows, nlists, Kw, lists_val, lists_idx, out_val, out_idx, S(stream));
+}
+
 int reid_rr_prepare(int nq, int q0, int q_stride, const int32_t* glo, const int32_t* glen, const int64_t* goff,
                     const int32_t* list, const float* gd, const int64_t* q_cam, const int64_t* g_cam,
                     const int32_t* rowmax_key, float c1, float c2, int cap_o, const int32_t* ocol, const reid_half* ot,

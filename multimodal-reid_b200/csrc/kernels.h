@@ -181,6 +181,13 @@ int launch_triplet_grad(const float* X, long long ldx, int m, const float* Y, lo
                         const float* g_ap, const float* g_an, float* gx, long long ldgx, float* gy, long long ldgy,
                         int accumulate_gy, cudaStream_t s);
 
+// stream_sym.cu (neighbour lists of the symmetric N x N matrix from its upper half)
+int launch_sym_push(const float* D, long long ld, int m, int row0, int n, int c0, const float* chunk_min, int cm_pitch,
+                    const float* tau, int* cthr_key, int* count, unsigned long long* pbuf, int cap, cudaStream_t s);
+int launch_sym_fold(int n, int c0, int Kw, float* Mv, int* Mi, float* tau, int* count, const unsigned long long* pbuf,
+                    int cap, int* overflow, cudaStream_t s);
+int launch_sym_merge(int rows, int S, int Kw, const float* Fv, const int* Fi, float* out_v, int* out_i, cudaStream_t s);
+
 // stream_score.cu (CMC / mAP without the q x g matrix)
 int launch_stream_group_lookup(const long long* q_pid, int nq, const unsigned long long* keys, const long long* start,
                                int T, int* glo, int* glen, cudaStream_t s);

@@ -13,6 +13,7 @@ from __future__ import annotations
 
 import ctypes as C
 import dataclasses
+import os
 
 import numpy as np
 import torch
@@ -242,6 +243,7 @@ class Engine:
         # world > 1: symmetric contraction sharded by tile rows + exchanges through peer memory (fabric.py); the NCCL
         # all-gather path of round 1 remains as the fallback when CUDA IPC / peer access is unavailable
         self.use_fabric = True
+        self.sym_sweep = os.environ.get("REID_SYM_SWEEP", "1") != "0"    # streamed re-ranking: N x N lists from half the matrix
         self.fabric = None
         self._fabric_failed = False
         self.fabric_pool_bytes = 24 << 30   # largest query-expansion pool the arena may hold (structural bound)
@@ -559,6 +561,125 @@ class Engine:
             self.symmetric = sym
         return out_i, out_v
 
+    def neighbour_lists_symmetric(self, F: Features, Kw: int, rows_per_pass: int = 16384, cols_per_pass: int = 65536):
+        """The Kw nearest rows of EVERY row of F among all of F (raw squared distances, stable (distance, column)
+        order) and every row's maximum, from the upper half of the symmetric N x N matrix only (csrc/stream_sym.cu):
+        diagonal blocks in upper-only form (initial lists and thresholds), then the rectangles right of them, each
+        serving its rows through the hinted selection and its columns through threshold-filtered pushes.  With P ranks
+        the row panels are dealt out in snake order; every rank folds the pushes of ITS panels into its own copy of the
+        lists and the copies are merged at the end.  Values are those of the materialised path's upper-only form.
+        Returns (idx int32 [N, Kw], val float32 [N, Kw], rowmax_key int32 [N]) on every rank, or None when a column
+        received more candidates than the buffers hold (the caller runs the full sweep instead)."""
+        cm = self.comm
+        r, P = cm.rank, cm.world
+        N, dev, st = F.n, self.device, _stream
+        B = max(256, rows_per_pass // 256 * 256)
+        CB = max(256, cols_per_pass // 256 * 256)
+        starts = list(range(0, N, B))
+        if len(starts) > 1 and N - starts[-1] < max(Kw, B // 4):
+            starts.pop()                # a short tail joins the last panel: its own diagonal block would give loose thresholds
+        bounds = starts + [N]
+        mine = [p for p in range(len(starts)) if _fabric.snake_owner(p, P) == r]
+        key = self._empty((N,), torch.int32)
+        _lib.call("reid_rowmax_init", _ptr(key), N, st())
+        Mv = torch.full((N, Kw), float("inf"), dtype=torch.float32, device=dev)
+        Mi = torch.full((N, Kw), 0x7FFFFFFF, dtype=torch.int32, device=dev)
+        tau = torch.full((N,), float("inf"), dtype=torch.float32, device=dev)
+        unit = torch.full((max(b1 - b0 for b0, b1 in zip(bounds, bounds[1:])),), _ONE_BITS, dtype=torch.int32, device=dev)
+        hs = F.hi.stride(0)
+        # ---- diagonal blocks: upper-only form, scatter selection -> the initial lists and thresholds of the own rows
+        for p in mine:
+            r0, r1 = bounds[p], bounds[p + 1]
+            m = r1 - r0
+            A = F.rows(slice(r0, r1))
+            with self.span("dist"):
+                D = self._empty((m, self.pitch(m)), torch.float32)
+                cpitch = self.lib.reid_chunk_pitch(m)
+                cmin = self._empty((m, cpitch), torch.float32)
+                _lib.call("reid_dist_block", _ptr(A.hi), _ptr(A.lo), hs, _ptr(A.sq), _ptr(F.amax), m, _ptr(A.hi),
+                          _ptr(A.lo), hs, _ptr(A.sq), _ptr(F.amax), m, F.dp, METRIC_SQEUCLIDEAN, _ptr(D), D.stride(0),
+                          _ptr(key[r0:]), _ptr(cmin), cpitch, 2, None, None, st())
+            with self.span("select"):
+                idx, val = self.topk_rows(D, m, unit[:m], Kw, want_values=True, chunk_min=cmin[:, : (m + 31) // 32],
+                                          upper_only=True)
+                Mi[r0:r1] = idx + r0
+                Mv[r0:r1] = val
+                tau[r0:r1] = val[:, Kw - 1]
+            del D, cmin
+        if P > 1:
+            cm.dist.all_reduce(tau, op=cm.dist.ReduceOp.MIN, group=cm.group)        # the other ranks hold +inf
+        # ---- rectangles right of the diagonal blocks
+        cap = 512
+        count = self._zeros((CB + Kw,), torch.int32)
+        pbuf = self._empty(((CB + Kw) * cap,), torch.int64)
+        cthr = self._empty(((CB + Kw + 31) // 32,), torch.int32)
+        ovf = self._zeros((1,), torch.int32)
+        for p in mine:
+            r0, r1 = bounds[p], bounds[p + 1]
+            m = r1 - r0
+            A = F.rows(slice(r0, r1))
+            blocks = [(r1 + c0, r1 + c1) for c0, c1 in self.column_blocks(N - r1, CB, Kw)] if r1 < N else []
+            if not blocks:
+                continue
+            nb = len(blocks)
+            cv = self._empty((m, self.pitch((nb + 1) * Kw)), torch.float32)
+            ci = self._empty((m, (nb + 1) * Kw), torch.int32)
+            for b, (c0, c1) in enumerate(blocks):
+                n = c1 - c0
+                Bf = F.rows(slice(c0, c1))
+                with self.span("dist"):
+                    D = self._empty((m, self.pitch(n)), torch.float32)
+                    cpitch = self.lib.reid_chunk_pitch(n)
+                    cmin = self._empty((m, cpitch), torch.float32)
+                    _lib.call("reid_dist_block", _ptr(A.hi), _ptr(A.lo), hs, _ptr(A.sq), _ptr(F.amax), m, _ptr(Bf.hi),
+                              _ptr(Bf.lo), hs, _ptr(Bf.sq), _ptr(F.amax), n, F.dp, METRIC_SQEUCLIDEAN, _ptr(D),
+                              D.stride(0), _ptr(key[r0:]), _ptr(cmin), cpitch, 3, _ptr(key[c0:]), None, st())
+                with self.span("select"):
+                    idx, val = self.topk_rows(D, n, unit[:m], Kw, want_values=True, chunk_min=cmin[:, : (n + 31) // 32])
+                    ci[:, (b + 1) * Kw:(b + 2) * Kw] = idx + c0
+                    cv[:, (b + 1) * Kw:(b + 2) * Kw] = val
+                with self.span("push"):
+                    # slabs of rows: the thresholds tighten between slabs, which bounds the candidates a column can
+                    # collect at once (rows much nearer to a column than its own block's -- queries against a gallery
+                    # column -- would otherwise arrive by the hundred)
+                    # expected candidates of a column per panel ~ Kw * m / (rows of the column's own diagonal block)
+                    t_min = min(bounds[pp + 1] - bounds[pp] for pp in range(len(starts))
+                                if bounds[pp] < c1 and bounds[pp + 1] > c0)
+                    nslab = max(1, -(-(Kw * m) // (t_min * 96)))
+                    slab = (-(-m // nslab) + 255) // 256 * 256 if nslab > 1 else m
+                    for s0 in range(0, m, slab):
+                        s1 = min(m, s0 + slab)
+                        _lib.call("reid_sym_push", _ptr(D[s0:]), D.stride(0), s1 - s0, r0 + s0, n, c0, _ptr(cmin[s0:]),
+                                  cpitch, _ptr(tau), _ptr(cthr), _ptr(count), _ptr(pbuf), cap, st())
+                        _lib.call("reid_sym_fold", n, c0, Kw, _ptr(Mv), _ptr(Mi), _ptr(tau), _ptr(count), _ptr(pbuf),
+                                  cap, _ptr(ovf), st())
+                del D, cmin
+            with self.span("merge"):
+                # the rows' own lists so far (diagonal block + pushes of earlier panels: columns below r1) in front of the
+                # rectangles' winners (columns from r1 on): position order == column order among equal distances
+                ci[:, :Kw] = Mi[r0:r1]
+                cv[:, :Kw] = Mv[r0:r1]
+                pos, val = self.topk_rows(cv, (nb + 1) * Kw, unit[:m], Kw, want_values=True)
+                Mi[r0:r1] = torch.gather(ci, 1, pos.long())
+                Mv[r0:r1] = val
+            del cv, ci
+        if P > 1:
+            with self.span("x_lists"):
+                Fv, Fi = cm.gather_stack(Mv), cm.gather_stack(Mi)
+                ovf_all = cm.gather_stack(ovf)
+                cm.dist.all_reduce(key, op=cm.dist.ReduceOp.MAX, group=cm.group)
+            self.last_sym_overflow = int(ovf_all.max().item())
+            if self.last_sym_overflow:
+                return None
+            with self.span("merge"):
+                _lib.call("reid_sym_merge", N, P, Kw, _ptr(Fv), _ptr(Fi), _ptr(Mv), _ptr(Mi), st())
+            del Fv, Fi
+        else:
+            self.last_sym_overflow = int(ovf.item())
+            if self.last_sym_overflow:
+                return None
+        return Mi, Mv, key
+
     def pair_distances(self, A: Features, B: Features, ri: torch.Tensor, ci: torch.Tensor,
                        metric: int = METRIC_SQEUCLIDEAN, chunk: int = 8192) -> torch.Tensor:
         """D[ri[p], ci[p]] for a list of (row of A, row of B) pairs with exactly the panels' arithmetic: the operand rows
@@ -694,14 +815,23 @@ class Engine:
             raise ValueError(f"topk={topk} / K={K} do not fit q={q}, g={g}")
         st = _stream
         # ---- A
+        lists = None
         with self.span("nn_sweep"):
-            A = allf.rows(slice(r, N, P))
-            key_l = self._empty((A.n,), torch.int32)
-            _lib.call("reid_rowmax_init", _ptr(key_l), A.n, st())
-            widx_l, wval_l = self.retrieve_topk(A, allf, Kw, METRIC_SQEUCLIDEAN, rows_per_pass, cols_per_pass,
-                                                rowmax=key_l)
-        with self.span("x_lists"):
-            widx, wval, key = cm.gather_rows(widx_l, N), cm.gather_rows(wval_l, N), cm.gather_rows(key_l, N)
+            if self.sym_sweep and self.symmetric and self.engine != ENGINES["simt"] and P * Kw <= 1024:
+                # half the matrix: values are the upper-triangle ones, as in the materialised path's upper-only form
+                lists = self.neighbour_lists_symmetric(allf, Kw, rows_per_pass, cols_per_pass)
+            if lists is None:
+                A = allf.rows(slice(r, N, P))
+                key_l = self._empty((A.n,), torch.int32)
+                _lib.call("reid_rowmax_init", _ptr(key_l), A.n, st())
+                widx_l, wval_l = self.retrieve_topk(A, allf, Kw, METRIC_SQEUCLIDEAN, rows_per_pass, cols_per_pass,
+                                                    rowmax=key_l)
+        if lists is not None:
+            widx, wval, key = lists
+        else:
+            with self.span("x_lists"):
+                widx, wval, key = cm.gather_rows(widx_l, N), cm.gather_rows(wval_l, N), cm.gather_rows(key_l, N)
+        upper = lists is not None
         # ---- B (replicated)
         flags = self._zeros((5,), torch.int32)      # rekey ambiguous | V misses | overlap overflow | group overflow | topk ambiguous
         with self.span("krecip"):
@@ -731,6 +861,9 @@ class Engine:
                 mt_keys = torch.sort(miss_out[:n_miss]).values
                 mt_vals = self._zeros((n_miss,), torch.float32)
                 ri, ci = (mt_keys >> 32), (mt_keys & 0xFFFFFFFF)
+                if upper:        # the value row i holds for column e: D[i, e] from i's 256-wide diagonal block on, else D[e, i]
+                    swap = ci < (ri & ~255)
+                    ri, ci = torch.where(swap, ci, ri), torch.where(swap, ri, ci)
                 sym = self.symmetric
                 self.symmetric = False
                 try:
@@ -844,7 +977,8 @@ class Engine:
         self._overlap_hint[(N, q, k1, k2)] = cm.max_int(int(osz[0]), self.device)     # same ranges on every rank next time
         diag = {"overlap_targets_max": int(osz[0]), "overlap_targets_mean": (osz[1] / nq if nq else 0.0),
                 "rekey_ambiguous": f[0], "v_misses": f[1], "v_pairs_recontracted": pairs_recomputed,
-                "overlap_overflow": f[2], "group_overflow": f[3], "topk_ambiguous": f[4], "Kw": Kw, "Kd": Kd}
+                "overlap_overflow": f[2], "group_overflow": f[3], "topk_ambiguous": f[4], "Kw": Kw, "Kd": Kd,
+                "nn_sweep": "upper half" if upper else "full", "sym_overflow": getattr(self, "last_sym_overflow", 0)}
         if f[2] or f[3]:
             raise _lib.ReidError(f"streamed re-ranking: {f[2]} queries touch more than cap_o={cap_o} gallery columns, "
                                  f"largest identity group {f[3]} (limit {GROUP_MAX})")

@@ -178,11 +178,13 @@ def test_streamed_eval_vs_reference_golden(path):
 
 @pytest.mark.parametrize("name,k1,k2,rows_pp,cols_pp,topk", [("small", 20, 6, 256, 512, 40), ("mid", 20, 6, 1024, 1536, 100),
                                                              ("small", 50, 15, 512, 768, 30), ("tiny", 7, 1, 256, 256, 20)])
-def test_streamed_rerank_equals_materialised(eng, engine_mod, synth, oracle, name, k1, k2, rows_pp, cols_pp, topk):
+@pytest.mark.parametrize("half", [True, False], ids=["upper-half-sweep", "full-sweep"])
+def test_streamed_rerank_equals_materialised(eng, engine_mod, synth, oracle, name, k1, k2, rows_pp, cols_pp, topk, half):
     """k-reciprocal re-ranking with no dense matrix (panel sweeps + lists) on a down-scaled instance against
-    the materialised path with the same (full, non-symmetric) tile schedule: neighbour lists, V rows, the exact top-k of
-    every re-ranked row, first hits and CMC must agree bit for bit, AP to 1e-13; and against the oracle within
-    north_star's tolerances."""
+    the materialised path with the same tile schedule -- the N x N lists from the upper half of the matrix
+    (csrc/stream_sym.cu) against the materialised upper-only form, the full sweep against the full schedule: neighbour
+    lists, V rows, the exact top-k of every re-ranked row, first hits and CMC must agree bit for bit, AP to 1e-13; and
+    against the oracle within north_star's tolerances."""
     sh = synth.SHAPES[name]
     qf, gf, qp, gp, qc, gc = synth.make(sh, 11)
     dev = eng.device
@@ -190,26 +192,26 @@ def test_streamed_rerank_equals_materialised(eng, engine_mod, synth, oracle, nam
     pids, cams = torch.cat([qp, gp]).to(dev), torch.cat([qc, gc]).to(dev)
     q, g = sh.q, sh.g
     ids = (pids[:q].contiguous(), pids[q:].contiguous(), cams[:q].contiguous(), cams[q:].contiguous())
-    saved = eng.symmetric
-    eng.symmetric = False
+    saved, saved_sweep = eng.symmetric, eng.sym_sweep
+    eng.symmetric, eng.sym_sweep = half, half
     try:
         det = {}
         final = eng.rerank_features(X, q, k1, k2, 0.3, normalize=True, detail=det)
         want = eng.evaluate_dist(final, g, *ids, 50)
+        allf = eng.prepare(X, True)
+        sdet = {}
+        res, (idx, val), diag = eng.evaluate_streamed_reranked(allf, q, pids, cams, k1, k2, 0.3, topk=topk, Kw=64,
+                                                               cap_o=12288 if name == "mid" else 4096,
+                                                               rows_per_pass=rows_pp, cols_per_pass=cols_pp, detail=sdet)
+        print(f"[a13] {name} k1={k1} k2={k2}: {diag}")
+        assert diag["nn_sweep"] == ("upper half" if half else "full")
+        assert diag["v_misses"] == 0, "a V weight fell back to the float32 recomputation on this instance"
+        # a second call sizes the Jaccard column ranges by the overlap lists the first one saw: same lists, same results
+        res2, (idx2, val2), _ = eng.evaluate_streamed_reranked(allf, q, pids, cams, k1, k2, 0.3, topk=topk, Kw=64,
+                                                              cap_o=12288 if name == "mid" else 4096,
+                                                              rows_per_pass=rows_pp, cols_per_pass=cols_pp)
     finally:
-        eng.symmetric = saved
-    allf = eng.prepare(X, True)
-    sdet = {}
-    res, (idx, val), diag = eng.evaluate_streamed_reranked(allf, q, pids, cams, k1, k2, 0.3, topk=topk, Kw=64,
-                                                           cap_o=12288 if name == "mid" else 4096, rows_per_pass=rows_pp,
-                                                           cols_per_pass=cols_pp,
-                                                           detail=sdet)
-    print(f"[a13] {name} k1={k1} k2={k2}: {diag}")
-    assert diag["v_misses"] == 0, "a V weight fell back to the float32 recomputation on this instance"
-    # a second call sizes the Jaccard column ranges by the overlap lists the first one saw: same lists, same results
-    res2, (idx2, val2), _ = eng.evaluate_streamed_reranked(allf, q, pids, cams, k1, k2, 0.3, topk=topk, Kw=64,
-                                                          cap_o=12288 if name == "mid" else 4096, rows_per_pass=rows_pp,
-                                                          cols_per_pass=cols_pp)
+        eng.symmetric, eng.sym_sweep = saved, saved_sweep
     assert torch.equal(idx, idx2) and torch.equal(val, val2) and all(torch.equal(a, b) for a, b in zip(res, res2))
     K = max(k1 + 1, k2)
     assert torch.equal(sdet["nbr"], det["nbr"][:, :K])
@@ -248,11 +250,11 @@ def test_streamed_rerank_large_identity_groups(eng):
     try:
         final = eng.rerank_features(X, q, k1, k2, 0.3, normalize=True, detail={})
         want = eng.evaluate_dist(final, g, *ids, 50)
+        allf = eng.prepare(X, True)
+        res, (idx, val), diag = eng.evaluate_streamed_reranked(allf, q, pids, cams, k1, k2, 0.3, topk=topk, Kw=64,
+                                                               cap_o=8192, rows_per_pass=512, cols_per_pass=1024)
     finally:
         eng.symmetric = saved
-    allf = eng.prepare(X, True)
-    res, (idx, val), diag = eng.evaluate_streamed_reranked(allf, q, pids, cams, k1, k2, 0.3, topk=topk, Kw=64, cap_o=8192,
-                                                           rows_per_pass=512, cols_per_pass=1024)
     assert diag["v_misses"] == 0 and diag["group_overflow"] == 0
     order = torch.sort(final[:, :g] + 0.0, dim=1, stable=True)
     assert torch.equal(idx.long(), order.indices[:, :topk]) and torch.equal(val, order.values[:, :topk])
