@@ -120,7 +120,10 @@ def main():
         if os.path.exists(pth):
             with open(pth) as f:
                 peaks = json.load(f)
-        bf16 = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops", 1400.0)))
+        # the sustained figure for contraction stages that run for seconds at the power cap; short per-rank stages (8 ranks)
+        # run at burst clocks, where the burst figure is the honest denominator
+        bf16_sus = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops", 1400.0)))
+        bf16_burst = float(peaks.get("bf16_tflops", bf16_sus))
         hbm = float(peaks.get("hbm_gbs", 6450.0))
         rows_local = cm.local_count(q)
         flops = 2.0 * rows_local * g * d
@@ -130,6 +133,9 @@ def main():
         if args.rerank:                          # + this rank's share of the N x N sweep (half of it from the upper triangle)
             half = diag_out.get("nn_sweep") == "upper half"
             flops += 2.0 * (q + g) * (q + g) * d / world * (0.5 if half else 1.0)
+        issued = 3.0 * flops / (dist_ms * 1e-3) / 1e12
+        long_run = dist_ms > 1000.0
+        bf16 = bf16_sus if long_run else bf16_burst
         line = {"metric": ("k-reciprocal re-ranked top-k + CMC/mAP" if args.rerank else
                            "top-k retrieval + CMC/mAP" if args.score else "top-k retrieval")
                           + " q x g pairs/sec (matrix never materialised)",
@@ -145,12 +151,12 @@ def main():
                 # rectangular panels: every tile is computed (no symmetry to exploit), three fp16 MMAs per K step; tiles are
                 # padded to 256 x 256, which the panel shapes used here divide evenly
                 "roofline": {"kernel": "dist_tc2_kernel (rectangular panels)", "bound": "tensor",
-                             "achieved": 3.0 * flops / (dist_ms * 1e-3) / 1e12, "peak": bf16, "unit": "TFLOP/s",
-                             "frac": 3.0 * flops / (dist_ms * 1e-3) / 1e12 / bf16, "ms": dist_ms,
+                             "achieved": issued, "peak": bf16, "unit": "TFLOP/s", "frac": issued / bf16, "ms": dist_ms,
                              "achieved_is": "issued fp16 MMA flops (3 x algorithmic 2*rows*cols*d) / CUDA-event time of the "
                                             "contraction launches",
                              "algorithmic_tflops": flops / (dist_ms * 1e-3) / 1e12,
-                             "peak_source": "MEASURED_PEAKS.json bf16 sustained"},
+                             "peak_source": "MEASURED_PEAKS.json bf16 " + ("sustained (contraction stages > 1 s)" if long_run
+                                                                            else "burst (contraction stages < 1 s)")},
                 "hbm_panel": {"bytes_written_per_step": 4.0 * rows_local * g * (1 + 1 / 32),
                               "GB/s_over_dist": 4.0 * rows_local * g * (1 + 1 / 32) / (dist_ms * 1e-3) / 1e9,
                               "peak": hbm},
