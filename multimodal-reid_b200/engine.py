@@ -561,6 +561,27 @@ class Engine:
             self.symmetric = sym
         return out_i, out_v
 
+    @staticmethod
+    def sym_panel_bounds(N: int, rows_per_pass: int, Kw: int) -> list[int]:
+        """Row-panel boundaries of the upper-half sweep: multiples of 256 (the contraction's block origins), a short tail
+        (fewer than max(Kw, a quarter panel) rows) joined to the last panel -- its own diagonal block would give loose
+        thresholds, and the selection needs Kw columns."""
+        B = max(256, rows_per_pass // 256 * 256)
+        starts = list(range(0, N, B))
+        if len(starts) > 1 and N - starts[-1] < max(Kw, B // 4):
+            starts.pop()
+        return starts + [N]
+
+    @staticmethod
+    def sym_slab_rows(bounds: list[int], m: int, c0: int, c1: int, Kw: int) -> int:
+        """Rows pushed at once into the columns [c0, c1) of a rectangle with m rows.  A column's threshold starts as the
+        Kw-th distance inside its own diagonal block of t rows, so a panel of m rows holds ~Kw * m / t candidates for it;
+        where that exceeds ~96 (a rectangle facing a short tail block) the rows go in slabs (multiples of 256) and the
+        thresholds tighten in between.  Regular rectangles (t == m) are pushed whole at Kw = 64."""
+        t_min = min(b1 - b0 for b0, b1 in zip(bounds, bounds[1:]) if b0 < c1 and b1 > c0)
+        nslab = max(1, -(-(Kw * m) // (t_min * 96)))
+        return (-(-m // nslab) + 255) // 256 * 256 if nslab > 1 else m
+
     def neighbour_lists_symmetric(self, F: Features, Kw: int, rows_per_pass: int = 16384, cols_per_pass: int = 65536):
         """The Kw nearest rows of EVERY row of F among all of F (raw squared distances, stable (distance, column)
         order) and every row's maximum, from the upper half of the symmetric N x N matrix only (csrc/stream_sym.cu):
@@ -573,12 +594,9 @@ class Engine:
         cm = self.comm
         r, P = cm.rank, cm.world
         N, dev, st = F.n, self.device, _stream
-        B = max(256, rows_per_pass // 256 * 256)
         CB = max(256, cols_per_pass // 256 * 256)
-        starts = list(range(0, N, B))
-        if len(starts) > 1 and N - starts[-1] < max(Kw, B // 4):
-            starts.pop()                # a short tail joins the last panel: its own diagonal block would give loose thresholds
-        bounds = starts + [N]
+        bounds = self.sym_panel_bounds(N, rows_per_pass, Kw)
+        starts = bounds[:-1]
         mine = [p for p in range(len(starts)) if _fabric.snake_owner(p, P) == r]
         key = self._empty((N,), torch.int32)
         _lib.call("reid_rowmax_init", _ptr(key), N, st())
@@ -643,10 +661,7 @@ class Engine:
                     # collect at once (rows much nearer to a column than its own block's -- queries against a gallery
                     # column -- would otherwise arrive by the hundred)
                     # expected candidates of a column per panel ~ Kw * m / (rows of the column's own diagonal block)
-                    t_min = min(bounds[pp + 1] - bounds[pp] for pp in range(len(starts))
-                                if bounds[pp] < c1 and bounds[pp + 1] > c0)
-                    nslab = max(1, -(-(Kw * m) // (t_min * 96)))
-                    slab = (-(-m // nslab) + 255) // 256 * 256 if nslab > 1 else m
+                    slab = self.sym_slab_rows(bounds, m, c0, c1, Kw)
                     for s0 in range(0, m, slab):
                         s1 = min(m, s0 + slab)
                         _lib.call("reid_sym_push", _ptr(D[s0:]), D.stride(0), s1 - s0, r0 + s0, n, c0, _ptr(cmin[s0:]),

@@ -62,3 +62,37 @@ def test_layout_is_deterministic_and_aligned():
     assert a.stats_slot % 16 == 0 and a.stats_slot >= 2 * 93820 * 4 and a.score_slot % 16 == 0
     assert a.nloc_max % 256 == 0 and a.nloc_max >= fab.owned_rows_max(93820, 8)
     assert a.total - a.panel == a.nloc_max * a.ld * 4
+
+
+def test_upper_half_sweep_panels_and_slabs():
+    """Host arithmetic of the upper-half N x N sweep (engine.neighbour_lists_symmetric): panel boundaries are multiples
+    of 256 with short tails joined, every rectangle right of a diagonal block splits into column blocks that tile
+    [r1, N) exactly, slabs are multiples of 256 and only appear where a column's own block is short."""
+    import importlib
+    E = importlib.import_module("multimodal-reid_b200.engine").Engine
+    for N, rpp, Kw in ((1_100_000, 16384, 64), (3204, 256, 64), (530, 256, 64), (200, 256, 64), (16384 * 3 + 5000, 16384, 64),
+                       (16384 * 3 + 100, 16384, 128), (70_000, 1000, 32)):
+        b = E.sym_panel_bounds(N, rpp, Kw)
+        assert b[0] == 0 and b[-1] == N and all(x < y for x, y in zip(b, b[1:]))
+        assert all(x % 256 == 0 for x in b[:-1])
+        B = max(256, rpp // 256 * 256)
+        sizes = [y - x for x, y in zip(b, b[1:])]
+        assert all(s == B for s in sizes[:-1]) and (len(sizes) == 1 or max(Kw, B // 4) <= sizes[-1] < B + max(Kw, B // 4))
+        for p in range(len(sizes)):
+            r1 = b[p + 1]
+            if r1 == N:
+                continue
+            blocks = [(r1 + c0, r1 + c1) for c0, c1 in E.column_blocks(N - r1, 4 * B, Kw)]
+            assert blocks[0][0] == r1 and blocks[-1][1] == N
+            assert all(a[1] == c[0] for a, c in zip(blocks, blocks[1:])) and all(c1 - c0 >= Kw for c0, c1 in blocks)
+            for c0, c1 in blocks:
+                slab = E.sym_slab_rows(b, sizes[p], c0, c1, Kw)
+                assert 0 < slab <= max(sizes[p], 256) and (slab == sizes[p] or slab % 256 == 0)
+                t = min(y - x for x, y in zip(b, b[1:]) if x < c1 and y > c0)
+                if Kw * sizes[p] <= 96 * t:
+                    assert slab == sizes[p]                      # regular rectangle at Kw = 64: pushed whole
+                else:
+                    assert Kw * min(slab, sizes[p]) / t <= 96 + Kw * 256 / t
+    # the 100k x 1M case: 67 regular panels + a tail of 2 272 rows joined (2 272 < 16 384 / 4)
+    b = E.sym_panel_bounds(1_100_000, 16384, 64)
+    assert len(b) - 1 == 67 and b[-1] - b[-2] == 16384 + 2272
