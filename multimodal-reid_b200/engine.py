@@ -244,6 +244,7 @@ class Engine:
         # all-gather path of round 1 remains as the fallback when CUDA IPC / peer access is unavailable
         self.use_fabric = True
         self.sym_sweep = os.environ.get("REID_SYM_SWEEP", "1") != "0"    # streamed re-ranking: N x N lists from half the matrix
+        self.sym_cap = 512          # candidate records per column and push of that sweep (Kw + sym_cap <= 1024)
         self.fabric = None
         self._fabric_failed = False
         self.fabric_pool_bytes = 24 << 30   # largest query-expansion pool the arena may hold (structural bound)
@@ -627,7 +628,7 @@ class Engine:
         if P > 1:
             cm.dist.all_reduce(tau, op=cm.dist.ReduceOp.MIN, group=cm.group)        # the other ranks hold +inf
         # ---- rectangles right of the diagonal blocks
-        cap = 512
+        cap = min(self.sym_cap, 1024 - Kw)
         count = self._zeros((CB + Kw,), torch.int32)
         pbuf = self._empty(((CB + Kw) * cap,), torch.int64)
         cthr = self._empty(((CB + Kw + 31) // 32,), torch.int32)
@@ -831,6 +832,7 @@ class Engine:
         st = _stream
         # ---- A
         lists = None
+        self.last_sym_overflow = 0
         with self.span("nn_sweep"):
             if self.sym_sweep and self.symmetric and self.engine != ENGINES["simt"] and P * Kw <= 1024:
                 # half the matrix: values are the upper-triangle ones, as in the materialised path's upper-only form
@@ -993,7 +995,7 @@ class Engine:
         diag = {"overlap_targets_max": int(osz[0]), "overlap_targets_mean": (osz[1] / nq if nq else 0.0),
                 "rekey_ambiguous": f[0], "v_misses": f[1], "v_pairs_recontracted": pairs_recomputed,
                 "overlap_overflow": f[2], "group_overflow": f[3], "topk_ambiguous": f[4], "Kw": Kw, "Kd": Kd,
-                "nn_sweep": "upper half" if upper else "full", "sym_overflow": getattr(self, "last_sym_overflow", 0)}
+                "nn_sweep": "upper half" if upper else "full", "sym_overflow": self.last_sym_overflow}
         if f[2] or f[3]:
             raise _lib.ReidError(f"streamed re-ranking: {f[2]} queries touch more than cap_o={cap_o} gallery columns, "
                                  f"largest identity group {f[3]} (limit {GROUP_MAX})")
