@@ -160,6 +160,18 @@ REID_API int64_t reid_topk_scatter_workspace_bytes(int n, int cap);
 REID_API int reid_topk_rows_scatter(const float* D, int n, int64_t ld, const int32_t* rowmax_key, const float* chunk_min,
                            int K, int32_t* nbr, float* nbr_val, int cap, void* workspace, int64_t workspace_bytes,
                            void* stream);
+/* reid_topk_rows_scatter without any device allocation by caller or library.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same inputs, outputs and bits as reid_topk_rows_scatter(cap = 0); the
+ * workspace is a device array built into the library (8.03 MiB per GPU that loads it, held until exit), which limits
+ * n to reid_topk_static_max_rows() = 4096 rows -- larger n is refused with REID_ERR_ARG and a message naming the limit.
+ * The call performs no cudaMalloc / cudaFree and uses no allocating library routine.  Every call shares the one array
+ * (its contents are those of the last call; what must start clean is re-initialised by the call itself), so calls on one
+ * stream may follow each other freely, but calls that OVERLAP on the GPU (other streams, concurrent graph replays) race:
+ * serialise them. */
+REID_API int reid_topk_static_max_rows(void);
+REID_API int reid_topk_rows_scatter_static(const float* D, int n, int64_t ld, const int32_t* rowmax_key,
+                                  const float* chunk_min, int K, int32_t* nbr, float* nbr_val, void* stream);
 /* test hook: same, with the candidate buffer capped so the exact fallback path is exercised */
 REID_API int reid_topk_rows_capped(const float* D, int rows, int cols, int64_t ld, const int32_t* rowmax_key,
                           int K, int32_t* nbr, float* nbr_val, int cap, void* stream);

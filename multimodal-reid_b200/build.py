@@ -10,7 +10,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libreid_b200.so")
 SOURCES = ["api.cu", "prep.cu", "dist_simt.cu", "dist_tc2.cu", "select.cu", "krecip.cu", "qe.cu",
-           "jaccard.cu", "jaccard_score.cu", "jaccard_sparse.cu", "rank.cu", "score.cu", "train.cu", "stream_score.cu", "stream_rerank.cu", "stream_sym.cu", "fabric.cu", "eval_e2e.cu"]
+           "jaccard.cu", "jaccard_score.cu", "jaccard_sparse.cu", "rank.cu", "score.cu", "train.cu", "stream_score.cu", "stream_rerank.cu", "stream_sym.cu", "no_alloc.cu", "fabric.cu", "eval_e2e.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "--threads", "0"]
 
